@@ -1,0 +1,119 @@
+"""ctypes/numpy front-end of the CPU ORACLE (oracle/mvt_oracle.c).
+
+TEST INFRASTRUCTURE ONLY.  May be imported by tests/, __graft_entry__.smoke()
+and bench.py's cpu_baseline / --impl reference leg -- never by mvtracker_b200/.
+
+Each function restates one reference call (paths under /root/reference):
+  unproject    -> mvtracker/models/core/model_utils.py:420-482  init_pointcloud_from_rgbd
+  knn          -> mvtracker/models/core/mvtracker/mvtracker.py:75-79 (canonical exact-fp32 arithmetic,
+                  (d2, index) order; see the header of mvt_oracle.c)
+  corr_sample  -> mvtracker/models/core/mvtracker/mvtracker.py:800-846
+Arrays are numpy; B (the reference's leading batch axis, asserted == 1 at
+mvtracker.py:275) is squeezed: fmaps [V,S,C,H,W], depths [V,S,H,W].
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libmvt_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "mvt_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_SO)
+        for name in ("orc_unproject", "orc_knn", "orc_corr_from_idx", "orc_corr_sample"):
+            getattr(_lib, name).restype = C.c_int
+        _lib.orc_num_threads.restype = C.c_int
+    return _lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def num_threads():
+    return int(lib().orc_num_threads())
+
+
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(int(n)))
+
+
+def unproject(fmaps, depths, intrs, extrs, stride=4, level=0, depth_interp_mode="nearest", return_validity_mask=False):
+    fmaps, depths, intrs, extrs = _f32(fmaps), _f32(depths), _f32(intrs), _f32(extrs)
+    V, S, Cc, H, W = fmaps.shape
+    assert depths.shape == (V, S, H, W) and intrs.shape == (V, S, 3, 3) and extrs.shape == (V, S, 3, 4)
+    Hl, Wl = H >> level, W >> level
+    P = V * Hl * Wl
+    xyz = np.empty((S, P, 3), np.float32)
+    fvec = np.empty((S, P, Cc), np.float32)
+    valid = np.empty((S, P), np.uint8)
+    rc = lib().orc_unproject(_p(fmaps), _p(depths), _p(intrs), _p(extrs), V, S, Cc, H, W, C.c_float(stride),
+                             int(level), int(depth_interp_mode == "avg"), _p(xyz), _p(fvec), _p(valid))
+    if rc:
+        raise RuntimeError(f"orc_unproject failed rc={rc}")
+    if return_validity_mask:
+        return xyz, fvec, valid.astype(bool)
+    return xyz, fvec
+
+
+def knn(k, xyz_ref, xyz_query, mask=None):
+    """-> (dists [B,M,k] f32 ascending, idx [B,M,k] int32), canonical order."""
+    ref, qry = _f32(xyz_ref), _f32(xyz_query)
+    B, N, _ = ref.shape
+    M = qry.shape[1]
+    assert qry.shape == (B, M, 3)
+    mk = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+    idx = np.empty((B, M, k), np.int32)
+    dist = np.empty((B, M, k), np.float32)
+    rc = lib().orc_knn(int(k), _p(ref), _p(mk), _p(qry), B, N, M, _p(idx), _p(dist))
+    if rc:
+        raise RuntimeError(f"orc_knn failed rc={rc}")
+    return dist, idx
+
+
+def corr_from_idx(xyz, fvec, targets, coords, idx, groups=1, add_offset=True, add_xyz=False):
+    xyz, fvec, targets, coords = _f32(xyz), _f32(fvec), _f32(targets), _f32(coords)
+    idx = np.ascontiguousarray(idx, dtype=np.int32)
+    B, N, Cc = fvec.shape
+    M, k = idx.shape[1], idx.shape[2]
+    D = groups + 3 * bool(add_offset) + 3 * bool(add_xyz)
+    out = np.empty((B, M, k, D), np.float32)
+    rc = lib().orc_corr_from_idx(_p(xyz), _p(fvec), _p(targets), _p(coords), _p(idx), B, N, M, Cc, k, int(groups),
+                                 int(bool(add_offset)), int(bool(add_xyz)), _p(out))
+    if rc:
+        raise RuntimeError(f"orc_corr_from_idx failed rc={rc}")
+    return out
+
+
+def corr_sample(k, xyz, fvec, targets, coords, groups=1, add_offset=True, add_xyz=False, mask=None,
+                return_idx=False):
+    """One PointcloudCorrBlock.corr_sample: kNN -> gather -> grouped dot / sqrt(C/G) -> offsets."""
+    dist, idx = knn(k, xyz, coords, mask)
+    out = corr_from_idx(xyz, fvec, targets, coords, idx, groups, add_offset, add_xyz)
+    return (out, idx, dist) if return_idx else out
+
+
+def dist2_f64(ref, q):
+    ref = _f32(ref)
+    q = _f32(q)
+    out = np.empty((ref.shape[0],), np.float64)
+    lib().orc_dist2_f64(_p(ref), _p(q), ref.shape[0], _p(out))
+    return out
