@@ -1,0 +1,124 @@
+/*
+ * mvt.h -- C ABI of libmvt.so: the B200 (sm_100a) implementation of MVTracker's
+ * data-parallel hot path.  Plain pointers and sizes only; every pointer named
+ * "device" must be CUDA device memory of the current device; `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  All entry points
+ * are asynchronous (enqueue only, no host sync, CUDA-graph capturable), never
+ * allocate user-visible memory, and return 0 on success or a negative MVT_E_*
+ * code; mvt_last_error() returns a thread-local message for the last failure.
+ *
+ * Reference interfaces replaced (paths under the reference repo):
+ *   mvt_camera_prep + mvt_cloud_build  <- init_pointcloud_from_rgbd
+ *        mvtracker/models/core/model_utils.py:420-482
+ *   mvt_grid_build + mvt_knn            <- knn(k, xyz_ref, xyz_query) i.e. _knn_pointops / _knn_torch
+ *        mvtracker/models/core/mvtracker/mvtracker.py:26-90  (native precedent: pointops.knn_query, :55-65)
+ *   mvt_knn_corr                        <- PointcloudCorrBlock.corr_sample
+ *        mvtracker/models/core/mvtracker/mvtracker.py:800-846 (and the level loop :355-369)
+ *   mvt_knn_gather                      <- feature init, k = 1
+ *        mvtracker/models/core/mvtracker/mvtracker.py:627-643
+ */
+#ifndef MVT_H_
+#define MVT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MVT_VERSION 100
+
+#define MVT_OK 0
+#define MVT_E_ARG (-1)      /* bad argument (shape, alignment, unsupported combination) */
+#define MVT_E_CUDA (-2)     /* a CUDA runtime call / launch failed */
+#define MVT_E_WORKSPACE (-3) /* workspace too small */
+
+#define MVT_F32 0
+#define MVT_BF16 1
+
+#define MVT_MAX_LEVELS 4    /* pyramid levels 0..3 (configs/model/mvtracker.yaml: corr_n_levels=4) */
+#define MVT_MAX_K 32
+
+int mvt_version(void);
+const char *mvt_last_error(void);
+
+/* Inverse camera matrices, fp64 on device, rounded to fp32 (model_utils.py:454-457).
+ * intrs [n,3,3], extrs [n,3,4] (world->camera), device fp32, n = V*S.
+ * cam   [n,24] device fp32:  Kinv (9, row major) | Einv rows 0..2 (12, row major 3x4) | 3 pad. */
+int mvt_camera_prep(const float *intrs, const float *extrs, int n, float *cam, void *stream);
+
+/* One pyramid level's outputs of the cloud build.  Any pointer may be NULL (skip that output). */
+typedef struct mvt_level_out {
+    float *xyz;             /* [S, P_l, 3] fp32, P_l = V*(H>>l)*(W>>l), point = v*H_l*W_l + y*W_l + x (model_utils.py:475) */
+    void *fvec;             /* [S, P_l, C] feature dtype (model_utils.py:476) */
+    unsigned char *valid;   /* [S, P_l]   depth > 0 (model_utils.py:478-480) */
+    float *spacing;         /* [S, 2]     sum and count of the pixel footprint depth*stride_l/fx over valid points
+                                          (kNN cell-size hint; accumulated, zeroed by the call) */
+} mvt_level_out;
+
+/* Fused unprojection + view fusion + feature pyramid, all requested levels in ONE pass over fmaps.
+ * fmaps  [V,S,C,H,W] device, feat_dtype MVT_F32|MVT_BF16;  depths [V,S,H,W] device fp32 (already strided by the caller,
+ * mvtracker.py:558-563);  cam from mvt_camera_prep;  stride = pixel stride of level 0 (model_utils.py:424).
+ * depth_avg: 0 = 'nearest' (depth_l = depth_0[y<<l, x<<l]), 1 = 'avg' (chained 2x2 means) (model_utils.py:441-446).
+ * levels[l] describes level l; level_mask bit l set = emit level l. */
+int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                    int V, int S, int C, int H, int W, float stride, int depth_avg,
+                    const mvt_level_out *levels, int level_mask, void *stream);
+
+/* Hashed uniform grid over B independent clouds ("segments", one per frame) of N points each. */
+size_t mvt_grid_workspace_bytes(int B, int N);
+
+typedef struct mvt_grid_job {
+    const float *xyz;           /* [B,N,3] device fp32 */
+    const unsigned char *mask;  /* [B,N] or NULL: points with mask==0 are left out of the search */
+    const float *spacing;       /* [B,2] (sum,count) cell-size hint from mvt_cloud_build, or NULL (volumetric estimate) */
+    void *workspace;            /* device, >= mvt_grid_workspace_bytes(B,N), 256-byte aligned */
+    int B, N;
+    int k_hint;                 /* the k the grid will mostly be queried with (cell size ~ k-NN radius) */
+    int index_mode;             /* 0: neighbours are reported by original index; 1: by rank among mask-valid points
+                                   (bit-compatible with the reference's filter_invalid path, mvtracker.py:820-829) */
+    float cell_scale;           /* multiplies the estimated cell size; <= 0 selects the default */
+} mvt_grid_job;
+
+/* Builds up to 8 grids (e.g. the 4 pyramid levels) with one set of launches. */
+int mvt_grid_build(const mvt_grid_job *jobs, int n_jobs, void *stream);
+
+/* Exact kNN.  query [B,M,3] device fp32.  idx_out [B,M,k] int32 or int64 (idx_is_i64), dist_out [B,M,k] fp32 Euclidean,
+ * either may be NULL.  Order: ascending (d2, index) with d2 = fma(dz,dz,fma(dy,dy,dx*dx)) in fp32.
+ * Missing neighbours (fewer than k searchable points): index -1, distance +inf. */
+int mvt_knn(const void *grid, int B, int N, const float *query, int M, int k,
+            void *idx_out, int idx_is_i64, float *dist_out, void *stream);
+
+typedef struct mvt_corr_level {
+    const void *grid;       /* built by mvt_grid_build over this level's xyz */
+    const float *xyz;       /* [B,N,3] */
+    const void *fvec;       /* [B,N,C] */
+    int N;
+    int k;
+    long long out_offset;   /* float offset of this level's k*D block inside an output row */
+} mvt_corr_level;
+
+/* Fused kNN + neighbour gather + grouped dot-product correlation + offset encoding for up to 4 levels in one launch.
+ * targets [B,M,C] (feature dtype), coords [B,M,3] fp32.
+ * out: fp32; row (b,m) starts at out + (b*M+m)*out_row_stride; level l writes k*D floats at its out_offset, neighbour j
+ * at j*D:  [corr_0..corr_{G-1}, dx,dy,dz (add_offset), x,y,z (add_xyz)],  D = G + 3*add_offset + 3*add_xyz,
+ * corr_g = <target_g, nbr_g> / sqrt(C/G)  (mvtracker.py:832-846).
+ * idx_out: optional [n_levels,B,M,k] int32. */
+int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
+                 const void *targets, const float *coords, int add_offset, int add_xyz,
+                 float *out, long long out_row_stride, int *idx_out, void *stream);
+
+/* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
+ * feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
+int mvt_knn_gather(const void *grid, const void *fvec, int feat_dtype, int B, int N, int C,
+                   const float *query, int M, void *feat_out, int *idx_out, void *stream);
+
+/* Debug / profiling: per-segment grid parameters copied out for inspection.
+ * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */
+int mvt_grid_info(const void *grid, int B, int N, float *info, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVT_H_ */

@@ -1,0 +1,76 @@
+"""ctypes binding of libmvt.so (the C ABI in include/mvt.h).  No CPU fallback: if the library is missing the import
+of any op fails loudly (build it with `python -c "import __graft_entry__ as g; g.build()"` or `make -C mvtracker_b200/csrc`)."""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libmvt.so")
+
+MVT_F32, MVT_BF16 = 0, 1
+MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
+
+SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info")
+
+
+class LevelOut(C.Structure):
+    _fields_ = [("xyz", C.c_void_p), ("fvec", C.c_void_p), ("valid", C.c_void_p), ("spacing", C.c_void_p)]
+
+
+class GridJob(C.Structure):
+    _fields_ = [("xyz", C.c_void_p), ("mask", C.c_void_p), ("spacing", C.c_void_p), ("workspace", C.c_void_p),
+                ("B", C.c_int), ("N", C.c_int), ("k_hint", C.c_int), ("index_mode", C.c_int), ("cell_scale", C.c_float)]
+
+
+class CorrLevel(C.Structure):
+    _fields_ = [("grid", C.c_void_p), ("xyz", C.c_void_p), ("fvec", C.c_void_p), ("N", C.c_int), ("k", C.c_int),
+                ("out_offset", C.c_longlong)]
+
+
+class MvtError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def build(force=False):
+    """Compile libmvt.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-s"] + (["-B"] if force else [])
+    subprocess.check_call(cmd)
+    return SO_PATH
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise MvtError(f"{SO_PATH} is missing: the CUDA library has not been built (there is no CPU fallback). "
+                       f"Run `make -C {os.path.join(_HERE, 'csrc')}`.")
+    L = C.CDLL(SO_PATH)
+    vp, ci, cf, ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
+    L.mvt_version.restype = ci
+    L.mvt_last_error.restype = C.c_char_p
+    L.mvt_camera_prep.argtypes = [vp, vp, ci, vp, vp]
+    L.mvt_cloud_build.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
+    L.mvt_grid_workspace_bytes.argtypes = [ci, ci]
+    L.mvt_grid_workspace_bytes.restype = C.c_size_t
+    L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
+    L.mvt_knn.argtypes = [vp, ci, ci, vp, ci, ci, vp, ci, vp, vp]
+    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, vp, vp]
+    L.mvt_knn_gather.argtypes = [vp, vp, ci, ci, ci, ci, vp, ci, vp, vp, vp]
+    L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
+    for name in SYMBOLS:
+        f = getattr(L, name)
+        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes"):
+            f.restype = ci
+    _lib = L
+    return L
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().mvt_last_error().decode("utf-8", "replace")
+        raise MvtError(f"{what} failed (code {rc}): {msg}")

@@ -1,0 +1,16 @@
+// Error reporting and version of libmvt.so.
+#include "mvt_common.cuh"
+#include <stdarg.h>
+
+namespace mvt {
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace mvt
+
+MVT_EXPORT int mvt_version(void) { return MVT_VERSION; }
+MVT_EXPORT const char *mvt_last_error(void) { return mvt::g_err; }

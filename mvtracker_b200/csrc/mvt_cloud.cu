@@ -1,0 +1,340 @@
+// Cloud build: fused depth unprojection + camera transform + multi-view fusion + feature pyramid.
+// Replaces init_pointcloud_from_rgbd (reference mvtracker/models/core/model_utils.py:420-482): one pass over
+// fmaps[V,S,C,H,W] emits every requested pyramid level's point-major xyz / feature records.
+//
+// Roofline: pure streaming, HBM bound.  Algorithmic bytes per level-0 pixel (fp32, all 4 levels):
+//   read C*4 + 4, write (C*4 + 12 [+1 valid]) * (1 + 1/4 + 1/16 + 1/64)   
+#include "mvt_common.cuh"
+
+namespace mvt {
+
+// ---------------------------------------------------------------------------------------------------------------
+// camera_prep: fp64 inverse of K (3x3) and [R|t;0001] (affine), rounded to fp32.  One thread per (view, frame).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ inline void inv3(const double *m, double *o) {
+    double c00 = m[4] * m[8] - m[5] * m[7], c01 = m[5] * m[6] - m[3] * m[8], c02 = m[3] * m[7] - m[4] * m[6];
+    double det = m[0] * c00 + m[1] * c01 + m[2] * c02;
+    double id = 1.0 / det;
+    o[0] = c00 * id; o[1] = (m[2] * m[7] - m[1] * m[8]) * id; o[2] = (m[1] * m[5] - m[2] * m[4]) * id;
+    o[3] = c01 * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[2] * m[3] - m[0] * m[5]) * id;
+    o[6] = c02 * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
+}
+
+__global__ void camera_prep_kernel(const float *__restrict__ intrs, const float *__restrict__ extrs, int n,
+                                   float *__restrict__ cam) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double K[9], Ki[9], A[9], Ai[9], t[3];
+    for (int j = 0; j < 9; ++j) K[j] = (double)intrs[i * 9 + j];
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) A[r * 3 + c] = (double)extrs[i * 12 + r * 4 + c];
+        t[r] = (double)extrs[i * 12 + r * 4 + 3];
+    }
+    inv3(K, Ki);
+    inv3(A, Ai);
+    float *o = cam + (size_t)i * 24;
+    for (int j = 0; j < 9; ++j) o[j] = (float)Ki[j];
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) o[9 + r * 4 + c] = (float)Ai[r * 3 + c];
+        o[9 + r * 4 + 3] = (float)(-(Ai[r * 3 + 0] * t[0] + Ai[r * 3 + 1] * t[1] + Ai[r * 3 + 2] * t[2]));
+    }
+    o[21] = o[22] = o[23] = 0.f;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// cloud_build
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int TH = 8;     // tile rows   (level-0 pixels) = one level-3 pixel high
+constexpr int TW = 32;    // tile cols   (level-0 pixels) = four level-3 pixels wide
+constexpr int CC = 32;    // channels per smem chunk
+constexpr int S0 = TH * TW + 1, S1 = 64 + 1, S2 = 16 + 1, S3 = 4 + 1;   // padded channel strides (== 1 mod 32 or odd)
+
+struct CloudParams {
+    const void *fmaps;
+    const float *depths;
+    const float *cam;
+    int V, S, C, H, W;
+    float stride;
+    int depth_avg;
+    int level_mask;
+    int tiles_x;
+    float *xyz[4];
+    void *fvec[4];
+    unsigned char *valid[4];
+    float *spacing[4];
+};
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <typename T> __device__ __forceinline__ float round_t(float v) { return to_f<T>(from_f<T>(v)); }
+
+// 2x2 mean in the order of avg_pool2d's window loop: ((a+b)+c)+d, then /4 (exact scaling).
+__device__ __forceinline__ float mean4(float a, float b, float c, float d) { return (((a + b) + c) + d) * 0.25f; }
+
+// Store one level's tile (npx pixels x CC channels, smem layout tile[c*cs + px]) to the point-major feature array.
+// Vector path: 8 lanes x 16 B cover one pixel's 32-channel chunk (128 B contiguous), 4 pixels per warp instruction.
+template <typename T, int LOG_TW>
+__device__ __forceinline__ void store_tile(const float *tile, int cs, int npx, T *out, size_t frame_base, int Wl, int Hl,
+                                           int gx0, int gy0, int C, int c0, bool vec) {
+    const int tid = threadIdx.x;
+    if (vec) {
+        const int c4 = tid & 7;
+        for (int px = tid >> 3; px < npx; px += 32) {
+            int ly = px >> LOG_TW, lx = px & ((1 << LOG_TW) - 1);
+            int gy = gy0 + ly, gx = gx0 + lx;
+            if (gy < Hl && gx < Wl && c0 + 4 * c4 < C) {
+                float v0 = tile[(4 * c4 + 0) * cs + px], v1 = tile[(4 * c4 + 1) * cs + px];
+                float v2 = tile[(4 * c4 + 2) * cs + px], v3 = tile[(4 * c4 + 3) * cs + px];
+                T *dst = out + (frame_base + (size_t)gy * Wl + gx) * C + c0 + 4 * c4;
+                if (sizeof(T) == 4) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(v0, v1, v2, v3);
+                } else {
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(v0, v1), hi = __floats2bfloat162_rn(v2, v3);
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<unsigned *>(&lo);
+                    pk.y = *reinterpret_cast<unsigned *>(&hi);
+                    *reinterpret_cast<uint2 *>(dst) = pk;
+                }
+            }
+        }
+    } else {
+        const int c = tid & 31;
+        for (int px = tid >> 5; px < npx; px += 8) {
+            int ly = px >> LOG_TW, lx = px & ((1 << LOG_TW) - 1);
+            int gy = gy0 + ly, gx = gx0 + lx;
+            if (gy < Hl && gx < Wl && c0 + c < C)
+                out[(frame_base + (size_t)gy * Wl + gx) * C + c0 + c] = from_f<T>(tile[c * cs + px]);
+        }
+    }
+}
+
+// Reduce the 2x2 blocks of `src` (sw pixels wide, channel stride ss) into `dst` (dw = sw/2 wide, dnpx pixels).
+template <typename T>
+__device__ __forceinline__ void pool_tile(const float *src, int ss, int sw, float *dst, int ds, int dw, int dnpx) {
+    const int c = threadIdx.x & 31;
+    for (int px = threadIdx.x >> 5; px < dnpx; px += 8) {
+        int y = px / dw, x = px - y * dw;
+        const float *s = src + c * ss + (2 * y) * sw + 2 * x;
+        dst[c * ds + px] = round_t<T>(mean4(s[0], s[1], s[sw], s[sw + 1]));
+    }
+}
+
+__device__ __forceinline__ void emit_point(const CloudParams &p, const float *cm, int lvl, int s, int v, int gy, int gx,
+                                           int Hl, int Wl, float depth, float &sp_sum, float &sp_cnt) {
+    float st = p.stride * (float)(1 << lvl);
+    float u = ((float)gx + 0.5f) * st - 0.5f;     // model_utils.py:462-466
+    float w = ((float)gy + 0.5f) * st - 0.5f;
+    float rx = fmaf(cm[0], u, fmaf(cm[1], w, cm[2]));
+    float ry = fmaf(cm[3], u, fmaf(cm[4], w, cm[5]));
+    float rz = fmaf(cm[6], u, fmaf(cm[7], w, cm[8]));
+    float cx = rx * depth, cy = ry * depth, cz = rz * depth;           // :470
+    float X = fmaf(cm[9], cx, fmaf(cm[10], cy, fmaf(cm[11], cz, cm[12])));   // :472 (w == 1 exactly: affine inverse)
+    float Y = fmaf(cm[13], cx, fmaf(cm[14], cy, fmaf(cm[15], cz, cm[16])));
+    float Z = fmaf(cm[17], cx, fmaf(cm[18], cy, fmaf(cm[19], cz, cm[20])));
+    size_t P = (size_t)p.V * Hl * Wl;
+    size_t pt = (size_t)s * P + (size_t)v * Hl * Wl + (size_t)gy * Wl + gx;
+    if (p.xyz[lvl]) {
+        float *o = p.xyz[lvl] + pt * 3;
+        o[0] = X; o[1] = Y; o[2] = Z;
+    }
+    bool ok = depth > 0.f;
+    if (p.valid[lvl]) p.valid[lvl][pt] = ok ? 1 : 0;
+    if (ok && depth < 3.0e38f) {
+        sp_sum += depth * st * fabsf(cm[0]);
+        sp_cnt += 1.f;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) cloud_build_kernel(const CloudParams p) {
+    __shared__ float t0[CC * S0];
+    __shared__ float t1[CC * S1];
+    __shared__ float t2[CC * S2];
+    __shared__ float t3[CC * S3];
+    __shared__ float dep[TH * TW + 64 + 16 + 4];
+    __shared__ float cm[24];
+    __shared__ float red[8][8];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int vs = blockIdx.y;                 // v * S + s
+    const int v = vs / p.S, s = vs - v * p.S;
+    const int ty = blockIdx.x / p.tiles_x, tx = blockIdx.x - ty * p.tiles_x;
+    const int y0 = ty * TH, x0 = tx * TW;
+    const int H = p.H, W = p.W, C = p.C;
+    const size_t HW = (size_t)H * W;
+
+    if (tid < 24) cm[tid] = p.cam[(size_t)vs * 24 + tid];
+    // depth pyramid of the tile
+    {
+        int yy = tid >> 5, xx = tid & 31;
+        int gy = y0 + yy, gx = x0 + xx;
+        dep[tid] = (gy < H && gx < W) ? p.depths[(size_t)vs * HW + (size_t)gy * W + gx] : 0.f;
+    }
+    __syncthreads();
+    float *d1 = dep + 256, *d2 = d1 + 64, *d3 = d2 + 16;
+    if (tid < 64) {
+        int y = tid >> 4, x = tid & 15;
+        const float *q = dep + (2 * y) * 32 + 2 * x;
+        d1[tid] = p.depth_avg ? mean4(q[0], q[1], q[32], q[33]) : q[0];
+    }
+    __syncthreads();
+    if (tid < 16) {
+        int y = tid >> 3, x = tid & 7;
+        const float *q = d1 + (2 * y) * 16 + 2 * x;
+        d2[tid] = p.depth_avg ? mean4(q[0], q[1], q[16], q[17]) : q[0];
+    }
+    __syncthreads();
+    if (tid < 4) {
+        const float *q = d2 + 2 * tid;
+        d3[tid] = p.depth_avg ? mean4(q[0], q[1], q[8], q[9]) : q[0];
+    }
+    __syncthreads();
+
+    // geometry: thread t emits level-l point t of the tile when t < 256 >> 2l
+    float sp[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        if (!((p.level_mask >> l) & 1)) continue;
+        int Hl = H >> l, Wl = W >> l;
+        int tw = TW >> l, npx = (TH >> l) * tw;
+        if (tid < npx) {
+            int ly = tid / tw, lx = tid - ly * tw;
+            int gy = (y0 >> l) + ly, gx = (x0 >> l) + lx;
+            if (gy < Hl && gx < Wl) {
+                const float *dl = (l == 0) ? dep : (l == 1) ? d1 : (l == 2) ? d2 : d3;
+                emit_point(p, cm, l, s, v, gy, gx, Hl, Wl, dl[tid], sp[2 * l], sp[2 * l + 1]);
+            }
+        }
+    }
+    if (p.spacing[0] || p.spacing[1] || p.spacing[2] || p.spacing[3]) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float x = sp[i];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+            if (lane == 0) red[warp][i] = x;
+        }
+        __syncthreads();
+        if (tid < 8) {
+            float x = 0.f;
+            for (int w2 = 0; w2 < 8; ++w2) x += red[w2][tid];
+            int l = tid >> 1;
+            if (p.spacing[l] && ((p.level_mask >> l) & 1) && x != 0.f) atomicAdd(p.spacing[l] + s * 2 + (tid & 1), x);
+        }
+    }
+
+    // features: channel chunks through shared memory, transposed to point-major rows
+    const bool any_f = p.fvec[0] || p.fvec[1] || p.fvec[2] || p.fvec[3];
+    if (!any_f) return;
+    const bool vec = (C % 4) == 0;
+    const T *fm = reinterpret_cast<const T *>(p.fmaps) + (size_t)vs * C * HW;
+    const bool need1 = (p.level_mask & 0xE) != 0, need2 = (p.level_mask & 0xC) != 0, need3 = (p.level_mask & 0x8) != 0;
+    const int yy = tid >> 5, xx = tid & 31;
+    const bool inside = (y0 + yy < H) && (x0 + xx < W);
+    const size_t pix = (size_t)(y0 + yy) * W + (x0 + xx);
+
+    for (int c0 = 0; c0 < C; c0 += CC) {
+        __syncthreads();   // previous chunk's readers of t0..t3 are done
+#pragma unroll 8
+        for (int c = 0; c < CC; ++c) {
+            float val = 0.f;
+            if (inside && c0 + c < C) val = to_f<T>(fm[(size_t)(c0 + c) * HW + pix]);
+            t0[c * S0 + tid] = val;
+        }
+        __syncthreads();
+        if (need1) pool_tile<T>(t0, S0, 32, t1, S1, 16, 64);
+        if (p.fvec[0] && (p.level_mask & 1))
+            store_tile<T, 5>(t0, S0, 256, reinterpret_cast<T *>(p.fvec[0]), ((size_t)s * p.V + v) * HW, W, H, x0, y0, C, c0, vec);
+        if (!need1) continue;
+        __syncthreads();
+        if (need2) pool_tile<T>(t1, S1, 16, t2, S2, 8, 16);
+        if (p.fvec[1] && (p.level_mask & 2)) {
+            int Hl = H >> 1, Wl = W >> 1;
+            store_tile<T, 4>(t1, S1, 64, reinterpret_cast<T *>(p.fvec[1]), ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 1, y0 >> 1, C, c0, vec);
+        }
+        if (!need2) continue;
+        __syncthreads();
+        if (need3) pool_tile<T>(t2, S2, 8, t3, S3, 4, 4);
+        if (p.fvec[2] && (p.level_mask & 4)) {
+            int Hl = H >> 2, Wl = W >> 2;
+            store_tile<T, 3>(t2, S2, 16, reinterpret_cast<T *>(p.fvec[2]), ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 2, y0 >> 2, C, c0, vec);
+        }
+        if (!need3) continue;
+        __syncthreads();
+        if (p.fvec[3] && (p.level_mask & 8)) {
+            int Hl = H >> 3, Wl = W >> 3;
+            store_tile<T, 2>(t3, S3, 4, reinterpret_cast<T *>(p.fvec[3]), ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 3, y0 >> 3, C, c0, vec);
+        }
+    }
+}
+
+__global__ void zero_spacing_kernel(float *a, float *b, float *c, float *d, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        if (a) a[i] = 0.f;
+        if (b) b[i] = 0.f;
+        if (c) c[i] = 0.f;
+        if (d) d[i] = 0.f;
+    }
+}
+
+}  // namespace mvt
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+MVT_EXPORT int mvt_camera_prep(const float *intrs, const float *extrs, int n, float *cam, void *stream) {
+    MVT_CHECK_ARG(intrs && extrs && cam, "mvt_camera_prep: null pointer");
+    MVT_CHECK_ARG(n > 0, "mvt_camera_prep: n must be positive (got %d)", n);
+    mvt::camera_prep_kernel<<<(n + 63) / 64, 64, 0, (cudaStream_t)stream>>>(intrs, extrs, n, cam);
+    MVT_CHECK_LAUNCH("camera_prep");
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                               int V, int S, int C, int H, int W, float stride, int depth_avg,
+                               const mvt_level_out *levels, int level_mask, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(depths && cam && levels, "mvt_cloud_build: null pointer");
+    MVT_CHECK_ARG(V > 0 && S > 0 && C > 0 && H > 0 && W > 0, "mvt_cloud_build: bad shape V=%d S=%d C=%d H=%d W=%d", V, S, C, H, W);
+    MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_cloud_build: feat_dtype %d", feat_dtype);
+    MVT_CHECK_ARG(level_mask > 0 && level_mask < (1 << MVT_MAX_LEVELS), "mvt_cloud_build: level_mask 0x%x (levels 0..3 supported)", level_mask);
+    MVT_CHECK_ARG((long long)V * S <= 65535, "mvt_cloud_build: V*S too large");
+    CloudParams p;
+    p.fmaps = fmaps; p.depths = depths; p.cam = cam;
+    p.V = V; p.S = S; p.C = C; p.H = H; p.W = W;
+    p.stride = stride; p.depth_avg = depth_avg; p.level_mask = level_mask;
+    bool any_f = false, any_sp = false;
+    for (int l = 0; l < 4; ++l) {
+        bool on = (level_mask >> l) & 1;
+        p.xyz[l] = on ? levels[l].xyz : nullptr;
+        p.fvec[l] = on ? levels[l].fvec : nullptr;
+        p.valid[l] = on ? levels[l].valid : nullptr;
+        p.spacing[l] = on ? levels[l].spacing : nullptr;
+        if (on) {
+            MVT_CHECK_ARG((H >> l) > 0 && (W >> l) > 0, "mvt_cloud_build: level %d is empty for %dx%d", l, H, W);
+            any_f |= p.fvec[l] != nullptr;
+            any_sp |= p.spacing[l] != nullptr;
+            if (p.fvec[l] && C % 4 == 0)
+                MVT_CHECK_ARG(((uintptr_t)p.fvec[l] & 15) == 0, "mvt_cloud_build: fvec[%d] must be 16-byte aligned", l);
+        }
+    }
+    MVT_CHECK_ARG(!any_f || fmaps, "mvt_cloud_build: fmaps is null but a feature output was requested");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (any_sp) {
+        int n = S * 2;
+        zero_spacing_kernel<<<(n + 127) / 128, 128, 0, st>>>(p.spacing[0], p.spacing[1], p.spacing[2], p.spacing[3], n);
+        MVT_CHECK_LAUNCH("zero_spacing");
+    }
+    p.tiles_x = (W + TW - 1) / TW;
+    int tiles_y = (H + TH - 1) / TH;
+    dim3 grid((unsigned)(p.tiles_x * tiles_y), (unsigned)(V * S));
+    if (feat_dtype == MVT_F32) cloud_build_kernel<float><<<grid, 256, 0, st>>>(p);
+    else cloud_build_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
+    MVT_CHECK_LAUNCH("cloud_build");
+    return MVT_OK;
+}
