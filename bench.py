@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py -- kNN-corr track-point queries/s of the MVTracker hot path on B200 (BASELINE.json metric).
+
+One STEP = the hot path of one sliding window (S=12 frames) on synthetic inputs already resident in HBM:
+    camera_prep + cloud_build (4 pyramid levels, one pass)  ->  grid_build (4 levels)  ->
+    iters x knn_corr (all levels / frames / tracks fused in one launch)
+queries per step = iters * levels * S * N_tracks  (one query = one (track, frame, level, iteration) tuple).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload droid|panoptic|dexycb|kubric] [--impl reference]
+N > 1 is launched by torchrun (one rank per GPU); see mvtracker_b200/dist.py for the sharding.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+S_WINDOW, C_FEAT, K_NN, LEVELS, STRIDE = 12, 128, 16, 4, 4
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None)
+    ap.add_argument("--iters", type=int, default=4)
+    ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--zero-frac", type=float, default=0.05)
+    ap.add_argument("--cell-scale", type=float, default=0.0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload_cfg(name):
+    from mvtracker_b200 import synth
+    w = dict(synth.WORKLOADS[name])
+    w["name"] = name
+    w["Hs"], w["Ws"] = w["H"] // STRIDE, w["W"] // STRIDE
+    return w
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# clocks: sample nvidia-smi DURING the timed region
+# ------------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.samples, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def window(self, t0, t1):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.samples:
+            if ts < t0 - 0.05 or ts > t1 + 0.15:
+                continue
+            parts = [p.strip() for p in line.split(",")]
+            try:
+                sm.append(float(parts[0])); mx = max(mx, float(parts[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port of the reference path, all host threads, bounded sample of the same workload
+# ------------------------------------------------------------------------------------------------------------------
+_scene_cache = {}
+
+
+def cpu_sample(w, iters, budget_s, zero_frac, seed=72):
+    """Times, on ONE frame of the workload: unproject x4 levels (re-pooling from level 0 per level, as
+    model_utils.py:439-446 does) and corr_sample x4 levels on a track subsample sized to the budget; cost is exactly
+    linear in frames and tracks, so the whole-step CPU time is S*t_build + iters*S*N*sum_l t_query_l.  -> dict"""
+    import numpy as np
+    import torch
+    from mvtracker_b200 import synth
+    from oracle import oracle
+
+    cores = oracle.num_threads()
+    ck = (w["name"], zero_frac, seed)
+    if _scene_cache.get("key") != ck:       # inputs are generated once; only the oracle calls are timed
+        sc = synth.make_scene(w["V"], w["H"], w["W"], S=1, C=C_FEAT, stride=STRIDE, zero_frac=zero_frac, seed=seed)
+        _scene_cache.update(key=ck, arrays=(sc.fmaps[0].numpy(), sc.depths[0, :, :, 0].numpy(), sc.intrs[0].numpy(),
+                                            sc.extrs[0].numpy()))
+    fm, dp, K, E = _scene_cache["arrays"]
+    t0 = time.perf_counter()
+    clouds = [oracle.unproject(fm, dp, K, E, stride=STRIDE, level=l) for l in range(LEVELS)]
+    t_build = time.perf_counter() - t0
+    coords, targets = synth.make_tracks(torch.from_numpy(clouds[0][0][0]), w["N"], 1, C=C_FEAT)
+    coords, targets = coords.numpy(), targets.numpy()
+
+    def run(m):
+        t = time.perf_counter()
+        for xyz, fvec in clouds:
+            oracle.corr_sample(K_NN, xyz, fvec, targets[:, :m], coords[:, :m])
+        return time.perf_counter() - t
+
+    m = min(w["N"], 16)
+    t_small = run(m)
+    per_track = t_small / m
+    m_big = int(max(m, min(w["N"], (budget_s - t_build - t_small) / max(per_track, 1e-9))))
+    reps = 1
+    if m_big >= w["N"]:                       # whole track set fits the budget: repeat it to fill the sample
+        reps = int(max(1, min(64, (budget_s - t_build - t_small) / max(per_track * m_big, 1e-9))))
+    t_corr = sum(run(m_big) for _ in range(reps)) / reps
+    t_q = t_corr / m_big                      # seconds per track per frame, all 4 levels
+    step_cpu = S_WINDOW * t_build + iters * S_WINDOW * w["N"] * t_q
+    queries = iters * LEVELS * S_WINDOW * w["N"]
+    return {"value": queries / step_cpu, "unit": "queries/s", "cores": cores, "kind": "port",
+            "sample": (f"oracle (C/OpenMP port of the reference path) on 1 of {S_WINDOW} frames: unproject x{LEVELS} levels "
+                       f"({t_build:.2f}s) + corr_sample x{LEVELS} levels on {m_big} of {w['N']} tracks ({t_corr:.2f}s, mean of {reps}); "
+                       f"scaled linearly to {S_WINDOW} frames x {w['N']} tracks x {iters} iters"),
+            "step_seconds_extrapolated": step_cpu, "sample_seconds": t_build + t_small + t_corr * reps}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port, all host threads), rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = workload_cfg(args.workload or ("droid" if args.gpus == 1 else "panoptic"))
+    budget = max(2.0, min(args.cpu_budget, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_sample(w, args.iters, budget, args.zero_frac)
+    vals, secs = [], []
+    for _ in range(args.steps):
+        r = cpu_sample(w, args.iters, budget, args.zero_frac)
+        vals.append(r["value"]); secs.append(r["step_seconds_extrapolated"])
+    vals.sort()
+    v = vals[len(vals) // 2]
+    r["value"] = v
+    line = {"impl": "reference", "metric": "knn_corr_queries_per_s", "value": v, "unit": "queries/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sorted(secs)[len(secs) // 2],
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(w, args), "cpu_baseline": r,
+            "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def config_dict(w, args):
+    return {"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
+                        f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
+            "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1,
+            "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
+            "l2": "inputs_exceed_l2 (feature maps and clouds are > 126 MB and are rewritten every step)"}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from mvtracker_b200 import _lib, dropin, ops, synth
+    from mvtracker_b200.hotpath import WindowClouds
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        from mvtracker_b200 import dist as mdist
+        return mdist.run_bench(args, sys.modules[__name__])
+    assert args.gpus == 1, "for --gpus N > 1 launch with torchrun (one rank per GPU)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    w = workload_cfg(args.workload or "droid")
+    fdtype = torch.float32 if args.dtype == "f32" else torch.bfloat16
+    esz = 4 if args.dtype == "f32" else 2
+    iters, N = args.iters, w["N"]
+
+    sc = synth.make_scene(w["V"], w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac, seed=72,
+                          device=dev, dtype=fdtype)
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
+    win = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale)
+    base_coords, base_targets = synth.make_tracks(win.clouds[0].xyz[0], N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype)
+    g = torch.Generator(device=dev).manual_seed(74)
+    coords_it = [(base_coords + 0.01 * torch.randn(base_coords.shape, device=dev, generator=g)).contiguous() for _ in range(iters)]
+    targets_it = [(base_targets * (1.0 - 0.1 * i)).contiguous() for i in range(iters)]
+    outs = [torch.empty(S_WINDOW, N, win.width, device=dev, dtype=torch.float32) for _ in range(iters)]
+    del win
+    L = _lib.lib()
+
+    def step(ev=None):
+        if ev is not None: ev[0].record()
+        wdw = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale)
+        # (build = camera_prep + zero + cloud_build, then 6 grid kernels; events split them below)
+        if ev is not None: ev[1].record()
+        for i in range(iters):
+            wdw.corr(targets_it[i], coords_it[i], out=outs[i])
+            if ev is not None: ev[2 + i].record()
+        return wdw
+
+    # split timing of the build needs an event between cloud_build and grid_build: do it with the ops directly
+    def step_split(ev):
+        ev[0].record()
+        clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS))
+        ev[1].record()
+        grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
+        ev[2].record()
+        wdw = WindowClouds(clouds, grids, K_NN, 1, True, False)
+        for i in range(iters):
+            wdw.corr(targets_it[i], coords_it[i], out=outs[i])
+            ev[3 + i].record()
+        return wdw
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+
+    # ---- timed region: K steps, CUDA events on the launching (current) stream ---------------------------------------
+    try:
+        gpu_id = "GPU-" + str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        gpu_id = str(local)
+    sampler = ClockSampler(gpu_id)
+    time.sleep(0.3)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 + iters)] for _ in range(args.steps)]
+    n0 = L.mvt_launch_count()
+    torch.cuda.synchronize()
+    t_wall0 = time.time()
+    for s_i in range(args.steps):
+        wdw = step_split(evs[s_i])
+    torch.cuda.synchronize()
+    t_wall1 = time.time()
+    launches = L.mvt_launch_count() - n0
+    total_ms = evs[0][0].elapsed_time(evs[-1][-1])
+    ms_step = total_ms / args.steps
+    t_cloud = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    t_grid = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+    t_corr = sum(e[2 + i].elapsed_time(e[3 + i]) for e in evs for i in range(iters)) / (args.steps * iters)
+    # keep the timed region long enough for nvidia-smi to see it
+    t_pad = time.time()
+    while time.time() - t_wall0 < 1.0:
+        step()
+    torch.cuda.synchronize()
+    clocks = sampler.window(t_wall0, max(t_wall1, time.time()))
+    queries = iters * LEVELS * S_WINDOW * N
+    value = queries / (ms_step * 1e-3)
+
+    # ---- roofline (algorithmic bytes / measured launch time / measured HBM peak) ------------------------------------
+    peak, peak_src = 6650.0, "fallback"
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak, peak_src = float(mp["hbm_gbs"]), "measured"
+    except Exception:
+        pass
+    D = 4
+    q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * D * 4
+    corr_bytes = LEVELS * S_WINDOW * N * q_bytes
+    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + sum(c.xyz.numel() * 4 + c.fvec.numel() * esz for c in wdw.clouds)
+    kern = {
+        "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6},
+        "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6},
+        "grid_build": {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0},
+    }
+    for kv in kern.values():
+        kv["frac"] = kv["gbs"] / peak
+        kv["share_of_step"] = kv["ms"] * kv["launches_per_step"] / ms_step if kv is not kern["grid_build"] else kv["ms"] / ms_step
+    dom = "knn_corr" if t_corr * iters >= t_cloud else "cloud_build"
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["gbs"], "peak": peak, "peak_source": peak_src,
+                "unit": "GB/s", "frac": kern[dom]["gbs"] / peak, "traffic": None,
+                "alg_bytes_per_launch": kern[dom]["alg_bytes"], "ms_per_launch": kern[dom]["ms"]}
+
+    line = {"metric": "knn_corr_queries_per_s", "value": value, "unit": "queries/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args), "clocks": clocks,
+            "gpu_launches": int(launches), "roofline": roofline, "kernels": kern}
+
+    # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------
+    if not args.no_e2e:
+        line["e2e"] = run_e2e(args, w, sc, coords_it, targets_it, dev)
+    del wdw
+    sampler.stop()
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_sample(w, iters, args.cpu_budget, args.zero_frac)
+    print(json.dumps(line))
+
+
+def run_e2e(args, w, sc, coords_it, targets_it, dev):
+    """Each step: pinned host inputs -> device, the reference's own call pattern through mvtracker_b200.dropin
+    (init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat),
+    then the concatenated correlation features of every iteration -> pinned host."""
+    import torch
+    from mvtracker_b200 import dropin
+    iters, N = args.iters, w["N"]
+    host_in = [t.cpu().pin_memory() for t in (sc.fmaps, sc.depths, sc.intrs, sc.extrs)]
+    host_ct = [(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(coords_it, targets_it)]
+    host_out = [torch.empty(1, S_WINDOW, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
+    h2d = sum(t.numel() * t.element_size() for t in host_in) + sum(c.numel() * c.element_size() + t.numel() * t.element_size() for c, t in host_ct)
+    d2h = sum(t.numel() * t.element_size() for t in host_out)
+
+    def step():
+        fm, dp, K, E = [t.to(dev, non_blocking=True) for t in host_in]
+        blocks = []
+        for lvl in range(LEVELS):
+            xyz, fvec = dropin.init_pointcloud_from_rgbd(fm, dp, K, E, stride=STRIDE, level=lvl)
+            blocks.append(dropin.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
+                                                     corr_add_neighbor_xyz=False))
+        for i in range(iters):
+            coords = host_ct[i][0].to(dev, non_blocking=True)
+            ffeats = host_ct[i][1].to(dev, non_blocking=True)
+            fcorrs = [blocks[l].corr_sample(ffeats, coords).reshape(1, S_WINDOW, N, -1) for l in range(LEVELS)]
+            host_out[i].copy_(torch.cat(fcorrs, dim=-1), non_blocking=True)
+
+    n = max(3, min(args.steps, 10))
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    dropin.clear_caches()
+    queries = iters * LEVELS * S_WINDOW * N
+    return {"value": queries / (ms * 1e-3), "unit": "queries/s", "ms_per_step": ms, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "steps": n,
+            "api": "mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample), pinned host buffers"}
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

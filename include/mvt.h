@@ -42,6 +42,8 @@ extern "C" {
 
 int mvt_version(void);
 const char *mvt_last_error(void);
+/* Number of kernels this library has launched in the process so far (monotone; for benchmarks' gpu_launches). */
+unsigned long long mvt_launch_count(void);
 
 /* Inverse camera matrices, fp64 on device, rounded to fp32 (model_utils.py:454-457).
  * intrs [n,3,3], extrs [n,3,4] (world->camera), device fp32, n = V*S.

@@ -11,7 +11,7 @@ MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info")
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count")
 
 
 class LevelOut(C.Structure):
@@ -53,6 +53,7 @@ def lib():
     vp, ci, cf, ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
     L.mvt_version.restype = ci
     L.mvt_last_error.restype = C.c_char_p
+    L.mvt_launch_count.restype = C.c_ulonglong
     L.mvt_camera_prep.argtypes = [vp, vp, ci, vp, vp]
     L.mvt_cloud_build.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
     L.mvt_grid_workspace_bytes.argtypes = [ci, ci]
@@ -64,7 +65,7 @@ def lib():
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     for name in SYMBOLS:
         f = getattr(L, name)
-        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes"):
+        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count"):
             f.restype = ci
     _lib = L
     return L

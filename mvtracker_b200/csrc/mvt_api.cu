@@ -1,6 +1,7 @@
 // Error reporting and version of libmvt.so.
 #include "mvt_common.cuh"
 #include <stdarg.h>
+#include <atomic>
 
 namespace mvt {
 static thread_local char g_err[512] = "";
@@ -10,7 +11,10 @@ void set_error(const char *fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace mvt
 
 MVT_EXPORT int mvt_version(void) { return MVT_VERSION; }
 MVT_EXPORT const char *mvt_last_error(void) { return mvt::g_err; }
+MVT_EXPORT unsigned long long mvt_launch_count(void) { return mvt::g_launches.load(); }

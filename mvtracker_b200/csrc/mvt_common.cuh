@@ -13,6 +13,7 @@
 namespace mvt {
 
 void set_error(const char *fmt, ...);
+void count_launch();
 
 #define MVT_EXPORT extern "C" __attribute__((visibility("default")))
 
@@ -31,6 +32,7 @@ void set_error(const char *fmt, ...);
             mvt::set_error("%s: %s", what, cudaGetErrorString(e__));                  \
             return MVT_E_CUDA;                                                        \
         }                                                                             \
+        mvt::count_launch();                                                          \
     } while (0)
 
 constexpr int kNumSMs = 148;   // B200

@@ -1,0 +1,257 @@
+"""Host-side mirror of the reference's seam for the hot path: same names, arguments, return shapes and assertion
+behaviour as the three module-level objects that `MVTracker.forward` resolves at call time
+(reference mvtracker/models/core/mvtracker/mvtracker.py:20, :87/:90, :312; called at :298, :608, :637, :816):
+
+    init_pointcloud_from_rgbd   mvtracker/models/core/model_utils.py:420-482
+    knn                         mvtracker/models/core/mvtracker/mvtracker.py:26-90
+    PointcloudCorrBlock         mvtracker/models/core/mvtracker/mvtracker.py:769-846
+
+`install()` rebinds them, so `MVTracker.forward(rgbs, depths, query_points, intrs, extrs)` is unchanged.
+CUDA tensors only; CPU tensors raise (the reference itself is the CPU path).
+
+Two memoisations keep the reference's call pattern (one call per pyramid level) from costing a launch per level:
+  * the first init_pointcloud_from_rgbd(level=l) call on a given (fmaps, depths, intrs, extrs) builds levels 0..3 in one
+    kernel pass; calls for the other levels return the cached tensors.  Entries hold references to their inputs and
+    are keyed on (data_ptr, _version), so an in-place edit or a new tensor is a miss.
+  * the first corr_sample of a refinement iteration runs all sibling levels in ONE fused launch; the sibling blocks'
+    corr_sample calls with the same (targets, coords) return their column slice.
+Set `settings.pyramid_cache = False` / `settings.fuse_levels = False` for the plain one-launch-per-call behaviour.
+"""
+import weakref
+from types import SimpleNamespace
+from typing import Callable, Optional
+
+import torch
+
+from . import ops
+from ._lib import MAX_LEVELS, MvtError
+
+settings = SimpleNamespace(
+    pyramid_cache=True,
+    fuse_levels=True,
+    # 'reference': bit-compatible with mvtracker.py:820-829 (kNN on the compacted valid cloud, gather with those
+    # indices from the uncompacted arrays).  'intended': invalid points are skipped and the true neighbours gathered.
+    filter_invalid_mode="reference",
+    cell_scale=0.0,
+)
+
+
+def _key(t: torch.Tensor):
+    return (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()), t.dtype)
+
+
+class _Pyramid:
+    """All levels built from one (fmaps, depths, intrs, extrs) window; also the sibling group of its corr blocks."""
+
+    def __init__(self, key, inputs, clouds):
+        self.key = key
+        self.inputs = inputs            # keeps the storages alive so data_ptr cannot be recycled while cached
+        self.clouds = clouds            # level -> ops.Cloud
+        self.blocks = weakref.WeakValueDictionary()   # level -> PointcloudCorrBlock registered on these clouds
+        self.corr_cache = None          # (key, {level: tensor})
+
+
+_pyramid_cache = []     # most recent first, at most 2 entries (feature-init call + forward_iteration call per window)
+
+
+def clear_caches():
+    _pyramid_cache.clear()
+    _pending_blocks.clear()
+
+
+def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, depth_interp_mode="nearest",
+                              return_validity_mask=False):
+    B, V, S, C, H, W = fmaps.shape
+    assert fmaps.shape == (B, V, S, C, H, W)
+    assert depths.shape == (B, V, S, 1, H, W)
+    assert intrs.shape == (B, V, S, 3, 3)
+    assert extrs.shape == (B, V, S, 3, 4)
+    if not fmaps.is_cuda:
+        raise MvtError("mvtracker_b200.init_pointcloud_from_rgbd needs CUDA tensors (no CPU fallback)")
+    if depth_interp_mode not in ("nearest", "avg"):
+        if level == 0:
+            depth_interp_mode = "nearest"      # callers pass "N/A" at level 0 (evaluator_3dpt.py:309-317)
+        else:
+            raise NotImplementedError
+    if level >= MAX_LEVELS:
+        raise MvtError(f"pyramid level {level} not supported (0..{MAX_LEVELS - 1})")
+
+    key = (_key(fmaps), _key(depths), _key(intrs), _key(extrs), float(stride), depth_interp_mode)
+    pyr = None
+    if settings.pyramid_cache:
+        for e in _pyramid_cache:
+            if e.key == key and level in e.clouds:
+                pyr = e
+                break
+    if pyr is None:
+        if settings.pyramid_cache:
+            levels = [l for l in range(MAX_LEVELS) if (H >> l) > 0 and (W >> l) > 0]
+            if level not in levels:
+                levels = [level]
+        else:
+            levels = [level]
+        per_b = []
+        for b in range(B):
+            per_b.append(ops.cloud_build(fmaps[b], depths[b, :, :, 0], intrs[b], extrs[b], stride=stride, levels=levels,
+                                         depth_interp_mode=depth_interp_mode, want_valid=True))
+        clouds = {}
+        for i, l in enumerate(levels):
+            if B == 1:
+                clouds[l] = per_b[0][i]
+            else:
+                cs = [pb[i] for pb in per_b]
+                clouds[l] = ops.Cloud(l, torch.cat([c.xyz for c in cs]), torch.cat([c.fvec for c in cs]),
+                                      torch.cat([c.valid for c in cs]), torch.cat([c.spacing for c in cs]))
+        pyr = _Pyramid(key, (fmaps, depths, intrs, extrs), clouds)
+        if settings.pyramid_cache:
+            _pyramid_cache.insert(0, pyr)
+            del _pyramid_cache[2:]
+    cloud = pyr.clouds[level]
+    xyz, fvec = cloud.xyz, cloud.fvec
+    xyz._mvt = (weakref.ref(pyr), level)   # lets PointcloudCorrBlock find the footprint hint and its sibling levels
+    if return_validity_mask:
+        return xyz, fvec, cloud.valid
+    return xyz, fvec
+
+
+def knn(k: int, xyz_ref: torch.Tensor, xyz_query: torch.Tensor):
+    """(B,N,3), (B,M,3) -> (dists (B,M,k) in xyz_ref.dtype, idx (B,M,k) int64), ascending distance."""
+    if not xyz_ref.is_cuda:
+        raise MvtError("mvtracker_b200.knn needs CUDA tensors (no CPU fallback)")
+    B, N, _ = xyz_ref.shape
+    assert xyz_query.shape[0] == B and xyz_query.shape[2] == 3
+    grid = ops.build_grids([(xyz_ref, None, None)], k_hint=k, cell_scale=settings.cell_scale)[0]
+    dists, idx = ops.knn(grid, xyz_query, k, idx_dtype=torch.int64)
+    return dists.to(xyz_ref.dtype), idx
+
+
+_pending_blocks = weakref.WeakSet()   # blocks whose grids have not been built yet (built together on first use)
+
+
+class PointcloudCorrBlock:
+    def __init__(
+            self,
+            k: int,
+            groups,
+            xyz: torch.Tensor,
+            fvec: torch.Tensor,
+            corr_add_neighbor_offset: bool,
+            corr_add_neighbor_xyz: bool,
+            filter_invalid: bool = False,
+            valid: Optional[torch.Tensor] = None,
+            rerun_fmap_coloring_fn: Optional[Callable] = None,
+    ):
+        self.B, self.N, self.C = fvec.shape
+        assert xyz.shape == (self.B, self.N, 3)
+        assert fvec.shape == (self.B, self.N, self.C)
+        assert k <= self.N, "k should be less than or equal to N"
+        assert groups <= self.C, "number of correlation groups should not be larger than the number of channels"
+        assert self.C % groups == 0, "number of channels must be divisible by the number of groups (for convenience)"
+        assert not filter_invalid or valid is not None
+        if not xyz.is_cuda:
+            raise MvtError("mvtracker_b200.PointcloudCorrBlock needs CUDA tensors (no CPU fallback)")
+
+        self.k = k
+        self.groups = groups
+        self.xyz = xyz
+        self.fvec = fvec
+        self.corr_add_neighbor_offset = corr_add_neighbor_offset
+        self.corr_add_neighbor_xyz = corr_add_neighbor_xyz
+        self.filter_invalid = filter_invalid
+        self.valid = valid
+        self.rerun_fmap_coloring_fn = rerun_fmap_coloring_fn
+
+        self._xyz_c = xyz if (xyz.dtype == torch.float32 and xyz.is_contiguous()) else xyz.float().contiguous()
+        self._fvec_c = fvec.contiguous()
+        self._grid = None
+        self._pyr, self._level, self._spacing = None, None, None
+        tag = getattr(xyz, "_mvt", None)
+        if tag is not None and tag[0]() is not None:
+            self._pyr, self._level = tag[0](), tag[1]
+            self._spacing = self._pyr.clouds[self._level].spacing
+            self._pyr.blocks[self._level] = self
+        _pending_blocks.add(self)
+
+    # -- grids of all blocks created since the last build go into one mvt_grid_build call -------------------------
+    def _ensure_grid(self):
+        if self._grid is not None:
+            return
+        todo = [b for b in list(_pending_blocks) if b is not self and b._grid is None
+                and b.filter_invalid == self.filter_invalid and b.k == self.k and b.xyz.device == self.xyz.device]
+        todo = [self] + todo[:7]
+        mode = 1 if (self.filter_invalid and settings.filter_invalid_mode == "reference") else 0
+        jobs = [(b._xyz_c, b.valid if b.filter_invalid else None, b._spacing) for b in todo]
+        grids = ops.build_grids(jobs, k_hint=self.k, index_mode=mode, cell_scale=settings.cell_scale)
+        for b, g in zip(todo, grids):
+            b._grid = g
+            _pending_blocks.discard(b)
+
+    def _siblings(self):
+        """Levels of the same pyramid that can share one fused launch with this block."""
+        if not settings.fuse_levels or self._pyr is None:
+            return [self]
+        sib = [b for _, b in sorted(self._pyr.blocks.items())
+               if b.B == self.B and b.C == self.C and b.groups == self.groups and b.fvec.dtype == self.fvec.dtype
+               and b.corr_add_neighbor_offset == self.corr_add_neighbor_offset
+               and b.corr_add_neighbor_xyz == self.corr_add_neighbor_xyz and b.filter_invalid == self.filter_invalid]
+        return sib if self in sib else [self]
+
+    def corr_sample(
+            self,
+            targets: torch.Tensor,
+            coords_world_xyz: torch.Tensor,
+            save_debug_logs=False,
+            debug_logs_path=".",
+            debug_logs_prefix="corr",
+            save_rerun_logs=False,
+    ):
+        _, M, _ = targets.shape
+        assert targets.shape == (self.B, M, self.C)
+        assert coords_world_xyz.shape == (self.B, M, 3)
+        if save_debug_logs or save_rerun_logs:
+            raise MvtError("debug / rerun logging lives in the reference implementation only")
+        if torch.is_grad_enabled() and (targets.requires_grad or self.fvec.requires_grad):
+            raise MvtError("mvtracker_b200 corr_sample is forward-only; run under torch.no_grad()")
+        D = self.groups + 3 * bool(self.corr_add_neighbor_offset) + 3 * bool(self.corr_add_neighbor_xyz)
+        if targets.dtype != self.fvec.dtype:
+            targets = targets.to(self.fvec.dtype)
+
+        sib = self._siblings()
+        ckey = (_key(targets), _key(coords_world_xyz))
+        if len(sib) > 1:
+            cache = self._pyr.corr_cache
+            if cache is not None and cache[0] == ckey and id(self) in cache[1]:
+                return cache[1].pop(id(self))
+        for b in sib:
+            b._ensure_grid()
+        levels = [(b._grid, b._xyz_c, b._fvec_c, b.k) for b in sib]
+        out = ops.knn_corr(levels, targets, coords_world_xyz, groups=self.groups, add_offset=self.corr_add_neighbor_offset,
+                           add_xyz=self.corr_add_neighbor_xyz)
+        res, off = {}, 0
+        for b in sib:
+            w = b.k * D
+            res[id(b)] = out[:, :, off:off + w].reshape(self.B, M, b.k, D)
+            off += w
+        mine = res.pop(id(self))
+        if len(sib) > 1:
+            # (targets, coords) are referenced by the key tensors' storages for the lifetime of this entry
+            self._pyr.corr_cache = (ckey, res, (targets, coords_world_xyz))
+        return mine
+
+
+def install(ref_module=None):
+    """Rebind the reference's three seam names to this implementation.  Returns a callable that restores them."""
+    if ref_module is None:
+        import importlib
+        ref_module = importlib.import_module("mvtracker.models.core.mvtracker.mvtracker")
+    saved = {n: getattr(ref_module, n) for n in ("init_pointcloud_from_rgbd", "knn", "PointcloudCorrBlock")}
+    ref_module.init_pointcloud_from_rgbd = init_pointcloud_from_rgbd
+    ref_module.knn = knn
+    ref_module.PointcloudCorrBlock = PointcloudCorrBlock
+
+    def uninstall():
+        for n, v in saved.items():
+            setattr(ref_module, n, v)
+        clear_caches()
+
+    return uninstall

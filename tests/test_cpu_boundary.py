@@ -1,0 +1,106 @@
+"""CPU-only checks of the boundary: the C-ABI library loads and exports every symbol include/mvt.h declares, argument
+validation works without touching the GPU, the host mirror refuses CPU tensors (no fallback), and install() rebinds the
+reference's seam names."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from mvtracker_b200 import _lib, dropin, ops
+from oracle import ref_import
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mvt.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mvt_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    L = _lib.lib()
+    names = _declared_symbols()
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(L, n), f"libmvt.so does not export {n}"
+    assert set(names) == set(_lib.SYMBOLS)
+    assert L.mvt_version() == 100
+
+
+def test_workspace_size_is_monotone_and_aligned():
+    L = _lib.lib()
+    prev = 0
+    for n in (1, 100, 4096, 172800, 1 << 20):
+        b = L.mvt_grid_workspace_bytes(12, n)
+        assert b % 256 == 0 and b > prev
+        prev = b
+    assert L.mvt_grid_workspace_bytes(0, 10) == 0
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    L = _lib.lib()
+    assert L.mvt_knn(None, 1, 10, None, 5, 16, None, 0, None, None) == -1
+    assert b"null" in L.mvt_last_error()
+    dummy = ctypes.c_void_p(256)
+    assert L.mvt_knn(dummy, 1, 10, dummy, 5, 64, None, 0, None, None) == -1      # k > 32
+    assert b"k must be" in L.mvt_last_error()
+    lv = (_lib.CorrLevel * 4)()
+    lv[0] = _lib.CorrLevel(256, 256, 256, 8, 16, 0)
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, None, None)
+    assert rc == -1 and b"k should be less than or equal to N" in L.mvt_last_error()   # mvtracker.py:785
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, None, None)
+    assert rc == -1 and b"groups" in L.mvt_last_error()                                 # mvtracker.py:786-787
+    outs = (_lib.LevelOut * 4)()
+    assert L.mvt_cloud_build(dummy, 0, dummy, dummy, 2, 2, 8, 16, 16, 4.0, 0, outs, 0x10, None) == -1   # level 4
+
+
+def test_no_cpu_fallback():
+    x = torch.zeros(1, 10, 3)
+    with pytest.raises(_lib.MvtError):
+        dropin.knn(1, x, x)
+    with pytest.raises(_lib.MvtError):
+        dropin.PointcloudCorrBlock(1, 1, x, torch.zeros(1, 10, 4), True, False)
+    with pytest.raises(_lib.MvtError):
+        dropin.init_pointcloud_from_rgbd(torch.zeros(1, 1, 1, 4, 8, 8), torch.zeros(1, 1, 1, 1, 8, 8),
+                                         torch.eye(3).expand(1, 1, 1, 3, 3), torch.eye(4)[:3].expand(1, 1, 1, 3, 4))
+    with pytest.raises(_lib.MvtError):
+        ops.camera_prep(torch.eye(3)[None], torch.eye(4)[:3][None])
+
+
+def test_block_asserts_match_reference():
+    """Same assertion conditions as mvtracker.py:782-788 (checked before any device work)."""
+    x = torch.zeros(1, 10, 3)
+    f = torch.zeros(1, 10, 6)
+    with pytest.raises(AssertionError):
+        dropin.PointcloudCorrBlock(11, 1, x, f, True, False)          # k > N
+    with pytest.raises(AssertionError):
+        dropin.PointcloudCorrBlock(4, 4, x, f, True, False)           # C % groups != 0
+    with pytest.raises(AssertionError):
+        dropin.PointcloudCorrBlock(4, 1, x, f, True, False, filter_invalid=True, valid=None)
+    with pytest.raises(AssertionError):
+        dropin.init_pointcloud_from_rgbd(torch.zeros(1, 1, 1, 4, 8, 8), torch.zeros(1, 1, 1, 1, 8, 9),
+                                         torch.eye(3).expand(1, 1, 1, 3, 3), torch.eye(4)[:3].expand(1, 1, 1, 3, 4))
+
+
+@pytest.mark.skipif(not ref_import.available(), reason="reference checkout not present (GPU box)")
+def test_install_rebinds_reference_seam():
+    ref = ref_import.load()
+    saved = (ref.mvt.init_pointcloud_from_rgbd, ref.mvt.knn, ref.mvt.PointcloudCorrBlock)
+    undo = dropin.install(ref.mvt)
+    try:
+        assert ref.mvt.init_pointcloud_from_rgbd is dropin.init_pointcloud_from_rgbd
+        assert ref.mvt.knn is dropin.knn
+        assert ref.mvt.PointcloudCorrBlock is dropin.PointcloudCorrBlock
+        import inspect
+        for ours, theirs in zip((dropin.init_pointcloud_from_rgbd, dropin.knn), saved[:2]):
+            assert list(inspect.signature(ours).parameters) == list(inspect.signature(theirs).parameters)
+        assert list(inspect.signature(dropin.PointcloudCorrBlock.__init__).parameters) == \
+            list(inspect.signature(saved[2].__init__).parameters)
+        assert list(inspect.signature(dropin.PointcloudCorrBlock.corr_sample).parameters) == \
+            list(inspect.signature(saved[2].corr_sample).parameters)
+    finally:
+        undo()
+    assert (ref.mvt.init_pointcloud_from_rgbd, ref.mvt.knn, ref.mvt.PointcloudCorrBlock) == saved

@@ -1,0 +1,201 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle and the reference-generated golden vectors.
+
+Bars (north_star): neighbour indices bit-exact against the canonical oracle (ties by index); unprojected points and
+correlation volumes within 1e-4 relative (fp32), 2e-2 with bf16 features."""
+import numpy as np
+import pytest
+import torch
+
+from mvtracker_b200 import dropin, ops, synth
+from oracle import oracle
+from parity import assert_close, golden, knn_sets_equivalent
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def t(a, dtype=torch.float32):
+    return torch.as_tensor(np.ascontiguousarray(a)).to(DEV, dtype)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# cloud build
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,g", golden("unproject"))
+def test_cloud_build_matches_golden(name, g):
+    levels = g["levels"].tolist()
+    clouds = ops.cloud_build(t(g["fmaps"]), t(g["depths"]), t(g["intrs"]), t(g["extrs"]), stride=int(g["stride"]),
+                             levels=levels, depth_interp_mode=str(g["mode"]), want_valid=True)
+    for c in clouds:
+        assert_close(c.xyz.cpu().numpy(), g[f"xyz_l{c.level}"], 1e-4, f"{name} xyz l{c.level}")
+        assert_close(c.fvec.cpu().numpy(), g[f"fvec_l{c.level}"], 1e-5, f"{name} fvec l{c.level}")
+        assert (c.valid.cpu().numpy() == g[f"valid_l{c.level}"]).all()
+
+
+@pytest.mark.parametrize("V,S,C,Hs,Ws,stride", [(3, 2, 128, 45, 80, 4), (2, 3, 32, 33, 70, 4), (1, 1, 3, 19, 21, 1),
+                                                (2, 2, 6, 8, 32, 4)])
+def test_cloud_build_matches_oracle(V, S, C, Hs, Ws, stride):
+    sc = synth.make_scene(V, Hs * stride, Ws * stride, S=S, C=C, stride=stride, zero_frac=0.2, seed=5, device=DEV)
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0]
+    levels = [l for l in range(4) if (Hs >> l) > 0 and (Ws >> l) > 0]
+    clouds = ops.cloud_build(fm, dp, K, E, stride=stride, levels=levels, want_valid=True)
+    for c in clouds:
+        xyz, fvec, valid = oracle.unproject(fm.cpu().numpy(), dp.cpu().numpy(), K.cpu().numpy(), E.cpu().numpy(),
+                                            stride=stride, level=c.level, return_validity_mask=True)
+        assert_close(c.xyz.cpu().numpy(), xyz, 1e-4, f"xyz l{c.level}")
+        assert_close(c.fvec.cpu().numpy(), fvec, 1e-5, f"fvec l{c.level}")
+        assert (c.valid.cpu().numpy() == valid).all()
+        # spacing hint = mean of depth*stride_l/fx over valid pixels
+        sp = c.spacing.cpu().numpy()
+        assert (sp[:, 1] == valid.sum(1)).all()
+    # one level at a time gives the same tensors as the fused pass
+    single = ops.cloud_build(fm, dp, K, E, stride=stride, levels=[levels[-1]])[0]
+    assert torch.equal(single.xyz, clouds[-1].xyz) and torch.equal(single.fvec, clouds[-1].fvec)
+
+
+def test_cloud_build_bf16_features():
+    sc = synth.make_scene(2, 64 * 4, 96 * 4, S=2, C=128, zero_frac=0.1, seed=6, device=DEV)
+    fm = sc.fmaps[0].to(torch.bfloat16)
+    clouds = ops.cloud_build(fm, sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3])
+    ref = ops.cloud_build(fm.float(), sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3])
+    for c, r in zip(clouds, ref):
+        assert c.fvec.dtype == torch.bfloat16
+        assert torch.equal(c.xyz, r.xyz)
+        assert_close(c.fvec.float().cpu().numpy(), r.fvec.cpu().numpy(), 2e-2, f"bf16 fvec l{c.level}")
+    assert torch.equal(clouds[0].fvec, ref[0].fvec.to(torch.bfloat16))   # level 0 is a pure transpose
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# kNN
+# ---------------------------------------------------------------------------------------------------------------
+def check_knn_exact(xyz, q, k, mask=None, spacing=None, cell_scale=0.0, k_hint=None):
+    grid = ops.build_grids([(xyz, mask, spacing)], k_hint=k_hint or k, cell_scale=cell_scale)[0]
+    dist, idx = ops.knn(grid, q, k, idx_dtype=torch.int32)
+    od, oi = oracle.knn(k, xyz.cpu().numpy(), q.cpu().numpy(), None if mask is None else mask.cpu().numpy())
+    idx, dist = idx.cpu().numpy(), dist.cpu().numpy()
+    assert (idx == oi).all(), f"{(idx != oi).any(-1).sum()} / {idx.shape[0] * idx.shape[1]} queries differ"
+    assert (dist == od).all()
+    return grid
+
+
+@pytest.mark.parametrize("name,g", golden("knn"))
+def test_knn_golden(name, g):
+    k = int(g["k"])
+    xyz, q = t(g["xyz"]), t(g["query"])
+    check_knn_exact(xyz, q, k)
+    # and, as sets, against the reference's own output (ties / cdist error adjudicated in f64)
+    grid = ops.build_grids([(xyz, None, None)], k_hint=k)[0]
+    _, idx = ops.knn(grid, q, k)
+    assert idx.dtype == torch.int64
+    knn_sets_equivalent(idx.cpu().numpy(), g["idx"], g["xyz"], g["query"], name)
+
+
+@pytest.mark.parametrize("k", [1, 8, 16, 32])
+@pytest.mark.parametrize("cell_scale", [0.0, 0.3, 4.0])
+def test_knn_scene_exact(k, cell_scale):
+    """Fused multi-view cloud incl. depth-0 pixels (thousands of identical points at each camera centre)."""
+    sc = synth.make_scene(3, 45 * 4, 80 * 4, S=2, C=4, zero_frac=0.3, seed=11, device=DEV)
+    c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
+    coords, _ = synth.make_tracks(c.xyz[0], 300, 2, C=4, valid=c.valid[0])
+    coords[:, :4] += 3.0                         # far from every surface -> ring fallback
+    coords[:, 4] = c.xyz[:, 0]                    # exactly on a cloud point
+    cam_centre = c.xyz[0][~c.valid[0]][0]
+    coords[:, 5] = cam_centre                     # on the depth-0 pile: all-ties, must resolve by index
+    coords[:, 6] = cam_centre + 1e-3
+    check_knn_exact(c.xyz, coords, k, spacing=c.spacing, cell_scale=cell_scale)
+    check_knn_exact(c.xyz, coords, k, spacing=None, cell_scale=cell_scale)      # measure-based cell size
+
+
+def test_knn_mask_and_degenerate_clouds():
+    g = torch.Generator(device=DEV).manual_seed(3)
+    xyz = torch.rand(2, 5000, 3, device=DEV, generator=g)
+    q = torch.rand(2, 200, 3, device=DEV, generator=g)
+    mask = torch.rand(2, 5000, device=DEV, generator=g) > 0.5
+    check_knn_exact(xyz, q, 16, mask=mask)
+    # planar cloud (one collapsed axis), all-identical cloud, tiny cloud (exhaustive path), k == N
+    flat = xyz.clone(); flat[..., 2] = 0.25
+    check_knn_exact(flat, q, 8)
+    same = torch.ones(1, 2000, 3, device=DEV)
+    check_knn_exact(same, q[:1], 16)
+    check_knn_exact(xyz[:, :40].contiguous(), q, 16)
+    check_knn_exact(xyz[:, :16].contiguous(), q, 16)
+    # far-from-origin scene (the case where the reference's cdist loses neighbours)
+    check_knn_exact(xyz + 100.0, q + 100.0, 16)
+
+
+def test_knn_fewer_points_than_k():
+    xyz = torch.rand(1, 2000, 3, device=DEV)
+    mask = torch.zeros(1, 2000, dtype=torch.bool, device=DEV); mask[0, :5] = True
+    grid = ops.build_grids([(xyz, mask, None)], k_hint=8)[0]
+    dist, idx = ops.knn(grid, torch.rand(1, 7, 3, device=DEV), 8)
+    assert (idx[..., 5:] == -1).all() and torch.isinf(dist[..., 5:]).all() and (idx[..., :5] >= 0).all()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# fused kNN + gather + correlation
+# ---------------------------------------------------------------------------------------------------------------
+def check_corr(xyz, fvec, targets, coords, k, G=1, add_offset=True, add_xyz=False, tol=1e-4, spacing=None):
+    grid = ops.build_grids([(xyz, None, spacing)], k_hint=k)[0]
+    out, idx = ops.knn_corr([(grid, xyz, fvec, k)], targets, coords, groups=G, add_offset=add_offset, add_xyz=add_xyz,
+                            return_idx=True)
+    D = G + 3 * add_offset + 3 * add_xyz
+    out = out.reshape(xyz.shape[0], coords.shape[1], k, D).cpu().numpy()
+    o_out, o_idx, _ = oracle.corr_sample(k, xyz.cpu().numpy(), fvec.float().cpu().numpy(), targets.float().cpu().numpy(),
+                                         coords.cpu().numpy(), G, add_offset, add_xyz, return_idx=True)
+    assert (idx[0].cpu().numpy() == o_idx).all()
+    assert_close(out[..., :G], o_out[..., :G], tol, "corr")
+    assert (out[..., G:] == o_out[..., G:]).all(), "offsets / xyz must be bit exact"
+    return out
+
+
+@pytest.mark.parametrize("name,g", golden("corr"))
+def test_corr_golden(name, g):
+    k, G = int(g["k"]), int(g["groups"])
+    out = check_corr(t(g["xyz"]), t(g["fvec"]), t(g["targets"]), t(g["coords"]), k, G, bool(g["add_offset"]),
+                     bool(g["add_xyz"]))
+    ref = g["out"]
+    same = np.isclose(out, ref, rtol=1e-4, atol=1e-5).reshape(-1, k * ref.shape[-1]).all(-1)
+    assert same.mean() >= 0.95, f"{name}: only {same.mean():.3f} of queries match the reference positionally"
+
+
+@pytest.mark.parametrize("C,G,k,add_xyz", [(128, 1, 16, False), (128, 1, 8, True), (128, 4, 16, False), (32, 1, 16, False),
+                                           (32, 4, 8, True), (6, 3, 4, False), (128, 1, 32, False)])
+def test_corr_scene(C, G, k, add_xyz):
+    sc = synth.make_scene(2, 40 * 4, 64 * 4, S=3, C=C, zero_frac=0.1, seed=21, device=DEV)
+    c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
+    coords, targets = synth.make_tracks(c.xyz[0], 257, 3, C=C, valid=c.valid[0])
+    check_corr(c.xyz, c.fvec, targets, coords, k, G, True, add_xyz, spacing=c.spacing)
+
+
+def test_corr_bf16():
+    sc = synth.make_scene(2, 40 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=22, device=DEV)
+    c = ops.cloud_build(sc.fmaps[0].to(torch.bfloat16), sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0],
+                        want_valid=True)[0]
+    coords, targets = synth.make_tracks(c.xyz[0], 200, 2, C=128, valid=c.valid[0], dtype=torch.bfloat16)
+    check_corr(c.xyz, c.fvec, targets, coords, 16, tol=2e-2, spacing=c.spacing)
+
+
+def test_corr_fused_levels_equal_separate_launches():
+    sc = synth.make_scene(3, 48 * 4, 64 * 4, S=4, C=128, zero_frac=0.05, seed=23, device=DEV)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True)
+    grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=16)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 333, 4, valid=clouds[0].valid[0])
+    fused = ops.knn_corr([(g, c.xyz, c.fvec, 16) for g, c in zip(grids, clouds)], targets, coords)
+    assert fused.shape == (4, 333, 4 * 16 * 4)
+    for i, (g, c) in enumerate(zip(grids, clouds)):
+        one = ops.knn_corr([(g, c.xyz, c.fvec, 16)], targets, coords)
+        assert torch.equal(one, fused[:, :, i * 64:(i + 1) * 64])
+        o_out = oracle.corr_sample(16, c.xyz.cpu().numpy(), c.fvec.cpu().numpy(), targets.cpu().numpy(), coords.cpu().numpy())
+        assert_close(one.reshape(4, 333, 16, 4).cpu().numpy(), o_out, 1e-4, f"level {i}")
+
+
+def test_knn_gather_feature_init():
+    sc = synth.make_scene(3, 40 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=24, device=DEV)
+    c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
+    coords, _ = synth.make_tracks(c.xyz[0], 100, 2, valid=c.valid[0])
+    grid = ops.build_grids([(c.xyz, None, c.spacing)], k_hint=1)[0]
+    feat, idx = ops.knn_gather(grid, c.fvec, coords, return_idx=True)
+    _, oi = oracle.knn(1, c.xyz.cpu().numpy(), coords.cpu().numpy())
+    assert (idx.cpu().numpy() == oi[..., 0]).all()
+    expect = torch.gather(c.fvec, 1, idx.long()[..., None].expand(-1, -1, 128))
+    assert torch.equal(feat, expect)
