@@ -120,6 +120,11 @@ int mvt_knn_gather(const void *grid, const void *fvec, int feat_dtype, int B, in
  * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */
 int mvt_grid_info(const void *grid, int B, int N, float *info, void *stream);
 
+/* Debug: device array of 16 uint64 counters the search kernels add to (NULL = off, the default):
+ * [0] queries [1..3] finished after ring 1..3 [4] exhaustive fallbacks [5] candidates scanned [6] top-k insertions
+ * [7] cell lookups [8] small-segment exhaustive scans. */
+int mvt_debug_set_stats(void *dev_counters);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,7 +11,7 @@ MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count")
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats")
 
 
 class LevelOut(C.Structure):
@@ -63,6 +63,7 @@ def lib():
     L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, vp, vp]
     L.mvt_knn_gather.argtypes = [vp, vp, ci, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
+    L.mvt_debug_set_stats.argtypes = [vp]
     for name in SYMBOLS:
         f = getattr(L, name)
         if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count"):

@@ -90,7 +90,10 @@ struct GridView {
     unsigned T;
     int tshift;
     int N;
+    unsigned long long *stats;   // optional debug counters (mvt_debug_set_stats), else nullptr
 };
+
+unsigned long long *debug_stats_ptr();
 
 __host__ inline GridView grid_view(const void *ws, int B, int N) {
     GridLayout L = grid_layout(B, N);
@@ -103,6 +106,7 @@ __host__ inline GridView grid_view(const void *ws, int B, int N) {
     g.T = L.T;
     g.tshift = L.tshift;
     g.N = N;
+    g.stats = debug_stats_ptr();
     return g;
 }
 

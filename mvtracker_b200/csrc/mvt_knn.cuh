@@ -36,9 +36,10 @@ __device__ __forceinline__ void topk_insert(float &bd, int &bi, float cd, int ci
 }
 
 // Offer one candidate per lane.  (td, ti) = current k-th best, uniform across the warp.
-__device__ __forceinline__ void topk_offer(float &bd, int &bi, float &td, int &ti, float d2, int idx, bool valid, int k,
-                                           int lane) {
+__device__ __forceinline__ int topk_offer(float &bd, int &bi, float &td, int &ti, float d2, int idx, bool valid, int k,
+                                          int lane) {
     unsigned m = __ballot_sync(FULL, valid && better(d2, idx, td, ti));
+    int ins = 0;
     while (m) {
         int src = __ffs(m) - 1;
         m &= m - 1;
@@ -48,8 +49,10 @@ __device__ __forceinline__ void topk_offer(float &bd, int &bi, float &td, int &t
             topk_insert(bd, bi, cd, ci, lane);
             td = __shfl_sync(FULL, bd, k - 1);
             ti = __shfl_sync(FULL, bi, k - 1);
+            ++ins;
         }
     }
+    return ins;
 }
 
 __device__ __forceinline__ uint2 cell_lookup(const unsigned *__restrict__ keys, const uint2 *__restrict__ vals,
@@ -64,15 +67,17 @@ __device__ __forceinline__ uint2 cell_lookup(const unsigned *__restrict__ keys, 
 }
 
 // Scan `n` consecutive records starting at pts.
-__device__ __forceinline__ void scan_range(const float4 *__restrict__ pts, unsigned n, float qx, float qy, float qz,
-                                           float &bd, int &bi, float &td, int &ti, int k, int lane) {
+__device__ __forceinline__ int scan_range(const float4 *__restrict__ pts, unsigned n, float qx, float qy, float qz,
+                                          float &bd, int &bi, float &td, int &ti, int k, int lane) {
+    int ins = 0;
     for (unsigned i0 = 0; i0 < n; i0 += 32) {
         unsigned t = i0 + lane;
         bool valid = t < n;
         float4 p = valid ? __ldg(pts + t) : make_float4(0.f, 0.f, 0.f, 0.f);
         float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-        topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
+        ins += topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
     }
+    return ins;
 }
 
 // Exact k nearest neighbours of (qx,qy,qz) in segment b.  On return lane i < k holds the i-th neighbour
@@ -88,6 +93,8 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
     if (n_valid == 0) return;
     const float4 *pts = g.sorted + (size_t)b * g.N;
     bool done = false;
+    unsigned long long st_cand = 0, st_ins = 0, st_look = 0;
+    int st_ring = 0;
     if (n_valid > kBruteN) {
         const float ox = sp->ox, oy = sp->oy, oz = sp->oz, h = sp->h, inv_h = sp->inv_h;
         const int nx = sp->nx, ny = sp->ny, nz = sp->nz;
@@ -123,6 +130,8 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
                 }
                 const unsigned excl = incl - cnt;
                 const unsigned total = __shfl_sync(FULL, incl, 31);
+                st_cand += total;
+                st_look += min(32, ncell - base);
                 for (unsigned i0 = 0; i0 < total; i0 += 32) {
                     unsigned t = i0 + lane;
                     bool valid = t < total;
@@ -136,9 +145,10 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
                     unsigned s0 = __shfl_sync(FULL, start, j), e0 = __shfl_sync(FULL, excl, j);
                     float4 p = valid ? __ldg(pts + s0 + (t - e0)) : make_float4(0.f, 0.f, 0.f, 0.f);
                     float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-                    topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
+                    st_ins += topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
                 }
             }
+            st_ring = r;
             // every unvisited point lies beyond a face of the searched cube [c-r, c+r]^3 that is inside the grid
             float bound = INFINITY;
             if (cx - r > 0) bound = fminf(bound, qx - (ox + (float)(cx - r) * h));
@@ -157,7 +167,16 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
     }
     if (!done) {   // exhaustive fallback (tiny segment, or a query far from the surface)
         bd = INFINITY; bi = kNoIdx; td = INFINITY; ti = kNoIdx;
-        scan_range(pts, n_valid, qx, qy, qz, bd, bi, td, ti, k, lane);
+        st_ins += scan_range(pts, n_valid, qx, qy, qz, bd, bi, td, ti, k, lane);
+        st_cand += n_valid;
+        st_ring = (n_valid > kBruteN) ? 4 : 8;
+    }
+    if (g.stats && lane == 0) {
+        atomicAdd(g.stats + 0, 1ull);
+        atomicAdd(g.stats + st_ring, 1ull);
+        atomicAdd(g.stats + 5, st_cand);
+        atomicAdd(g.stats + 6, st_ins);
+        atomicAdd(g.stats + 7, st_look);
     }
 }
 

@@ -1,0 +1,43 @@
+"""Diagnostics (GPU): grid parameters and search statistics of the kNN kernel for a workload / cell scale sweep.
+    python tools/diag_knn.py --workload droid --scales 0.5,1,2,4
+"""
+import argparse, ctypes, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from mvtracker_b200 import _lib, ops, synth
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--workload", default="droid")
+ap.add_argument("--scales", default="1")
+ap.add_argument("--S", type=int, default=12)
+ap.add_argument("--zero-frac", type=float, default=0.05)
+ap.add_argument("--jitter", type=float, default=0.02)
+a = ap.parse_args()
+w = synth.WORKLOADS[a.workload]
+dev = "cuda"
+sc = synth.make_scene(w["V"], w["H"], w["W"], S=a.S, C=128, zero_frac=a.zero_frac, seed=72, device=dev)
+clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
+coords, targets = synth.make_tracks(clouds[0].xyz[0], w["N"], a.S, seed=73, jitter=a.jitter)
+L = _lib.lib()
+stats = torch.zeros(16, dtype=torch.int64, device=dev)
+names = ["queries", "ring1", "ring2", "ring3", "fallback", "cand", "ins", "lookups", "small"]
+for sc_ in [float(x) for x in a.scales.split(",")]:
+    grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=16, cell_scale=sc_)
+    for lvl, (g, c) in enumerate(zip(grids, clouds)):
+        info = g.info().cpu()
+        i0 = info[0]
+        L.mvt_debug_set_stats(ctypes.c_void_p(stats.data_ptr()))
+        stats.zero_()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.knn_corr([(g, c.xyz, c.fvec, 16)], targets, coords)
+        e1.record()
+        torch.cuda.synchronize()
+        L.mvt_debug_set_stats(None)
+        st = stats.cpu().tolist()
+        q = max(st[0], 1)
+        print(f"scale {sc_:4.2f} lvl {lvl} N={g.N:7d} h={i0[3]:.4f} dims={int(i0[4])}x{int(i0[5])}x{int(i0[6])} cells={int(i0[8])} "
+              f"pts/cell={i0[7] / max(i0[8], 1):.1f} | ms={e0.elapsed_time(e1):.3f} ring1={st[1] / q:.3f} ring2={st[2] / q:.3f} "
+              f"ring3={st[3] / q:.3f} fallback={st[4] / q:.4f} small={st[8] / q:.3f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f} "
+              f"lookups/q={st[7] / q:.0f}")
