@@ -2,8 +2,8 @@
 """bench.py -- kNN-corr track-point queries/s of the MVTracker hot path on B200 (BASELINE.json metric).
 
 One STEP = the hot path of one sliding window (S=12 frames) on synthetic inputs already resident in HBM:
-    camera_prep + cloud_build (4 pyramid levels, one pass)  ->  grid_build (4 levels)  ->
-    iters x knn_corr (all levels / frames / tracks fused in one launch)
+    camera_prep + cloud_build (4 pyramid levels, one pass)  [-> grid_build (4 levels) with --search grid]  ->
+    iters x knn_corr (all levels / frames / tracks fused in one launch; raster search needs no index)
 queries per step = iters * levels * S * N_tracks  (one query = one (track, frame, level, iteration) tuple).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload droid|panoptic|dexycb|kubric] [--impl reference]
@@ -34,6 +34,8 @@ def parse_args():
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
     ap.add_argument("--zero-frac", type=float, default=0.05)
     ap.add_argument("--cell-scale", type=float, default=0.0)
+    ap.add_argument("--search", default="raster", choices=["raster", "grid"],
+                    help="raster: search the depth rasters directly (no index build); grid: hashed grid")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
@@ -171,7 +173,7 @@ def run_reference(args):
 def config_dict(w, args):
     return {"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
-            "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1,
+            "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
             "l2": "inputs_exceed_l2 (feature maps and clouds are > 126 MB and are rewritten every step)"}
 
@@ -202,7 +204,7 @@ def run_ours(args):
     sc = synth.make_scene(w["V"], w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac, seed=72,
                           device=dev, dtype=fdtype)
     fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
-    win = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale)
+    win = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale, search=args.search)
     base_coords, base_targets = synth.make_tracks(win.clouds[0].xyz[0], N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype)
     g = torch.Generator(device=dev).manual_seed(74)
     coords_it = [(base_coords + 0.01 * torch.randn(base_coords.shape, device=dev, generator=g)).contiguous() for _ in range(iters)]
@@ -213,7 +215,7 @@ def run_ours(args):
 
     def step(ev=None):
         if ev is not None: ev[0].record()
-        wdw = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale)
+        wdw = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale, search=args.search)
         # (build = camera_prep + zero + cloud_build, then 6 grid kernels; events split them below)
         if ev is not None: ev[1].record()
         for i in range(iters):
@@ -226,7 +228,9 @@ def run_ours(args):
         ev[0].record()
         clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS))
         ev[1].record()
-        grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
+        grids = None
+        if args.search == "grid":
+            grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
         ev[2].record()
         wdw = WindowClouds(clouds, grids, K_NN, 1, True, False)
         for i in range(iters):
@@ -278,11 +282,11 @@ def run_ours(args):
     D = 4
     q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * D * 4
     corr_bytes = LEVELS * S_WINDOW * N * q_bytes
-    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + sum(c.xyz.numel() * 4 + c.fvec.numel() * esz for c in wdw.clouds)
+    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + sum(c.xyz.numel() * 4 + c.fvec.numel() * esz for c in wdw.clouds)   # (the 16 B/pt xyz4 raster records are overhead, not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6},
-        "grid_build": {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0},
+        "grid_build": {"ms": t_grid, "launches_per_step": 6 if args.search == "grid" else 0, "alg_bytes": 0, "gbs": 0.0},
     }
     for kv in kern.values():
         kv["frac"] = kv["gbs"] / peak

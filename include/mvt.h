@@ -39,6 +39,8 @@ extern "C" {
 
 #define MVT_MAX_LEVELS 4    /* pyramid levels 0..3 (configs/model/mvtracker.yaml: corr_n_levels=4) */
 #define MVT_MAX_K 32
+#define MVT_CAM_STRIDE 48  /* floats per camera record written by mvt_camera_prep */
+#define MVT_MAX_VIEWS 32
 
 int mvt_version(void);
 const char *mvt_last_error(void);
@@ -47,12 +49,15 @@ unsigned long long mvt_launch_count(void);
 
 /* Inverse camera matrices, fp64 on device, rounded to fp32 (model_utils.py:454-457).
  * intrs [n,3,3], extrs [n,3,4] (world->camera), device fp32, n = V*S.
- * cam   [n,24] device fp32:  Kinv (9, row major) | Einv rows 0..2 (12, row major 3x4) | 3 pad. */
+ * cam   [n,MVT_CAM_STRIDE] device fp32:  [0..8] Kinv | [9..20] Einv rows 0..2 (3x4) | [24..32] R | [33..35] t |
+ *       [36..40] fx, skew, cx, fy, cy | [41] 1 if K is upper triangular with K22 == 1 (raster search usable). */
 int mvt_camera_prep(const float *intrs, const float *extrs, int n, float *cam, void *stream);
 
 /* One pyramid level's outputs of the cloud build.  Any pointer may be NULL (skip that output). */
 typedef struct mvt_level_out {
     float *xyz;             /* [S, P_l, 3] fp32, P_l = V*(H>>l)*(W>>l), point = v*H_l*W_l + y*W_l + x (model_utils.py:475) */
+    float *xyz4;            /* [S, P_l, 4] fp32 {x, y, z, depth}: the same points as 16-byte raster records, the
+                               search structure of the raster kNN (no build step) */
     void *fvec;             /* [S, P_l, C] feature dtype (model_utils.py:476) */
     unsigned char *valid;   /* [S, P_l]   depth > 0 (model_utils.py:478-480) */
     float *spacing;         /* [S, 2]     sum and count of the pixel footprint depth*stride_l/fx over valid points
@@ -86,17 +91,31 @@ typedef struct mvt_grid_job {
 /* Builds up to 8 grids (e.g. the 4 pyramid levels) with one set of launches. */
 int mvt_grid_build(const mvt_grid_job *jobs, int n_jobs, void *stream);
 
+/* What a query kernel searches in.  Two structures give identical (exact) results:
+ *   grid mode   (grid != NULL): the hashed grid built by mvt_grid_build over xyz [B,N,3]; any cloud.
+ *   raster mode (grid == NULL): the {x,y,z,depth} records xyz4 [B,N,4] written by mvt_cloud_build plus the camera
+ *                records of mvt_camera_prep; N == V*H*W.  No build step; needs a cloud that came from depth rasters. */
+typedef struct mvt_search {
+    const void *grid;
+    const float *xyz;        /* grid mode: [B,N,3] (neighbour coordinates for the offsets) */
+    const float *xyz4;       /* raster mode: [B,N,4] */
+    const float *cam;        /* raster mode: record of (view v, batch element b) at cam + (v*cam_view_stride + b)*MVT_CAM_STRIDE */
+    int cam_view_stride;     /* records between consecutive views (= S of the mvt_camera_prep call) */
+    int N;
+    int V, H, W;             /* raster mode: rasters of this pyramid level */
+    float stride;            /* raster mode: input-image pixels per raster pixel (stride * 2^level) */
+    int skip_invalid;        /* raster mode: 1 = points with depth <= 0 are not searchable */
+} mvt_search;
+
 /* Exact kNN.  query [B,M,3] device fp32.  idx_out [B,M,k] int32 or int64 (idx_is_i64), dist_out [B,M,k] fp32 Euclidean,
  * either may be NULL.  Order: ascending (d2, index) with d2 = fma(dz,dz,fma(dy,dy,dx*dx)) in fp32.
  * Missing neighbours (fewer than k searchable points): index -1, distance +inf. */
-int mvt_knn(const void *grid, int B, int N, const float *query, int M, int k,
+int mvt_knn(const mvt_search *search, int B, const float *query, int M, int k,
             void *idx_out, int idx_is_i64, float *dist_out, void *stream);
 
 typedef struct mvt_corr_level {
-    const void *grid;       /* built by mvt_grid_build over this level's xyz */
-    const float *xyz;       /* [B,N,3] */
+    mvt_search search;
     const void *fvec;       /* [B,N,C] */
-    int N;
     int k;
     long long out_offset;   /* float offset of this level's k*D block inside an output row */
 } mvt_corr_level;
@@ -112,8 +131,8 @@ int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C
                  float *out, long long out_row_stride, int *idx_out, void *stream);
 
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
- * feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
-int mvt_knn_gather(const void *grid, const void *fvec, int feat_dtype, int B, int N, int C,
+ * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
+int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, int B, int C,
                    const float *query, int M, void *feat_out, int *idx_out, void *stream);
 
 /* Debug / profiling: per-segment grid parameters copied out for inspection.
@@ -121,8 +140,9 @@ int mvt_knn_gather(const void *grid, const void *fvec, int feat_dtype, int B, in
 int mvt_grid_info(const void *grid, int B, int N, float *info, void *stream);
 
 /* Debug: device array of 16 uint64 counters the search kernels add to (NULL = off, the default):
- * [0] queries [1..3] finished after ring 1..3 [4] exhaustive fallbacks [5] candidates scanned [6] top-k insertions
- * [7] cell lookups [8] small-segment exhaustive scans. */
+ * grid mode:   [0] queries [1..3] finished after ring 1..3 [4] exhaustive fallbacks [5] candidates scanned
+ *              [6] top-k insertions [7] cell lookups [8] small-segment exhaustive scans;
+ * raster mode: [0] queries [1..4] finished after 1, 2, 3, >=4 passes [5] candidates scanned [6] insertions. */
 int mvt_debug_set_stats(void *dev_counters);
 
 #ifdef __cplusplus

@@ -9,13 +9,15 @@ SO_PATH = os.path.join(_HERE, "libmvt.so")
 
 MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
+CAM_STRIDE, MAX_VIEWS = 48, 32
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
            "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats")
 
 
 class LevelOut(C.Structure):
-    _fields_ = [("xyz", C.c_void_p), ("fvec", C.c_void_p), ("valid", C.c_void_p), ("spacing", C.c_void_p)]
+    _fields_ = [("xyz", C.c_void_p), ("xyz4", C.c_void_p), ("fvec", C.c_void_p), ("valid", C.c_void_p),
+                ("spacing", C.c_void_p)]
 
 
 class GridJob(C.Structure):
@@ -23,9 +25,14 @@ class GridJob(C.Structure):
                 ("B", C.c_int), ("N", C.c_int), ("k_hint", C.c_int), ("index_mode", C.c_int), ("cell_scale", C.c_float)]
 
 
+class Search(C.Structure):
+    _fields_ = [("grid", C.c_void_p), ("xyz", C.c_void_p), ("xyz4", C.c_void_p), ("cam", C.c_void_p),
+                ("cam_view_stride", C.c_int), ("N", C.c_int), ("V", C.c_int), ("H", C.c_int), ("W", C.c_int),
+                ("stride", C.c_float), ("skip_invalid", C.c_int)]
+
+
 class CorrLevel(C.Structure):
-    _fields_ = [("grid", C.c_void_p), ("xyz", C.c_void_p), ("fvec", C.c_void_p), ("N", C.c_int), ("k", C.c_int),
-                ("out_offset", C.c_longlong)]
+    _fields_ = [("search", Search), ("fvec", C.c_void_p), ("k", C.c_int), ("out_offset", C.c_longlong)]
 
 
 class MvtError(RuntimeError):
@@ -59,9 +66,9 @@ def lib():
     L.mvt_grid_workspace_bytes.argtypes = [ci, ci]
     L.mvt_grid_workspace_bytes.restype = C.c_size_t
     L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
-    L.mvt_knn.argtypes = [vp, ci, ci, vp, ci, ci, vp, ci, vp, vp]
+    L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
     L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, vp, vp]
-    L.mvt_knn_gather.argtypes = [vp, vp, ci, ci, ci, ci, vp, ci, vp, vp, vp]
+    L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
     for name in SYMBOLS:

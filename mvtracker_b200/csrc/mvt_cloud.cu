@@ -32,13 +32,24 @@ __global__ void camera_prep_kernel(const float *__restrict__ intrs, const float 
     }
     inv3(K, Ki);
     inv3(A, Ai);
-    float *o = cam + (size_t)i * 24;
+    float *o = cam + (size_t)i * kCamStride;
     for (int j = 0; j < 9; ++j) o[j] = (float)Ki[j];
     for (int r = 0; r < 3; ++r) {
         for (int c = 0; c < 3; ++c) o[9 + r * 4 + c] = (float)Ai[r * 3 + c];
         o[9 + r * 4 + 3] = (float)(-(Ai[r * 3 + 0] * t[0] + Ai[r * 3 + 1] * t[1] + Ai[r * 3 + 2] * t[2]));
     }
     o[21] = o[22] = o[23] = 0.f;
+    // forward camera for the raster search: R (9), t (3), fx, skew, cx, fy, cy, "K is upper triangular with K22 == 1"
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) o[24 + r * 3 + c] = extrs[i * 12 + r * 4 + c];
+        o[33 + r] = extrs[i * 12 + r * 4 + 3];
+    }
+    o[36] = intrs[i * 9 + 0]; o[37] = intrs[i * 9 + 1]; o[38] = intrs[i * 9 + 2];
+    o[39] = intrs[i * 9 + 4]; o[40] = intrs[i * 9 + 5];
+    bool ok = intrs[i * 9 + 3] == 0.f && intrs[i * 9 + 6] == 0.f && intrs[i * 9 + 7] == 0.f && intrs[i * 9 + 8] == 1.f &&
+              intrs[i * 9 + 0] > 0.f && intrs[i * 9 + 4] > 0.f;
+    o[41] = ok ? 1.f : 0.f;
+    for (int j = 42; j < kCamStride; ++j) o[j] = 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -59,6 +70,7 @@ struct CloudParams {
     int level_mask;
     int tiles_x;
     float *xyz[4];
+    float4 *xyz4[4];
     void *fvec[4];
     unsigned char *valid[4];
     float *spacing[4];
@@ -141,6 +153,7 @@ __device__ __forceinline__ void emit_point(const CloudParams &p, const float *cm
         float *o = p.xyz[lvl] + pt * 3;
         o[0] = X; o[1] = Y; o[2] = Z;
     }
+    if (p.xyz4[lvl]) p.xyz4[lvl][pt] = make_float4(X, Y, Z, depth);
     bool ok = depth > 0.f;
     if (p.valid[lvl]) p.valid[lvl][pt] = ok ? 1 : 0;
     if (ok && depth < 3.0e38f) {
@@ -167,7 +180,7 @@ __global__ void __launch_bounds__(256) cloud_build_kernel(const CloudParams p) {
     const int H = p.H, W = p.W, C = p.C;
     const size_t HW = (size_t)H * W;
 
-    if (tid < 24) cm[tid] = p.cam[(size_t)vs * 24 + tid];
+    if (tid < 24) cm[tid] = p.cam[(size_t)vs * kCamStride + tid];
     // depth pyramid of the tile
     {
         int yy = tid >> 5, xx = tid & 31;
@@ -312,6 +325,7 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
     for (int l = 0; l < 4; ++l) {
         bool on = (level_mask >> l) & 1;
         p.xyz[l] = on ? levels[l].xyz : nullptr;
+        p.xyz4[l] = on ? (float4 *)levels[l].xyz4 : nullptr;
         p.fvec[l] = on ? levels[l].fvec : nullptr;
         p.valid[l] = on ? levels[l].valid : nullptr;
         p.spacing[l] = on ? levels[l].spacing : nullptr;
@@ -319,6 +333,7 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
             MVT_CHECK_ARG((H >> l) > 0 && (W >> l) > 0, "mvt_cloud_build: level %d is empty for %dx%d", l, H, W);
             any_f |= p.fvec[l] != nullptr;
             any_sp |= p.spacing[l] != nullptr;
+            MVT_CHECK_ARG(((uintptr_t)p.xyz4[l] & 15) == 0, "mvt_cloud_build: xyz4[%d] must be 16-byte aligned", l);
             if (p.fvec[l] && C % 4 == 0)
                 MVT_CHECK_ARG(((uintptr_t)p.fvec[l] & 15) == 0, "mvt_cloud_build: fvec[%d] must be 16-byte aligned", l);
         }

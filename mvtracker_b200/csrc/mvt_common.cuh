@@ -39,6 +39,7 @@ constexpr int kNumSMs = 148;   // B200
 constexpr unsigned kEmptyKey = 0xFFFFFFFFu;
 constexpr int kMaxGridDim = 1023;   // 10 bits per axis in the packed cell key
 constexpr int kMaxJobs = 8;
+constexpr int kCamStride = MVT_CAM_STRIDE;   // floats per (view, frame) camera record
 
 // Per-segment grid parameters, written on device by grid_plan.
 struct __align__(16) GridSeg {

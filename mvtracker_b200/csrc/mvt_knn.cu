@@ -2,17 +2,44 @@
 // Replaces knn / PointcloudCorrBlock.corr_sample / the feature-init block of the reference
 // (mvtracker/models/core/mvtracker/mvtracker.py:26-90, 800-846, 627-643).
 //
+// Two exact search back ends behind one interface: the raster search (mvt_raster.cuh; clouds built by cloud_build,
+// no index to build) and the hashed-grid search (mvt_knn.cuh; any cloud).
+//
 // Roofline of knn_corr: HBM bound on the neighbour-feature gather.  Algorithmic bytes per query (k=16, C=128, fp32):
 //   read 12 (xyz) + 512 (target) + 16*(512 + 12) (neighbour rows + xyz), write 16*16  = 9 164 B  (SURVEY.md 8d).
 // The neighbour rows go HBM -> registers -> dot product; they are never written back.
-#include "mvt_knn.cuh"
+#include "mvt_raster.cuh"
 
 namespace mvt {
+
+struct SearchDev {
+    int raster;          // 1: rv is valid, 0: g is valid
+    GridView g;
+    const float *xyz;    // grid mode neighbour coordinates [B,N,3]
+    RasterView rv;
+    int N;
+};
+
+__device__ __forceinline__ void search(const SearchDev &sd, int b, float qx, float qy, float qz, int k, int lane, float &bd,
+                                       int &bi) {
+    if (sd.raster) raster_search(sd.rv, b, qx, qy, qz, k, lane, bd, bi, sd.g.stats);
+    else knn_search(sd.g, b, qx, qy, qz, k, lane, bd, bi);
+}
+
+// coordinates of neighbour `i` of batch element b
+__device__ __forceinline__ float3 nbr_xyz(const SearchDev &sd, int b, int i) {
+    if (sd.raster) {
+        float4 p = __ldg(sd.rv.xyz4 + (size_t)b * sd.N + i);
+        return make_float3(p.x, p.y, p.z);
+    }
+    const float *px = sd.xyz + ((size_t)b * sd.N + i) * 3;
+    return make_float3(__ldg(px), __ldg(px + 1), __ldg(px + 2));
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // plain kNN
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) knn_kernel(const GridView g, int B, int M, const float *__restrict__ query, int k,
+__global__ void __launch_bounds__(256) knn_kernel(const SearchDev sd, int B, int M, const float *__restrict__ query, int k,
                                                   int *__restrict__ idx32, long long *__restrict__ idx64,
                                                   float *__restrict__ dist) {
     const int lane = threadIdx.x & 31;
@@ -21,7 +48,7 @@ __global__ void __launch_bounds__(256) knn_kernel(const GridView g, int B, int M
     const int b = (int)(w / M);
     const float qx = __ldg(query + w * 3), qy = __ldg(query + w * 3 + 1), qz = __ldg(query + w * 3 + 2);
     float bd; int bi;
-    knn_search(g, b, qx, qy, qz, k, lane, bd, bi);
+    search(sd, b, qx, qy, qz, k, lane, bd, bi);
     if (lane < k) {
         bool ok = bi != kNoIdx;
         if (idx32) idx32[w * k + lane] = ok ? bi : -1;
@@ -34,8 +61,7 @@ __global__ void __launch_bounds__(256) knn_kernel(const GridView g, int B, int M
 // fused kNN + gather + correlation
 // ---------------------------------------------------------------------------------------------------------------
 struct CorrLevelDev {
-    GridView g;
-    const float *xyz;
+    SearchDev sd;
     const void *fvec;
     int k;
     long long out_off;
@@ -53,6 +79,56 @@ struct CorrParams {
     float scale;      // sqrt(C/G)
     int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4)
 };
+
+// 16 partial sums per lane (one per neighbour) -> lane L ends with the warp total of neighbour L>>1 (16 shuffles).
+__device__ __forceinline__ float transpose_reduce16(float (&pr)[16], int lane) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        bool hi = lane & 16;
+        float send = hi ? pr[i] : pr[i + 8], keep = hi ? pr[i + 8] : pr[i];
+        pr[i] = keep + __shfl_xor_sync(FULL, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        bool hi = lane & 8;
+        float send = hi ? pr[i] : pr[i + 4], keep = hi ? pr[i + 4] : pr[i];
+        pr[i] = keep + __shfl_xor_sync(FULL, send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        bool hi = lane & 4;
+        float send = hi ? pr[i] : pr[i + 2], keep = hi ? pr[i + 2] : pr[i];
+        pr[i] = keep + __shfl_xor_sync(FULL, send, 4);
+    }
+    {
+        bool hi = lane & 2;
+        float send = hi ? pr[0] : pr[1], keep = hi ? pr[1] : pr[0];
+        pr[0] = keep + __shfl_xor_sync(FULL, send, 2);
+    }
+    return pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
+}
+
+// 8 partial sums per lane, reduced over the 16 lanes of each half-warp -> lane l of a half holds partial (l&15)>>1.
+__device__ __forceinline__ float transpose_reduce8_half(float (&pr)[8], int lane) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        bool hi = lane & 8;
+        float send = hi ? pr[i] : pr[i + 4], keep = hi ? pr[i + 4] : pr[i];
+        pr[i] = keep + __shfl_xor_sync(FULL, send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        bool hi = lane & 4;
+        float send = hi ? pr[i] : pr[i + 2], keep = hi ? pr[i + 2] : pr[i];
+        pr[i] = keep + __shfl_xor_sync(FULL, send, 4);
+    }
+    {
+        bool hi = lane & 2;
+        float send = hi ? pr[0] : pr[1], keep = hi ? pr[1] : pr[0];
+        pr[0] = keep + __shfl_xor_sync(FULL, send, 2);
+    }
+    return pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
+}
 
 // MODE 0: generic fp32 (any C, G).   MODE 1: fp32, C == 128, G == 1, k <= 16 (one float4 of the row per lane).
 // MODE 2: bf16, C == 128, G == 1, k <= 16 (16 lanes x 16 B per row, two rows per warp load).
@@ -76,13 +152,13 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
     if (MODE == 2) tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
 
     float bd; int bi;
-    knn_search(L.g, b, qx, qy, qz, k, lane, bd, bi);
+    search(L.sd, b, qx, qy, qz, k, lane, bd, bi);
 
     if (p.idx_out && lane < k) p.idx_out[(w * k) + lane] = (bi != kNoIdx) ? bi : -1;
 
     const int D = p.G + 3 * p.add_offset + 3 * p.add_xyz;
     float *orow = p.out + q * p.row_stride + L.out_off;
-    const size_t seg = (size_t)b * L.g.N;
+    const size_t seg = (size_t)b * L.sd.N;
     float corr_mine = 0.f;   // MODE 1/2: correlation of neighbour `lane`
 
     if (MODE == 1) {
@@ -95,32 +171,8 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
             if (j < k && ij != kNoIdx) f = __ldg(fv + (seg + (size_t)ij) * 32 + lane);
             pr[j] = fmaf(tg.w, f.w, fmaf(tg.z, f.z, fmaf(tg.y, f.y, tg.x * f.x)));
         }
-        // transpose-reduce: 16 partials x 32 lanes -> lane L holds the total of neighbour L>>1  (16 shuffles)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            bool hi = lane & 16;
-            float send = hi ? pr[i] : pr[i + 8], keep = hi ? pr[i + 8] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, 16);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            bool hi = lane & 8;
-            float send = hi ? pr[i] : pr[i + 4], keep = hi ? pr[i + 4] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, 8);
-        }
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            bool hi = lane & 4;
-            float send = hi ? pr[i] : pr[i + 2], keep = hi ? pr[i + 2] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, 4);
-        }
-        {
-            bool hi = lane & 2;
-            float send = hi ? pr[0] : pr[1], keep = hi ? pr[1] : pr[0];
-            pr[0] = keep + __shfl_xor_sync(FULL, send, 2);
-        }
-        pr[0] += __shfl_xor_sync(FULL, pr[0], 1);
-        corr_mine = __shfl_sync(FULL, pr[0], (2 * lane) & 31);
+        float tot = transpose_reduce16(pr, lane);
+        corr_mine = __shfl_sync(FULL, tot, (2 * lane) & 31);
     } else if (MODE == 2) {
         const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec);
         const int half = lane >> 4, l16 = lane & 15;
@@ -142,46 +194,24 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
             }
             pr[i] = acc;
         }
-        // reduce over the 16 lanes of each half: 8 partials -> lane (within half) l holds neighbour 2*(l>>1) + half
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            bool hi = lane & 8;
-            float send = hi ? pr[i] : pr[i + 4], keep = hi ? pr[i + 4] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, 8);
-        }
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            bool hi = lane & 4;
-            float send = hi ? pr[i] : pr[i + 2], keep = hi ? pr[i + 2] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, 4);
-        }
-        {
-            bool hi = lane & 2;
-            float send = hi ? pr[0] : pr[1], keep = hi ? pr[1] : pr[0];
-            pr[0] = keep + __shfl_xor_sync(FULL, send, 2);
-        }
-        pr[0] += __shfl_xor_sync(FULL, pr[0], 1);
+        float tot = transpose_reduce8_half(pr, lane);
         // neighbour j lives in half (j & 1), lanes 2*(j>>1), 2*(j>>1)+1 of that half
-        corr_mine = __shfl_sync(FULL, pr[0], ((lane & 1) << 4) | ((lane >> 1) << 1));
+        corr_mine = __shfl_sync(FULL, tot, ((lane & 1) << 4) | ((lane >> 1) << 1));
     }
 
     if (MODE != 0) {
         if (lane < k) {
             bool ok = bi != kNoIdx;
-            float nx = 0.f, ny = 0.f, nz = 0.f;
-            if (ok) {
-                const float *px = L.xyz + (seg + (size_t)bi) * 3;
-                nx = __ldg(px); ny = __ldg(px + 1); nz = __ldg(px + 2);
-            }
+            float3 n = ok ? nbr_xyz(L.sd, b, bi) : make_float3(0.f, 0.f, 0.f);
             float cv = ok ? __fdiv_rn(corr_mine, p.scale) : 0.f;
             float *o = orow + (size_t)lane * D;
             if (p.vec_out) {
-                *reinterpret_cast<float4 *>(o) = ok ? make_float4(cv, nx - qx, ny - qy, nz - qz) : make_float4(0.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4 *>(o) = ok ? make_float4(cv, n.x - qx, n.y - qy, n.z - qz) : make_float4(0.f, 0.f, 0.f, 0.f);
             } else {
                 int wpos = 0;
                 o[wpos++] = cv;
-                if (p.add_offset) { o[wpos++] = ok ? nx - qx : 0.f; o[wpos++] = ok ? ny - qy : 0.f; o[wpos++] = ok ? nz - qz : 0.f; }
-                if (p.add_xyz) { o[wpos++] = nx; o[wpos++] = ny; o[wpos++] = nz; }
+                if (p.add_offset) { o[wpos++] = ok ? n.x - qx : 0.f; o[wpos++] = ok ? n.y - qy : 0.f; o[wpos++] = ok ? n.z - qz : 0.f; }
+                if (p.add_xyz) { o[wpos++] = n.x; o[wpos++] = n.y; o[wpos++] = n.z; }
             }
         }
         return;
@@ -204,12 +234,15 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
             for (int o2 = 16; o2; o2 >>= 1) acc += __shfl_xor_sync(FULL, acc, o2);
             if (lane == 0) o[gi] = ok ? __fdiv_rn(acc, p.scale) : 0.f;
         }
-        if (lane < 3 && (p.add_offset || p.add_xyz)) {
-            float pv = ok ? __ldg(L.xyz + (seg + (size_t)ij) * 3 + lane) : 0.f;
-            float qv = lane == 0 ? qx : (lane == 1 ? qy : qz);
-            int wpos = p.G;
-            if (p.add_offset) { o[wpos + lane] = ok ? pv - qv : 0.f; wpos += 3; }
-            if (p.add_xyz) o[wpos + lane] = pv;
+        if (p.add_offset || p.add_xyz) {
+            float3 n = ok ? nbr_xyz(L.sd, b, ij) : make_float3(0.f, 0.f, 0.f);
+            if (lane < 3) {
+                float pv = lane == 0 ? n.x : (lane == 1 ? n.y : n.z);
+                float qv = lane == 0 ? qx : (lane == 1 ? qy : qz);
+                int wpos = p.G;
+                if (p.add_offset) { o[wpos + lane] = ok ? pv - qv : 0.f; wpos += 3; }
+                if (p.add_xyz) o[wpos + lane] = pv;
+            }
         }
     }
 }
@@ -217,7 +250,7 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
 // ---------------------------------------------------------------------------------------------------------------
 // k = 1 search + feature row copy (feature init)
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) knn_gather_kernel(const GridView g, const void *__restrict__ fvec, int elem_bytes,
+__global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, const void *__restrict__ fvec, int elem_bytes,
                                                          int B, int M, int C, const float *__restrict__ query,
                                                          void *__restrict__ feat_out, int *__restrict__ idx_out) {
     const int lane = threadIdx.x & 31;
@@ -226,11 +259,11 @@ __global__ void __launch_bounds__(256) knn_gather_kernel(const GridView g, const
     const int b = (int)(w / M);
     const float qx = __ldg(query + w * 3), qy = __ldg(query + w * 3 + 1), qz = __ldg(query + w * 3 + 2);
     float bd; int bi;
-    knn_search(g, b, qx, qy, qz, 1, lane, bd, bi);
+    search(sd, b, qx, qy, qz, 1, lane, bd, bi);
     int i0 = __shfl_sync(FULL, bi, 0);
     if (idx_out && lane == 0) idx_out[w] = (i0 != kNoIdx) ? i0 : -1;
     const size_t row_bytes = (size_t)C * elem_bytes;
-    const unsigned char *src = reinterpret_cast<const unsigned char *>(fvec) + ((size_t)b * g.N + (size_t)(i0 != kNoIdx ? i0 : 0)) * row_bytes;
+    const unsigned char *src = reinterpret_cast<const unsigned char *>(fvec) + ((size_t)b * sd.N + (size_t)(i0 != kNoIdx ? i0 : 0)) * row_bytes;
     unsigned char *dst = reinterpret_cast<unsigned char *>(feat_out) + (size_t)w * row_bytes;
     if ((row_bytes & 15) == 0 && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
         for (size_t o = (size_t)lane * 16; o < row_bytes; o += 512) {
@@ -249,18 +282,52 @@ __global__ void __launch_bounds__(256) knn_gather_kernel(const GridView g, const
 // ---------------------------------------------------------------------------------------------------------------
 static inline unsigned warp_blocks(long long warps) { return (unsigned)((warps + 7) / 8); }
 
-MVT_EXPORT int mvt_knn(const void *grid, int B, int N, const float *query, int M, int k,
+static int make_search(const mvt_search *u, int B, int need_xyz, mvt::SearchDev &sd, const char *who) {
+    using namespace mvt;
+    MVT_CHECK_ARG(u, "%s: null search descriptor", who);
+    MVT_CHECK_ARG(u->N > 0, "%s: bad N=%d", who, u->N);
+    sd.N = u->N;
+    sd.xyz = u->xyz;
+    if (u->grid) {
+        sd.raster = 0;
+        sd.g = grid_view(u->grid, B, u->N);
+        sd.rv = RasterView{};
+        MVT_CHECK_ARG(!need_xyz || u->xyz, "%s: grid mode needs xyz", who);
+    } else {
+        MVT_CHECK_ARG(u->xyz4 && u->cam, "%s: neither a grid nor raster records (xyz4 + cam) were given", who);
+        MVT_CHECK_ARG(u->V > 0 && u->V <= MVT_MAX_VIEWS && u->H > 0 && u->W > 0, "%s: bad raster V=%d H=%d W=%d (V <= %d)", who,
+                      u->V, u->H, u->W, MVT_MAX_VIEWS);
+        MVT_CHECK_ARG((long long)u->V * u->H * u->W == (long long)u->N, "%s: N=%d != V*H*W=%lld", who, u->N,
+                      (long long)u->V * u->H * u->W);
+        MVT_CHECK_ARG(u->stride > 0.f && u->cam_view_stride >= B, "%s: bad stride %f / cam_view_stride %d", who, u->stride,
+                      u->cam_view_stride);
+        MVT_CHECK_ARG(((uintptr_t)u->xyz4 & 15) == 0, "%s: xyz4 must be 16-byte aligned", who);
+        sd.raster = 1;
+        sd.g = GridView{};
+        sd.g.stats = debug_stats_ptr();
+        sd.rv.xyz4 = reinterpret_cast<const float4 *>(u->xyz4);
+        sd.rv.cam = u->cam;
+        sd.rv.V = u->V; sd.rv.S = u->cam_view_stride; sd.rv.H = u->H; sd.rv.W = u->W;
+        sd.rv.stride = u->stride;
+        sd.rv.skip_invalid = u->skip_invalid ? 1 : 0;
+    }
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_knn(const mvt_search *search, int B, const float *query, int M, int k,
                        void *idx_out, int idx_is_i64, float *dist_out, void *stream) {
     using namespace mvt;
-    MVT_CHECK_ARG(grid && query, "mvt_knn: null pointer");
-    MVT_CHECK_ARG(B > 0 && N > 0 && M >= 0, "mvt_knn: bad shape B=%d N=%d M=%d", B, N, M);
+    MVT_CHECK_ARG(search && query, "mvt_knn: null pointer");
+    MVT_CHECK_ARG(B > 0 && M >= 0, "mvt_knn: bad shape B=%d M=%d", B, M);
     MVT_CHECK_ARG(k >= 1 && k <= MVT_MAX_K, "mvt_knn: k must be 1..%d (got %d)", MVT_MAX_K, k);
     if (M == 0) return MVT_OK;
+    SearchDev sd;
+    int rc = make_search(search, B, 0, sd, "mvt_knn");
+    if (rc) return rc;
     long long warps = (long long)B * M;
     MVT_CHECK_ARG(warps / 8 < 0x7fffffffLL, "mvt_knn: too many queries");
-    GridView g = grid_view(grid, B, N);
     knn_kernel<<<warp_blocks(warps), 256, 0, (cudaStream_t)stream>>>(
-        g, B, M, query, k, idx_is_i64 ? nullptr : (int *)idx_out, idx_is_i64 ? (long long *)idx_out : nullptr, dist_out);
+        sd, B, M, query, k, idx_is_i64 ? nullptr : (int *)idx_out, idx_is_i64 ? (long long *)idx_out : nullptr, dist_out);
     MVT_CHECK_LAUNCH("knn");
     return MVT_OK;
 }
@@ -286,12 +353,14 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     bool aligned = (((uintptr_t)targets & 15) == 0);
     for (int l = 0; l < n_levels; ++l) {
         const mvt_corr_level &u = levels[l];
-        MVT_CHECK_ARG(u.grid && u.xyz && u.fvec, "mvt_knn_corr: level %d has a null pointer", l);
-        MVT_CHECK_ARG(u.N > 0 && u.k >= 1 && u.k <= MVT_MAX_K, "mvt_knn_corr: level %d bad N=%d k=%d", l, u.N, u.k);
-        MVT_CHECK_ARG(u.k <= u.N, "mvt_knn_corr: k should be less than or equal to N (level %d: k=%d N=%d)", l, u.k, u.N);   // mvtracker.py:785
+        MVT_CHECK_ARG(u.fvec, "mvt_knn_corr: level %d has a null fvec", l);
+        MVT_CHECK_ARG(u.k >= 1 && u.k <= MVT_MAX_K, "mvt_knn_corr: level %d bad k=%d", l, u.k);
+        MVT_CHECK_ARG(u.k <= u.search.N, "mvt_knn_corr: k should be less than or equal to N (level %d: k=%d N=%d)", l, u.k,
+                      u.search.N);   // mvtracker.py:785
         MVT_CHECK_ARG(idx_out == nullptr || u.k == levels[0].k, "mvt_knn_corr: idx_out needs the same k on every level");
-        p.lv[l].g = grid_view(u.grid, B, u.N);
-        p.lv[l].xyz = u.xyz; p.lv[l].fvec = u.fvec; p.lv[l].k = u.k; p.lv[l].out_off = u.out_offset;
+        int rc = make_search(&u.search, B, p.add_offset || p.add_xyz, p.lv[l].sd, "mvt_knn_corr");
+        if (rc) return rc;
+        p.lv[l].fvec = u.fvec; p.lv[l].k = u.k; p.lv[l].out_off = u.out_offset;
         fast = fast && u.k <= 16;
         vec = vec && (u.out_offset % 4 == 0);
         aligned = aligned && (((uintptr_t)u.fvec & 15) == 0);
@@ -309,16 +378,18 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     return MVT_OK;
 }
 
-MVT_EXPORT int mvt_knn_gather(const void *grid, const void *fvec, int feat_dtype, int B, int N, int C,
+MVT_EXPORT int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, int B, int C,
                               const float *query, int M, void *feat_out, int *idx_out, void *stream) {
     using namespace mvt;
-    MVT_CHECK_ARG(grid && fvec && query && feat_out, "mvt_knn_gather: null pointer");
-    MVT_CHECK_ARG(B > 0 && N > 0 && M >= 0 && C > 0, "mvt_knn_gather: bad shape B=%d N=%d M=%d C=%d", B, N, M, C);
+    MVT_CHECK_ARG(search && fvec && query && feat_out, "mvt_knn_gather: null pointer");
+    MVT_CHECK_ARG(B > 0 && M >= 0 && C > 0, "mvt_knn_gather: bad shape B=%d M=%d C=%d", B, M, C);
     MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_knn_gather: feat_dtype %d", feat_dtype);
     if (M == 0) return MVT_OK;
+    SearchDev sd;
+    int rc = make_search(search, B, 0, sd, "mvt_knn_gather");
+    if (rc) return rc;
     long long warps = (long long)B * M;
-    GridView g = grid_view(grid, B, N);
-    knn_gather_kernel<<<warp_blocks(warps), 256, 0, (cudaStream_t)stream>>>(g, fvec, feat_dtype == MVT_F32 ? 4 : 2, B, M, C, query,
+    knn_gather_kernel<<<warp_blocks(warps), 256, 0, (cudaStream_t)stream>>>(sd, fvec, feat_dtype == MVT_F32 ? 4 : 2, B, M, C, query,
                                                                           feat_out, idx_out);
     MVT_CHECK_LAUNCH("knn_gather");
     return MVT_OK;

@@ -33,6 +33,9 @@ settings = SimpleNamespace(
     # indices from the uncompacted arrays).  'intended': invalid points are skipped and the true neighbours gathered.
     filter_invalid_mode="reference",
     cell_scale=0.0,
+    # 'raster': clouds that came from init_pointcloud_from_rgbd are searched directly in their depth rasters (no index
+    # to build); 'grid': always build the hashed grid.  Clouds of unknown origin always use the grid.
+    search="raster",
 )
 
 
@@ -120,9 +123,34 @@ def knn(k: int, xyz_ref: torch.Tensor, xyz_query: torch.Tensor):
         raise MvtError("mvtracker_b200.knn needs CUDA tensors (no CPU fallback)")
     B, N, _ = xyz_ref.shape
     assert xyz_query.shape[0] == B and xyz_query.shape[2] == 3
-    grid = ops.build_grids([(xyz_ref, None, None)], k_hint=k, cell_scale=settings.cell_scale)[0]
-    dists, idx = ops.knn(grid, xyz_query, k, idx_dtype=torch.int64)
+    where = _find_raster(xyz_ref) if settings.search == "raster" else None
+    if where is None:
+        where = ops.build_grids([(xyz_ref, None, None)], k_hint=k, cell_scale=settings.cell_scale)[0]
+    dists, idx = ops.knn(where, xyz_query, k, idx_dtype=torch.int64)
     return dists.to(xyz_ref.dtype), idx
+
+
+def _find_raster(xyz_ref: torch.Tensor):
+    """If xyz_ref is (a run of whole frames of) a cloud produced by init_pointcloud_from_rgbd that is still cached --
+    e.g. `rgbd_xyz[b, t].reshape(-1, 3)[None]` in the feature-init loop (mvtracker.py:633-637) -- return the raster
+    search over exactly those frames; else None."""
+    if xyz_ref.dtype != torch.float32 or not xyz_ref.is_contiguous():
+        return None
+    Bq, N, _ = xyz_ref.shape
+    ptr = xyz_ref.data_ptr()
+    for pyr in _pyramid_cache:
+        for cloud in pyr.clouds.values():
+            S, P = cloud.xyz.shape[0], cloud.xyz.shape[1]
+            base = cloud.xyz.data_ptr()
+            if cloud.xyz4 is None or P != N or cloud.xyz._version != 0 or cloud.xyz4._version != 0:
+                continue
+            off = ptr - base
+            if off < 0 or off % (P * 12) != 0:
+                continue
+            f0 = off // (P * 12)
+            if f0 + Bq <= S:
+                return ops.Search.from_cloud(cloud, frame=int(f0), nframes=int(Bq))
+    return None
 
 
 _pending_blocks = weakref.WeakSet()   # blocks whose grids have not been built yet (built together on first use)
@@ -164,13 +192,23 @@ class PointcloudCorrBlock:
         self._xyz_c = xyz if (xyz.dtype == torch.float32 and xyz.is_contiguous()) else xyz.float().contiguous()
         self._fvec_c = fvec.contiguous()
         self._grid = None
-        self._pyr, self._level, self._spacing = None, None, None
+        self._pyr, self._level, self._spacing, self._cloud = None, None, None, None
         tag = getattr(xyz, "_mvt", None)
-        if tag is not None and tag[0]() is not None:
+        if tag is not None and tag[0]() is not None and xyz._version == 0:
             self._pyr, self._level = tag[0](), tag[1]
-            self._spacing = self._pyr.clouds[self._level].spacing
+            self._cloud = self._pyr.clouds[self._level]
+            self._spacing = self._cloud.spacing
             self._pyr.blocks[self._level] = self
-        _pending_blocks.add(self)
+        self._raster = (settings.search == "raster" and self._cloud is not None and self._cloud.xyz4 is not None
+                        and not (filter_invalid and settings.filter_invalid_mode == "reference"))
+        if not self._raster:
+            _pending_blocks.add(self)
+
+    def _search(self):
+        if self._raster:
+            return ops.Search.from_cloud(self._cloud, skip_invalid=self.filter_invalid)
+        self._ensure_grid()
+        return ops.Search.from_grid(self._grid, self._xyz_c)
 
     # -- grids of all blocks created since the last build go into one mvt_grid_build call -------------------------
     def _ensure_grid(self):
@@ -193,7 +231,8 @@ class PointcloudCorrBlock:
         sib = [b for _, b in sorted(self._pyr.blocks.items())
                if b.B == self.B and b.C == self.C and b.groups == self.groups and b.fvec.dtype == self.fvec.dtype
                and b.corr_add_neighbor_offset == self.corr_add_neighbor_offset
-               and b.corr_add_neighbor_xyz == self.corr_add_neighbor_xyz and b.filter_invalid == self.filter_invalid]
+               and b.corr_add_neighbor_xyz == self.corr_add_neighbor_xyz and b.filter_invalid == self.filter_invalid
+               and b._raster == self._raster]
         return sib if self in sib else [self]
 
     def corr_sample(
@@ -222,9 +261,7 @@ class PointcloudCorrBlock:
             cache = self._pyr.corr_cache
             if cache is not None and cache[0] == ckey and id(self) in cache[1]:
                 return cache[1].pop(id(self))
-        for b in sib:
-            b._ensure_grid()
-        levels = [(b._grid, b._xyz_c, b._fvec_c, b.k) for b in sib]
+        levels = [(b._search(), b._fvec_c, b.k) for b in sib]
         out = ops.knn_corr(levels, targets, coords_world_xyz, groups=self.groups, add_offset=self.corr_add_neighbor_offset,
                            add_xyz=self.corr_add_neighbor_xyz)
         res, off = {}, 0

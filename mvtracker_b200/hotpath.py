@@ -1,7 +1,7 @@
 """The hot path of one sliding window as two calls (the loop structure of forward_iteration, reference
 mvtracker/models/core/mvtracker/mvtracker.py:296-322 and :350-376, without the per-level Python round trips):
 
-    win = WindowClouds.build(fmaps, depths, intrs, extrs)        # 4-level cloud + grids: 1 + 1 + 6 kernel launches
+    win = WindowClouds.build(fmaps, depths, intrs, extrs)        # 4-level cloud in one pass; raster search: no index build
     fcorrs = win.corr(ffeats, coords)                            # all levels, all frames, all tracks: 1 launch
     # fcorrs [S, N, levels*k*(G+3)] == torch.cat([corr_sample(level l) ...], -1) at mvtracker.py:374
 """
@@ -13,35 +13,43 @@ from . import ops
 
 
 class WindowClouds:
-    def __init__(self, clouds: List[ops.Cloud], grids: List[ops.Grid], k: int, groups: int, add_offset: bool, add_xyz: bool):
+    def __init__(self, clouds: List[ops.Cloud], grids: Optional[List[ops.Grid]], k: int, groups: int, add_offset: bool,
+                 add_xyz: bool):
         self.clouds, self.grids = clouds, grids
+        self.searches = ([ops.Search.from_cloud(c) for c in clouds] if grids is None
+                         else [ops.Search.from_grid(g, c.xyz) for g, c in zip(grids, clouds)])
         self.k, self.groups, self.add_offset, self.add_xyz = k, groups, add_offset, add_xyz
         self.D = groups + 3 * bool(add_offset) + 3 * bool(add_xyz)
         self.width = len(clouds) * k * self.D
 
     @classmethod
     def build(cls, fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0, 1, 2, 3), k=16, groups=1,
-              add_offset=True, add_xyz=False, cell_scale=0.0, depth_interp_mode="nearest") -> "WindowClouds":
-        """fmaps [V,S,C,H',W'] (or with a leading batch axis of 1), depths [V,S,H',W'] / [V,S,1,H',W']."""
+              add_offset=True, add_xyz=False, cell_scale=0.0, depth_interp_mode="nearest", search="raster") -> "WindowClouds":
+        """fmaps [V,S,C,H',W'] (or with a leading batch axis of 1), depths [V,S,H',W'] / [V,S,1,H',W'].
+        search: "raster" (search the depth rasters directly, nothing to build) or "grid" (hashed grid, 6 more launches)."""
         if fmaps.dim() == 6:
             assert fmaps.shape[0] == 1, "B must be 1 (mvtracker.py:275)"
             fmaps, depths, intrs, extrs = fmaps[0], depths[0], intrs[0], extrs[0]
         clouds = ops.cloud_build(fmaps, depths, intrs, extrs, stride=stride, levels=levels,
                                  depth_interp_mode=depth_interp_mode)
-        grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=k, cell_scale=cell_scale)
+        grids = None
+        if search == "grid":
+            grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=k, cell_scale=cell_scale)
+        elif search != "raster":
+            raise ValueError(search)
         return cls(clouds, grids, k, groups, add_offset, add_xyz)
 
     def corr(self, targets: torch.Tensor, coords: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """targets [S,N,C], coords [S,N,3] -> [S,N,width]."""
-        levels = [(g, c.xyz, c.fvec, self.k) for g, c in zip(self.grids, self.clouds)]
+        levels = [(sr, c.fvec, self.k) for sr, c in zip(self.searches, self.clouds)]
         return ops.knn_corr(levels, targets, coords, groups=self.groups, add_offset=self.add_offset, add_xyz=self.add_xyz,
                             out=out)
 
     def feature_init(self, frame: int, query_xyz: torch.Tensor) -> torch.Tensor:
-        """Nearest level-0 point's feature for each query of `frame` (mvtracker.py:627-643).  query_xyz [n,3] -> [n,C].
-        Uses the window grid of that frame (cell size tuned for k, still exact for k=1)."""
-        c, g = self.clouds[0], self.grids[0]
-        S = c.xyz.shape[0]
-        q = torch.zeros(S, query_xyz.shape[0], 3, device=query_xyz.device, dtype=torch.float32)
-        q[frame] = query_xyz
-        return ops.knn_gather(g, c.fvec, q)[frame]
+        """Nearest level-0 point's feature for each query of `frame` (mvtracker.py:627-643).  query_xyz [n,3] -> [n,C]."""
+        c = self.clouds[0]
+        if self.grids is None:
+            sr = ops.Search.from_cloud(c, frame=frame)
+            return ops.knn_gather(sr, c.fvec[frame:frame + 1], query_xyz[None])[0]
+        g = ops.build_grids([(c.xyz[frame:frame + 1], None, c.spacing[frame:frame + 1])], k_hint=1)[0]
+        return ops.knn_gather(g, c.fvec[frame:frame + 1], query_xyz[None])[0]

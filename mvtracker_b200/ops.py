@@ -7,6 +7,7 @@ import torch
 
 from . import _lib
 from ._lib import C, CorrLevel, GridJob, LevelOut, MvtError, check, lib
+from ._lib import Search as _CSearch
 
 
 def _stream():
@@ -31,12 +32,12 @@ def _feat_dtype(t: torch.Tensor) -> int:
 
 
 def camera_prep(intrs: torch.Tensor, extrs: torch.Tensor) -> torch.Tensor:
-    """intrs [...,3,3], extrs [...,3,4] -> cam [n,24] fp32 (Kinv | Einv rows), see mvt_camera_prep."""
+    """intrs [...,3,3], extrs [...,3,4] -> cam [n, CAM_STRIDE] fp32 records, see mvt_camera_prep."""
     _need_cuda(intrs, "intrs"); _need_cuda(extrs, "extrs")
     K = intrs.reshape(-1, 3, 3).float().contiguous()
     E = extrs.reshape(-1, 3, 4).float().contiguous()
     assert K.shape[0] == E.shape[0]
-    cam = torch.empty(K.shape[0], 24, device=K.device, dtype=torch.float32)
+    cam = torch.empty(K.shape[0], _lib.CAM_STRIDE, device=K.device, dtype=torch.float32)
     check(lib().mvt_camera_prep(_ptr(K), _ptr(E), K.shape[0], _ptr(cam), _stream()), "mvt_camera_prep")
     return cam
 
@@ -49,10 +50,16 @@ class Cloud:
     fvec: Optional[torch.Tensor]       # [S, P, C]
     valid: Optional[torch.Tensor]      # [S, P] bool
     spacing: Optional[torch.Tensor]    # [S, 2] (sum, count) footprint hint for the grid
+    xyz4: Optional[torch.Tensor] = None  # [S, P, 4] {x,y,z,depth} raster records (the raster search structure)
+    cam: Optional[torch.Tensor] = None   # [V*S, CAM_STRIDE] camera records
+    V: int = 0
+    H: int = 0                           # raster height / width of this level
+    W: int = 0
+    stride: float = 0.0                  # input pixels per raster pixel at this level
 
 
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
-                want_valid=False, want_fvec=True, cam=None) -> List[Cloud]:
+                want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None) -> List[Cloud]:
     """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass."""
     _need_cuda(fmaps, "fmaps"); _need_cuda(depths, "depths")
     V, S, Cc, H, W = fmaps.shape
@@ -77,11 +84,13 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         xyz = torch.empty(S, P, 3, device=dev, dtype=torch.float32)
         fvec = torch.empty(S, P, Cc, device=dev, dtype=fm.dtype) if want_fvec else None
         valid = torch.empty(S, P, device=dev, dtype=torch.uint8) if want_valid else None
-        spacing = torch.empty(S, 2, device=dev, dtype=torch.float32)
-        outs[l] = LevelOut(xyz.data_ptr(), fvec.data_ptr() if want_fvec else None,
-                           valid.data_ptr() if want_valid else None, spacing.data_ptr())
+        spacing = torch.empty(S, 2, device=dev, dtype=torch.float32) if want_spacing else None
+        xyz4 = torch.empty(S, P, 4, device=dev, dtype=torch.float32) if want_xyz4 else None
+        outs[l] = LevelOut(xyz.data_ptr(), xyz4.data_ptr() if want_xyz4 else None, fvec.data_ptr() if want_fvec else None,
+                           valid.data_ptr() if want_valid else None, spacing.data_ptr() if want_spacing else None)
         mask |= 1 << l
-        clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing))
+        clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
+                            float(stride) * (1 << l)))
     check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                 int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
     return clouds
@@ -130,38 +139,88 @@ def build_grids(clouds: Sequence, k_hint=16, index_mode=0, cell_scale=0.0) -> Li
     return grids
 
 
-def knn(grid: Grid, query: torch.Tensor, k: int, idx_dtype=torch.int64, want_dist=True):
-    """-> (dists [B,M,k] fp32 ascending, idx [B,M,k]); canonical (d2, index) order; -1 / inf where fewer than k points."""
+class Search:
+    """What a query kernel searches in (mvt_search): a hashed grid over any cloud, or the raster records of a Cloud."""
+
+    def __init__(self, c_struct, B, N, keep):
+        self.c, self.B, self.N, self._keep = c_struct, B, N, keep
+
+    @classmethod
+    def from_grid(cls, grid: Grid, xyz: Optional[torch.Tensor] = None):
+        x = grid.xyz if xyz is None else xyz
+        c = _CSearch(grid.ptr, x.data_ptr(), None, None, 0, grid.N, 0, 0, 0, 0.0, 0)
+        return cls(c, grid.B, grid.N, (grid, x))
+
+    @classmethod
+    def from_cloud(cls, cloud: Cloud, skip_invalid=False, frame: Optional[int] = None, nframes: int = 1):
+        """Raster search over a Cloud from cloud_build (no build step).  frame=f restricts to frames f..f+nframes-1."""
+        if cloud.xyz4 is None or cloud.cam is None:
+            raise MvtError("this Cloud has no raster records (build it with want_xyz4=True)")
+        S, P = cloud.xyz4.shape[0], cloud.xyz4.shape[1]
+        x4, cam, B = cloud.xyz4, cloud.cam, S
+        x4_ptr, cam_ptr = x4.data_ptr(), cam.data_ptr()
+        if frame is not None:
+            x4_ptr += frame * P * 16
+            cam_ptr += frame * _lib.CAM_STRIDE * 4
+            B = int(nframes)
+            assert 0 <= frame and frame + B <= S
+        c = _CSearch(None, None, x4_ptr, cam_ptr, S, P, cloud.V, cloud.H, cloud.W, float(cloud.stride), int(bool(skip_invalid)))
+        return cls(c, B, P, (x4, cam))
+
+
+def _as_search(obj) -> Search:
+    if isinstance(obj, Search):
+        return obj
+    if isinstance(obj, Grid):
+        return Search.from_grid(obj)
+    if isinstance(obj, Cloud):
+        return Search.from_cloud(obj)
+    raise MvtError(f"cannot search in {type(obj)}")
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.float().contiguous()
+
+
+def knn(where, query: torch.Tensor, k: int, idx_dtype=torch.int64, want_dist=True):
+    """where: Grid | Cloud | Search.  -> (dists [B,M,k] fp32 ascending, idx [B,M,k]); canonical (d2, index) order;
+    -1 / inf where fewer than k searchable points exist."""
     _need_cuda(query, "query")
-    q = query if (query.dtype == torch.float32 and query.is_contiguous()) else query.float().contiguous()
+    sr = _as_search(where)
+    q = _f32c(query)
     B, M, _ = q.shape
-    if B != grid.B:
-        raise MvtError(f"query batch {B} != grid batch {grid.B}")
+    if B != sr.B:
+        raise MvtError(f"query batch {B} != search batch {sr.B}")
     idx = torch.empty(B, M, k, device=q.device, dtype=idx_dtype)
     dist = torch.empty(B, M, k, device=q.device, dtype=torch.float32) if want_dist else None
-    check(lib().mvt_knn(C.c_void_p(grid.ptr), B, grid.N, _ptr(q), M, int(k), _ptr(idx), int(idx_dtype == torch.int64),
-                        _ptr(dist), _stream()), "mvt_knn")
+    check(lib().mvt_knn(C.byref(sr.c), B, _ptr(q), M, int(k), _ptr(idx), int(idx_dtype == torch.int64), _ptr(dist),
+                        _stream()), "mvt_knn")
     return dist, idx
 
 
 def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, groups=1, add_offset=True, add_xyz=False,
              out: Optional[torch.Tensor] = None, return_idx=False):
-    """levels: sequence of (grid, xyz [B,N,3], fvec [B,N,C], k).  -> out [B, M, sum_l k_l*D] fp32 (level-major columns,
-    the layout of torch.cat(fcorrs, -1) at mvtracker.py:374), D = groups + 3*add_offset + 3*add_xyz."""
+    """levels: sequence of (where, fvec [B,N,C], k) with where = Grid | Cloud | Search.
+    -> out [B, M, sum_l k_l*D] fp32 (level-major columns, the layout of torch.cat(fcorrs, -1) at mvtracker.py:374),
+    D = groups + 3*add_offset + 3*add_xyz."""
     _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
     B, M, Cc = targets.shape
     tg = targets.contiguous()
-    cq = coords if (coords.dtype == torch.float32 and coords.is_contiguous()) else coords.float().contiguous()
+    cq = _f32c(coords)
     D = groups + 3 * bool(add_offset) + 3 * bool(add_xyz)
     n = len(levels)
     lv = (CorrLevel * _lib.MAX_LEVELS)()
-    off = 0
-    for i, (grid, xyz, fvec, k) in enumerate(levels):
+    off, keep = 0, []
+    for i, (where, fvec, k) in enumerate(levels):
+        sr = _as_search(where)
+        keep.append(sr)
+        if sr.B != B:
+            raise MvtError(f"targets batch {B} != search batch {sr.B}")
         if fvec.dtype != tg.dtype:
             raise MvtError(f"targets dtype {tg.dtype} != fvec dtype {fvec.dtype}")
-        if not (fvec.is_contiguous() and xyz.is_contiguous() and xyz.dtype == torch.float32):
-            raise MvtError("xyz / fvec must be contiguous (xyz fp32)")
-        lv[i] = CorrLevel(grid.ptr, xyz.data_ptr(), fvec.data_ptr(), grid.N, int(k), off)
+        if not fvec.is_contiguous() or fvec.shape[-1] != Cc:
+            raise MvtError("fvec must be contiguous [B,N,C] with the targets' C")
+        lv[i] = CorrLevel(sr.c, fvec.data_ptr(), int(k), off)
         off += int(k) * D
     if out is None:
         out = torch.empty(B, M, off, device=tg.device, dtype=torch.float32)
@@ -169,20 +228,23 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     assert out.shape[0] == B and out.shape[1] == M and out.stride(2) == 1 and out.stride(0) == M * row_stride
     idx = None
     if return_idx:
-        idx = torch.empty(n, B, M, int(levels[0][3]), device=tg.device, dtype=torch.int32)
+        idx = torch.empty(n, B, M, int(levels[0][2]), device=tg.device, dtype=torch.int32)
     check(lib().mvt_knn_corr(lv, n, B, M, Cc, int(groups), _feat_dtype(tg), _ptr(tg), _ptr(cq), int(bool(add_offset)),
                              int(bool(add_xyz)), _ptr(out), row_stride, _ptr(idx), _stream()), "mvt_knn_corr")
     return (out, idx) if return_idx else out
 
 
-def knn_gather(grid: Grid, fvec: torch.Tensor, query: torch.Tensor, return_idx=False):
-    """k=1: feature row of the nearest cloud point per query.  fvec [B,N,C], query [B,M,3] -> [B,M,C]."""
+def knn_gather(where, fvec: torch.Tensor, query: torch.Tensor, return_idx=False):
+    """k=1: feature row of the nearest cloud point per query.  fvec [B,N,C] (or the frame's [1,N,C]), query [B,M,3]."""
     _need_cuda(query, "query"); _need_cuda(fvec, "fvec")
-    q = query if (query.dtype == torch.float32 and query.is_contiguous()) else query.float().contiguous()
+    sr = _as_search(where)
+    q = _f32c(query)
     fv = fvec.contiguous()
     B, M, _ = q.shape
+    if B != sr.B or fv.shape[0] != B or fv.shape[1] != sr.N:
+        raise MvtError(f"shape mismatch: query batch {B}, search batch {sr.B}, fvec {tuple(fv.shape)}")
     out = torch.empty(B, M, fv.shape[-1], device=q.device, dtype=fv.dtype)
     idx = torch.empty(B, M, device=q.device, dtype=torch.int32) if return_idx else None
-    check(lib().mvt_knn_gather(C.c_void_p(grid.ptr), _ptr(fv), _feat_dtype(fv), B, grid.N, fv.shape[-1], _ptr(q), M,
-                               _ptr(out), _ptr(idx), _stream()), "mvt_knn_gather")
+    check(lib().mvt_knn_gather(C.byref(sr.c), _ptr(fv), _feat_dtype(fv), B, fv.shape[-1], _ptr(q), M, _ptr(out), _ptr(idx),
+                               _stream()), "mvt_knn_gather")
     return (out, idx) if return_idx else out

@@ -42,13 +42,20 @@ def test_workspace_size_is_monotone_and_aligned():
 
 def test_argument_errors_are_reported_without_a_gpu():
     L = _lib.lib()
-    assert L.mvt_knn(None, 1, 10, None, 5, 16, None, 0, None, None) == -1
-    assert b"null" in L.mvt_last_error()
     dummy = ctypes.c_void_p(256)
-    assert L.mvt_knn(dummy, 1, 10, dummy, 5, 64, None, 0, None, None) == -1      # k > 32
+    assert L.mvt_knn(None, 1, None, 5, 16, None, 0, None, None) == -1
+    assert b"null" in L.mvt_last_error()
+    sr = _lib.Search(256, 256, None, None, 0, 10, 0, 0, 0, 0.0, 0)           # grid mode
+    assert L.mvt_knn(ctypes.byref(sr), 1, dummy, 5, 64, None, 0, None, None) == -1      # k > 32
     assert b"k must be" in L.mvt_last_error()
+    empty = _lib.Search(None, None, None, None, 0, 10, 0, 0, 0, 0.0, 0)
+    assert L.mvt_knn(ctypes.byref(empty), 1, dummy, 5, 8, None, 0, None, None) == -1
+    assert b"neither a grid nor raster" in L.mvt_last_error()
+    bad = _lib.Search(None, None, 256, 256, 12, 100, 3, 5, 5, 4.0, 0)        # N != V*H*W
+    assert L.mvt_knn(ctypes.byref(bad), 1, dummy, 5, 8, None, 0, None, None) == -1
+    assert b"V*H*W" in L.mvt_last_error()
     lv = (_lib.CorrLevel * 4)()
-    lv[0] = _lib.CorrLevel(256, 256, 256, 8, 16, 0)
+    lv[0] = _lib.CorrLevel(_lib.Search(256, 256, None, None, 0, 8, 0, 0, 0, 0.0, 0), 256, 16, 0)
     rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, None, None)
     assert rc == -1 and b"k should be less than or equal to N" in L.mvt_last_error()   # mvtracker.py:785
     rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, None, None)

@@ -22,6 +22,7 @@ def _fresh():
     dropin.settings.pyramid_cache = True
     dropin.settings.fuse_levels = True
     dropin.settings.filter_invalid_mode = "reference"
+    dropin.settings.search = "raster"
     yield
     dropin.clear_caches()
 
@@ -79,10 +80,12 @@ def test_corr_block_golden(name, g):
     assert same.mean() >= 0.95
 
 
+@pytest.mark.parametrize("search", ["raster", "grid"])
 @pytest.mark.parametrize("fuse", [True, False])
-def test_forward_iteration_call_pattern(fuse):
+def test_forward_iteration_call_pattern(fuse, search):
     """4 levels built level by level, 4 blocks, then iters x levels corr_sample calls, concatenated as at mvtracker.py:374."""
     dropin.settings.fuse_levels = fuse
+    dropin.settings.search = search
     V, S, N, C, k = 3, 12, 200, 128, 16
     sc = synth.make_scene(V, 48 * 4, 64 * 4, S=S, C=C, zero_frac=0.1, seed=31, device=DEV)
     blocks, clouds = [], []
@@ -104,11 +107,15 @@ def test_forward_iteration_call_pattern(fuse):
             assert_close(fcorrs[0, :, :, l * 64:(l + 1) * 64].cpu().numpy(), o.reshape(S, N, 64), 1e-4, f"it {it} level {l}")
 
 
-def test_feature_init_call_pattern():
+@pytest.mark.parametrize("search", ["raster", "grid"])
+def test_feature_init_call_pattern(search):
     """k = 1 kNN of query points against one frame's fused level-0 cloud, then a row gather (mvtracker.py:627-643)."""
+    dropin.settings.search = search
     sc = synth.make_scene(3, 40 * 4, 64 * 4, S=6, C=128, zero_frac=0.1, seed=32, device=DEV)
     xyz, fvec = dropin.init_pointcloud_from_rgbd(sc.fmaps, sc.depths, sc.intrs, sc.extrs, stride=4)
     q, _ = synth.make_tracks(xyz[0], 50, 1)
+    if search == "raster":
+        assert dropin._find_raster(xyz[3][None]) is not None and dropin._find_raster(xyz[3][None].clone()) is None
     for f in range(2):
         dists, idx = dropin.knn(1, xyz[f][None], q[0][None])
         feat = fvec[f][idx[0, :, 0]]

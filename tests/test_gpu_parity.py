@@ -61,7 +61,8 @@ def test_cloud_build_bf16_features():
     for c, r in zip(clouds, ref):
         assert c.fvec.dtype == torch.bfloat16
         assert torch.equal(c.xyz, r.xyz)
-        assert_close(c.fvec.float().cpu().numpy(), r.fvec.cpu().numpy(), 2e-2, f"bf16 fvec l{c.level}")
+        err = (c.fvec.float() - r.fvec).abs().max().item()
+        assert err <= 2e-2 * r.fvec.abs().max().item(), f"bf16 fvec l{c.level}: {err}"
     assert torch.equal(clouds[0].fvec, ref[0].fvec.to(torch.bfloat16))   # level 0 is a pure transpose
 
 
@@ -76,6 +77,17 @@ def check_knn_exact(xyz, q, k, mask=None, spacing=None, cell_scale=0.0, k_hint=N
     assert (idx == oi).all(), f"{(idx != oi).any(-1).sum()} / {idx.shape[0] * idx.shape[1]} queries differ"
     assert (dist == od).all()
     return grid
+
+
+def check_knn_raster(cloud, q, k, skip_invalid=False):
+    """Raster search (no index) against the canonical oracle on the same CUDA-built cloud: bit exact."""
+    dist, idx = ops.knn(ops.Search.from_cloud(cloud, skip_invalid=skip_invalid), q, k, idx_dtype=torch.int32)
+    mask = cloud.valid.cpu().numpy() if skip_invalid else None
+    od, oi = oracle.knn(k, cloud.xyz.cpu().numpy(), q.cpu().numpy(), mask)
+    idx, dist = idx.cpu().numpy(), dist.cpu().numpy()
+    bad = (idx != oi).any(-1)
+    assert not bad.any(), f"{bad.sum()} / {bad.size} queries differ, first at {np.argwhere(bad)[0]}"
+    assert (dist == od).all()
 
 
 @pytest.mark.parametrize("name,g", golden("knn"))
@@ -104,6 +116,8 @@ def test_knn_scene_exact(k, cell_scale):
     coords[:, 6] = cam_centre + 1e-3
     check_knn_exact(c.xyz, coords, k, spacing=c.spacing, cell_scale=cell_scale)
     check_knn_exact(c.xyz, coords, k, spacing=None, cell_scale=cell_scale)      # measure-based cell size
+    if cell_scale == 0.0:
+        check_knn_raster(c, coords, k)
 
 
 def test_knn_mask_and_degenerate_clouds():
@@ -134,9 +148,9 @@ def test_knn_fewer_points_than_k():
 # ---------------------------------------------------------------------------------------------------------------
 # fused kNN + gather + correlation
 # ---------------------------------------------------------------------------------------------------------------
-def check_corr(xyz, fvec, targets, coords, k, G=1, add_offset=True, add_xyz=False, tol=1e-4, spacing=None):
-    grid = ops.build_grids([(xyz, None, spacing)], k_hint=k)[0]
-    out, idx = ops.knn_corr([(grid, xyz, fvec, k)], targets, coords, groups=G, add_offset=add_offset, add_xyz=add_xyz,
+def check_corr(xyz, fvec, targets, coords, k, G=1, add_offset=True, add_xyz=False, tol=1e-4, spacing=None, cloud=None):
+    where = cloud if cloud is not None else ops.build_grids([(xyz, None, spacing)], k_hint=k)[0]
+    out, idx = ops.knn_corr([(where, fvec, k)], targets, coords, groups=G, add_offset=add_offset, add_xyz=add_xyz,
                             return_idx=True)
     D = G + 3 * add_offset + 3 * add_xyz
     out = out.reshape(xyz.shape[0], coords.shape[1], k, D).cpu().numpy()
@@ -165,6 +179,7 @@ def test_corr_scene(C, G, k, add_xyz):
     c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
     coords, targets = synth.make_tracks(c.xyz[0], 257, 3, C=C, valid=c.valid[0])
     check_corr(c.xyz, c.fvec, targets, coords, k, G, True, add_xyz, spacing=c.spacing)
+    check_corr(c.xyz, c.fvec, targets, coords, k, G, True, add_xyz, cloud=c)
 
 
 def test_corr_bf16():
@@ -173,6 +188,7 @@ def test_corr_bf16():
                         want_valid=True)[0]
     coords, targets = synth.make_tracks(c.xyz[0], 200, 2, C=128, valid=c.valid[0], dtype=torch.bfloat16)
     check_corr(c.xyz, c.fvec, targets, coords, 16, tol=2e-2, spacing=c.spacing)
+    check_corr(c.xyz, c.fvec, targets, coords, 16, tol=2e-2, cloud=c)
 
 
 def test_corr_fused_levels_equal_separate_launches():
@@ -180,10 +196,12 @@ def test_corr_fused_levels_equal_separate_launches():
     clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True)
     grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=16)
     coords, targets = synth.make_tracks(clouds[0].xyz[0], 333, 4, valid=clouds[0].valid[0])
-    fused = ops.knn_corr([(g, c.xyz, c.fvec, 16) for g, c in zip(grids, clouds)], targets, coords)
+    fused = ops.knn_corr([(g, c.fvec, 16) for g, c in zip(grids, clouds)], targets, coords)
     assert fused.shape == (4, 333, 4 * 16 * 4)
+    fused_r = ops.knn_corr([(c, c.fvec, 16) for c in clouds], targets, coords)
+    assert torch.equal(fused, fused_r), "raster and grid search must give identical outputs"
     for i, (g, c) in enumerate(zip(grids, clouds)):
-        one = ops.knn_corr([(g, c.xyz, c.fvec, 16)], targets, coords)
+        one = ops.knn_corr([(g, c.fvec, 16)], targets, coords)
         assert torch.equal(one, fused[:, :, i * 64:(i + 1) * 64])
         o_out = oracle.corr_sample(16, c.xyz.cpu().numpy(), c.fvec.cpu().numpy(), targets.cpu().numpy(), coords.cpu().numpy())
         assert_close(one.reshape(4, 333, 16, 4).cpu().numpy(), o_out, 1e-4, f"level {i}")
@@ -194,8 +212,74 @@ def test_knn_gather_feature_init():
     c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
     coords, _ = synth.make_tracks(c.xyz[0], 100, 2, valid=c.valid[0])
     grid = ops.build_grids([(c.xyz, None, c.spacing)], k_hint=1)[0]
-    feat, idx = ops.knn_gather(grid, c.fvec, coords, return_idx=True)
     _, oi = oracle.knn(1, c.xyz.cpu().numpy(), coords.cpu().numpy())
-    assert (idx.cpu().numpy() == oi[..., 0]).all()
-    expect = torch.gather(c.fvec, 1, idx.long()[..., None].expand(-1, -1, 128))
-    assert torch.equal(feat, expect)
+    for where in (grid, c):
+        feat, idx = ops.knn_gather(where, c.fvec, coords, return_idx=True)
+        assert (idx.cpu().numpy() == oi[..., 0]).all()
+        expect = torch.gather(c.fvec, 1, idx.long()[..., None].expand(-1, -1, 128))
+        assert torch.equal(feat, expect)
+    # one frame of the window (what the feature-init loop asks for)
+    feat1 = ops.knn_gather(ops.Search.from_cloud(c, frame=1), c.fvec[1:2], coords[1:2])
+    assert torch.equal(feat1[0], expect[1])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# raster search: geometry edge cases (all must stay bit exact against the brute-force oracle)
+# ---------------------------------------------------------------------------------------------------------------
+def _edge_queries(c, sc, n=160):
+    """Queries on and off the surfaces, outside every frustum, behind cameras, on camera centres and principal planes."""
+    S = c.xyz.shape[0]
+    coords, _ = synth.make_tracks(c.xyz[0], n, S, C=4, valid=c.valid[0], jitter=0.03)
+    g = torch.Generator(device=DEV).manual_seed(5)
+    E = sc.extrs[0, :, 0]                                     # [V,3,4]
+    centres = -(E[:, :, :3].transpose(1, 2) @ E[:, :, 3:]).squeeze(-1)     # camera centres in world coordinates
+    coords[:, 0:8] += 0.5 * torch.randn(S, 8, 3, device=DEV, generator=g)   # floating off the surfaces (big balls)
+    coords[:, 8:12] *= 3.0                                    # far outside the scene
+    coords[:, 12] = centres[0]                                # exactly a camera centre (the depth-0 pile)
+    coords[:, 13] = centres[0] + 0.002
+    coords[:, 14] = centres[-1] * 1.3                         # behind a camera
+    coords[:, 15] = centres[0] + 0.3 * E[0, 0, :3]            # on camera 0's principal plane (z_cam == 0)
+    coords[:, 16] = 0.0                                       # scene centre, inside the ground plane
+    coords[:, 17] = torch.tensor([0.0, 0.0, 50.0], device=DEV)
+    coords[:, 18] = c.xyz[:, 0]                               # exactly a cloud point
+    return coords
+
+
+@pytest.mark.parametrize("V,Hs,Ws,zero", [(3, 45, 80, 0.3), (1, 40, 64, 0.0), (8, 24, 40, 0.05), (2, 17, 23, 0.6)])
+@pytest.mark.parametrize("k", [1, 16])
+def test_raster_knn_edge_cases(V, Hs, Ws, zero, k):
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=2, C=4, zero_frac=zero, seed=40 + V, device=DEV)
+    levels = [l for l in range(4) if (Hs >> l) * (Ws >> l) * V >= 16]
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=levels, want_valid=True)
+    coords = _edge_queries(clouds[0], sc)
+    for c in clouds:
+        check_knn_raster(c, coords, k)
+        check_knn_raster(c, coords, k, skip_invalid=True)     # "intended" filter_invalid: depth <= 0 not searchable
+
+
+def test_raster_knn_skewed_intrinsics_and_moving_cameras():
+    sc = synth.make_scene(3, 40 * 4, 56 * 4, S=3, C=4, zero_frac=0.1, seed=50, device=DEV)
+    g = torch.Generator(device=DEV).manual_seed(51)
+    sc.intrs[..., 0, 1] = 7.5                                                      # skew
+    sc.intrs[..., 0, 0] *= 1.2                                                     # fx != fy
+    sc.extrs[..., 3] += 0.05 * torch.randn(sc.extrs[..., 3].shape, device=DEV, generator=g)   # per-frame cameras
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 2], want_valid=True)
+    coords = _edge_queries(clouds[0], sc)
+    for c in clouds:
+        check_knn_raster(c, coords, 16)
+    # non upper-triangular K: the raster search must notice and fall back to scanning whole rasters (still exact)
+    sc.intrs[..., 1, 0] = 0.5
+    c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[1], want_valid=True)[0]
+    check_knn_raster(c, coords[:, :40].contiguous(), 8)
+
+
+def test_raster_knn_fewer_points_than_k_and_nan_depth():
+    sc = synth.make_scene(2, 8 * 4, 8 * 4, S=1, C=4, zero_frac=0.0, seed=52, device=DEV)
+    dp = sc.depths[0, :, :, 0].clone()
+    dp[0, 0, 2, 3] = float("nan")
+    dp[1, 0, :4] = float("inf")
+    c = ops.cloud_build(sc.fmaps[0], dp, sc.intrs[0], sc.extrs[0], levels=[0, 3], want_valid=True)
+    q = torch.randn(1, 30, 3, device=DEV)
+    check_knn_raster(c[0], q, 16)
+    dist, idx = ops.knn(c[1], q, 8)                # level 3 has 2 points only
+    assert c[1].xyz.shape[1] == 2 and (idx[..., 2:] == -1).all() and (idx[..., :2] >= 0).all()

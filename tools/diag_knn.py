@@ -21,6 +21,24 @@ coords, targets = synth.make_tracks(clouds[0].xyz[0], w["N"], a.S, seed=73, jitt
 L = _lib.lib()
 stats = torch.zeros(16, dtype=torch.int64, device=dev)
 names = ["queries", "ring1", "ring2", "ring3", "fallback", "cand", "ins", "lookups", "small"]
+def run(tag, levels_of):
+    for lvl, c in enumerate(clouds):
+        L.mvt_debug_set_stats(ctypes.c_void_p(stats.data_ptr()))
+        stats.zero_()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.knn_corr([(levels_of(lvl), c.fvec, 16)], targets, coords)
+        e1.record()
+        torch.cuda.synchronize()
+        L.mvt_debug_set_stats(None)
+        st = stats.cpu().tolist()
+        q = max(st[0], 1)
+        print(f"{tag} lvl {lvl} N={c.xyz.shape[1]:7d} | ms={e0.elapsed_time(e1):.3f} pass1={st[1] / q:.3f} pass2={st[2] / q:.3f} "
+              f"pass3={st[3] / q:.3f} pass4+={st[4] / q:.4f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f}")
+
+
+run("raster", lambda l: clouds[l])
 for sc_ in [float(x) for x in a.scales.split(",")]:
     grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=16, cell_scale=sc_)
     for lvl, (g, c) in enumerate(zip(grids, clouds)):
@@ -31,7 +49,7 @@ for sc_ in [float(x) for x in a.scales.split(",")]:
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ops.knn_corr([(g, c.xyz, c.fvec, 16)], targets, coords)
+        ops.knn_corr([(g, c.fvec, 16)], targets, coords)
         e1.record()
         torch.cuda.synchronize()
         L.mvt_debug_set_stats(None)
