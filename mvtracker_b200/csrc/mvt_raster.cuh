@@ -3,12 +3,13 @@
 //
 // Every cloud point lies on the camera ray of its pixel, so a point within distance r of the query q must have its
 // pixel inside the projection of the ball B(q, r) into that view.  One warp per query:
-//   pass 1   scan a 5x5 pixel window around q's projection in every view (lane v owns view v's rectangle; the
-//            rectangles of all views are flattened into one candidate list, 32 candidates per step);
+//   scan     a (2m+1)^2 pixel window around q's projection in every view, m = 2 first (lane v owns view v's
+//            rectangle; the rectangles of all views are flattened into one candidate list, 32 candidates per step);
 //   bound    r = current k-th best distance;  lane v computes the pixel bounding box of B(q, r) in view v
 //            (tangent directions of the ball seen from the camera centre, clipped to z > 0);
-//   pass 2   if some box is not covered yet, scan (box U window) \ window.  The result is then exact.
-// If pass 1 finds fewer than k points the windows grow geometrically (x4) until they cover the rasters.
+//   done     when every view's box lies inside what has been scanned -- the result is then exact;
+//   grow     otherwise m -> 2m+1, windows clipped to the boxes; only the new pixels are scanned.  r shrinks as nearer
+//            points turn up, so the scanned area stays within a small factor of the final ball's projection.
 // Density adapts by construction: pixels are uniformly spaced in the raster wherever the surface is.
 // Points with negative depth are not searchable (they are not on the forward ray); depth == 0 points collapse onto
 // the camera centre and are handled exactly (a ball containing the centre maps to the whole raster).
@@ -99,7 +100,6 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
         return r;
     };
     B = window(m);
-    bool final_pass = false;
     unsigned long long st_cand = 0, st_ins = 0;
     int st_pass = 0;
 
@@ -145,31 +145,13 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
         if (!rect_empty(B)) A = B;
 
         const bool have_k = ti != kNoIdx;
-        if (!have_k) {
-            // fewer than k searchable points so far: grow every window; stop when all rasters are covered
-            bool sat = !mine || (A.x0 == 0 && A.y0 == 0 && A.x1 == W && A.y1 == H);
-            if (__all_sync(FULL, sat)) break;
-            m = (m < (1 << 24)) ? m * 4 + 2 : m;
-            Rect g = window(m);
-            // union with A keeps B a superset of what has been scanned
-            if (!rect_empty(A) && !rect_empty(g)) {
-                g.x0 = min(g.x0, A.x0); g.y0 = min(g.y0, A.y0); g.x1 = max(g.x1, A.x1); g.y1 = max(g.y1, A.y1);
-            } else if (rect_empty(g)) {
-                g = A;
-            }
-            if (m >= (1 << 24) && mine) g = whole;
-            B = g;
-            continue;
-        }
-        if (final_pass) break;
-        // ---- have k candidates: pixel bounding box of the ball B(q, r) in my view ----
-        float r = sqrtf(td);
-        float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
-        Rect R = {0, 0, 0, 0};
-        if (mine) {
-            if (!kok) {
-                R = whole;
-            } else {
+        Rect R = whole;      // pixels of my view that can still hold a neighbour
+        if (have_k) {
+            // pixel bounding box of the ball B(q, r), r = current k-th best distance (an upper bound of the final one)
+            float r = sqrtf(td);
+            float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
+            if (mine && kok) {
+                R = Rect{0, 0, 0, 0};
                 float alo, ahi, blo, bhi;
                 bool vis = tan_range(X, Z, reff, alo, ahi) && tan_range(Y, Z, reff, blo, bhi);
                 if (fmaf(X, X, fmaf(Y, Y, Z * Z)) <= reff * reff) { vis = true; alo = blo = -INFINITY; ahi = bhi = INFINITY; }
@@ -185,16 +167,28 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
                     if (rect_empty(R)) R = Rect{0, 0, 0, 0};
                 }
             }
-        }
-        bool covered = rect_empty(R) || (!rect_empty(A) && R.x0 >= A.x0 && R.y0 >= A.y0 && R.x1 <= A.x1 && R.y1 <= A.y1);
-        if (__all_sync(FULL, covered)) break;
-        if (!rect_empty(R)) {
-            if (!rect_empty(A)) { R.x0 = min(R.x0, A.x0); R.y0 = min(R.y0, A.y0); R.x1 = max(R.x1, A.x1); R.y1 = max(R.y1, A.y1); }
-            B = R;
+            bool covered = !mine || rect_empty(R) ||
+                           (!rect_empty(A) && R.x0 >= A.x0 && R.y0 >= A.y0 && R.x1 <= A.x1 && R.y1 <= A.y1);
+            if (__all_sync(FULL, covered)) break;     // every view's ball projection has been scanned: exact
         } else {
-            B = A;
+            // fewer than k searchable points so far; stop only when all rasters are covered
+            bool sat = !mine || (A.x0 == 0 && A.y0 == 0 && A.x1 == W && A.y1 == H);
+            if (__all_sync(FULL, sat)) break;
         }
-        final_pass = true;
+        // grow the windows geometrically, but never beyond what the current ball can reach; the bound tightens as
+        // nearer points are found, so the scanned area stays within a small factor of the final ball's projection
+        m = (m < (1 << 24)) ? 2 * m + 1 : m;
+        Rect g = (m >= (1 << 24) && mine) ? whole : window(m);
+        if (!rect_empty(g)) {
+            g.x0 = max(g.x0, R.x0); g.y0 = max(g.y0, R.y0); g.x1 = min(g.x1, R.x1); g.y1 = min(g.y1, R.y1);
+        }
+        if (rect_empty(g)) {
+            B = A;
+        } else if (rect_empty(A)) {
+            B = g;
+        } else {
+            B.x0 = min(g.x0, A.x0); B.y0 = min(g.y0, A.y0); B.x1 = max(g.x1, A.x1); B.y1 = max(g.y1, A.y1);
+        }
     }
     if (stats && lane == 0) {
         atomicAdd(stats + 0, 1ull);
