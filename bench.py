@@ -205,7 +205,9 @@ def run_ours(args):
                           device=dev, dtype=fdtype)
     fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
     win = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale, search=args.search)
-    base_coords, base_targets = synth.make_tracks(win.clouds[0].xyz[0], N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype)
+    # tracks follow the surface at their pixel (+ N(0, 2 cm)), i.e. near the cloud in every frame like converged tracks
+    base_coords, base_targets = synth.make_tracks(win.clouds[0].xyz, N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype,
+                                                  valid=win.clouds[0].xyz4[..., 3] > 0)
     g = torch.Generator(device=dev).manual_seed(74)
     coords_it = [(base_coords + 0.01 * torch.randn(base_coords.shape, device=dev, generator=g)).contiguous() for _ in range(iters)]
     targets_it = [(base_targets * (1.0 - 0.1 * i)).contiguous() for i in range(iters)]

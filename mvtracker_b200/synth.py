@@ -107,16 +107,21 @@ def make_scene(V, H, W, S=12, C=128, stride=4, zero_frac=0.05, seed=72, device="
 
 
 def make_tracks(xyz0, N, S, C=128, jitter=0.02, seed=73, valid=None, dtype=torch.float32):
-    """Tracks as in demo.py:781-806: sample N points of frame 0's fused cloud; per-frame coords = point + N(0, jitter).
-    xyz0 [P,3] (frame 0, level 0), valid [P] optional.  -> coords [S,N,3] fp32, targets [S,N,C]."""
+    """Tracks as in demo.py:781-806: N points of the fused level-0 cloud, per-frame coords = point + N(0, jitter).
+    xyz0 [P,3]: frame 0's cloud, the same point in every frame (static tracks);
+    xyz0 [S,P,3]: the track follows the surface seen at its pixel in every frame (stays near the cloud even when the
+    scene moves, as converged tracks do).  valid [P] / [S,P] optional.  -> coords [S,N,3] fp32, targets [S,N,C]."""
     device = xyz0.device
     g = torch.Generator(device=device)
     g.manual_seed(seed)
-    pool = torch.arange(xyz0.shape[0], device=device)
+    per_frame = xyz0.dim() == 3
+    P = xyz0.shape[-2]
+    pool = torch.arange(P, device=device)
     if valid is not None:
-        pool = pool[valid.bool()]
+        v = valid.bool()
+        pool = pool[v.all(0) if v.dim() == 2 else v]
     sel = pool[torch.randint(0, pool.numel(), (N,), generator=g, device=device)]
-    base = xyz0[sel].float()
-    coords = base[None] + jitter * torch.randn(S, N, 3, generator=g, device=device)
+    base = xyz0[:, sel].float() if per_frame else xyz0[sel].float()[None]
+    coords = base + jitter * torch.randn(S, N, 3, generator=g, device=device)
     targets = torch.randn(S, N, C, generator=g, device=device, dtype=torch.float32).to(dtype)
     return coords.contiguous(), targets.contiguous()

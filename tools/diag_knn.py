@@ -12,12 +12,14 @@ ap.add_argument("--scales", default="1")
 ap.add_argument("--S", type=int, default=12)
 ap.add_argument("--zero-frac", type=float, default=0.05)
 ap.add_argument("--jitter", type=float, default=0.02)
+ap.add_argument("--static", action="store_true", help="tracks fixed at their frame-0 position (drift off moving surfaces)")
 a = ap.parse_args()
 w = synth.WORKLOADS[a.workload]
 dev = "cuda"
 sc = synth.make_scene(w["V"], w["H"], w["W"], S=a.S, C=128, zero_frac=a.zero_frac, seed=72, device=dev)
 clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
-coords, targets = synth.make_tracks(clouds[0].xyz[0], w["N"], a.S, seed=73, jitter=a.jitter)
+coords, targets = synth.make_tracks(clouds[0].xyz if not a.static else clouds[0].xyz[0], w["N"], a.S, seed=73, jitter=a.jitter,
+                                    valid=clouds[0].valid if not a.static else clouds[0].valid[0])
 L = _lib.lib()
 stats = torch.zeros(16, dtype=torch.int64, device=dev)
 names = ["queries", "ring1", "ring2", "ring3", "fallback", "cand", "ins", "lookups", "small"]
