@@ -21,8 +21,8 @@ struct SearchDev {
 };
 
 __device__ __forceinline__ void search(const SearchDev &sd, int b, float qx, float qy, float qz, int k, int lane, float &bd,
-                                       int &bi) {
-    if (sd.raster) raster_search(sd.rv, b, qx, qy, qz, k, lane, bd, bi, sd.g.stats);
+                                       int &bi, int qtag = 0) {
+    if (sd.raster) raster_search(sd.rv, b, qx, qy, qz, k, lane, bd, bi, sd.g.stats, qtag);
     else knn_search(sd.g, b, qx, qy, qz, k, lane, bd, bi);
 }
 
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
     if (MODE == 2) tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
 
     float bd; int bi;
-    search(L.sd, b, qx, qy, qz, k, lane, bd, bi);
+    search(L.sd, b, qx, qy, qz, k, lane, bd, bi, (int)q);
 
     if (p.idx_out && lane < k) p.idx_out[(w * k) + lane] = (bi != kNoIdx) ? bi : -1;
 

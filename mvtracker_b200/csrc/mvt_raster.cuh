@@ -56,7 +56,7 @@ __device__ __forceinline__ void pix_range(float ulo, float uhi, float st, int n,
 }
 
 __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float qx, float qy, float qz, int k, int lane,
-                                              float &bd, int &bi, unsigned long long *stats) {
+                                              float &bd, int &bi, unsigned long long *stats, int qtag = 0) {
     bd = INFINITY;
     bi = kNoIdx;
     float td = INFINITY;
@@ -93,7 +93,7 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
     auto window = [&](int mm) {
         Rect r = {0, 0, 0, 0};
         if (!mine) return r;
-        if (!front) return (mm > 2) ? whole : r;       // behind the camera / odd intrinsics: nothing in pass 1, everything when growing
+        if (!front) return r;       // behind the camera / odd intrinsics: no window centre (handled in the growth step)
         r.x0 = max(ci - mm, 0); r.x1 = min(ci + mm + 1, W);
         r.y0 = max(cj - mm, 0); r.y1 = min(cj + mm + 1, H);
         if (rect_empty(r)) r = Rect{0, 0, 0, 0};
@@ -146,6 +146,7 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
 
         const bool have_k = ti != kNoIdx;
         Rect R = whole;      // pixels of my view that can still hold a neighbour
+        bool covered;
         if (have_k) {
             // pixel bounding box of the ball B(q, r), r = current k-th best distance (an upper bound of the final one)
             float r = sqrtf(td);
@@ -167,18 +168,22 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
                     if (rect_empty(R)) R = Rect{0, 0, 0, 0};
                 }
             }
-            bool covered = !mine || rect_empty(R) ||
-                           (!rect_empty(A) && R.x0 >= A.x0 && R.y0 >= A.y0 && R.x1 <= A.x1 && R.y1 <= A.y1);
-            if (__all_sync(FULL, covered)) break;     // every view's ball projection has been scanned: exact
+            covered = !mine || rect_empty(R) ||
+                      (!rect_empty(A) && R.x0 >= A.x0 && R.y0 >= A.y0 && R.x1 <= A.x1 && R.y1 <= A.y1);
         } else {
             // fewer than k searchable points so far; stop only when all rasters are covered
-            bool sat = !mine || (A.x0 == 0 && A.y0 == 0 && A.x1 == W && A.y1 == H);
-            if (__all_sync(FULL, sat)) break;
+            covered = !mine || (A.x0 == 0 && A.y0 == 0 && A.x1 == W && A.y1 == H);
         }
+        if (__all_sync(FULL, covered)) break;     // every view's ball projection has been scanned: exact
+        // views without a window centre (q behind the camera, odd intrinsics) wait until the views that have one are
+        // done, so that they are scanned once, with the final (tight) radius
+        const bool front_pending = __any_sync(FULL, front && !covered);
         // grow the windows geometrically, but never beyond what the current ball can reach; the bound tightens as
         // nearer points are found, so the scanned area stays within a small factor of the final ball's projection
         m = (m < (1 << 24)) ? 2 * m + 1 : m;
-        Rect g = (m >= (1 << 24) && mine) ? whole : window(m);
+        Rect g = {0, 0, 0, 0};
+        if (front) g = (m >= (1 << 24)) ? whole : window(m);
+        else if (mine && !front_pending) g = whole;
         if (!rect_empty(g)) {
             g.x0 = max(g.x0, R.x0); g.y0 = max(g.y0, R.y0); g.x1 = min(g.x1, R.x1); g.y1 = min(g.y1, R.y1);
         }
@@ -195,6 +200,12 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
         atomicAdd(stats + min(st_pass, 4), 1ull);     // [1] one pass, [2] two passes, [3] three, [4] four or more
         atomicAdd(stats + 5, st_cand);
         atomicAdd(stats + 6, st_ins);
+        // [9] worst query: candidates << 32 | (frame << 24 ^ low bits of qx as a tag is not needed: host recomputes)
+        atomicMax(stats + 9, (st_cand << 24) | (unsigned long long)(qtag & 0xFFFFFF));
+        int bin = 0;
+        unsigned long long c = st_cand;
+        while (c > 1 && bin < 5) { c >>= 3; ++bin; }       // bins: <2, <16, <128, <1024, <8192, >=8192 candidates
+        atomicAdd(stats + 10 + bin, 1ull);
     }
 }
 

@@ -37,7 +37,17 @@ def run(tag, levels_of):
         st = stats.cpu().tolist()
         q = max(st[0], 1)
         print(f"{tag} lvl {lvl} N={c.xyz.shape[1]:7d} | ms={e0.elapsed_time(e1):.3f} pass1={st[1] / q:.3f} pass2={st[2] / q:.3f} "
-              f"pass3={st[3] / q:.3f} pass4+={st[4] / q:.4f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f}")
+              f"pass3={st[3] / q:.3f} pass4+={st[4] / q:.4f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f} "
+              f"hist(<2,<16,<128,<1k,<8k,>=8k)={st[10:16]}")
+        worst_c, worst_q = st[9] >> 24, st[9] & 0xFFFFFF
+        b, m_ = divmod(worst_q, coords.shape[1])
+        qq = coords[b, m_]
+        cam = c.cam.view(c.V, -1, 48)[:, b]
+        R, t = cam[:, 24:33].view(-1, 3, 3), cam[:, 33:36]
+        qc = (R @ qq) + t
+        d, i = ops.knn(ops.Search.from_cloud(c, frame=b), qq[None, None], 16)
+        print(f"    worst query: {worst_c} candidates, frame {b} track {m_} q={[round(x, 3) for x in qq.tolist()]} "
+              f"q_cam per view={[[round(x, 2) for x in r] for r in qc.tolist()]} d16={d[0, 0, -1].item():.4f} d1={d[0, 0, 0].item():.4f}")
 
 
 run("raster", lambda l: clouds[l])
@@ -61,3 +71,18 @@ for sc_ in [float(x) for x in a.scales.split(",")]:
               f"pts/cell={i0[7] / max(i0[8], 1):.1f} | ms={e0.elapsed_time(e1):.3f} ring1={st[1] / q:.3f} ring2={st[2] / q:.3f} "
               f"ring3={st[3] / q:.3f} fallback={st[4] / q:.4f} small={st[8] / q:.3f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f} "
               f"lookups/q={st[7] / q:.0f}")
+
+# fused launch, stats off, back-to-back (true kernel time) and host cost of one call
+import time
+for tag, lv in (("raster fused x4", [(c, c.fvec, 16) for c in clouds]), ("raster lvl0 only", [(clouds[0], clouds[0].fvec, 16)])):
+    out = ops.knn_corr(lv, targets, coords)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(20):
+        ops.knn_corr(lv, targets, coords, out=out)
+    e1.record()
+    t_host = (time.perf_counter() - t0) / 20
+    torch.cuda.synchronize()
+    print(f"{tag}: {e0.elapsed_time(e1) / 20:.3f} ms per launch (host {t_host * 1e3:.3f} ms per call)")
