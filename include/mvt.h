@@ -145,6 +145,10 @@ int mvt_grid_info(const void *grid, int B, int N, float *info, void *stream);
  * raster mode: [0] queries [1..4] finished after 1, 2, 3, >=4 passes [5] candidates scanned [6] insertions. */
 int mvt_debug_set_stats(void *dev_counters);
 
+/* Debug / experiments: lanes that own one query in mvt_knn_corr's raster kernels, 32 (default) or 16 (two queries per
+ * warp in lock step; needs k <= 16, V <= 16, C == 128, groups == 1, else 32 is used).  Results are identical. */
+int mvt_debug_set_group_width(int lanes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,14 +5,15 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libmvt.so")
+SO_PATH = os.environ.get("MVT_LIB") or os.path.join(_HERE, "libmvt.so")   # MVT_LIB: A/B builds in experiments
 
 MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
 CAM_STRIDE, MAX_VIEWS = 48, 32
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats")
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
+           "mvt_debug_set_group_width")
 
 
 class LevelOut(C.Structure):
@@ -71,6 +72,7 @@ def lib():
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
+    L.mvt_debug_set_group_width.argtypes = [ci]
     for name in SYMBOLS:
         f = getattr(L, name)
         if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count"):

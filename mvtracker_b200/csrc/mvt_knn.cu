@@ -12,6 +12,10 @@
 
 namespace mvt {
 
+// Lanes per query of the fused raster kernel: 32 (default) or 16 (two queries per warp in lock step; measured slightly
+// slower on B200 so far -- kept selectable through mvt_debug_set_group_width for experiments and tests).
+static int g_group_width = 32;
+
 struct SearchDev {
     int raster;          // 1: rv is valid, 0: g is valid
     GridView g;
@@ -20,15 +24,22 @@ struct SearchDev {
     int N;
 };
 
-__device__ __forceinline__ void search(const SearchDev &sd, int b, float qx, float qy, float qz, int k, int lane, float &bd,
-                                       int &bi, int qtag = 0) {
-    if (sd.raster) raster_search(sd.rv, b, qx, qy, qz, k, lane, bd, bi, sd.g.stats, qtag);
-    else knn_search(sd.g, b, qx, qy, qz, k, lane, bd, bi);
+// RASTER_ONLY: the caller guarantees sd.raster (the grid code is then not even compiled into the kernel).
+template <bool RASTER_ONLY = false>
+__device__ __forceinline__ void search(const SearchDev &sd, const unsigned char *win_tab, int b, float qx, float qy, float qz,
+                                       int k, int lane, float &bd, int &bi, int qtag = 0) {
+    TopK tk;
+    const Group<32> g(lane);
+    if (RASTER_ONLY || sd.raster) raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, qtag);
+    else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
+    bd = key_d2(tk.t);
+    bi = key_idx(tk.t);
 }
 
 // coordinates of neighbour `i` of batch element b
+template <bool RASTER_ONLY = false>
 __device__ __forceinline__ float3 nbr_xyz(const SearchDev &sd, int b, int i) {
-    if (sd.raster) {
+    if (RASTER_ONLY || sd.raster) {
         float4 p = __ldg(sd.rv.xyz4 + (size_t)b * sd.N + i);
         return make_float3(p.x, p.y, p.z);
     }
@@ -42,13 +53,15 @@ __device__ __forceinline__ float3 nbr_xyz(const SearchDev &sd, int b, int i) {
 __global__ void __launch_bounds__(256) knn_kernel(const SearchDev sd, int B, int M, const float *__restrict__ query, int k,
                                                   int *__restrict__ idx32, long long *__restrict__ idx64,
                                                   float *__restrict__ dist) {
+    __shared__ unsigned char win_tab[32];
+    init_window_table(win_tab);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;
     const int b = (int)(w / M);
     const float qx = __ldg(query + w * 3), qy = __ldg(query + w * 3 + 1), qz = __ldg(query + w * 3 + 2);
     float bd; int bi;
-    search(sd, b, qx, qy, qz, k, lane, bd, bi);
+    search(sd, win_tab, b, qx, qy, qz, k, lane, bd, bi);
     if (lane < k) {
         bool ok = bi != kNoIdx;
         if (idx32) idx32[w * k + lane] = ok ? bi : -1;
@@ -130,81 +143,151 @@ __device__ __forceinline__ float transpose_reduce8_half(float (&pr)[8], int lane
     return pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
 }
 
-// MODE 0: generic fp32 (any C, G).   MODE 1: fp32, C == 128, G == 1, k <= 16 (one float4 of the row per lane).
-// MODE 2: bf16, C == 128, G == 1, k <= 16 (16 lanes x 16 B per row, two rows per warp load).
-template <int MODE>
-__global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
+// 16 partial sums per lane, reduced over the 16 lanes of a half-warp group -> group lane l holds the total of partial l.
+template <int GW>
+__device__ __forceinline__ float transpose_reduce16_half(const Group<GW> &g, float (&pr)[16]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        bool hi = g.gl & 8;
+        float send = hi ? pr[i] : pr[i + 8], keep = hi ? pr[i + 8] : pr[i];
+        pr[i] = keep + g.shfl_xor(send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        bool hi = g.gl & 4;
+        float send = hi ? pr[i] : pr[i + 4], keep = hi ? pr[i + 4] : pr[i];
+        pr[i] = keep + g.shfl_xor(send, 4);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        bool hi = g.gl & 2;
+        float send = hi ? pr[i] : pr[i + 2], keep = hi ? pr[i + 2] : pr[i];
+        pr[i] = keep + g.shfl_xor(send, 2);
+    }
+    {
+        bool hi = g.gl & 1;
+        float send = hi ? pr[0] : pr[1], keep = hi ? pr[1] : pr[0];
+        pr[0] = keep + g.shfl_xor(send, 1);
+    }
+    return pr[0];
+}
+
+__device__ __forceinline__ float dot4(const float4 &a, const float4 &b) {
+    return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)));
+}
+__device__ __forceinline__ float dot8_bf16(const uint4 &a, const uint4 &b) {
+    const __nv_bfloat162 *x = reinterpret_cast<const __nv_bfloat162 *>(&a);
+    const __nv_bfloat162 *y = reinterpret_cast<const __nv_bfloat162 *>(&b);
+    float acc = 0.f;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        float2 u = __bfloat1622float2(x[e]), v = __bfloat1622float2(y[e]);
+        acc = fmaf(u.x, v.x, acc);
+        acc = fmaf(u.y, v.y, acc);
+    }
+    return acc;
+}
+
+// MODE 0: generic fp32 (any C, G).   MODE 1: fp32, C == 128, G == 1, k <= 16.   MODE 2: bf16, C == 128, G == 1, k <= 16.
+// GW = 32: one warp per query.   GW = 16 (raster search, MODE 1/2, V <= 16): one half warp per query.
+// Grid: x = query blocks of one frame, y = frame b, z = pyramid level.
+#ifndef MVT_CORR_MINB
+#define MVT_CORR_MINB 1
+#endif
+template <int MODE, bool RASTER_ONLY, int GW>
+__global__ void __launch_bounds__(256, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
+    __shared__ unsigned char win_tab[32];
+    init_window_table(win_tab);
     const int lane = threadIdx.x & 31;
-    const long long per_level = (long long)p.B * p.M;
-    const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (w >= per_level * p.n_levels) return;
-    const int lvl = (int)(w / per_level);
-    const long long q = w - (long long)lvl * per_level;   // b * M + m
-    const int b = (int)(q / p.M);
+    const Group<GW> g(lane);
+    const int gl = g.gl;
+    const int m_raw = (int)((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 / GW)) + (GW == 32 ? 0 : (lane >> 4));
+    const bool live = m_raw < p.M;       // half-warp groups: the last group of a frame may be padding
+    if (GW == 32 && !live) return;
+    const int m = live ? m_raw : p.M - 1;
+    const int b = blockIdx.y, lvl = blockIdx.z;
+    const long long q = (long long)b * p.M + m;
     const CorrLevelDev &L = p.lv[lvl];
     const int k = L.k, C = p.C;
     const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
 
-    // the target row is fetched before the search so its latency hides behind it
-    float4 tg = make_float4(0.f, 0.f, 0.f, 0.f);
-    uint4 tgh = make_uint4(0u, 0u, 0u, 0u);
-    if (MODE == 1) tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + lane);
-    if (MODE == 2) tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
+    TopK tk;
+    if (RASTER_ONLY || L.sd.raster) raster_search<GW>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q);
+    else if (GW == 32) knn_search(L.sd.g, b, qx, qy, qz, k, lane, tk);
+    const int bi = key_idx(tk.t);       // group lane j < k: the j-th neighbour
 
-    float bd; int bi;
-    search(L.sd, b, qx, qy, qz, k, lane, bd, bi, (int)q);
-
-    if (p.idx_out && lane < k) p.idx_out[(w * k) + lane] = (bi != kNoIdx) ? bi : -1;
+    if (p.idx_out && live && gl < k) p.idx_out[(((long long)lvl * p.B + b) * p.M + m) * k + gl] = (bi != kNoIdx) ? bi : -1;
 
     const int D = p.G + 3 * p.add_offset + 3 * p.add_xyz;
     float *orow = p.out + q * p.row_stride + L.out_off;
     const size_t seg = (size_t)b * L.sd.N;
-    float corr_mine = 0.f;   // MODE 1/2: correlation of neighbour `lane`
+    float corr_mine = 0.f;   // MODE 1/2: correlation of neighbour `gl` (GW == 16) / `lane` (GW == 32)
 
-    if (MODE == 1) {
-        const float4 *fv = reinterpret_cast<const float4 *>(L.fvec);
+    if (MODE == 1 && GW == 32) {
+        const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + lane);
+        const float4 *fv = reinterpret_cast<const float4 *>(L.fvec) + seg * 32 + lane;
         float pr[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             int ij = __shfl_sync(FULL, bi, j);
             float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (j < k && ij != kNoIdx) f = __ldg(fv + (seg + (size_t)ij) * 32 + lane);
-            pr[j] = fmaf(tg.w, f.w, fmaf(tg.z, f.z, fmaf(tg.y, f.y, tg.x * f.x)));
+            if (j < k && ij != kNoIdx) f = __ldg(fv + (size_t)ij * 32);
+            pr[j] = dot4(tg, f);
         }
         float tot = transpose_reduce16(pr, lane);
         corr_mine = __shfl_sync(FULL, tot, (2 * lane) & 31);
-    } else if (MODE == 2) {
-        const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec);
-        const int half = lane >> 4, l16 = lane & 15;
+    } else if (MODE == 1) {
+        const float4 tg0 = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + gl);
+        const float4 tg1 = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + 16 + gl);
+        const float4 *fv = reinterpret_cast<const float4 *>(L.fvec) + seg * 32 + gl;
+        float pr[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            int ij = g.shfl(bi, j);
+            float4 f0 = make_float4(0.f, 0.f, 0.f, 0.f), f1 = f0;
+            if (j < k && ij != kNoIdx) {
+                f0 = __ldg(fv + (size_t)ij * 32);
+                f1 = __ldg(fv + (size_t)ij * 32 + 16);
+            }
+            pr[j] = dot4(tg0, f0) + dot4(tg1, f1);
+        }
+        corr_mine = transpose_reduce16_half(g, pr);
+    } else if (MODE == 2 && GW == 32) {
+        const uint4 tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
+        const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec) + seg * 16 + (lane & 15);
+        const int half = lane >> 4;
         float pr[8];   // pr[i]: partial of neighbour 2i + half
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             int j = 2 * i + half;
             int ij = __shfl_sync(FULL, bi, j);
             uint4 f = make_uint4(0u, 0u, 0u, 0u);
-            if (j < k && ij != kNoIdx) f = __ldg(fv + (seg + (size_t)ij) * 16 + l16);
-            const __nv_bfloat162 *a = reinterpret_cast<const __nv_bfloat162 *>(&tgh);
-            const __nv_bfloat162 *c = reinterpret_cast<const __nv_bfloat162 *>(&f);
-            float acc = 0.f;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                float2 x = __bfloat1622float2(a[e]), y = __bfloat1622float2(c[e]);
-                acc = fmaf(x.x, y.x, acc);
-                acc = fmaf(x.y, y.y, acc);
-            }
-            pr[i] = acc;
+            if (j < k && ij != kNoIdx) f = __ldg(fv + (size_t)ij * 16);
+            pr[i] = dot8_bf16(tgh, f);
         }
         float tot = transpose_reduce8_half(pr, lane);
         // neighbour j lives in half (j & 1), lanes 2*(j>>1), 2*(j>>1)+1 of that half
         corr_mine = __shfl_sync(FULL, tot, ((lane & 1) << 4) | ((lane >> 1) << 1));
+    } else if (MODE == 2) {
+        const uint4 tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + gl);
+        const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec) + seg * 16 + gl;
+        float pr[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            int ij = g.shfl(bi, j);
+            uint4 f = make_uint4(0u, 0u, 0u, 0u);
+            if (j < k && ij != kNoIdx) f = __ldg(fv + (size_t)ij * 16);
+            pr[j] = dot8_bf16(tgh, f);
+        }
+        corr_mine = transpose_reduce16_half(g, pr);
     }
 
     if (MODE != 0) {
-        if (lane < k) {
+        if (live && gl < k) {
             bool ok = bi != kNoIdx;
-            float3 n = ok ? nbr_xyz(L.sd, b, bi) : make_float3(0.f, 0.f, 0.f);
+            float3 n = ok ? nbr_xyz<RASTER_ONLY>(L.sd, b, bi) : make_float3(0.f, 0.f, 0.f);
             float cv = ok ? __fdiv_rn(corr_mine, p.scale) : 0.f;
-            float *o = orow + (size_t)lane * D;
+            float *o = orow + (size_t)gl * D;
             if (p.vec_out) {
                 *reinterpret_cast<float4 *>(o) = ok ? make_float4(cv, n.x - qx, n.y - qy, n.z - qz) : make_float4(0.f, 0.f, 0.f, 0.f);
             } else {
@@ -217,7 +300,7 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
         return;
     }
 
-    // ---- MODE 0: generic path, one neighbour and one group at a time ----
+    // ---- MODE 0: generic path (GW == 32), one neighbour and one group at a time ----
     const float *tgt = reinterpret_cast<const float *>(p.targets) + q * C;
     const float *fvf = reinterpret_cast<const float *>(L.fvec);
     const int Cg = C / p.G;
@@ -235,7 +318,7 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
             if (lane == 0) o[gi] = ok ? __fdiv_rn(acc, p.scale) : 0.f;
         }
         if (p.add_offset || p.add_xyz) {
-            float3 n = ok ? nbr_xyz(L.sd, b, ij) : make_float3(0.f, 0.f, 0.f);
+            float3 n = ok ? nbr_xyz<RASTER_ONLY>(L.sd, b, ij) : make_float3(0.f, 0.f, 0.f);
             if (lane < 3) {
                 float pv = lane == 0 ? n.x : (lane == 1 ? n.y : n.z);
                 float qv = lane == 0 ? qx : (lane == 1 ? qy : qz);
@@ -253,13 +336,15 @@ __global__ void __launch_bounds__(256) knn_corr_kernel(const CorrParams p) {
 __global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, const void *__restrict__ fvec, int elem_bytes,
                                                          int B, int M, int C, const float *__restrict__ query,
                                                          void *__restrict__ feat_out, int *__restrict__ idx_out) {
+    __shared__ unsigned char win_tab[32];
+    init_window_table(win_tab);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;
     const int b = (int)(w / M);
     const float qx = __ldg(query + w * 3), qy = __ldg(query + w * 3 + 1), qz = __ldg(query + w * 3 + 2);
     float bd; int bi;
-    search(sd, b, qx, qy, qz, 1, lane, bd, bi);
+    search(sd, win_tab, b, qx, qy, qz, 1, lane, bd, bi);
     int i0 = __shfl_sync(FULL, bi, 0);
     if (idx_out && lane == 0) idx_out[w] = (i0 != kNoIdx) ? i0 : -1;
     const size_t row_bytes = (size_t)C * elem_bytes;
@@ -351,6 +436,7 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     bool fast = (C == 128 && G == 1);
     bool vec = (D == 4) && (((uintptr_t)out & 15) == 0) && (out_row_stride % 4 == 0);
     bool aligned = (((uintptr_t)targets & 15) == 0);
+    bool all_raster = true;
     for (int l = 0; l < n_levels; ++l) {
         const mvt_corr_level &u = levels[l];
         MVT_CHECK_ARG(u.fvec, "mvt_knn_corr: level %d has a null fvec", l);
@@ -361,6 +447,7 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
         int rc = make_search(&u.search, B, p.add_offset || p.add_xyz, p.lv[l].sd, "mvt_knn_corr");
         if (rc) return rc;
         p.lv[l].fvec = u.fvec; p.lv[l].k = u.k; p.lv[l].out_off = u.out_offset;
+        all_raster = all_raster && p.lv[l].sd.raster;
         fast = fast && u.k <= 16;
         vec = vec && (u.out_offset % 4 == 0);
         aligned = aligned && (((uintptr_t)u.fvec & 15) == 0);
@@ -368,13 +455,31 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
     p.vec_out = vec ? 1 : 0;
     MVT_CHECK_ARG(feat_dtype == MVT_F32 || (fast && aligned), "mvt_knn_corr: bf16 features need C=128, groups=1, k<=16, 16-byte aligned rows");
-    long long warps = (long long)B * M * n_levels;
-    MVT_CHECK_ARG(warps / 8 < 0x7fffffffLL, "mvt_knn_corr: too many queries");
+    MVT_CHECK_ARG(B <= 65535, "mvt_knn_corr: B=%d too large", B);
     cudaStream_t st = (cudaStream_t)stream;
-    if (feat_dtype == MVT_BF16) knn_corr_kernel<2><<<warp_blocks(warps), 256, 0, st>>>(p);
-    else if (fast && aligned) knn_corr_kernel<1><<<warp_blocks(warps), 256, 0, st>>>(p);
-    else knn_corr_kernel<0><<<warp_blocks(warps), 256, 0, st>>>(p);
+    bool half = all_raster && fast && aligned;      // half-warp groups: k <= 16 (part of `fast`) and V <= 16
+    for (int l = 0; l < n_levels; ++l) half = half && levels[l].search.V <= 16;
+    if (mvt::g_group_width != 16) half = false;
+    const int qpb = half ? 16 : 8;                  // queries per 256-thread block
+    const dim3 grid((unsigned)((M + qpb - 1) / qpb), (unsigned)B, (unsigned)n_levels);
+    if (feat_dtype == MVT_BF16) {
+        if (half) knn_corr_kernel<2, true, 16><<<grid, 256, 0, st>>>(p);
+        else if (all_raster) knn_corr_kernel<2, true, 32><<<grid, 256, 0, st>>>(p);
+        else knn_corr_kernel<2, false, 32><<<grid, 256, 0, st>>>(p);
+    } else if (fast && aligned) {
+        if (half) knn_corr_kernel<1, true, 16><<<grid, 256, 0, st>>>(p);
+        else if (all_raster) knn_corr_kernel<1, true, 32><<<grid, 256, 0, st>>>(p);
+        else knn_corr_kernel<1, false, 32><<<grid, 256, 0, st>>>(p);
+    } else {
+        knn_corr_kernel<0, false, 32><<<grid, 256, 0, st>>>(p);
+    }
     MVT_CHECK_LAUNCH("knn_corr");
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_debug_set_group_width(int lanes) {
+    MVT_CHECK_ARG(lanes == 16 || lanes == 32, "mvt_debug_set_group_width: 16 or 32 (got %d)", lanes);
+    mvt::g_group_width = lanes;
     return MVT_OK;
 }
 

@@ -1,5 +1,6 @@
-// Warp-per-query exact kNN over the hashed grid (device side).  One warp owns one query; lane i holds the i-th best
-// (d2, index) pair of a sorted top-32 list in registers; candidates are offered 32 at a time and inserted with warp
+// Exact kNN, device side: the register top-k list shared by both searches, and the warp-per-query search over the
+// hashed grid.  A group of lanes (a warp, or a half warp in the raster search) owns one query; group lane i holds the
+// i-th best (d2, index) pair of a sorted list in registers; candidates are offered one per lane and merged with
 // shuffles.  Candidate order never matters: the list is ordered by the total order (d2, index).
 //
 // Canonical arithmetic (bit-exact contract with oracle/mvt_oracle.c):
@@ -15,44 +16,98 @@ constexpr float kMarginCells = 2e-3f;    // slack on the ring bound: covers fp32
 constexpr unsigned kBruteN = 512;        // segments this small are scanned exhaustively
 constexpr int kNoIdx = 0x7fffffff;
 
-__device__ __forceinline__ bool better(float d, int i, float bd, int bi) { return d < bd || (d == bd && i < bi); }
-
 __device__ __forceinline__ float dist2(float px, float py, float pz, float qx, float qy, float qz) {
     float dx = __fsub_rn(px, qx), dy = __fsub_rn(py, qy), dz = __fsub_rn(pz, qz);
     return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 }
 
-// Insert (cd, ci) -- known to every lane and strictly better than the current k-th -- into the sorted list.
-__device__ __forceinline__ void topk_insert(float &bd, int &bi, float cd, int ci, int lane) {
-    bool displaced = better(cd, ci, bd, bi);
-    float ud = __shfl_up_sync(FULL, bd, 1);
-    int ui = __shfl_up_sync(FULL, bi, 1);
-    unsigned dm = __ballot_sync(FULL, displaced);
-    if (displaced) {
-        bool first = (lane == 0) || !((dm >> (lane - 1)) & 1u);
-        bd = first ? cd : ud;
-        bi = first ? ci : ui;
-    }
-}
+// A (d2, index) pair as one 64-bit key: d2 >= 0 (or NaN), so its bit pattern orders like the float and one unsigned
+// compare is the total order (d2, index).  NaN distances (0x7fc00000 or above) order after every real entry and
+// after the empty key, i.e. they are never inserted -- the same as `d < bd || (d == bd && i < bi)` in the oracle.
+typedef unsigned long long u64;
+constexpr u64 kEmptyKey64 = 0x7f8000007fffffffull;   // (+inf, kNoIdx)
+__device__ __forceinline__ u64 pack_key(float d2, int idx) { return ((u64)__float_as_uint(d2) << 32) | (u64)(unsigned)idx; }
+__device__ __forceinline__ float key_d2(u64 key) { return __uint_as_float((unsigned)(key >> 32)); }
+__device__ __forceinline__ int key_idx(u64 key) { return (int)(unsigned)(key & 0xffffffffull); }
 
-// Offer one candidate per lane.  (td, ti) = current k-th best, uniform across the warp.
-__device__ __forceinline__ int topk_offer(float &bd, int &bi, float &td, int &ti, float d2, int idx, bool valid, int k,
-                                          int lane) {
-    unsigned m = __ballot_sync(FULL, valid && better(d2, idx, td, ti));
-    int ins = 0;
-    while (m) {
-        int src = __ffs(m) - 1;
-        m &= m - 1;
-        float cd = __shfl_sync(FULL, d2, src);
-        int ci = __shfl_sync(FULL, idx, src);
-        if (better(cd, ci, td, ti)) {
-            topk_insert(bd, bi, cd, ci, lane);
-            td = __shfl_sync(FULL, bd, k - 1);
-            ti = __shfl_sync(FULL, bi, k - 1);
-            ++ins;
+// A query is owned by a GROUP of GW lanes: a whole warp (GW = 32: any k <= 32, up to 32 views) or a half warp
+// (GW = 16: k <= 16, up to 16 views).  With half-warp groups the two queries of a warp run in lock step: every
+// collective is executed by all 32 lanes (full mask, width GW), control flow is decided by warp-level votes
+// (wany / wall) and each group's work is predicated on its own state -- so one instruction stream serves two queries.
+template <int GW>
+struct Group {
+    int gl;          // lane index inside the group
+    int shift;       // first lane of the group
+    __device__ __forceinline__ explicit Group(int lane) : gl(lane & (GW - 1)), shift(GW == 32 ? 0 : (lane & 16)) {}
+    template <typename T> __device__ __forceinline__ T shfl(T v, int src) const { return __shfl_sync(FULL, v, src, GW); }
+    template <typename T> __device__ __forceinline__ T shfl_up(T v, int d) const { return __shfl_up_sync(FULL, v, d, GW); }
+    template <typename T> __device__ __forceinline__ T shfl_xor(T v, int j) const { return __shfl_xor_sync(FULL, v, j, GW); }
+    __device__ __forceinline__ unsigned ballot(bool p) const {
+        unsigned b = __ballot_sync(FULL, p);
+        return GW == 32 ? b : ((b >> shift) & 0xffffu);
+    }
+    __device__ __forceinline__ bool all(bool p) const { return GW == 32 ? __all_sync(FULL, p) : (ballot(!p) == 0u); }
+    __device__ __forceinline__ bool any(bool p) const { return GW == 32 ? __any_sync(FULL, p) : (ballot(p) != 0u); }
+    // warp-level votes on group-uniform predicates
+    static __device__ __forceinline__ bool wany(bool p) { return GW == 32 ? p : __any_sync(FULL, p); }
+    static __device__ __forceinline__ bool wall(bool p) { return GW == 32 ? p : __all_sync(FULL, p); }
+};
+
+// Ascending bitonic sort of one key per lane of the group (15 compare-exchange stages for 32 lanes, 10 for 16).
+template <int GW>
+__device__ __forceinline__ u64 group_sort(const Group<GW> &g, u64 v) {
+#pragma unroll
+    for (int k2 = 2; k2 <= GW; k2 <<= 1) {
+#pragma unroll
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            u64 o = g.shfl_xor(v, j);
+            bool take_min = ((g.gl & k2) == 0) == ((g.gl & j) == 0);
+            v = ((o < v) == take_min) ? o : v;
         }
     }
-    return ins;
+    return v;
+}
+
+// The running result of one query: group lane i holds the i-th best key of a sorted top-GW list (kEmptyKey64 = no
+// entry); th = the k-th best, uniform across the group; empty = nothing has been offered yet (uniform).
+struct TopK {
+    u64 t, th;
+    bool empty;
+    __device__ __forceinline__ void init() { t = kEmptyKey64; th = kEmptyKey64; empty = true; }
+    __device__ __forceinline__ bool have_k() const { return th != kEmptyKey64; }
+};
+
+// Offer one candidate key per lane (kEmptyKey64 for "no candidate").  Returns the number of candidates that beat the
+// k-th best at entry.  The first non-empty batch is sorted as a whole; later ones are inserted one by one (few survive
+// the threshold).  Within a batch the threshold is not refreshed: a candidate that no longer makes the top k after an
+// earlier insertion of the same batch lands at a position >= k, which is harmless.
+// Must be called by all 32 lanes (see Group).
+template <int GW>
+__device__ __forceinline__ int topk_offer(const Group<GW> &g, TopK &tk, u64 key, int k) {
+    unsigned m = g.ballot(key < tk.th);
+    if (!Group<GW>::wany(m != 0u)) return 0;
+    const int n = __popc(m);
+    const bool do_sort = tk.empty && m != 0u;
+    if (Group<GW>::wany(do_sort)) {
+        u64 sorted = group_sort(g, key);
+        if (do_sort) {
+            tk.t = sorted;
+            tk.empty = false;
+            m = 0u;
+        }
+    }
+    while (Group<GW>::wany(m != 0u)) {
+        const bool act = m != 0u;
+        const int src = act ? __ffs(m) - 1 : 0;
+        m &= m - 1;
+        u64 c = g.shfl(key, src);
+        bool disp = act && c < tk.t;                // entries after c move up one lane
+        u64 up = g.shfl_up(tk.t, 1);
+        unsigned dm = g.ballot(disp);               // a suffix of the group's lanes (the list is sorted)
+        if (disp) tk.t = (g.gl == __ffs(dm) - 1) ? c : up;
+    }
+    tk.th = g.shfl(tk.t, k - 1);
+    return n;
 }
 
 __device__ __forceinline__ uint2 cell_lookup(const unsigned *__restrict__ keys, const uint2 *__restrict__ vals,
@@ -68,26 +123,25 @@ __device__ __forceinline__ uint2 cell_lookup(const unsigned *__restrict__ keys, 
 
 // Scan `n` consecutive records starting at pts.
 __device__ __forceinline__ int scan_range(const float4 *__restrict__ pts, unsigned n, float qx, float qy, float qz,
-                                          float &bd, int &bi, float &td, int &ti, int k, int lane) {
+                                          TopK &tk, int k, int lane) {
+    const Group<32> g(lane);
     int ins = 0;
     for (unsigned i0 = 0; i0 < n; i0 += 32) {
         unsigned t = i0 + lane;
         bool valid = t < n;
         float4 p = valid ? __ldg(pts + t) : make_float4(0.f, 0.f, 0.f, 0.f);
         float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-        ins += topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
+        ins += topk_offer(g, tk, valid ? pack_key(d2, __float_as_int(p.w)) : kEmptyKey64, k);
     }
     return ins;
 }
 
 // Exact k nearest neighbours of (qx,qy,qz) in segment b.  On return lane i < k holds the i-th neighbour
-// (bi == kNoIdx when fewer than k searchable points exist).
+// (key_idx == kNoIdx when fewer than k searchable points exist).
 __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, float qy, float qz, int k, int lane,
-                                           float &bd, int &bi) {
-    bd = INFINITY;
-    bi = kNoIdx;
-    float td = INFINITY;
-    int ti = kNoIdx;
+                                           TopK &tk) {
+    tk.init();
+    const Group<32> g32(lane);
     const GridSeg *sp = g.segs + b;
     const unsigned n_valid = sp->n_valid;
     if (n_valid == 0) return;
@@ -145,7 +199,7 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
                     unsigned s0 = __shfl_sync(FULL, start, j), e0 = __shfl_sync(FULL, excl, j);
                     float4 p = valid ? __ldg(pts + s0 + (t - e0)) : make_float4(0.f, 0.f, 0.f, 0.f);
                     float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-                    st_ins += topk_offer(bd, bi, td, ti, d2, __float_as_int(p.w), valid, k, lane);
+                    st_ins += topk_offer(g32, tk, valid ? pack_key(d2, __float_as_int(p.w)) : kEmptyKey64, k);
                 }
             }
             st_ring = r;
@@ -161,13 +215,13 @@ __device__ __forceinline__ void knn_search(const GridView &g, int b, float qx, f
                 done = true;   // the cube covers the whole grid
             } else {
                 float bm = bound - kMarginCells * h;
-                if (ti != kNoIdx && bm > 0.f && td < bm * bm) done = true;
+                if (tk.have_k() && bm > 0.f && key_d2(tk.th) < bm * bm) done = true;
             }
         }
     }
     if (!done) {   // exhaustive fallback (tiny segment, or a query far from the surface)
-        bd = INFINITY; bi = kNoIdx; td = INFINITY; ti = kNoIdx;
-        st_ins += scan_range(pts, n_valid, qx, qy, qz, bd, bi, td, ti, k, lane);
+        tk.init();
+        st_ins += scan_range(pts, n_valid, qx, qy, qz, tk, k, lane);
         st_cand += n_valid;
         st_ring = (n_valid > kBruteN) ? 4 : 8;
     }

@@ -2,14 +2,18 @@
 // records), searched directly in the rasters -- no spatial index and no build step.
 //
 // Every cloud point lies on the camera ray of its pixel, so a point within distance r of the query q must have its
-// pixel inside the projection of the ball B(q, r) into that view.  One warp per query:
-//   scan     a (2m+1)^2 pixel window around q's projection in every view, m = 2 first (lane v owns view v's
-//            rectangle; the rectangles of all views are flattened into one candidate list, 32 candidates per step);
-//   bound    r = current k-th best distance;  lane v computes the pixel bounding box of B(q, r) in view v
+// pixel inside the projection of the ball B(q, r) into that view.  One group of GW lanes per query (a warp, or a half
+// warp when k <= 16 and V <= 16 -- two queries per warp halve the per-query cost of everything that is not per candidate):
+//   pass 1   a fixed kPW x kPH pixel window around q's projection in every view: one 16-byte record per lane, the
+//            loads of several chunks in flight together.  Pixels are taken nearest-to-the-projection first across
+//            all views, so the first batch (sorted as a whole, bitonic) already holds most of the answer and few of
+//            the later candidates beat its k-th best (those are inserted one by one);
+//   bound    r = current k-th best distance;  group lane v computes the pixel bounding box R_v of B(q, r) in view v
 //            (tangent directions of the ball seen from the camera centre, clipped to z > 0);
-//   done     when every view's box lies inside what has been scanned -- the result is then exact;
-//   grow     otherwise m -> 2m+1, windows clipped to the boxes; only the new pixels are scanned.  r shrinks as nearer
-//            points turn up, so the scanned area stays within a small factor of the final ball's projection.
+//   done     when every R_v lies inside what has been scanned -- the result is then exact;
+//   grow     otherwise the windows grow (m -> 2m+1) clipped to R_v; only the NEW pixels are scanned: the up to four
+//            strips of (new window \ old window) of every view are flattened into one candidate list, GW per step.
+//            r only shrinks, so once every R_v has been scanned the search is over without another bound.
 // Density adapts by construction: pixels are uniformly spaced in the raster wherever the surface is.
 // Points with negative depth are not searchable (they are not on the forward ray); depth == 0 points collapse onto
 // the camera centre and are handled exactly (a ball containing the centre maps to the whole raster).
@@ -26,8 +30,36 @@ struct RasterView {
     int skip_invalid;     // 1: points with depth <= 0 are not searchable
 };
 
+#ifndef MVT_M0
+#define MVT_M0 2
+#endif
+constexpr int kM0 = MVT_M0;                            // first-pass half window
+constexpr int kPW = 2 * kM0 + 2, kPH = 2 * kM0 + 1;    // 6 x 5 pixels: x in [floor(u)-2, floor(u)+3], y in [rint(v)-2, rint(v)+2]
+
+// The first-pass window pixels ordered nearest-first from the query's projection (which lies in [0,1) x [-0.5,0.5]
+// relative to pixel (kM0, kM0) of the window): tab[rank] = wx | wy << 4.  Candidates are then enumerated rank-major,
+// view-minor, so the first batch -- the one that is sorted and sets the first threshold -- holds the pixels nearest
+// to the projection in EVERY view and few later candidates survive it.  Call with all threads of the block.
+constexpr int kNW = kPW * kPH;
+__device__ __forceinline__ void init_window_table(unsigned char *tab) {
+    const int l = threadIdx.x;
+    if (l < kNW) {
+        const int wy = l / kPW, wx = l - wy * kPW;
+        auto key = [](int x, int y) { int a = 2 * x - (2 * kM0 + 1), b = 2 * (y - kM0); return a * a + b * b; };
+        const int mykey = key(wx, wy);
+        int rank = 0;
+        for (int o = 0; o < kNW; ++o) {
+            const int oy = o / kPW, ox = o - oy * kPW, ok = key(ox, oy);
+            rank += (ok < mykey || (ok == mykey && o < l)) ? 1 : 0;
+        }
+        tab[rank] = (unsigned char)(wx | (wy << 4));
+    }
+    __syncthreads();
+}
+
 // tan-range [lo, hi] of the directions (in the half plane z > 0) from the origin to the disk of radius r centred at
-// (z = cz, a = ca).  false = the disk is not visible at all.
+// (z = cz, a = ca).  false = the disk is not visible at all.  Approximate divisions: callers inflate r and the pixel
+// range by margins that are orders of magnitude above their error.
 __device__ __forceinline__ bool tan_range(float ca, float cz, float r, float &lo, float &hi) {
     float rho2 = fmaf(ca, ca, cz * cz), r2 = r * r;
     lo = -INFINITY;
@@ -36,18 +68,31 @@ __device__ __forceinline__ bool tan_range(float ca, float cz, float r, float &lo
     float s = sqrtf(rho2 - r2);
     float cl = fmaf(cz, s, ca * r), sl = fmaf(ca, s, -cz * r);     // cos, sin of (theta0 - alpha), scaled by rho^2
     float ch = fmaf(cz, s, -ca * r), sh = fmaf(ca, s, cz * r);     // cos, sin of (theta0 + alpha)
-    if (cl > 0.f) lo = sl / cl; else if (sl > 0.f) return false;
-    if (ch > 0.f) hi = sh / ch; else if (sh < 0.f) return false;
+    if (cl > 0.f) lo = __fdividef(sl, cl); else if (sl > 0.f) return false;
+    if (ch > 0.f) hi = __fdividef(sh, ch); else if (sh < 0.f) return false;
     return true;
+}
+
+// The same range when the disk lies strictly in front (cz > r, checked by the caller): tan(theta0 -+ alpha) by the
+// addition formula, tan(alpha) = r / sqrt(rho^2 - r^2).  lo is always finite; hi is +inf when theta0 + alpha >= 90 deg.
+__device__ __forceinline__ void tan_range_front(float ca, float cz, float icz, float r, float &lo, float &hi) {
+    float t0 = ca * icz;
+    float ta = r * rsqrtf(fmaf(ca, ca, fmaf(cz, cz, -r * r)));
+    float dl = fmaf(t0, ta, 1.f), dh = fmaf(-t0, ta, 1.f);
+    lo = (dl > 0.f) ? __fdividef(t0 - ta, dl) : -INFINITY;
+    hi = (dh > 0.f) ? __fdividef(t0 + ta, dh) : INFINITY;
 }
 
 struct Rect { int x0, y0, x1, y1; };   // [x0,x1) x [y0,y1); empty when x1 <= x0 or y1 <= y0
 __device__ __forceinline__ bool rect_empty(const Rect &r) { return r.x1 <= r.x0 || r.y1 <= r.y0; }
+__device__ __forceinline__ bool rect_inside(const Rect &r, const Rect &a) {   // r (non-empty) inside a
+    return !rect_empty(a) && r.x0 >= a.x0 && r.y0 >= a.y0 && r.x1 <= a.x1 && r.y1 <= a.y1;
+}
 
-// float interval [lo, hi] of raster coordinates -> clipped integer pixel range [i0, i1)
-__device__ __forceinline__ void pix_range(float ulo, float uhi, float st, int n, int &i0, int &i1) {
+// float interval [lo, hi] of input-image coordinates -> clipped integer raster pixel range [i0, i1)
+__device__ __forceinline__ void pix_range(float ulo, float uhi, float inv_st, int n, int &i0, int &i1) {
     const float pm = 0.05f;
-    float flo = ceilf((ulo + 0.5f) / st - 0.5f - pm), fhi = floorf((uhi + 0.5f) / st - 0.5f + pm);
+    float flo = ceilf(fmaf(ulo + 0.5f, inv_st, -0.5f - pm)), fhi = floorf(fmaf(uhi + 0.5f, inv_st, -0.5f + pm));
     flo = fmaxf(flo, 0.f);                 // NaN-safe: fmaxf/fminf return the non-NaN operand
     fhi = fminf(fhi, (float)(n - 1));
     if (!(flo <= fhi)) { i0 = 0; i1 = 0; return; }
@@ -55,21 +100,26 @@ __device__ __forceinline__ void pix_range(float ulo, float uhi, float st, int n,
     i1 = (int)fhi + 1;
 }
 
-__device__ __forceinline__ void raster_search(const RasterView &rv, int s, float qx, float qy, float qz, int k, int lane,
-                                              float &bd, int &bi, unsigned long long *stats, int qtag = 0) {
-    bd = INFINITY;
-    bi = kNoIdx;
-    float td = INFINITY;
-    int ti = kNoIdx;
-    const int W = rv.W, H = rv.H, HW = W * H;
-    const float4 *frame = rv.xyz4 + (size_t)s * rv.V * HW;
-    const bool mine = lane < rv.V;
+// win_tab: shared-memory table of init_window_table.
+// live = false: the group has no query (padding at the end of a frame's track list); it only takes part in the
+// collectives.  Must be called by all 32 lanes.
+template <int GW>
+__device__ __forceinline__ void raster_search(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
+                                              bool live, float qx, float qy, float qz, int k, TopK &tk,
+                                              unsigned long long *stats, int qtag = 0) {
+    tk.init();
+    const int gl = g.gl;
+    const int W = rv.W, H = rv.H, HW = W * H, V = rv.V;
+    const float4 *frame = rv.xyz4 + (size_t)s * V * HW;
+    const bool mine = live && gl < V;
+    const float inv_st = __frcp_rn(rv.stride);
+    const bool skip_invalid = rv.skip_invalid != 0;
 
     // per-lane (= per-view) camera and projection of q
-    float X = 0.f, Y = 0.f, Z = -1.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, tnorm = 0.f;
+    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, tnorm = 0.f;
     bool kok = false;
     if (mine) {
-        const float *cm = rv.cam + ((size_t)lane * rv.S + s) * kCamStride;
+        const float *cm = rv.cam + ((size_t)gl * rv.S + s) * kCamStride;
         X = fmaf(cm[24], qx, fmaf(cm[25], qy, fmaf(cm[26], qz, cm[33])));
         Y = fmaf(cm[27], qx, fmaf(cm[28], qy, fmaf(cm[29], qz, cm[34])));
         Z = fmaf(cm[30], qx, fmaf(cm[31], qy, fmaf(cm[32], qz, cm[35])));
@@ -78,84 +128,82 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
         tnorm = fabsf(cm[33]) + fabsf(cm[34]) + fabsf(cm[35]);
     }
     const bool front = mine && kok && Z > 1e-12f;
-    // integer window centre (clamped so that centre +- m cannot overflow)
+    // integer window centre (clamped so that centre +- m cannot overflow): x windows are [ci-m, ci+m+1], y [cj-m, cj+m]
     int ci = 0, cj = 0;
     if (front) {
-        float a = X / Z, b = Y / Z;
-        float fi = (fmaf(fx, a, fmaf(sk, b, cx0)) + 0.5f) / rv.stride - 0.5f;
-        float fj = (fmaf(fy, b, cy0) + 0.5f) / rv.stride - 0.5f;
-        ci = (int)fminf(fmaxf(rintf(fi), -1.0e8f), 1.0e8f);
+        iz = __frcp_rn(Z);
+        float a = X * iz, b = Y * iz;
+        float fi = fmaf(fmaf(fx, a, fmaf(sk, b, cx0)) + 0.5f, inv_st, -0.5f);
+        float fj = fmaf(fmaf(fy, b, cy0) + 0.5f, inv_st, -0.5f);
+        ci = (int)fminf(fmaxf(floorf(fi), -1.0e8f), 1.0e8f);
         cj = (int)fminf(fmaxf(rintf(fj), -1.0e8f), 1.0e8f);
     }
     const Rect whole = {0, 0, W, H};
-    Rect A = {0, 0, 0, 0}, B = {0, 0, 0, 0};
-    int m = 2;
     auto window = [&](int mm) {
         Rect r = {0, 0, 0, 0};
-        if (!mine) return r;
         if (!front) return r;       // behind the camera / odd intrinsics: no window centre (handled in the growth step)
-        r.x0 = max(ci - mm, 0); r.x1 = min(ci + mm + 1, W);
+        r.x0 = max(ci - mm, 0); r.x1 = min(ci + mm + 2, W);
         r.y0 = max(cj - mm, 0); r.y1 = min(cj + mm + 1, H);
         if (rect_empty(r)) r = Rect{0, 0, 0, 0};
         return r;
     };
-    B = window(m);
-    unsigned long long st_cand = 0, st_ins = 0;
-    int st_pass = 0;
+    unsigned st_cand = 0, st_ins = 0;
+    int st_pass = 1;
+
+    // ---- pass 1: the fixed window of every view that sees q in front of it; candidate t = rank * V + view ----
+    {
+        constexpr int kCB = 4;                              // chunks whose loads are in flight together
+        const unsigned front_mask = g.ballot(front);
+        const int total = kNW * V;
+        const unsigned magic = (65536u + (unsigned)V - 1u) / (unsigned)V;     // t / V == (t * magic) >> 16 for t < 960
+        const int x00 = ci - kM0, y00 = cj - kM0;
+        for (int t0 = 0; t0 < total; t0 += kCB * GW) {
+            float4 p[kCB];
+            int id[kCB];
+            bool ok[kCB];
+#pragma unroll
+            for (int c = 0; c < kCB; ++c) {
+                const int t = t0 + c * GW + gl;
+                const int rk = (int)(((unsigned)t * magic) >> 16), v = t - rk * V;
+                const unsigned wo = win_tab[min(rk, kNW - 1)];
+                const int px = g.shfl(x00, v) + (int)(wo & 15u), py = g.shfl(y00, v) + (int)(wo >> 4);
+                ok[c] = t < total && ((front_mask >> v) & 1u) && (unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H;
+                id[c] = (int)((unsigned)v * (unsigned)HW + (unsigned)py * (unsigned)W + (unsigned)px);
+                p[c] = ok[c] ? __ldg(frame + id[c]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int c = 0; c < kCB; ++c) {
+                if (t0 + c * GW >= total) break;
+                bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < 0.f));
+                float d2 = dist2(p[c].x, p[c].y, p[c].z, qx, qy, qz);
+                st_ins += topk_offer(g, tk, valid ? pack_key(d2, id[c]) : kEmptyKey64, k);
+            }
+        }
+        st_cand += kNW * __popc(front_mask);
+    }
+    Rect A = window(kM0);     // scanned so far (per view)
+    int m = kM0;
+    bool done = false;        // this group's result is final (uniform in the group)
 
     while (true) {
-        // ---- scan B \ A over all views ----
-        const bool same = (B.x0 == A.x0 && B.y0 == A.y0 && B.x1 == A.x1 && B.y1 == A.y1);
-        const int bw = B.x1 - B.x0;
-        unsigned cnt = (rect_empty(B) || same) ? 0u : (unsigned)bw * (unsigned)(B.y1 - B.y0);
-        unsigned incl = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned t = __shfl_up_sync(FULL, incl, o);
-            if (lane >= o) incl += t;
-        }
-        const unsigned excl = incl - cnt;
-        const unsigned total = __shfl_sync(FULL, incl, 31);
-        st_cand += total;
-        ++st_pass;
-        for (unsigned i0 = 0; i0 < total; i0 += 32) {
-            unsigned t = i0 + lane;
-            bool valid = t < total;
-            int j = 0;
-#pragma unroll
-            for (int step = 16; step; step >>= 1) {
-                int pr = j + step;
-                unsigned e = __shfl_sync(FULL, excl, pr);
-                if (e <= t) j = pr;
-            }
-            unsigned e0 = __shfl_sync(FULL, excl, j);
-            int wj = __shfl_sync(FULL, bw, j), x0 = __shfl_sync(FULL, B.x0, j), y0 = __shfl_sync(FULL, B.y0, j);
-            int ax0 = __shfl_sync(FULL, A.x0, j), ay0 = __shfl_sync(FULL, A.y0, j);
-            int ax1 = __shfl_sync(FULL, A.x1, j), ay1 = __shfl_sync(FULL, A.y1, j);
-            unsigned o = valid ? t - e0 : 0u;
-            unsigned row = o / (unsigned)max(wj, 1);
-            int px = x0 + (int)(o - row * (unsigned)max(wj, 1)), py = y0 + (int)row;
-            valid = valid && !(px >= ax0 && px < ax1 && py >= ay0 && py < ay1);
-            int idx = j * HW + py * W + px;
-            float4 p = valid ? __ldg(frame + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-            valid = valid && (rv.skip_invalid ? (p.w > 0.f) : !(p.w < 0.f));
-            float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-            st_ins += topk_offer(bd, bi, td, ti, d2, idx, valid, k, lane);
-        }
-        if (!rect_empty(B)) A = B;
-
-        const bool have_k = ti != kNoIdx;
+        const bool have_k = tk.have_k();
         Rect R = whole;      // pixels of my view that can still hold a neighbour
         bool covered;
         if (have_k) {
             // pixel bounding box of the ball B(q, r), r = current k-th best distance (an upper bound of the final one)
-            float r = sqrtf(td);
+            float r = sqrtf(key_d2(tk.th));
             float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
             if (mine && kok) {
                 R = Rect{0, 0, 0, 0};
                 float alo, ahi, blo, bhi;
-                bool vis = tan_range(X, Z, reff, alo, ahi) && tan_range(Y, Z, reff, blo, bhi);
-                if (fmaf(X, X, fmaf(Y, Y, Z * Z)) <= reff * reff) { vis = true; alo = blo = -INFINITY; ahi = bhi = INFINITY; }
+                bool vis = true;
+                if (front && Z > 1.01f * reff) {   // the usual case: the ball is strictly in front of the camera
+                    tan_range_front(X, Z, iz, reff, alo, ahi);
+                    tan_range_front(Y, Z, iz, reff, blo, bhi);
+                } else {
+                    vis = tan_range(X, Z, reff, alo, ahi) && tan_range(Y, Z, reff, blo, bhi);
+                    if (fmaf(X, X, fmaf(Y, Y, Z * Z)) <= reff * reff) { vis = true; alo = blo = -INFINITY; ahi = bhi = INFINITY; }
+                }
                 if (vis) {
                     float ulo = fmaf(fx, alo, cx0), uhi = fmaf(fx, ahi, cx0);
                     if (sk != 0.f) {
@@ -163,47 +211,106 @@ __device__ __forceinline__ void raster_search(const RasterView &rv, int s, float
                         ulo += fminf(s0, s1); uhi += fmaxf(s0, s1);
                     }
                     float vlo = fmaf(fy, blo, cy0), vhi = fmaf(fy, bhi, cy0);
-                    pix_range(ulo, uhi, rv.stride, W, R.x0, R.x1);
-                    pix_range(vlo, vhi, rv.stride, H, R.y0, R.y1);
+                    pix_range(ulo, uhi, inv_st, W, R.x0, R.x1);
+                    pix_range(vlo, vhi, inv_st, H, R.y0, R.y1);
                     if (rect_empty(R)) R = Rect{0, 0, 0, 0};
                 }
             }
-            covered = !mine || rect_empty(R) ||
-                      (!rect_empty(A) && R.x0 >= A.x0 && R.y0 >= A.y0 && R.x1 <= A.x1 && R.y1 <= A.y1);
+            covered = !mine || rect_empty(R) || rect_inside(R, A);
         } else {
             // fewer than k searchable points so far; stop only when all rasters are covered
             covered = !mine || (A.x0 == 0 && A.y0 == 0 && A.x1 == W && A.y1 == H);
         }
-        if (__all_sync(FULL, covered)) break;     // every view's ball projection has been scanned: exact
+        const bool all_covered = g.all(covered);  // every view's ball projection has been scanned: exact
+        done = done || all_covered;
+        if (Group<GW>::wall(done)) break;
         // views without a window centre (q behind the camera, odd intrinsics) wait until the views that have one are
         // done, so that they are scanned once, with the final (tight) radius
-        const bool front_pending = __any_sync(FULL, front && !covered);
+        const bool front_pending = g.any(front && !covered);
         // grow the windows geometrically, but never beyond what the current ball can reach; the bound tightens as
         // nearer points are found, so the scanned area stays within a small factor of the final ball's projection
         m = (m < (1 << 24)) ? 2 * m + 1 : m;
-        Rect g = {0, 0, 0, 0};
-        if (front) g = (m >= (1 << 24)) ? whole : window(m);
-        else if (mine && !front_pending) g = whole;
-        if (!rect_empty(g)) {
-            g.x0 = max(g.x0, R.x0); g.y0 = max(g.y0, R.y0); g.x1 = min(g.x1, R.x1); g.y1 = min(g.y1, R.y1);
+        Rect gr = {0, 0, 0, 0};
+        if (front) gr = (m >= (1 << 24)) ? whole : window(m);
+        else if (mine && !front_pending) gr = whole;
+        if (!rect_empty(gr)) {
+            gr.x0 = max(gr.x0, R.x0); gr.y0 = max(gr.y0, R.y0); gr.x1 = min(gr.x1, R.x1); gr.y1 = min(gr.y1, R.y1);
         }
-        if (rect_empty(g)) {
+        Rect B;
+        if (rect_empty(gr) || done) {
             B = A;
         } else if (rect_empty(A)) {
-            B = g;
+            B = gr;
         } else {
-            B.x0 = min(g.x0, A.x0); B.y0 = min(g.y0, A.y0); B.x1 = max(g.x1, A.x1); B.y1 = max(g.y1, A.y1);
+            B.x0 = min(gr.x0, A.x0); B.y0 = min(gr.y0, A.y0); B.x1 = max(gr.x1, A.x1); B.y1 = max(gr.y1, A.y1);
         }
+        // r only shrinks: if this pass reaches every R, nothing outside can matter afterwards
+        const bool reaches_all = g.all(!mine || rect_empty(R) || rect_inside(R, B));
+        const bool last = have_k && reaches_all;
+
+        // ---- scan B \ A of every view: four strips per view (top, bottom, left, right), GW/4 views per round ----
+        for (int v0 = 0; v0 < V; v0 += GW / 4) {
+            const int ev = v0 + (gl >> 2), es = gl & 3, el = ev & (GW - 1);
+            int ax0 = g.shfl(A.x0, el), ay0 = g.shfl(A.y0, el), ax1 = g.shfl(A.x1, el), ay1 = g.shfl(A.y1, el);
+            const int bx0 = g.shfl(B.x0, el), by0 = g.shfl(B.y0, el), bx1 = g.shfl(B.x1, el), by1 = g.shfl(B.y1, el);
+            if (ax1 <= ax0 || ay1 <= ay0) { ax0 = ax1 = bx0; ay0 = ay1 = by1; }   // nothing scanned yet: all of B is "top"
+            const int sx0 = (es == 3) ? ax1 : bx0, sx1 = (es == 2) ? ax0 : bx1;
+            const int sy0 = (es == 0) ? by0 : (es == 1) ? ay1 : ay0, sy1 = (es == 0) ? ay0 : (es == 1) ? by1 : ay1;
+            const int sw = sx1 - sx0, sh = sy1 - sy0;
+            const unsigned cnt = (!done && ev < V && sw > 0 && sh > 0) ? (unsigned)sw * (unsigned)sh : 0u;
+            const float inv_w = __frcp_rn((float)max(sw, 1));
+            unsigned incl = cnt;
+#pragma unroll
+            for (int o = 1; o < GW; o <<= 1) {
+                unsigned t = g.shfl_up(incl, o);
+                if (gl >= o) incl += t;
+            }
+            const unsigned excl = incl - cnt;
+            const unsigned total = g.shfl(incl, GW - 1);
+            st_cand += total;
+            for (unsigned i0 = 0; Group<GW>::wany(i0 < total); i0 += GW) {
+                const unsigned t = i0 + gl;
+                bool valid = t < total;
+                int j = 0;
+#pragma unroll
+                for (int step = GW / 2; step; step >>= 1) {
+                    int pr = j + step;
+                    unsigned e = g.shfl(excl, pr);
+                    if (e <= t) j = pr;
+                }
+                const unsigned e0 = g.shfl(excl, j);
+                const int wj = g.shfl(sw, j), xj = g.shfl(sx0, j), yj = g.shfl(sy0, j);
+                const float iw = g.shfl(inv_w, j);
+                const unsigned o = valid ? t - e0 : 0u;
+                unsigned row;
+                if (o < (1u << 22)) {
+                    row = (unsigned)(((float)o + 0.5f) * iw);      // within one of o / wj; fixed below
+                } else {
+                    row = o / (unsigned)max(wj, 1);
+                }
+                int col = (int)o - (int)row * wj;
+                if (col < 0) { --row; col += wj; } else if (col >= wj) { ++row; col -= wj; }
+                const int idx = (v0 + (j >> 2)) * HW + (yj + (int)row) * W + xj + col;
+                float4 p = valid ? __ldg(frame + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+                valid = valid && (skip_invalid ? (p.w > 0.f) : !(p.w < 0.f));
+                float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
+                st_ins += topk_offer(g, tk, valid ? pack_key(d2, idx) : kEmptyKey64, k);
+            }
+        }
+        if (!rect_empty(B)) A = B;
+        if (!done) ++st_pass;
+        done = done || last;
+        if (Group<GW>::wall(done)) break;
     }
-    if (stats && lane == 0) {
+    if (stats && live && gl == 0) {
         atomicAdd(stats + 0, 1ull);
         atomicAdd(stats + min(st_pass, 4), 1ull);     // [1] one pass, [2] two passes, [3] three, [4] four or more
-        atomicAdd(stats + 5, st_cand);
-        atomicAdd(stats + 6, st_ins);
-        // [9] worst query: candidates << 32 | (frame << 24 ^ low bits of qx as a tag is not needed: host recomputes)
-        atomicMax(stats + 9, (st_cand << 24) | (unsigned long long)(qtag & 0xFFFFFF));
+        atomicAdd(stats + 5, (unsigned long long)st_cand);
+        atomicAdd(stats + 6, (unsigned long long)st_ins);
+        // [9] worst query: candidates << 24 | query tag (the host recomputes the rest)
+        atomicMax(stats + 9, ((unsigned long long)st_cand << 24) | (unsigned long long)(qtag & 0xFFFFFF));
         int bin = 0;
-        unsigned long long c = st_cand;
+        unsigned c = st_cand;
         while (c > 1 && bin < 5) { c >>= 3; ++bin; }       // bins: <2, <16, <128, <1024, <8192, >=8192 candidates
         atomicAdd(stats + 10 + bin, 1ull);
     }

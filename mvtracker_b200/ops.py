@@ -59,8 +59,11 @@ class Cloud:
 
 
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
-                want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None) -> List[Cloud]:
-    """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass."""
+                want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None,
+                reuse: Optional[Sequence["Cloud"]] = None) -> List[Cloud]:
+    """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass.
+    reuse: Clouds of an earlier call with the same shapes / levels / dtype whose buffers are overwritten in place (no
+    allocation in steady state, e.g. one set of buffers per sliding window)."""
     _need_cuda(fmaps, "fmaps"); _need_cuda(depths, "depths")
     V, S, Cc, H, W = fmaps.shape
     depths = depths.reshape(V, S, H, W)
@@ -71,6 +74,15 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         raise MvtError(f"levels {levels} outside 0..{_lib.MAX_LEVELS - 1}")
     fm = fmaps.contiguous()
     dp = depths.float().contiguous()
+    if reuse is not None:
+        reuse = {c.level: c for c in reuse}
+        if cam is None:
+            cam = next(iter(reuse.values())).cam
+            K = intrs.reshape(-1, 3, 3).float().contiguous()
+            E = extrs.reshape(-1, 3, 4).float().contiguous()
+            if cam is None or cam.shape[0] != K.shape[0]:
+                raise MvtError("reuse: camera record buffer has the wrong size")
+            check(lib().mvt_camera_prep(_ptr(K), _ptr(E), K.shape[0], _ptr(cam), _stream()), "mvt_camera_prep")
     if cam is None:
         cam = camera_prep(intrs, extrs)
     dev = fm.device
@@ -81,11 +93,23 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         if Hl <= 0 or Wl <= 0:
             raise MvtError(f"level {l} is empty for a {H}x{W} map")
         P = V * Hl * Wl
-        xyz = torch.empty(S, P, 3, device=dev, dtype=torch.float32)
-        fvec = torch.empty(S, P, Cc, device=dev, dtype=fm.dtype) if want_fvec else None
-        valid = torch.empty(S, P, device=dev, dtype=torch.uint8) if want_valid else None
-        spacing = torch.empty(S, 2, device=dev, dtype=torch.float32) if want_spacing else None
-        xyz4 = torch.empty(S, P, 4, device=dev, dtype=torch.float32) if want_xyz4 else None
+        if reuse is not None:
+            old = reuse.get(l)
+            if old is None or old.xyz.shape != (S, P, 3) or (want_fvec and (old.fvec is None or old.fvec.shape != (S, P, Cc)
+                                                                          or old.fvec.dtype != fm.dtype)):
+                raise MvtError(f"reuse: no matching buffers for level {l}")
+            xyz, fvec = old.xyz, (old.fvec if want_fvec else None)
+            valid = old.valid.view(torch.uint8) if (want_valid and old.valid is not None) else None
+            spacing = old.spacing if want_spacing else None
+            xyz4 = old.xyz4 if want_xyz4 else None
+            if (want_valid and valid is None) or (want_spacing and spacing is None) or (want_xyz4 and xyz4 is None):
+                raise MvtError(f"reuse: level {l} lacks a requested output buffer")
+        else:
+            xyz = torch.empty(S, P, 3, device=dev, dtype=torch.float32)
+            fvec = torch.empty(S, P, Cc, device=dev, dtype=fm.dtype) if want_fvec else None
+            valid = torch.empty(S, P, device=dev, dtype=torch.uint8) if want_valid else None
+            spacing = torch.empty(S, 2, device=dev, dtype=torch.float32) if want_spacing else None
+            xyz4 = torch.empty(S, P, 4, device=dev, dtype=torch.float32) if want_xyz4 else None
         outs[l] = LevelOut(xyz.data_ptr(), xyz4.data_ptr() if want_xyz4 else None, fvec.data_ptr() if want_fvec else None,
                            valid.data_ptr() if want_valid else None, spacing.data_ptr() if want_spacing else None)
         mask |= 1 << l

@@ -207,6 +207,31 @@ def test_corr_fused_levels_equal_separate_launches():
         assert_close(one.reshape(4, 333, 16, 4).cpu().numpy(), o_out, 1e-4, f"level {i}")
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("k", [16, 8])
+def test_corr_half_warp_groups_identical(dtype, k):
+    """mvt_debug_set_group_width(16): two queries per warp in lock step; outputs must equal the warp-per-query kernel
+    bit for bit (odd M -> the last half-warp group of every frame is padding)."""
+    from mvtracker_b200 import _lib
+    sc = synth.make_scene(3, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.2, seed=29, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 301, 3, valid=clouds[0].valid[0], dtype=dtype, jitter=0.05)
+    coords[:, :7] += 3.0          # a few queries far from every surface (many passes)
+    lv = [(c, c.fvec, k) for c in clouds]
+    L = _lib.lib()
+    try:
+        _lib.check(L.mvt_debug_set_group_width(32), "set_group_width")
+        a, ia = ops.knn_corr(lv, targets, coords, return_idx=True)
+        _lib.check(L.mvt_debug_set_group_width(16), "set_group_width")
+        b, ib = ops.knn_corr(lv, targets, coords, return_idx=True)
+    finally:
+        L.mvt_debug_set_group_width(32)
+    assert torch.equal(ia, ib)
+    assert torch.equal(a, b)
+    _, oi = oracle.knn(k, clouds[0].xyz.cpu().numpy(), coords.cpu().numpy())
+    assert (ib[0].cpu().numpy() == oi).all()
+
+
 def test_knn_gather_feature_init():
     sc = synth.make_scene(3, 40 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=24, device=DEV)
     c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]
