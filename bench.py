@@ -21,6 +21,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 S_WINDOW, C_FEAT, K_NN, LEVELS, STRIDE = 12, 128, 16, 4, 4
+# The workload every N runs by default: the 8-view / ~1M-point window north_star quotes its 1-GPU roofline and 8-GPU scaling
+# targets on (BASELINE.json configs[2]); it fits one GPU (~17 GB), so the 1/2/4/8-GPU series is one fixed job (strong scaling).
+DEFAULT_WORKLOAD = "panoptic"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full captures under
+# profiles/ (workload, dtype, kernel) -> bytes; None until that capture exists.
+NCU_TRAFFIC = {}
 
 
 def parse_args():
@@ -151,7 +157,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    w = workload_cfg(args.workload or ("droid" if args.gpus == 1 else "panoptic"))
+    w = workload_cfg(args.workload or DEFAULT_WORKLOAD)
     budget = max(2.0, min(args.cpu_budget, 150.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_sample(w, args.iters, budget, args.zero_frac)
@@ -170,8 +176,9 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def config_dict(w, args):
-    return {"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
+def config_dict(w, args, world=1):
+    return {"parallelism": "1 GPU: fused knn_corr kernel" if world == 1 else
+            f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard, merged indices all-gathered, result records all-reduced (NCCL)","workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
             "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
@@ -181,180 +188,243 @@ def config_dict(w, args):
 # ------------------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------------------
+def _peak():
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(mp["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from mvtracker_b200 import _lib, dropin, ops, synth
+    from mvtracker_b200 import _lib, ops, synth
+    from mvtracker_b200.dist import ShardedWindow, view_range
     from mvtracker_b200.hotpath import WindowClouds
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        from mvtracker_b200 import dist as mdist
-        return mdist.run_bench(args, sys.modules[__name__])
-    assert args.gpus == 1, "for --gpus N > 1 launch with torchrun (one rank per GPU)"
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun, one rank per GPU"
+    assert args.gpus == 1 or world > 1, "for --gpus N > 1 launch with torchrun (one rank per GPU)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    w = workload_cfg(args.workload or "droid")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w = workload_cfg(args.workload or DEFAULT_WORKLOAD)
     fdtype = torch.float32 if args.dtype == "f32" else torch.bfloat16
     esz = 4 if args.dtype == "f32" else 2
-    iters, N = args.iters, w["N"]
+    iters, N, V = args.iters, w["N"], w["V"]
+    warmup = max(args.warmup, 3)
+    L = _lib.lib()
 
-    sc = synth.make_scene(w["V"], w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac, seed=72,
+    # ---- synthetic inputs, identical on every rank (same seed); tracks are sampled from the full level-0 cloud ---------
+    sc = synth.make_scene(V, w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac, seed=72,
                           device=dev, dtype=fdtype)
     fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
-    win = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale, search=args.search)
+    c0 = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=[0], want_fvec=False, want_spacing=False)[0]
     # tracks follow the surface at their pixel (+ N(0, 2 cm)), i.e. near the cloud in every frame like converged tracks
-    base_coords, base_targets = synth.make_tracks(win.clouds[0].xyz, N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype,
-                                                  valid=win.clouds[0].xyz4[..., 3] > 0)
+    base_coords, base_targets = synth.make_tracks(c0.xyz, N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype, valid=c0.xyz4[..., 3] > 0)
+    del c0
     g = torch.Generator(device=dev).manual_seed(74)
     coords_it = [(base_coords + 0.01 * torch.randn(base_coords.shape, device=dev, generator=g)).contiguous() for _ in range(iters)]
     targets_it = [(base_targets * (1.0 - 0.1 * i)).contiguous() for i in range(iters)]
-    outs = [torch.empty(S_WINDOW, N, win.width, device=dev, dtype=torch.float32) for _ in range(iters)]
-    del win
-    L = _lib.lib()
+    width = LEVELS * K_NN * 4
+    outs = [torch.empty(S_WINDOW, N, width, device=dev, dtype=torch.float32) for _ in range(iters)]
+    if world > 1:
+        v0, v1 = view_range(rank, world, V)
+        fm, dp, K, E = fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous()
+        del sc
+        torch.cuda.empty_cache()
+
+    # ---- one step = the hot path of one sliding window; output buffers are allocated once and rebuilt in place --------
+    state = {"win": None}
 
     def step(ev=None):
         if ev is not None: ev[0].record()
-        wdw = WindowClouds.build(fm, dp, K, E, k=K_NN, cell_scale=args.cell_scale, search=args.search)
-        # (build = camera_prep + zero + cloud_build, then 6 grid kernels; events split them below)
-        if ev is not None: ev[1].record()
+        if world == 1:
+            clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=(args.search == "grid"),
+                                     reuse=None if state["win"] is None else state["win"].clouds)
+            if ev is not None: ev[1].record()
+            grids = None
+            if args.search == "grid":
+                grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
+            win = WindowClouds(clouds, grids, K_NN, 1, True, False)
+        else:
+            win = ShardedWindow.build(fm, dp, K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"])
+            if ev is not None: ev[1].record()
+        if ev is not None: ev[2].record()
         for i in range(iters):
-            wdw.corr(targets_it[i], coords_it[i], out=outs[i])
-            if ev is not None: ev[2 + i].record()
-        return wdw
+            win.corr(targets_it[i], coords_it[i], out=outs[i])
+            if ev is not None: ev[3 + i].record()
+        state["win"] = win
 
-    # split timing of the build needs an event between cloud_build and grid_build: do it with the ops directly
-    def step_split(ev):
-        ev[0].record()
-        clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS))
-        ev[1].record()
-        grids = None
-        if args.search == "grid":
-            grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
-        ev[2].record()
-        wdw = WindowClouds(clouds, grids, K_NN, 1, True, False)
-        for i in range(iters):
-            wdw.corr(targets_it[i], coords_it[i], out=outs[i])
-            ev[3 + i].record()
-        return wdw
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         step()
-    torch.cuda.synchronize()
+    sync()
 
-    # ---- timed region: K steps, CUDA events on the launching (current) stream ---------------------------------------
+    # ---- timed region: exactly K steps between two events on the launching (current) stream, barrier + sync around ---
     try:
         gpu_id = "GPU-" + str(torch.cuda.get_device_properties(local).uuid)
     except Exception:
         gpu_id = str(local)
-    sampler = ClockSampler(gpu_id)
+    sampler = ClockSampler(gpu_id) if rank == 0 else None
     time.sleep(0.3)
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 + iters)] for _ in range(args.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = L.mvt_launch_count()
-    torch.cuda.synchronize()
+    sync()
     t_wall0 = time.time()
-    for s_i in range(args.steps):
-        wdw = step_split(evs[s_i])
-    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    sync()
     t_wall1 = time.time()
     launches = L.mvt_launch_count() - n0
-    total_ms = evs[0][0].elapsed_time(evs[-1][-1])
+    total_ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
     ms_step = total_ms / args.steps
-    t_cloud = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
-    t_grid = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
-    t_corr = sum(e[2 + i].elapsed_time(e[3 + i]) for e in evs for i in range(iters)) / (args.steps * iters)
-    # keep the timed region long enough for nvidia-smi to see it
-    t_pad = time.time()
-    while time.time() - t_wall0 < 1.0:
-        step()
-    torch.cuda.synchronize()
-    clocks = sampler.window(t_wall0, max(t_wall1, time.time()))
     queries = iters * LEVELS * S_WINDOW * N
     value = queries / (ms_step * 1e-3)
 
-    # ---- roofline (algorithmic bytes / measured launch time / measured HBM peak) ------------------------------------
-    peak, peak_src = 6650.0, "fallback"
-    try:
-        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        peak, peak_src = float(mp["hbm_gbs"]), "measured"
-    except Exception:
-        pass
-    D = 4
-    q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * D * 4
-    corr_bytes = LEVELS * S_WINDOW * N * q_bytes
-    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + sum(c.xyz.numel() * 4 + c.fvec.numel() * esz for c in wdw.clouds)   # (the 16 B/pt xyz4 raster records are overhead, not counted)
+    # ---- per-kernel split (separate, untimed-for-the-metric pass with events between the stages) -------------------------
+    n_split = max(3, min(args.steps, 10))
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 + iters)] for _ in range(n_split)]
+    sync()
+    for e in evs:
+        step(e)
+    # keep the GPU busy long enough for nvidia-smi to have samples of the loaded clocks
+    while time.time() - t_wall0 < 1.2:
+        step()
+    sync()
+    t_cloud = sum(e[0].elapsed_time(e[1]) for e in evs) / n_split
+    t_grid = sum(e[1].elapsed_time(e[2]) for e in evs) / n_split
+    t_corr = sum(e[2 + i].elapsed_time(e[3 + i]) for e in evs for i in range(iters)) / (n_split * iters)
+    clocks = sampler.window(t_wall0, time.time()) if sampler else None
+
+    # ---- roofline (algorithmic bytes / measured time / measured HBM peak), per GPU -----------------------------------------
+    peak, peak_src = _peak()
+    v_loc = fm.shape[0]
+    q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4          # 9164 B (fp32) / 4812 B (bf16)
+    corr_bytes = LEVELS * S_WINDOW * N * q_bytes / world                              # per rank: its share of the gathers
+    pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * S_WINDOW
+    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + pts * (C_FEAT * esz + 12)       # SURVEY.md 8d (xyz4 records not counted)
     kern = {
-        "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6},
-        "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6},
-        "grid_build": {"ms": t_grid, "launches_per_step": 6 if args.search == "grid" else 0, "alg_bytes": 0, "gbs": 0.0},
+        "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
+                     "what": "fused knn_corr kernel" if world == 1 else "knn_keys + all-to-all + topk_merge + all-gather + corr_from_idx + all-reduce"},
+        "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6,
+                        "what": "camera_prep + cloud_build (4 levels, one pass)"},
     }
-    for kv in kern.values():
+    if args.search == "grid" and world == 1:
+        kern["grid_build"] = {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0}
+    step_sum = sum(kv["ms"] * kv["launches_per_step"] if name != "grid_build" else kv["ms"] for name, kv in kern.items())
+    for name, kv in kern.items():
         kv["frac"] = kv["gbs"] / peak
-        kv["share_of_step"] = kv["ms"] * kv["launches_per_step"] / ms_step if kv is not kern["grid_build"] else kv["ms"] / ms_step
+        kv["share_of_step"] = (kv["ms"] * kv["launches_per_step"] if name != "grid_build" else kv["ms"]) / step_sum
     dom = "knn_corr" if t_corr * iters >= t_cloud else "cloud_build"
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["gbs"], "peak": peak, "peak_source": peak_src,
-                "unit": "GB/s", "frac": kern[dom]["gbs"] / peak, "traffic": None,
-                "alg_bytes_per_launch": kern[dom]["alg_bytes"], "ms_per_launch": kern[dom]["ms"]}
+                "unit": "GB/s", "frac": kern[dom]["gbs"] / peak, "traffic": NCU_TRAFFIC.get((w["name"], args.dtype, dom)),
+                "alg_bytes_per_launch": kern[dom]["alg_bytes"], "ms_per_launch": kern[dom]["ms"],
+                "step_frac": (corr_bytes * iters + cloud_bytes) / (ms_step * 1e-3) / 1e9 / peak}
 
-    line = {"metric": "knn_corr_queries_per_s", "value": value, "unit": "queries/s", "n_gpus": 1, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args), "clocks": clocks,
+    line = {"metric": "knn_corr_queries_per_s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args, world), "clocks": clocks,
             "gpu_launches": int(launches), "roofline": roofline, "kernels": kern}
 
-    # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------
+    # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------------
     if not args.no_e2e:
-        line["e2e"] = run_e2e(args, w, sc, coords_it, targets_it, dev)
-    del wdw
-    sampler.stop()
-    if not args.no_cpu:
-        line["cpu_baseline"] = cpu_sample(w, iters, args.cpu_budget, args.zero_frac)
-    print(json.dumps(line))
+        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if world > 1 else 0)
+        line["e2e"] = e2e
+    state["win"] = None
+    if sampler:
+        sampler.stop()
+    if rank == 0:
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_sample(w, iters, args.cpu_budget, args.zero_frac)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
-def run_e2e(args, w, sc, coords_it, targets_it, dev):
-    """Each step: pinned host inputs -> device, the reference's own call pattern through mvtracker_b200.dropin
-    (init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat),
-    then the concatenated correlation features of every iteration -> pinned host."""
+def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0):
+    """Each step: this rank's inputs pinned host -> device, the public API (N = 1: the drop-in mirror of the reference seam --
+    init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat;
+    N > 1: mvtracker_b200.dist.ShardedWindow), then every iteration's correlation block -> pinned host."""
     import torch
+    import torch.distributed as dist
     from mvtracker_b200 import dropin
-    iters, N = args.iters, w["N"]
-    host_in = [t.cpu().pin_memory() for t in (sc.fmaps, sc.depths, sc.intrs, sc.extrs)]
+    from mvtracker_b200.dist import ShardedWindow
+    iters, N, V = args.iters, w["N"], w["V"]
+    host_in = [t.cpu().pin_memory() for t in (fm, dp, K, E)]
     host_ct = [(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(coords_it, targets_it)]
-    host_out = [torch.empty(1, S_WINDOW, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
+    host_out = [torch.empty(S_WINDOW, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
     h2d = sum(t.numel() * t.element_size() for t in host_in) + sum(c.numel() * c.element_size() + t.numel() * t.element_size() for c, t in host_ct)
     d2h = sum(t.numel() * t.element_size() for t in host_out)
+    state = {"win": None}
 
     def step():
-        fm, dp, K, E = [t.to(dev, non_blocking=True) for t in host_in]
-        blocks = []
-        for lvl in range(LEVELS):
-            xyz, fvec = dropin.init_pointcloud_from_rgbd(fm, dp, K, E, stride=STRIDE, level=lvl)
-            blocks.append(dropin.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
-                                                     corr_add_neighbor_xyz=False))
+        fmd, dpd, Kd, Ed = [t.to(dev, non_blocking=True) for t in host_in]
+        if world == 1:
+            blocks = []
+            for lvl in range(LEVELS):
+                xyz, fvec = dropin.init_pointcloud_from_rgbd(fmd[None], dpd[None, :, :, None], Kd[None], Ed[None], stride=STRIDE, level=lvl)
+                blocks.append(dropin.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
+                                                         corr_add_neighbor_xyz=False))
+        else:
+            win = ShardedWindow.build(fmd, dpd, Kd, Ed, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"])
+            state["win"] = win
         for i in range(iters):
             coords = host_ct[i][0].to(dev, non_blocking=True)
             ffeats = host_ct[i][1].to(dev, non_blocking=True)
-            fcorrs = [blocks[l].corr_sample(ffeats, coords).reshape(1, S_WINDOW, N, -1) for l in range(LEVELS)]
-            host_out[i].copy_(torch.cat(fcorrs, dim=-1), non_blocking=True)
+            if world == 1:
+                fcorrs = [blocks[l].corr_sample(ffeats, coords).reshape(S_WINDOW, N, -1) for l in range(LEVELS)]
+                host_out[i].copy_(torch.cat(fcorrs, dim=-1), non_blocking=True)
+            else:
+                host_out[i].copy_(win.corr(ffeats, coords), non_blocking=True)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
 
     n = max(3, min(args.steps, 10))
     for _ in range(3):
         step()
-    torch.cuda.synchronize()
+    sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(n):
         step()
     e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / n
+    sync()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        hb = torch.tensor([float(h2d), float(d2h)], device=dev, dtype=torch.float64)
+        dist.all_reduce(hb)
+        h2d, d2h = int(hb[0].item()), int(hb[1].item())
+    ms /= n
     dropin.clear_caches()
     queries = iters * LEVELS * S_WINDOW * N
     return {"value": queries / (ms * 1e-3), "unit": "queries/s", "ms_per_step": ms, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": n,
-            "api": "mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample), pinned host buffers"}
+            "api": ("mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample)" if world == 1 else
+                    "mvtracker_b200.dist.ShardedWindow (build / corr)") + ", pinned host buffers, all ranks summed"}
 
 
 if __name__ == "__main__":

@@ -135,6 +135,37 @@ int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C
 int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, int B, int C,
                    const float *query, int M, void *feat_out, int *idx_out, void *stream);
 
+/* ---- view-sharded kNN correlation across GPUs (mvtracker_b200/csrc/mvt_shard.cu; driven by mvtracker_b200/dist.py) --------
+ * Each rank keeps only the clouds of the views it unprojected; 8-byte (d2, index) keys and 16-byte result records are
+ * all that crosses NVLink.  The reference has no multi-GPU inference; the three calls below are
+ * the per-rank halves of PointcloudCorrBlock.corr_sample (mvtracker.py:800-846) split at the two exchange points. */
+
+/* Exact top-k of all queries among THIS rank's points, as sorted packed keys: (bits(d2) << 32) | (index + index_offset),
+ * missing = 0x7f8000007fffffff.  searches[l] / index_offsets[l] describe level l (same k on every level).
+ * keys_out [n_shards, n_levels, B, Ms, k] with Ms = ceil(M / n_shards): track m goes to shard m / Ms, padded tracks are
+ * filled with missing keys -- the layout an all-to-all over track shards sends as is. */
+int mvt_knn_keys(const mvt_search *searches, const long long *index_offsets, int n_levels, int B,
+                 const float *query, int M, int k, int n_shards, unsigned long long *keys_out, void *stream);
+
+/* Merges n_lists sorted candidate lists per query: keys_in [n_lists, Q, k] -> idx_out [Q, k] int32 (-1 = missing) and /
+ * or keys_out [Q, k], ascending (d2, index). */
+int mvt_topk_merge(const unsigned long long *keys_in, int n_lists, long long Q, int k, int *idx_out,
+                   unsigned long long *keys_out, void *stream);
+
+typedef struct mvt_owned_level {
+    const float *xyz4;      /* [B, hi-lo, 4] raster records of the points this rank owns at this level */
+    const void *fvec;       /* [B, hi-lo, C] */
+    long long lo, hi;       /* owned global index range [lo, hi) */
+    long long out_offset;   /* float offset of the level's k*4 block inside an output row */
+} mvt_owned_level;
+
+/* Correlation + offsets for GIVEN neighbour lists, for the neighbours this rank owns; records of neighbours owned by other
+ * ranks are written as zeros, so the sum over ranks is the full mvt_knn_corr output (add_offset = 1, add_xyz = 0, C = 128,
+ * groups = 1).  idx [n_shards, n_levels, B, Ms, k] global indices in the layout of mvt_knn_keys. */
+int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                      int n_shards, const int *idx, const void *targets, const float *coords, float *out,
+                      long long out_row_stride, void *stream);
+
 /* Debug / profiling: per-segment grid parameters copied out for inspection.
  * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */
 int mvt_grid_info(const void *grid, int B, int N, float *info, void *stream);

@@ -13,7 +13,7 @@ CAM_STRIDE, MAX_VIEWS = 48, 32
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
            "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
-           "mvt_debug_set_group_width")
+           "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx")
 
 
 class LevelOut(C.Structure):
@@ -34,6 +34,11 @@ class Search(C.Structure):
 
 class CorrLevel(C.Structure):
     _fields_ = [("search", Search), ("fvec", C.c_void_p), ("k", C.c_int), ("out_offset", C.c_longlong)]
+
+
+class OwnedLevel(C.Structure):
+    _fields_ = [("xyz4", C.c_void_p), ("fvec", C.c_void_p), ("lo", C.c_longlong), ("hi", C.c_longlong),
+                ("out_offset", C.c_longlong)]
 
 
 class MvtError(RuntimeError):
@@ -73,6 +78,9 @@ def lib():
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
     L.mvt_debug_set_group_width.argtypes = [ci]
+    L.mvt_knn_keys.argtypes = [C.POINTER(Search), C.POINTER(ll), ci, ci, vp, ci, ci, ci, vp, vp]
+    L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
+    L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
     for name in SYMBOLS:
         f = getattr(L, name)
         if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count"):

@@ -8,21 +8,13 @@
 // Roofline of knn_corr: HBM bound on the neighbour-feature gather.  Algorithmic bytes per query (k=16, C=128, fp32):
 //   read 12 (xyz) + 512 (target) + 16*(512 + 12) (neighbour rows + xyz), write 16*16  = 9 164 B  (SURVEY.md 8d).
 // The neighbour rows go HBM -> registers -> dot product; they are never written back.
-#include "mvt_raster.cuh"
+#include "mvt_search.cuh"
 
 namespace mvt {
 
 // Lanes per query of the fused raster kernel: 32 (default) or 16 (two queries per warp in lock step; measured slightly
 // slower on B200 so far -- kept selectable through mvt_debug_set_group_width for experiments and tests).
 static int g_group_width = 32;
-
-struct SearchDev {
-    int raster;          // 1: rv is valid, 0: g is valid
-    GridView g;
-    const float *xyz;    // grid mode neighbour coordinates [B,N,3]
-    RasterView rv;
-    int N;
-};
 
 // RASTER_ONLY: the caller guarantees sd.raster (the grid code is then not even compiled into the kernel).
 template <bool RASTER_ONLY = false>
@@ -34,17 +26,6 @@ __device__ __forceinline__ void search(const SearchDev &sd, const unsigned char 
     else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
     bd = key_d2(tk.t);
     bi = key_idx(tk.t);
-}
-
-// coordinates of neighbour `i` of batch element b
-template <bool RASTER_ONLY = false>
-__device__ __forceinline__ float3 nbr_xyz(const SearchDev &sd, int b, int i) {
-    if (RASTER_ONLY || sd.raster) {
-        float4 p = __ldg(sd.rv.xyz4 + (size_t)b * sd.N + i);
-        return make_float3(p.x, p.y, p.z);
-    }
-    const float *px = sd.xyz + ((size_t)b * sd.N + i) * 3;
-    return make_float3(__ldg(px), __ldg(px + 1), __ldg(px + 2));
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -367,8 +348,8 @@ __global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, con
 // ---------------------------------------------------------------------------------------------------------------
 static inline unsigned warp_blocks(long long warps) { return (unsigned)((warps + 7) / 8); }
 
-static int make_search(const mvt_search *u, int B, int need_xyz, mvt::SearchDev &sd, const char *who) {
-    using namespace mvt;
+namespace mvt {
+int make_search(const mvt_search *u, int B, int need_xyz, SearchDev &sd, const char *who) {
     MVT_CHECK_ARG(u, "%s: null search descriptor", who);
     MVT_CHECK_ARG(u->N > 0, "%s: bad N=%d", who, u->N);
     sd.N = u->N;
@@ -398,6 +379,8 @@ static int make_search(const mvt_search *u, int B, int need_xyz, mvt::SearchDev 
     }
     return MVT_OK;
 }
+}  // namespace mvt
+using mvt::make_search;
 
 MVT_EXPORT int mvt_knn(const mvt_search *search, int B, const float *query, int M, int k,
                        void *idx_out, int idx_is_i64, float *dist_out, void *stream) {

@@ -68,9 +68,17 @@ __device__ __forceinline__ bool tan_range(float ca, float cz, float r, float &lo
     float s = sqrtf(rho2 - r2);
     float cl = fmaf(cz, s, ca * r), sl = fmaf(ca, s, -cz * r);     // cos, sin of (theta0 - alpha), scaled by rho^2
     float ch = fmaf(cz, s, -ca * r), sh = fmaf(ca, s, cz * r);     // cos, sin of (theta0 + alpha)
-    if (cl > 0.f) lo = __fdividef(sl, cl); else if (sl > 0.f) return false;
-    if (ch > 0.f) hi = __fdividef(sh, ch); else if (sh < 0.f) return false;
-    return true;
+    // The directions seen are the arc [theta0 - alpha, theta0 + alpha] (shorter than 180 degrees); keep its part with z > 0.
+    if (cl > 0.f) {                        // the arc starts in front: it ends in front too (hi finite) or leaves over +90 deg
+        lo = __fdividef(sl, cl);
+        if (ch > 0.f) hi = __fdividef(sh, ch);
+        return true;
+    }
+    if (ch > 0.f) {                        // the arc starts behind the camera and enters the front half over -90 deg
+        hi = __fdividef(sh, ch);
+        return true;
+    }
+    return false;                          // both ends behind: nothing of the disk has z > 0
 }
 
 // The same range when the disk lies strictly in front (cz > r, checked by the caller): tan(theta0 -+ alpha) by the

@@ -1,0 +1,253 @@
+// View-sharded kNN correlation across GPUs: every rank keeps ONLY the clouds of the views it unprojected (features
+// never cross NVLink); what crosses are 8-byte (d2, index) keys and 16-byte result records.  Per refinement iteration
+//
+//   K1  mvt_knn_keys       every rank: exact top-k of ALL queries among its own views -> sorted keys, written in the
+//                          [track shard][level][frame][track][k] layout that all_to_all_single sends as is
+//   C1  all-to-all         rank j receives, for its track shard, the n_ranks candidate lists of every query
+//   K2  mvt_topk_merge     exact global top-k of each query of the shard (global top-k is a subset of the union of the
+//                          local top-k's; (d2, index) is a total order, so the merge is deterministic) -> int32 indices
+//   C2  all-gather         every rank gets the merged index lists of all queries
+//   K3  mvt_corr_from_idx  every rank: correlation + offsets of the neighbours that live in ITS views, zeros elsewhere
+//   C3  all-reduce (sum)   each record has exactly one non-zero contributor, so the sum is exact; every rank ends with
+//                          the full [S, M, levels*k*4] block the (replicated) transformer consumes
+// (mvtracker_b200/dist.py drives this with torch.distributed / NCCL.)  Replaces, for N > 1, the single-GPU fused kernel
+// of mvt_knn.cu; same arithmetic, bit-identical neighbour sets and offsets, identical correlations.
+#include "mvt_search.cuh"
+
+namespace mvt {
+
+struct KeysParams {
+    SearchDev sd[MVT_MAX_LEVELS];
+    long long idx_off[MVT_MAX_LEVELS];
+    int n_levels, B, M, k, n_shards, Ms;
+    const float *query;
+    u64 *out;
+};
+
+// grid: x = blocks of 8 queries over n_shards*Ms padded tracks, y = frame, z = level
+__global__ void __launch_bounds__(256, 4) knn_keys_kernel(const KeysParams p) {
+    __shared__ unsigned char win_tab[32];
+    init_window_table(win_tab);
+    const int lane = threadIdx.x & 31;
+    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (m >= p.n_shards * p.Ms) return;
+    const int b = blockIdx.y, lvl = blockIdx.z, k = p.k;
+    const int shard = m / p.Ms, mm = m - shard * p.Ms;
+    u64 *o = p.out + ((((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm) * k;
+    u64 key = kEmptyKey64;
+    if (m < p.M) {
+        const long long q = (long long)b * p.M + m;
+        const float qx = __ldg(p.query + q * 3), qy = __ldg(p.query + q * 3 + 1), qz = __ldg(p.query + q * 3 + 2);
+        const Group<32> g(lane);
+        TopK tk;
+        const SearchDev &sd = p.sd[lvl];
+        if (sd.raster) raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q);
+        else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
+        key = tk.t;
+        if (key_idx(key) != kNoIdx) key += (u64)p.idx_off[lvl];      // local -> global index (no carry: idx < 2^31)
+        else key = kEmptyKey64;
+    }
+    if (lane < k) o[lane] = key;
+}
+
+// one warp per query: merge n_lists sorted lists of k keys
+__global__ void __launch_bounds__(256) topk_merge_kernel(const u64 *__restrict__ keys, int n_lists, long long Q, int k,
+                                                         int *__restrict__ idx_out, u64 *__restrict__ keys_out) {
+    const int lane = threadIdx.x & 31;
+    const long long q = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (q >= Q) return;
+    const Group<32> g(lane);
+    TopK tk;
+    tk.init();
+    const int total = n_lists * k;
+    for (int t0 = 0; t0 < total; t0 += 32) {
+        const int t = t0 + lane;
+        u64 key = kEmptyKey64;
+        if (t < total) {
+            const int list = t / k, j = t - list * k;
+            key = keys[((size_t)list * Q + q) * k + j];
+        }
+        topk_offer(g, tk, key, k);
+    }
+    if (lane < k) {
+        const int i = key_idx(tk.t);
+        if (idx_out) idx_out[q * k + lane] = (i != kNoIdx) ? i : -1;
+        if (keys_out) keys_out[q * k + lane] = tk.t;
+    }
+}
+
+struct OwnedLevel {
+    const float4 *xyz4;     // [B, Nloc] records of the owned points
+    const void *fvec;       // [B, Nloc, 128]
+    long long lo, hi;       // owned global index range [lo, hi), Nloc = hi - lo
+    long long out_off;
+};
+struct CorrIdxParams {
+    OwnedLevel lv[MVT_MAX_LEVELS];
+    int n_levels, B, M, k, n_shards, Ms;
+    const int *idx;         // [n_shards, n_levels, B, Ms, k] global indices (-1 = missing)
+    const void *targets;    // [B, M, 128]
+    const float *coords;    // [B, M, 3]
+    float *out;
+    long long row_stride;
+    float scale;
+};
+
+// 16 partial sums per lane -> lane L holds the warp total of neighbour L >> 1 (same network as mvt_knn.cu)
+__device__ __forceinline__ float shard_reduce16(float (&pr)[16], int lane) {
+#pragma unroll
+    for (int w = 16, n = 8; n >= 1; w >>= 1, n >>= 1) {
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+            bool hi = lane & w;
+            float send = hi ? pr[i] : pr[i + n], keep = hi ? pr[i + n] : pr[i];
+            pr[i] = keep + __shfl_xor_sync(FULL, send, w);
+        }
+    }
+    return pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxParams p) {
+    const int lane = threadIdx.x & 31;
+    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (m >= p.M) return;
+    const int b = blockIdx.y, lvl = blockIdx.z, k = p.k;
+    const OwnedLevel &L = p.lv[lvl];
+    const long long q = (long long)b * p.M + m;
+    const int shard = m / p.Ms, mm = m - shard * p.Ms;
+    const int *ip = p.idx + ((((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm) * k;
+    const long long gi = (lane < k) ? (long long)__ldg(ip + lane) : -1ll;
+    const bool own = gi >= L.lo && gi < L.hi;
+    const int row = own ? (int)(gi - L.lo) : -1;       // local row of neighbour `lane`
+    const size_t nloc = (size_t)(L.hi - L.lo);
+    float corr_mine;
+    if (!BF16) {
+        const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + lane);
+        const float4 *fv = reinterpret_cast<const float4 *>(L.fvec) + (size_t)b * nloc * 32 + lane;
+        float pr[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            int rj = __shfl_sync(FULL, row, j);
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rj >= 0) f = __ldg(fv + (size_t)rj * 32);
+            pr[j] = fmaf(tg.w, f.w, fmaf(tg.z, f.z, fmaf(tg.y, f.y, tg.x * f.x)));
+        }
+        float tot = shard_reduce16(pr, lane);
+        corr_mine = __shfl_sync(FULL, tot, (2 * lane) & 31);
+    } else {
+        // same summation order as knn_corr_kernel<2, *, 32>: 16 lanes x 8 channels per row, two rows per warp load
+        const uint4 tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
+        const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec) + (size_t)b * nloc * 16 + (lane & 15);
+        const int half = lane >> 4;
+        float pr[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int rj = __shfl_sync(FULL, row, 2 * i + half);
+            uint4 f = make_uint4(0u, 0u, 0u, 0u);
+            if (rj >= 0) f = __ldg(fv + (size_t)rj * 16);
+            const __nv_bfloat162 *x = reinterpret_cast<const __nv_bfloat162 *>(&tgh);
+            const __nv_bfloat162 *y = reinterpret_cast<const __nv_bfloat162 *>(&f);
+            float acc = 0.f;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float2 u = __bfloat1622float2(x[e]), v = __bfloat1622float2(y[e]);
+                acc = fmaf(u.x, v.x, acc);
+                acc = fmaf(u.y, v.y, acc);
+            }
+            pr[i] = acc;
+        }
+#pragma unroll
+        for (int w = 8, n = 4; n >= 1; w >>= 1, n >>= 1) {
+#pragma unroll
+            for (int i = 0; i < n; ++i) {
+                bool hi = lane & w;
+                float send = hi ? pr[i] : pr[i + n], keep = hi ? pr[i + n] : pr[i];
+                pr[i] = keep + __shfl_xor_sync(FULL, send, w);
+            }
+        }
+        float tot = pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
+        corr_mine = __shfl_sync(FULL, tot, ((lane & 1) << 4) | ((lane >> 1) << 1));
+    }
+    if (lane < k) {
+        float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (own) {
+            const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+            const float4 n = __ldg(L.xyz4 + (size_t)b * nloc + row);
+            rec = make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz);
+        }
+        *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = rec;
+    }
+}
+
+}  // namespace mvt
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_offsets, int n_levels, int B,
+                            const float *query, int M, int k, int n_shards, unsigned long long *keys_out, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(searches && index_offsets && query && keys_out, "mvt_knn_keys: null pointer");
+    MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_keys: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
+    MVT_CHECK_ARG(B > 0 && B <= 65535 && M > 0, "mvt_knn_keys: bad shape B=%d M=%d", B, M);
+    MVT_CHECK_ARG(k >= 1 && k <= MVT_MAX_K, "mvt_knn_keys: k must be 1..%d (got %d)", MVT_MAX_K, k);
+    MVT_CHECK_ARG(n_shards >= 1, "mvt_knn_keys: n_shards=%d", n_shards);
+    KeysParams p;
+    p.n_levels = n_levels; p.B = B; p.M = M; p.k = k; p.n_shards = n_shards; p.Ms = (M + n_shards - 1) / n_shards;
+    p.query = query; p.out = (u64 *)keys_out;
+    for (int l = 0; l < n_levels; ++l) {
+        int rc = make_search(&searches[l], B, 0, p.sd[l], "mvt_knn_keys");
+        if (rc) return rc;
+        MVT_CHECK_ARG(index_offsets[l] >= 0 && index_offsets[l] + searches[l].N < 0x7fffffffLL, "mvt_knn_keys: index offset %lld out of range", index_offsets[l]);
+        p.idx_off[l] = index_offsets[l];
+    }
+    for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) { p.sd[l] = p.sd[0]; p.idx_off[l] = 0; }
+    const int padded = p.n_shards * p.Ms;
+    dim3 grid((unsigned)((padded + 7) / 8), (unsigned)B, (unsigned)n_levels);
+    knn_keys_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    MVT_CHECK_LAUNCH("knn_keys");
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_topk_merge(const unsigned long long *keys_in, int n_lists, long long Q, int k, int *idx_out,
+                              unsigned long long *keys_out, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(keys_in && (idx_out || keys_out), "mvt_topk_merge: null pointer");
+    MVT_CHECK_ARG(n_lists >= 1 && Q >= 0 && k >= 1 && k <= MVT_MAX_K, "mvt_topk_merge: bad n_lists=%d Q=%lld k=%d", n_lists, Q, k);
+    if (Q == 0) return MVT_OK;
+    MVT_CHECK_ARG((Q + 7) / 8 < 0x7fffffffLL, "mvt_topk_merge: too many queries");
+    topk_merge_kernel<<<(unsigned)((Q + 7) / 8), 256, 0, (cudaStream_t)stream>>>((const u64 *)keys_in, n_lists, Q, k, idx_out, (u64 *)keys_out);
+    MVT_CHECK_LAUNCH("topk_merge");
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                                 int n_shards, const int *idx, const void *targets, const float *coords, float *out,
+                                 long long out_row_stride, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(levels && idx && targets && coords && out, "mvt_corr_from_idx: null pointer");
+    MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_corr_from_idx: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
+    MVT_CHECK_ARG(B > 0 && B <= 65535 && M > 0, "mvt_corr_from_idx: bad shape B=%d M=%d", B, M);
+    MVT_CHECK_ARG(C == 128, "mvt_corr_from_idx: the sharded path supports C == 128, groups == 1 (got C=%d)", C);
+    MVT_CHECK_ARG(k >= 1 && k <= 16, "mvt_corr_from_idx: k must be 1..16 (got %d)", k);
+    MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_corr_from_idx: feat_dtype %d", feat_dtype);
+    MVT_CHECK_ARG(n_shards >= 1, "mvt_corr_from_idx: n_shards=%d", n_shards);
+    MVT_CHECK_ARG((((uintptr_t)out | (uintptr_t)targets) & 15) == 0 && out_row_stride % 4 == 0, "mvt_corr_from_idx: out/targets must be 16-byte aligned");
+    CorrIdxParams p;
+    p.n_levels = n_levels; p.B = B; p.M = M; p.k = k; p.n_shards = n_shards; p.Ms = (M + n_shards - 1) / n_shards;
+    p.idx = idx; p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride;
+    p.scale = sqrtf((float)C);
+    for (int l = 0; l < n_levels; ++l) {
+        const mvt_owned_level &u = levels[l];
+        MVT_CHECK_ARG(u.xyz4 && u.fvec && u.hi > u.lo && u.lo >= 0, "mvt_corr_from_idx: level %d: bad shard", l);
+        MVT_CHECK_ARG((((uintptr_t)u.xyz4 | (uintptr_t)u.fvec) & 15) == 0 && u.out_offset % 4 == 0, "mvt_corr_from_idx: level %d: 16-byte alignment", l);
+        p.lv[l].xyz4 = (const float4 *)u.xyz4; p.lv[l].fvec = u.fvec; p.lv[l].lo = u.lo; p.lv[l].hi = u.hi; p.lv[l].out_off = u.out_offset;
+    }
+    for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
+    dim3 grid((unsigned)((M + 7) / 8), (unsigned)B, (unsigned)n_levels);
+    if (feat_dtype == MVT_BF16) corr_from_idx_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else corr_from_idx_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    MVT_CHECK_LAUNCH("corr_from_idx");
+    return MVT_OK;
+}

@@ -272,3 +272,63 @@ def knn_gather(where, fvec: torch.Tensor, query: torch.Tensor, return_idx=False)
     check(lib().mvt_knn_gather(C.byref(sr.c), _ptr(fv), _feat_dtype(fv), B, fv.shape[-1], _ptr(q), M, _ptr(out), _ptr(idx),
                                _stream()), "mvt_knn_gather")
     return (out, idx) if return_idx else out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# view-sharded path (one rank's halves of corr_sample; mvtracker_b200/dist.py adds the exchanges)
+# ---------------------------------------------------------------------------------------------------------------------
+EMPTY_KEY = 0x7F8000007FFFFFFF      # (+inf, no index): a missing neighbour in a packed key list
+
+
+def knn_keys(searches: Sequence, index_offsets: Sequence[int], query: torch.Tensor, k: int, n_shards: int = 1,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Exact top-k of every query among this rank's points, for all levels in one launch.
+    -> keys [n_shards, L, B, Ms, k] int64 storage of packed (bits(d2) << 32 | global index), ascending; Ms = ceil(M / n_shards)."""
+    _need_cuda(query, "query")
+    q = _f32c(query)
+    B, M, _ = q.shape
+    L = len(searches)
+    srs = [_as_search(s) for s in searches]
+    arr = (_CSearch * L)(*[s.c for s in srs])
+    offs = (C.c_longlong * L)(*[int(o) for o in index_offsets])
+    Ms = (M + n_shards - 1) // n_shards
+    if out is None:
+        out = torch.empty(n_shards, L, B, Ms, k, device=q.device, dtype=torch.int64)
+    assert out.is_contiguous() and out.numel() == n_shards * L * B * Ms * k and out.dtype == torch.int64
+    check(lib().mvt_knn_keys(arr, offs, L, B, _ptr(q), M, int(k), int(n_shards), _ptr(out), _stream()), "mvt_knn_keys")
+    return out
+
+
+def topk_merge(keys: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """keys [n_lists, Q, k] packed sorted lists -> idx [Q, k] int32 (global indices, -1 = missing) of the merged top-k."""
+    _need_cuda(keys, "keys")
+    assert keys.dtype == torch.int64 and keys.is_contiguous() and keys.dim() == 3
+    n_lists, Q, k = keys.shape
+    if out is None:
+        out = torch.empty(Q, k, device=keys.device, dtype=torch.int32)
+    check(lib().mvt_topk_merge(_ptr(keys), n_lists, Q, k, _ptr(out), None, _stream()), "mvt_topk_merge")
+    return out
+
+
+def corr_from_idx(owned: Sequence, idx: torch.Tensor, targets: torch.Tensor, coords: torch.Tensor, k: int,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """owned: per level (xyz4 [B,Nloc,4], fvec [B,Nloc,C], lo, hi); idx [n_shards, L, B, Ms, k] int32 global indices.
+    -> out [B, M, L*k*4] fp32 with the records of the neighbours owned here, zeros elsewhere."""
+    _need_cuda(targets, "targets"); _need_cuda(idx, "idx")
+    B, M, Cc = targets.shape
+    tg, cq = targets.contiguous(), _f32c(coords)
+    L = len(owned)
+    n_shards = idx.shape[0]
+    assert idx.dtype == torch.int32 and idx.is_contiguous() and idx.shape[1] == L and idx.shape[2] == B and idx.shape[4] == k
+    lv = (_lib.OwnedLevel * L)()
+    for i, (xyz4, fvec, lo, hi) in enumerate(owned):
+        if fvec.dtype != tg.dtype:
+            raise MvtError(f"targets dtype {tg.dtype} != fvec dtype {fvec.dtype}")
+        assert xyz4.is_contiguous() and fvec.is_contiguous() and xyz4.shape[1] == hi - lo
+        lv[i] = _lib.OwnedLevel(xyz4.data_ptr(), fvec.data_ptr(), int(lo), int(hi), i * k * 4)
+    if out is None:
+        out = torch.empty(B, M, L * k * 4, device=tg.device, dtype=torch.float32)
+    assert out.is_contiguous()
+    check(lib().mvt_corr_from_idx(lv, L, B, M, Cc, _feat_dtype(tg), int(k), int(n_shards), _ptr(idx), _ptr(tg), _ptr(cq),
+                                  _ptr(out), out.stride(1), _stream()), "mvt_corr_from_idx")
+    return out

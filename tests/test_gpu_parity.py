@@ -282,6 +282,23 @@ def test_raster_knn_edge_cases(V, Hs, Ws, zero, k):
         check_knn_raster(c, coords, k, skip_invalid=True)     # "intended" filter_invalid: depth <= 0 not searchable
 
 
+@pytest.mark.parametrize("V", [2, 4])
+def test_raster_knn_queries_beside_and_behind_cameras(V):
+    """Random queries all over the camera ring, searched in coarse rasters: the k-th distance is metres, balls reach
+    behind / beside the cameras, and their arc of directions wraps past +-90 and 180 degrees (regression: an arc that
+    started in front of a camera and ended past 180 degrees was declared invisible)."""
+    sc = synth.make_scene(V, 48 * 4, 64 * 4, S=2, C=4, zero_frac=0.1, seed=60 + V, device=DEV)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[1, 2, 3], want_valid=True)
+    g = torch.Generator(device=DEV).manual_seed(61)
+    coords = (torch.rand(2, 1500, 3, device=DEV, generator=g) - 0.5) * torch.tensor([12.0, 12.0, 4.0], device=DEV)
+    E = sc.extrs[0, :, 0]
+    centres = -(E[:, :, :3].transpose(1, 2) @ E[:, :, 3:]).squeeze(-1)
+    coords[:, :500] = centres[torch.arange(500, device=DEV) % V] + 0.8 * torch.randn(2, 500, 3, device=DEV, generator=g)
+    for c in clouds:
+        check_knn_raster(c, coords, 16)
+        check_knn_raster(c, coords, 3, skip_invalid=True)
+
+
 def test_raster_knn_skewed_intrinsics_and_moving_cameras():
     sc = synth.make_scene(3, 40 * 4, 56 * 4, S=3, C=4, zero_frac=0.1, seed=50, device=DEV)
     g = torch.Generator(device=DEV).manual_seed(51)

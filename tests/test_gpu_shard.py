@@ -1,0 +1,78 @@
+"""View-sharded kNN correlation (mvt_shard.cu): the three per-rank kernels, with the exchanges emulated in one process,
+must reproduce the single-GPU fused kernel bit for bit."""
+import numpy as np
+import pytest
+import torch
+
+from mvtracker_b200 import ops, synth
+from mvtracker_b200.dist import track_shard, view_range
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def emulate(sc, coords, targets, world, k, levels=(0, 1, 2, 3)):
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0]
+    V = fm.shape[0]
+    S, M, _ = targets.shape
+    L, Ms = len(levels), track_shard(world, M)
+    ranks = []
+    for r in range(world):
+        v0, v1 = view_range(r, world, V)
+        clouds = ops.cloud_build(fm[v0:v1], dp[v0:v1], K[v0:v1], E[v0:v1], levels=levels, want_spacing=False) if v1 > v0 else []
+        ranks.append((v0, v1, clouds))
+    keys = []
+    for v0, v1, clouds in ranks:
+        if clouds:
+            keys.append(ops.knn_keys(clouds, [v0 * c.H * c.W for c in clouds], coords, k, n_shards=world))
+        else:
+            keys.append(torch.full((world, L, S, Ms, k), ops.EMPTY_KEY, dtype=torch.int64, device=DEV))
+    idx_all = torch.empty(world, L, S, Ms, k, dtype=torch.int32, device=DEV)
+    for j in range(world):      # all-to-all: rank j receives shard j of every rank; then merges
+        recv = torch.stack([keys[r][j] for r in range(world)]).contiguous()
+        idx_all[j] = ops.topk_merge(recv.view(world, L * S * Ms, k)).view(L, S, Ms, k)
+    total = torch.zeros(S, M, L * k * 4, device=DEV)
+    for v0, v1, clouds in ranks:
+        if clouds:
+            owned = [(c.xyz4, c.fvec, v0 * c.H * c.W, v1 * c.H * c.W) for c in clouds]
+            total += ops.corr_from_idx(owned, idx_all, targets, coords, k)
+    return total, idx_all
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_sharded_equals_fused(world, dtype):
+    sc = synth.make_scene(4, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.1, seed=31, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 203, 3, valid=clouds[0].valid[0], dtype=dtype, jitter=0.04)
+    coords[:, :5] += 2.5
+    fused, fidx = ops.knn_corr([(c, c.fvec, 16) for c in clouds], targets, coords, return_idx=True)
+    total, idx_all = emulate(sc, coords, targets, world, 16)
+    Ms = track_shard(world, 203)
+    # idx_all [world, L, S, Ms, k] -> [L, S, M, k]
+    merged = idx_all.permute(1, 2, 0, 3, 4).reshape(4, 3, world * Ms, 16)[:, :, :203]
+    assert torch.equal(merged, fidx)
+    assert torch.equal(total, fused)
+
+
+def test_sharded_small_k_and_oracle():
+    sc = synth.make_scene(3, 40 * 4, 56 * 4, S=2, C=128, zero_frac=0.3, seed=33, device=DEV)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 2], want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 64, 2, valid=clouds[0].valid[0])
+    total, idx_all = emulate(sc, coords, targets, 3, 8, levels=(0, 2))
+    for i, c in enumerate(clouds):
+        ref = oracle.corr_sample(8, c.xyz.cpu().numpy(), c.fvec.cpu().numpy(), targets.cpu().numpy(), coords.cpu().numpy())
+        got = total[:, :, i * 32:(i + 1) * 32].reshape(2, 64, 8, 4).cpu().numpy()
+        assert (got[..., 1:] == ref[..., 1:]).all()
+        assert np.abs(got[..., 0] - ref[..., 0]).max() <= 1e-4 * max(1.0, np.abs(ref[..., 0]).max())
+
+
+def test_shard_argument_errors():
+    from mvtracker_b200._lib import MvtError
+    sc = synth.make_scene(2, 32 * 4, 32 * 4, S=1, C=32, zero_frac=0.0, seed=34, device=DEV)
+    c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0])[0]
+    coords, targets = synth.make_tracks(c.xyz[0], 16, 1, C=32)
+    idx = torch.zeros(1, 1, 1, 16, 16, dtype=torch.int32, device=DEV)
+    with pytest.raises(MvtError, match="C == 128"):
+        ops.corr_from_idx([(c.xyz4, c.fvec, 0, c.xyz4.shape[1])], idx, targets, coords, 16)
