@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--cell-scale", type=float, default=0.0)
     ap.add_argument("--search", default="raster", choices=["raster", "grid"],
                     help="raster: search the depth rasters directly (no index build); grid: hashed grid")
+    ap.add_argument("--dist-mode", default="tracks", choices=["tracks", "views"],
+                    help="N > 1: tracks = replicate the 16-byte records, search per track shard; views = search own views, merge candidates")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
@@ -178,7 +180,9 @@ def run_reference(args):
 
 def config_dict(w, args, world=1):
     return {"parallelism": "1 GPU: fused knn_corr kernel" if world == 1 else
-            f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard, merged indices all-gathered, result records all-reduced (NCCL)","workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
+            (f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
+             f"index lists all-gathered; records of locally owned neighbours all-reduced (NCCL)" if getattr(args, "dist_mode", "tracks") == "tracks" else
+             f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard (two bounded phases), merged indices all-gathered, result records all-reduced (NCCL)"),"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
             "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
@@ -232,6 +236,7 @@ def run_ours(args):
     targets_it = [(base_targets * (1.0 - 0.1 * i)).contiguous() for i in range(iters)]
     width = LEVELS * K_NN * 4
     outs = [torch.empty(S_WINDOW, N, width, device=dev, dtype=torch.float32) for _ in range(iters)]
+    K_all, E_all = K, E
     if world > 1:
         v0, v1 = view_range(rank, world, V)
         fm, dp, K, E = fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous()
@@ -252,7 +257,8 @@ def run_ours(args):
                 grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
             win = WindowClouds(clouds, grids, K_NN, 1, True, False)
         else:
-            win = ShardedWindow.build(fm, dp, K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"])
+            win = ShardedWindow.build(fm, dp, K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
+                                      intrs_all=K_all, extrs_all=E_all, mode=args.dist_mode)
             if ev is not None: ev[1].record()
         if ev is not None: ev[2].record()
         for i in range(iters):
@@ -321,9 +327,9 @@ def run_ours(args):
     cloud_bytes = fm.numel() * esz + dp.numel() * 4 + pts * (C_FEAT * esz + 12)       # SURVEY.md 8d (xyz4 records not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
-                     "what": "fused knn_corr kernel" if world == 1 else "knn_keys + all-to-all + topk_merge + all-gather + corr_from_idx + all-reduce"},
+                     "what": "fused knn_corr kernel" if world == 1 else "search kernels + index all-gather + corr_from_idx + all-reduce (per iteration)"},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6,
-                        "what": "camera_prep + cloud_build (4 levels, one pass)"},
+                        "what": "camera_prep + cloud_build (4 levels, one pass)" + ("" if world == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
     }
     if args.search == "grid" and world == 1:
         kern["grid_build"] = {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0}
@@ -344,7 +350,7 @@ def run_ours(args):
 
     # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------------
     if not args.no_e2e:
-        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if world > 1 else 0)
+        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if world > 1 else 0, K_all, E_all)
         line["e2e"] = e2e
     state["win"] = None
     if sampler:
@@ -358,7 +364,7 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0):
+def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, K_all, E_all):
     """Each step: this rank's inputs pinned host -> device, the public API (N = 1: the drop-in mirror of the reference seam --
     init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat;
     N > 1: mvtracker_b200.dist.ShardedWindow), then every iteration's correlation block -> pinned host."""
@@ -368,6 +374,7 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0):
     from mvtracker_b200.dist import ShardedWindow
     iters, N, V = args.iters, w["N"], w["V"]
     host_in = [t.cpu().pin_memory() for t in (fm, dp, K, E)]
+    host_cam = [t.cpu().pin_memory() for t in (K_all, E_all)]
     host_ct = [(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(coords_it, targets_it)]
     host_out = [torch.empty(S_WINDOW, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
     h2d = sum(t.numel() * t.element_size() for t in host_in) + sum(c.numel() * c.element_size() + t.numel() * t.element_size() for c, t in host_ct)
@@ -383,7 +390,9 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0):
                 blocks.append(dropin.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
                                                          corr_add_neighbor_xyz=False))
         else:
-            win = ShardedWindow.build(fmd, dpd, Kd, Ed, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"])
+            Ka, Ea = [t.to(dev, non_blocking=True) for t in host_cam]
+            win = ShardedWindow.build(fmd, dpd, Kd, Ed, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
+                                      intrs_all=Ka, extrs_all=Ea, mode=args.dist_mode)
             state["win"] = win
         for i in range(iters):
             coords = host_ct[i][0].to(dev, non_blocking=True)

@@ -143,9 +143,17 @@ int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, i
 /* Exact top-k of all queries among THIS rank's points, as sorted packed keys: (bits(d2) << 32) | (index + index_offset),
  * missing = 0x7f8000007fffffff.  searches[l] / index_offsets[l] describe level l (same k on every level).
  * keys_out [n_shards, n_levels, B, Ms, k] with Ms = ceil(M / n_shards): track m goes to shard m / Ms, padded tracks are
- * filled with missing keys -- the layout an all-to-all over track shards sends as is. */
+ * filled with missing keys -- the layout an all-to-all over track shards sends as is.
+ * cap_keys (optional, [n_shards, n_levels, B, Ms] in the same track layout): only points whose squared distance is <= the
+ * cap key's distance part are searched for (an upper bound of the GLOBAL k-th distance obtained from other ranks, so that a
+ * rank whose views do not see the query's surface stops early); fewer than k keys may then come back.
+ * budget > 0: bounded effort -- a query's search gives up once it knows k points and has looked at `budget` candidates; its
+ * list is then k real points (a valid bound), not the exact answer.  exact_out (optional, same layout, bytes): 1 where the list
+ * is exact.  skip (optional, same layout): queries flagged 1 are not searched and their keys in keys_out are left untouched
+ * (second phase over the buffer of the first). */
 int mvt_knn_keys(const mvt_search *searches, const long long *index_offsets, int n_levels, int B,
-                 const float *query, int M, int k, int n_shards, unsigned long long *keys_out, void *stream);
+                 const float *query, int M, int k, int n_shards, const unsigned long long *cap_keys, int budget,
+                 unsigned char *exact_out, const unsigned char *skip, unsigned long long *keys_out, void *stream);
 
 /* Merges n_lists sorted candidate lists per query: keys_in [n_lists, Q, k] -> idx_out [Q, k] int32 (-1 = missing) and /
  * or keys_out [Q, k], ascending (d2, index). */

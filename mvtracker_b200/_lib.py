@@ -78,7 +78,7 @@ def lib():
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
     L.mvt_debug_set_group_width.argtypes = [ci]
-    L.mvt_knn_keys.argtypes = [C.POINTER(Search), C.POINTER(ll), ci, ci, vp, ci, ci, ci, vp, vp]
+    L.mvt_knn_keys.argtypes = [C.POINTER(Search), C.POINTER(ll), ci, ci, vp, ci, ci, ci, vp, ci, vp, vp, vp, vp]
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
     for name in SYMBOLS:

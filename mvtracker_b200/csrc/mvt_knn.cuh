@@ -70,10 +70,12 @@ __device__ __forceinline__ u64 group_sort(const Group<GW> &g, u64 v) {
 
 // The running result of one query: group lane i holds the i-th best key of a sorted top-GW list (kEmptyKey64 = no
 // entry); th = the k-th best, uniform across the group; empty = nothing has been offered yet (uniform).
+// cap: an optional a-priori bound -- only keys below it are ever accepted (th = min(k-th best, cap)); a search that
+// is given the cap of a wider search (other views, an earlier iteration) stops as early as that wider search would.
 struct TopK {
-    u64 t, th;
+    u64 t, th, cap;
     bool empty;
-    __device__ __forceinline__ void init() { t = kEmptyKey64; th = kEmptyKey64; empty = true; }
+    __device__ __forceinline__ void init(u64 cap_key = kEmptyKey64) { t = kEmptyKey64; th = cap_key; cap = cap_key; empty = true; }
     __device__ __forceinline__ bool have_k() const { return th != kEmptyKey64; }
 };
 
@@ -89,7 +91,7 @@ __device__ __forceinline__ int topk_offer(const Group<GW> &g, TopK &tk, u64 key,
     const int n = __popc(m);
     const bool do_sort = tk.empty && m != 0u;
     if (Group<GW>::wany(do_sort)) {
-        u64 sorted = group_sort(g, key);
+        u64 sorted = group_sort(g, key < tk.th ? key : kEmptyKey64);
         if (do_sort) {
             tk.t = sorted;
             tk.empty = false;
@@ -106,7 +108,8 @@ __device__ __forceinline__ int topk_offer(const Group<GW> &g, TopK &tk, u64 key,
         unsigned dm = g.ballot(disp);               // a suffix of the group's lanes (the list is sorted)
         if (disp) tk.t = (g.gl == __ffs(dm) - 1) ? c : up;
     }
-    tk.th = g.shfl(tk.t, k - 1);
+    const u64 kth = g.shfl(tk.t, k - 1);
+    tk.th = kth < tk.cap ? kth : tk.cap;
     return n;
 }
 

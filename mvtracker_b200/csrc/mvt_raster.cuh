@@ -109,13 +109,16 @@ __device__ __forceinline__ void pix_range(float ulo, float uhi, float inv_st, in
 }
 
 // win_tab: shared-memory table of init_window_table.
+// cap: only points whose key is below it are wanted (see TopK).  budget != 0: bounded effort, see below.
+// Returns true when the list is the exact answer (always, unless a budget made the search give up).
 // live = false: the group has no query (padding at the end of a frame's track list); it only takes part in the
 // collectives.  Must be called by all 32 lanes.
 template <int GW>
-__device__ __forceinline__ void raster_search(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
+__device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
                                               bool live, float qx, float qy, float qz, int k, TopK &tk,
-                                              unsigned long long *stats, int qtag = 0) {
-    tk.init();
+                                              unsigned long long *stats, int qtag = 0, u64 cap = kEmptyKey64,
+                                              unsigned budget = 0u) {
+    tk.init(cap);
     const int gl = g.gl;
     const int W = rv.W, H = rv.H, HW = W * H, V = rv.V;
     const float4 *frame = rv.xyz4 + (size_t)s * V * HW;
@@ -195,6 +198,9 @@ __device__ __forceinline__ void raster_search(const Group<GW> &g, const RasterVi
 
     while (true) {
         const bool have_k = tk.have_k();
+        // budget (view-sharded search, phase A): give up once k points are known and `budget` candidates have been
+        // looked at -- the list is then k real points (an upper bound of the k-th best), not the exact answer
+        if (budget != 0u && Group<GW>::wall(have_k && st_cand >= budget)) return false;
         Rect R = whole;      // pixels of my view that can still hold a neighbour
         bool covered;
         if (have_k) {
@@ -277,6 +283,8 @@ __device__ __forceinline__ void raster_search(const Group<GW> &g, const RasterVi
             const unsigned total = g.shfl(incl, GW - 1);
             st_cand += total;
             for (unsigned i0 = 0; Group<GW>::wany(i0 < total); i0 += GW) {
+                // bounded effort: a single pass can be large (a view behind the query gets its whole box at once)
+                if (budget != 0u && i0 >= budget && Group<GW>::wall(tk.have_k())) return false;
                 const unsigned t = i0 + gl;
                 bool valid = t < total;
                 int j = 0;
@@ -322,6 +330,7 @@ __device__ __forceinline__ void raster_search(const Group<GW> &g, const RasterVi
         while (c > 1 && bin < 5) { c >>= 3; ++bin; }       // bins: <2, <16, <128, <1024, <8192, >=8192 candidates
         atomicAdd(stats + 10 + bin, 1ull);
     }
+    return true;
 }
 
 }  // namespace mvt

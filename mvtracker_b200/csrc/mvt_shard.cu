@@ -1,8 +1,13 @@
 // View-sharded kNN correlation across GPUs: every rank keeps ONLY the clouds of the views it unprojected (features
 // never cross NVLink); what crosses are 8-byte (d2, index) keys and 16-byte result records.  Per refinement iteration
 //
-//   K1  mvt_knn_keys       every rank: exact top-k of ALL queries among its own views -> sorted keys, written in the
-//                          [track shard][level][frame][track][k] layout that all_to_all_single sends as is
+//   K0  mvt_knn_keys(budget)  every rank: bounded-effort search of its views: exact where it converges within the budget
+//                          (a rank that sees the query's surface), k real but far points where it does not
+//   C0  all-to-all + K2 merge + all-gather: the k-th best of the union is an upper bound ("cap") of the global k-th
+//                          distance, known to every rank.  Without it a rank whose views do not see a query's surface
+//                          would search out to ITS k-th distance (metres): measured 16x the whole single-GPU kernel.
+//   K1  mvt_knn_keys(caps, skip)  every rank: the queries that did not converge in K0, exactly, within the cap -> sorted keys,
+//                          written in the [track shard][level][frame][track][k] layout that all_to_all_single sends as is
 //   C1  all-to-all         rank j receives, for its track shard, the n_ranks candidate lists of every query
 //   K2  mvt_topk_merge     exact global top-k of each query of the shard (global top-k is a subset of the union of the
 //                          local top-k's; (d2, index) is a total order, so the merge is deterministic) -> int32 indices
@@ -20,6 +25,10 @@ struct KeysParams {
     SearchDev sd[MVT_MAX_LEVELS];
     long long idx_off[MVT_MAX_LEVELS];
     int n_levels, B, M, k, n_shards, Ms;
+    unsigned budget;             // != 0: bounded-effort search (phase A)
+    const u64 *caps;             // [n_shards, n_levels, B, Ms] or null
+    unsigned char *exact_out;    // same layout, or null: 1 = the emitted list is the exact local answer
+    const unsigned char *skip;   // same layout, or null: 1 = leave this query's keys as they are
     const float *query;
     u64 *out;
 };
@@ -33,21 +42,31 @@ __global__ void __launch_bounds__(256, 4) knn_keys_kernel(const KeysParams p) {
     if (m >= p.n_shards * p.Ms) return;
     const int b = blockIdx.y, lvl = blockIdx.z, k = p.k;
     const int shard = m / p.Ms, mm = m - shard * p.Ms;
-    u64 *o = p.out + ((((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm) * k;
+    const size_t qslot = (((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm;
+    u64 *o = p.out + qslot * k;
     u64 key = kEmptyKey64;
+    if (p.skip && p.skip[qslot]) return;          // warp-uniform
+    bool exact = true;
     if (m < p.M) {
         const long long q = (long long)b * p.M + m;
         const float qx = __ldg(p.query + q * 3), qy = __ldg(p.query + q * 3 + 1), qz = __ldg(p.query + q * 3 + 2);
         const Group<32> g(lane);
         TopK tk;
         const SearchDev &sd = p.sd[lvl];
-        if (sd.raster) raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q);
+        // cap: distance-only bound from phase A -- keep every point with d2 <= the bound's d2 (any index: ties stay in)
+        u64 cap = kEmptyKey64;
+        if (p.caps) {
+            const u64 c = __ldg(p.caps + qslot);
+            if ((c >> 32) < 0x7f800000ull) cap = c | 0xffffffffull;      // finite distance; else no bound is known
+        }
+        if (sd.raster) exact = raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q, cap, p.budget);
         else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
         key = tk.t;
         if (key_idx(key) != kNoIdx) key += (u64)p.idx_off[lvl];      // local -> global index (no carry: idx < 2^31)
         else key = kEmptyKey64;
     }
     if (lane < k) o[lane] = key;
+    if (p.exact_out && lane == 0) p.exact_out[qslot] = exact ? 1 : 0;
 }
 
 // one warp per query: merge n_lists sorted lists of k keys
@@ -186,7 +205,9 @@ __global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxPara
 // C ABI
 // ---------------------------------------------------------------------------------------------------------------
 MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_offsets, int n_levels, int B,
-                            const float *query, int M, int k, int n_shards, unsigned long long *keys_out, void *stream) {
+                            const float *query, int M, int k, int n_shards, const unsigned long long *cap_keys,
+                            int budget, unsigned char *exact_out, const unsigned char *skip,
+                            unsigned long long *keys_out, void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(searches && index_offsets && query && keys_out, "mvt_knn_keys: null pointer");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_keys: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
@@ -196,8 +217,11 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     KeysParams p;
     p.n_levels = n_levels; p.B = B; p.M = M; p.k = k; p.n_shards = n_shards; p.Ms = (M + n_shards - 1) / n_shards;
     p.query = query; p.out = (u64 *)keys_out;
+    MVT_CHECK_ARG(budget >= 0, "mvt_knn_keys: budget=%d", budget);
+    p.caps = (const u64 *)cap_keys; p.budget = (unsigned)budget; p.exact_out = exact_out; p.skip = skip;
     for (int l = 0; l < n_levels; ++l) {
         int rc = make_search(&searches[l], B, 0, p.sd[l], "mvt_knn_keys");
+        MVT_CHECK_ARG(!(cap_keys || budget) || p.sd[l].raster, "mvt_knn_keys: caps / budget need the raster search");
         if (rc) return rc;
         MVT_CHECK_ARG(index_offsets[l] >= 0 && index_offsets[l] + searches[l].N < 0x7fffffffLL, "mvt_knn_keys: index offset %lld out of range", index_offsets[l]);
         p.idx_off[l] = index_offsets[l];

@@ -281,9 +281,11 @@ EMPTY_KEY = 0x7F8000007FFFFFFF      # (+inf, no index): a missing neighbour in a
 
 
 def knn_keys(searches: Sequence, index_offsets: Sequence[int], query: torch.Tensor, k: int, n_shards: int = 1,
-             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+             out: Optional[torch.Tensor] = None, caps: Optional[torch.Tensor] = None, budget: int = 0,
+             exact_out: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Exact top-k of every query among this rank's points, for all levels in one launch.
-    -> keys [n_shards, L, B, Ms, k] int64 storage of packed (bits(d2) << 32 | global index), ascending; Ms = ceil(M / n_shards)."""
+    -> keys [n_shards, L, B, Ms, k] int64 storage of packed (bits(d2) << 32 | global index), ascending; Ms = ceil(M / n_shards).
+    caps [n_shards, L, B, Ms] int64: per-query bound keys; budget / exact_out / skip (uint8, same layout): see mvt_knn_keys."""
     _need_cuda(query, "query")
     q = _f32c(query)
     B, M, _ = q.shape
@@ -295,15 +297,26 @@ def knn_keys(searches: Sequence, index_offsets: Sequence[int], query: torch.Tens
     if out is None:
         out = torch.empty(n_shards, L, B, Ms, k, device=q.device, dtype=torch.int64)
     assert out.is_contiguous() and out.numel() == n_shards * L * B * Ms * k and out.dtype == torch.int64
-    check(lib().mvt_knn_keys(arr, offs, L, B, _ptr(q), M, int(k), int(n_shards), _ptr(out), _stream()), "mvt_knn_keys")
+    if caps is not None:
+        assert caps.dtype == torch.int64 and caps.is_contiguous() and caps.numel() == n_shards * L * B * Ms
+    for t in (exact_out, skip):
+        if t is not None:
+            assert t.dtype == torch.uint8 and t.is_contiguous() and t.numel() == n_shards * L * B * Ms
+    check(lib().mvt_knn_keys(arr, offs, L, B, _ptr(q), M, int(k), int(n_shards), _ptr(caps), int(budget), _ptr(exact_out),
+                             _ptr(skip), _ptr(out), _stream()), "mvt_knn_keys")
     return out
 
 
-def topk_merge(keys: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """keys [n_lists, Q, k] packed sorted lists -> idx [Q, k] int32 (global indices, -1 = missing) of the merged top-k."""
+def topk_merge(keys: torch.Tensor, out: Optional[torch.Tensor] = None, keys_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """keys [n_lists, Q, k] packed sorted lists -> idx [Q, k] int32 (global indices, -1 = missing) of the merged top-k.
+    keys_out [Q, k] int64: receive the merged keys instead (then no index tensor is made and keys_out is returned)."""
     _need_cuda(keys, "keys")
     assert keys.dtype == torch.int64 and keys.is_contiguous() and keys.dim() == 3
     n_lists, Q, k = keys.shape
+    if keys_out is not None:
+        assert keys_out.dtype == torch.int64 and keys_out.is_contiguous() and keys_out.numel() == Q * k
+        check(lib().mvt_topk_merge(_ptr(keys), n_lists, Q, k, None, _ptr(keys_out), _stream()), "mvt_topk_merge")
+        return keys_out
     if out is None:
         out = torch.empty(Q, k, device=keys.device, dtype=torch.int32)
     check(lib().mvt_topk_merge(_ptr(keys), n_lists, Q, k, _ptr(out), None, _stream()), "mvt_topk_merge")
@@ -332,3 +345,9 @@ def corr_from_idx(owned: Sequence, idx: torch.Tensor, targets: torch.Tensor, coo
     check(lib().mvt_corr_from_idx(lv, L, B, M, Cc, _feat_dtype(tg), int(k), int(n_shards), _ptr(idx), _ptr(tg), _ptr(cq),
                                   _ptr(out), out.stride(1), _stream()), "mvt_corr_from_idx")
     return out
+
+
+def full_cloud(level: int, xyz4: torch.Tensor, cam: torch.Tensor, V: int, H: int, W: int, stride: float) -> Cloud:
+    """Search-only Cloud over replicated raster records [S, V*H*W, 4] (no features): what mvtracker_b200.dist searches
+    in "tracks" mode."""
+    return Cloud(level, None, None, None, None, xyz4, cam, V, H, W, stride)

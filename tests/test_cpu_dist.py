@@ -26,15 +26,28 @@ class NumpyBackend:
     EMPTY_KEY = EMPTY
 
     @staticmethod
+    def camera_prep(intrs, extrs):
+        return None
+
+    @staticmethod
+    def full_cloud(level, xyz4, cam, V, H, W, stride):
+        return FakeCloud(xyz4, None, H, W)
+
+    @staticmethod
     def _d2(p, q):
         d = p.astype(np.float32) - q.astype(np.float32)
         return ((d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]).astype(np.float32)
 
-    def knn_keys(self, clouds, offs, coords, k, n_shards, out):
+    def knn_keys(self, clouds, offs, coords, k, n_shards, out, caps=None, budget=0, exact_out=None, skip=None):
+        # budget: "gave up" is emulated for every third query, which then returns every other point of the exact list
+        # (k real points = a valid bound) and must be redone in the second phase
         S, M, _ = coords.shape
         Ms = track_shard(n_shards, M)
-        out.fill_(EMPTY)
+        if skip is None:
+            out.fill_(EMPTY)
         o = out.numpy()
+        sk = None if skip is None else skip.numpy().reshape(n_shards, -1, S, Ms)
+        ex = None if exact_out is None else exact_out.numpy().reshape(n_shards, -1, S, Ms)
         q = coords.numpy()
         for l, (c, off) in enumerate(zip(clouds, offs)):
             pts = c.xyz4.numpy()[..., :3]
@@ -44,13 +57,28 @@ class NumpyBackend:
                 keys.sort(axis=1)
                 kk = min(k, keys.shape[1])
                 for m in range(M):
-                    o[m // Ms, l, s, m % Ms, :kk] = keys[m, :kk]
+                    if sk is not None and sk[m // Ms, l, s, m % Ms]:
+                        continue
+                    o[m // Ms, l, s, m % Ms, :] = EMPTY
+                    row = keys[m, :kk]
+                    gave_up = budget and (m + s + l) % 3 == 0
+                    if ex is not None:
+                        ex[m // Ms, l, s, m % Ms] = 0 if gave_up else 1
+                    if gave_up:
+                        row = keys[m, 0:2 * kk:2]
+                    if caps is not None:
+                        cap = int(caps.view(n_shards, -1, S, Ms)[m // Ms, l, s, m % Ms])
+                        row = row[(row >> 32) <= (cap >> 32)]
+                    o[m // Ms, l, s, m % Ms, :len(row)] = row
         return out
 
-    def topk_merge(self, keys, out):
+    def topk_merge(self, keys, out=None, keys_out=None):
         a = keys.numpy()                               # [n_lists, Q, k]
         n, Q, k = a.shape
         merged = np.sort(a.transpose(1, 0, 2).reshape(Q, n * k), axis=1)[:, :k]
+        if keys_out is not None:
+            keys_out.copy_(torch.from_numpy(merged.copy()))
+            return keys_out
         idx = (merged & 0xFFFFFFFF).astype(np.int64)
         idx[merged == EMPTY] = -1
         out.copy_(torch.from_numpy(idx.astype(np.int32)))
@@ -89,7 +117,7 @@ def _scene(seed=5, V=5, S=2, Hs=(6, 3), Ws=(8, 4), C=8, M=11):
     return levels, coords, targets, V
 
 
-def _worker(rank, world, port, k, V, ret):
+def _worker(rank, world, port, k, V, mode, ret):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -98,19 +126,23 @@ def _worker(rank, world, port, k, V, ret):
         clouds = [FakeCloud(torch.from_numpy(x[:, v0 * H * W:v1 * H * W].copy()), torch.from_numpy(f[:, v0 * H * W:v1 * H * W].copy()), H, W)
                   for x, f, H, W in levels] if v1 > v0 else []
         win = ShardedWindow(clouds, v0, v1, V, k=k, backend=NumpyBackend(), n_levels=len(levels))
+        if mode == "tracks":
+            win.mode = "tracks"
+            win._replicate_records(torch.empty(v1 - v0, coords.shape[0], 1, levels[0][2], levels[0][3]), None, None, 4, [0, 1])
         out = win.corr(torch.from_numpy(targets), torch.from_numpy(coords))
         ret[rank] = out.numpy().copy()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,V", [(2, 5), (3, 5), (3, 2)])      # (3, 2): the last rank owns no view at all
-def test_sharded_window_over_gloo(world, V):
+@pytest.mark.parametrize("mode", ["tracks", "views"])
+@pytest.mark.parametrize("world,V", [(2, 4), (3, 5), (3, 2)])      # (3, 5): uneven shards; (3, 2): a rank without views
+def test_sharded_window_over_gloo(world, V, mode):
     k = 4
-    port = 29500 + os.getpid() % 2000 + 10 * world + V
+    port = 29500 + os.getpid() % 2000 + 10 * world + V + (100 if mode == "tracks" else 0)
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(world, port, k, V, ret), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, k, V, mode, ret), nprocs=world, join=True)
     # single-process answer with the same stand-in arithmetic
     levels, coords, targets, V = _scene(V=V)
     be = NumpyBackend()
@@ -119,7 +151,7 @@ def test_sharded_window_over_gloo(world, V):
     keys = torch.empty(1, len(levels), S, M, k, dtype=torch.int64)
     be.knn_keys(clouds, [0] * len(levels), torch.from_numpy(coords), k, 1, keys)
     idx = torch.empty(len(levels) * S * M, k, dtype=torch.int32)
-    be.topk_merge(keys.view(1, -1, k), idx)
+    be.topk_merge(keys.view(1, -1, k), out=idx)
     want = torch.empty(S, M, len(levels) * k * 4)
     be.corr_from_idx([(c.xyz4, c.fvec, 0, c.xyz4.shape[1]) for c in clouds], idx.view(1, len(levels), S, M, k),
                      torch.from_numpy(targets), torch.from_numpy(coords), k, want)

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-def emulate(sc, coords, targets, world, k, levels=(0, 1, 2, 3)):
+def emulate(sc, coords, targets, world, k, levels=(0, 1, 2, 3), two_phase=True):
     fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0]
     V = fm.shape[0]
     S, M, _ = targets.shape
@@ -22,12 +22,28 @@ def emulate(sc, coords, targets, world, k, levels=(0, 1, 2, 3)):
         v0, v1 = view_range(r, world, V)
         clouds = ops.cloud_build(fm[v0:v1], dp[v0:v1], K[v0:v1], E[v0:v1], levels=levels, want_spacing=False) if v1 > v0 else []
         ranks.append((v0, v1, clouds))
-    keys = []
-    for v0, v1, clouds in ranks:
-        if clouds:
-            keys.append(ops.knn_keys(clouds, [v0 * c.H * c.W for c in clouds], coords, k, n_shards=world))
-        else:
-            keys.append(torch.full((world, L, S, Ms, k), ops.EMPTY_KEY, dtype=torch.int64, device=DEV))
+    empty = torch.full((world, L, S, Ms, k), ops.EMPTY_KEY, dtype=torch.int64, device=DEV)
+
+    flags = [torch.ones(world, L, S, Ms, dtype=torch.uint8, device=DEV) for _ in ranks]
+    bufs = [empty.clone() for _ in ranks]
+
+    def all_keys(caps=None, budget=0):
+        for (v0, v1, clouds), fl, buf in zip(ranks, flags, bufs):
+            if clouds:
+                ops.knn_keys(clouds, [v0 * c.H * c.W for c in clouds], coords, k, n_shards=world, caps=caps, budget=budget,
+                             exact_out=fl if budget else None, skip=fl if caps is not None else None, out=buf)
+        return bufs
+
+    caps = None
+    if two_phase:      # phase A: bounded-effort searches -> merged k-th best = cap of the global k-th distance
+        keys = all_keys(budget=two_phase)
+        caps = torch.empty(world, L * S * Ms, dtype=torch.int64, device=DEV)
+        for j in range(world):
+            recv = torch.stack([keys[r][j] for r in range(world)]).contiguous()
+            merged = torch.empty(L * S * Ms, k, dtype=torch.int64, device=DEV)
+            ops.topk_merge(recv.view(world, L * S * Ms, k), keys_out=merged)
+            caps[j] = merged[:, k - 1]
+    keys = all_keys(caps=caps)
     idx_all = torch.empty(world, L, S, Ms, k, dtype=torch.int32, device=DEV)
     for j in range(world):      # all-to-all: rank j receives shard j of every rank; then merges
         recv = torch.stack([keys[r][j] for r in range(world)]).contiguous()
@@ -42,13 +58,14 @@ def emulate(sc, coords, targets, world, k, levels=(0, 1, 2, 3)):
 
 @pytest.mark.parametrize("world", [1, 2, 3, 5])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_sharded_equals_fused(world, dtype):
+@pytest.mark.parametrize("two_phase", [0, 1, 150, 100000])     # 0: one uncapped phase; else the phase-A budget
+def test_sharded_equals_fused(world, dtype, two_phase):
     sc = synth.make_scene(4, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.1, seed=31, device=DEV, dtype=dtype)
     clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
     coords, targets = synth.make_tracks(clouds[0].xyz[0], 203, 3, valid=clouds[0].valid[0], dtype=dtype, jitter=0.04)
     coords[:, :5] += 2.5
     fused, fidx = ops.knn_corr([(c, c.fvec, 16) for c in clouds], targets, coords, return_idx=True)
-    total, idx_all = emulate(sc, coords, targets, world, 16)
+    total, idx_all = emulate(sc, coords, targets, world, 16, two_phase=two_phase)
     Ms = track_shard(world, 203)
     # idx_all [world, L, S, Ms, k] -> [L, S, M, k]
     merged = idx_all.permute(1, 2, 0, 3, 4).reshape(4, 3, world * Ms, 16)[:, :, :203]
