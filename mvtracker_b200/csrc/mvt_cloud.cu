@@ -55,6 +55,12 @@ __global__ void camera_prep_kernel(const float *__restrict__ intrs, const float 
 // ---------------------------------------------------------------------------------------------------------------
 // cloud_build
 // ---------------------------------------------------------------------------------------------------------------
+#ifndef MVT_CLOUD_BATCH
+#define MVT_CLOUD_BATCH 32
+#endif
+#ifndef MVT_CLOUD_MINB
+#define MVT_CLOUD_MINB 4
+#endif
 constexpr int TH = 8;     // tile rows   (level-0 pixels) = one level-3 pixel high
 constexpr int TW = 32;    // tile cols   (level-0 pixels) = four level-3 pixels wide
 constexpr int CC = 32;    // channels per smem chunk
@@ -163,7 +169,7 @@ __device__ __forceinline__ void emit_point(const CloudParams &p, const float *cm
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) cloud_build_kernel(const CloudParams p) {
+__global__ void __launch_bounds__(256, MVT_CLOUD_MINB) cloud_build_kernel(const CloudParams p) {
     __shared__ float t0[CC * S0];
     __shared__ float t1[CC * S1];
     __shared__ float t2[CC * S2];
@@ -252,11 +258,17 @@ __global__ void __launch_bounds__(256) cloud_build_kernel(const CloudParams p) {
 
     for (int c0 = 0; c0 < C; c0 += CC) {
         __syncthreads();   // previous chunk's readers of t0..t3 are done
-#pragma unroll 8
-        for (int c = 0; c < CC; ++c) {
-            float val = 0.f;
-            if (inside && c0 + c < C) val = to_f<T>(fm[(size_t)(c0 + c) * HW + pix]);
-            t0[c * S0 + tid] = val;
+        // all loads of a batch are issued before the first shared-memory store: MVT_CLOUD_BATCH x 4 B per thread in flight
+#pragma unroll
+        for (int cb = 0; cb < CC; cb += MVT_CLOUD_BATCH) {
+            float val[MVT_CLOUD_BATCH];
+#pragma unroll
+            for (int c = 0; c < MVT_CLOUD_BATCH; ++c) {
+                val[c] = 0.f;
+                if (inside && c0 + cb + c < C) val[c] = to_f<T>(__ldg(fm + (size_t)(c0 + cb + c) * HW + pix));
+            }
+#pragma unroll
+            for (int c = 0; c < MVT_CLOUD_BATCH; ++c) t0[(cb + c) * S0 + tid] = val[c];
         }
         __syncthreads();
         if (need1) pool_tile<T>(t0, S0, 32, t1, S1, 16, 64);

@@ -34,7 +34,8 @@ struct KeysParams {
 };
 
 // grid: x = blocks of 8 queries over n_shards*Ms padded tracks, y = frame, z = level
-__global__ void __launch_bounds__(256, 4) knn_keys_kernel(const KeysParams p) {
+template <bool RASTER_ONLY>
+__global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
     __shared__ unsigned char win_tab[32];
     init_window_table(win_tab);
     const int lane = threadIdx.x & 31;
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(256, 4) knn_keys_kernel(const KeysParams p) {
             const u64 c = __ldg(p.caps + qslot);
             if ((c >> 32) < 0x7f800000ull) cap = c | 0xffffffffull;      // finite distance; else no bound is known
         }
-        if (sd.raster) exact = raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q, cap, p.budget);
+        if (RASTER_ONLY || sd.raster) exact = raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q, cap, p.budget);
         else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
         key = tk.t;
         if (key_idx(key) != kNoIdx) key += (u64)p.idx_off[lvl];      // local -> global index (no carry: idx < 2^31)
@@ -229,7 +230,10 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) { p.sd[l] = p.sd[0]; p.idx_off[l] = 0; }
     const int padded = p.n_shards * p.Ms;
     dim3 grid((unsigned)((padded + 7) / 8), (unsigned)B, (unsigned)n_levels);
-    knn_keys_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    bool all_raster = true;
+    for (int l = 0; l < n_levels; ++l) all_raster = all_raster && p.sd[l].raster;
+    if (all_raster) knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else knn_keys_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_keys");
     return MVT_OK;
 }
