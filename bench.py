@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument("--cell-scale", type=float, default=0.0)
     ap.add_argument("--search", default="raster", choices=["raster", "grid"],
                     help="raster: search the depth rasters directly (no index build); grid: hashed grid")
-    ap.add_argument("--dist-mode", default="tracks", choices=["tracks", "views"],
+    ap.add_argument("--dist-mode", default="p2p", choices=["p2p", "tracks", "views"],
                     help="N > 1: tracks = replicate the 16-byte records, search per track shard; views = search own views, merge candidates")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
@@ -182,6 +182,8 @@ def config_dict(w, args, world=1):
     return {"parallelism": "1 GPU: fused knn_corr kernel" if world == 1 else
             (f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
              f"index lists all-gathered; records of locally owned neighbours all-reduced (NCCL)" if getattr(args, "dist_mode", "tracks") == "tracks" else
+             f"{world} GPUs: views sharded for the cloud build (features stay local); point records, index lists and result records are stored by the producing kernels "
+             f"straight into every rank's buffers (symmetric memory, NVSwitch multicast stores), two signal-pad barriers per iteration, no NCCL on the data path" if args.dist_mode == "p2p" else
              f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard (two bounded phases), merged indices all-gathered, result records all-reduced (NCCL)"),"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
             "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),

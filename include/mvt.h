@@ -41,6 +41,7 @@ extern "C" {
 #define MVT_MAX_K 32
 #define MVT_CAM_STRIDE 48  /* floats per camera record written by mvt_camera_prep */
 #define MVT_MAX_VIEWS 32
+#define MVT_MAX_PEERS 8     /* GPUs of one node sharing a symmetric buffer */
 
 int mvt_version(void);
 const char *mvt_last_error(void);
@@ -125,10 +126,14 @@ typedef struct mvt_corr_level {
  * out: fp32; row (b,m) starts at out + (b*M+m)*out_row_stride; level l writes k*D floats at its out_offset, neighbour j
  * at j*D:  [corr_0..corr_{G-1}, dx,dy,dz (add_offset), x,y,z (add_xyz)],  D = G + 3*add_offset + 3*add_xyz,
  * corr_g = <target_g, nbr_g> / sqrt(C/G)  (mvtracker.py:832-846).
- * idx_out: optional [n_levels,B,M,k] int32. */
+ * idx_out: optional [n_levels,B,M,k] int32.
+ * idx_hint: optional [n_levels,B,M,k] int32 -- ANY k points of the same clouds per query, typically the idx_out of the
+ * previous refinement iteration (tracks move by centimetres between iterations, mvtracker.py:392): the largest distance
+ * to them bounds the k-th best, so the raster search starts with a tight radius.  A warm start only: results are exact
+ * and identical with or without it (entries < 0 or of unsearchable points disable it for that query).  May alias idx_out. */
 int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                  const void *targets, const float *coords, int add_offset, int add_xyz,
-                 float *out, long long out_row_stride, int *idx_out, void *stream);
+                 float *out, long long out_row_stride, const int *idx_hint, int *idx_out, void *stream);
 
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
@@ -173,6 +178,37 @@ typedef struct mvt_owned_level {
 int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
                       int n_shards, const int *idx, const void *targets, const float *coords, float *out,
                       long long out_row_stride, void *stream);
+
+/* ---- fused compute + exchange over NVLink (symmetric memory; csrc/mvt_shard.cu, csrc/mvt_cloud.cu) ----------------------
+ * The three exchanges of the track-sharded path are folded into the kernels that produce the data: every 16-byte unit
+ * (a point record, four neighbour indices, a [corr,dx,dy,dz] record) has exactly ONE producer, which stores it into the
+ * same buffer on every rank -- through the NVSwitch multicast address (one multimem.st) when the buffer has one, else
+ * through the per-rank peer mappings.  No NCCL call, no reduction, no zero fill; the caller puts a cross-rank barrier
+ * (symmetric-memory signal pads, ~6 us) between producer and consumer kernels. */
+typedef struct mvt_peers {
+    void *mc;                    /* multicast address of the buffer, or NULL */
+    void *ptr[MVT_MAX_PEERS];    /* the buffer as mapped for rank 0..n-1 (ptr[own rank] = the local address) */
+    int n;                       /* ranks; 16-byte aligned addresses */
+} mvt_peers;
+
+/* mvt_cloud_build that ALSO stores the {x,y,z,depth} records of this rank's views into the replicated
+ * [S, V_total*H_l*W_l, 4] buffers records[l] of every rank (views view_offset .. view_offset+V-1). */
+int mvt_cloud_build_shared(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                           int V, int S, int C, int H, int W, float stride, int depth_avg,
+                           const mvt_level_out *levels, int level_mask, const mvt_peers *records /* [MVT_MAX_LEVELS] */,
+                           int view_offset, int V_total, void *stream);
+
+/* Exact kNN of THIS rank's track shard (query [B, Ms, 3]) over the replicated records; the int32 index lists are stored
+ * into idx_all [n_shards, n_levels, B, Ms, k] of every rank at shard `shard`.  k must be a multiple of 4. */
+int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int B, const float *query, int Ms, int k,
+                       int shard, int n_shards, const mvt_peers *idx_all, void *stream);
+
+/* mvt_corr_from_idx whose records go to out [B, M, n_levels*k*4] of every rank: a record is stored by the rank that owns
+ * the neighbour's features; records of missing neighbours (index < 0) are stored as zeros by rank `shard` for its own
+ * track shard.  After the barrier every rank holds the complete block. */
+int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                             int n_shards, int shard, const int *idx, const void *targets, const float *coords,
+                             const mvt_peers *out, long long out_row_stride, void *stream);
 
 /* Debug / profiling: per-segment grid parameters copied out for inspection.
  * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */

@@ -13,7 +13,8 @@ CAM_STRIDE, MAX_VIEWS = 48, 32
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
            "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
-           "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx")
+           "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
+           "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared")
 
 
 class LevelOut(C.Structure):
@@ -39,6 +40,10 @@ class CorrLevel(C.Structure):
 class OwnedLevel(C.Structure):
     _fields_ = [("xyz4", C.c_void_p), ("fvec", C.c_void_p), ("lo", C.c_longlong), ("hi", C.c_longlong),
                 ("out_offset", C.c_longlong)]
+
+
+class Peers(C.Structure):
+    _fields_ = [("mc", C.c_void_p), ("ptr", C.c_void_p * 8), ("n", C.c_int)]
 
 
 class MvtError(RuntimeError):
@@ -73,12 +78,15 @@ def lib():
     L.mvt_grid_workspace_bytes.restype = C.c_size_t
     L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
     L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
-    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, vp, vp]
+    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, vp, vp, vp]
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
     L.mvt_debug_set_group_width.argtypes = [ci]
     L.mvt_knn_keys.argtypes = [C.POINTER(Search), C.POINTER(ll), ci, ci, vp, ci, ci, ci, vp, ci, vp, vp, vp, vp]
+    L.mvt_cloud_build_shared.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, C.POINTER(Peers), ci, ci, vp]
+    L.mvt_knn_idx_shared.argtypes = [C.POINTER(Search), ci, ci, vp, ci, ci, ci, ci, C.POINTER(Peers), vp]
+    L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll, vp]
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
     for name in SYMBOLS:

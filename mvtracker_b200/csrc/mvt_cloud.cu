@@ -80,6 +80,8 @@ struct CloudParams {
     void *fvec[4];
     unsigned char *valid[4];
     float *spacing[4];
+    PeersDev rec[4];       // replicated record buffers [S, V_total*H_l*W_l] of every rank (n == 0: not shared)
+    int view_off, V_total;
 };
 
 template <typename T> __device__ __forceinline__ float to_f(T v);
@@ -160,6 +162,9 @@ __device__ __forceinline__ void emit_point(const CloudParams &p, const float *cm
         o[0] = X; o[1] = Y; o[2] = Z;
     }
     if (p.xyz4[lvl]) p.xyz4[lvl][pt] = make_float4(X, Y, Z, depth);
+    if (p.rec[lvl].n)      // the search records of this view, straight into every rank's copy of the fused cloud
+        store_all(p.rec[lvl], ((size_t)s * p.V_total + (size_t)(p.view_off + v)) * Hl * Wl + (size_t)gy * Wl + gx,
+                  make_float4(X, Y, Z, depth));
     bool ok = depth > 0.f;
     if (p.valid[lvl]) p.valid[lvl][pt] = ok ? 1 : 0;
     if (ok && depth < 3.0e38f) {
@@ -320,9 +325,10 @@ MVT_EXPORT int mvt_camera_prep(const float *intrs, const float *extrs, int n, fl
     return MVT_OK;
 }
 
-MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
-                               int V, int S, int C, int H, int W, float stride, int depth_avg,
-                               const mvt_level_out *levels, int level_mask, void *stream) {
+static int cloud_build_impl(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                            int V, int S, int C, int H, int W, float stride, int depth_avg,
+                            const mvt_level_out *levels, int level_mask, const mvt_peers *records, int view_offset,
+                            int V_total, void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(depths && cam && levels, "mvt_cloud_build: null pointer");
     MVT_CHECK_ARG(V > 0 && S > 0 && C > 0 && H > 0 && W > 0, "mvt_cloud_build: bad shape V=%d S=%d C=%d H=%d W=%d", V, S, C, H, W);
@@ -351,6 +357,15 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
         }
     }
     MVT_CHECK_ARG(!any_f || fmaps, "mvt_cloud_build: fmaps is null but a feature output was requested");
+    p.view_off = view_offset; p.V_total = V_total;
+    for (int l = 0; l < 4; ++l) {
+        p.rec[l] = peers_dev(nullptr);
+        if (records && ((level_mask >> l) & 1)) {
+            MVT_CHECK_ARG(records[l].n >= 1 && records[l].n <= MVT_MAX_PEERS, "mvt_cloud_build_shared: level %d: %d ranks", l, records[l].n);
+            MVT_CHECK_ARG(view_offset >= 0 && view_offset + V <= V_total, "mvt_cloud_build_shared: views %d..%d outside 0..%d", view_offset, view_offset + V, V_total);
+            p.rec[l] = peers_dev(&records[l]);
+        }
+    }
     cudaStream_t st = (cudaStream_t)stream;
     if (any_sp) {
         int n = S * 2;
@@ -364,4 +379,20 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
     else cloud_build_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
     MVT_CHECK_LAUNCH("cloud_build");
     return MVT_OK;
+}
+
+MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                               int V, int S, int C, int H, int W, float stride, int depth_avg,
+                               const mvt_level_out *levels, int level_mask, void *stream) {
+    return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, nullptr, 0, V,
+                            stream);
+}
+
+MVT_EXPORT int mvt_cloud_build_shared(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
+                                      int V, int S, int C, int H, int W, float stride, int depth_avg,
+                                      const mvt_level_out *levels, int level_mask, const mvt_peers *records,
+                                      int view_offset, int V_total, void *stream) {
+    MVT_CHECK_ARG(records, "mvt_cloud_build_shared: null records");
+    return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, records,
+                            view_offset, V_total, stream);
 }

@@ -41,6 +41,33 @@ constexpr int kMaxGridDim = 1023;   // 10 bits per axis in the packed cell key
 constexpr int kMaxJobs = 8;
 constexpr int kCamStride = MVT_CAM_STRIDE;   // floats per (view, frame) camera record
 
+// The same 16-byte-record buffer on every rank of the node (symmetric memory): stores go to all ranks at once through
+// the NVSwitch multicast address when there is one (one multimem.st per record), else to each rank's mapping in turn.
+struct PeersDev {
+    float4 *mc;
+    float4 *ptr[MVT_MAX_PEERS];
+    int n;      // 0 = not shared (nothing is stored)
+};
+__device__ __forceinline__ void store_all(const PeersDev &P, size_t i, float4 v) {
+    if (P.mc) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(P.mc + i), "f"(v.x), "f"(v.y),
+                     "f"(v.z), "f"(v.w)
+                     : "memory");
+    } else {
+        for (int r = 0; r < P.n; ++r) P.ptr[r][i] = v;
+    }
+}
+__host__ inline PeersDev peers_dev(const mvt_peers *u) {
+    PeersDev d;
+    d.mc = nullptr; d.n = 0;
+    for (int r = 0; r < MVT_MAX_PEERS; ++r) d.ptr[r] = nullptr;
+    if (u) {
+        d.mc = (float4 *)u->mc; d.n = u->n;
+        for (int r = 0; r < u->n && r < MVT_MAX_PEERS; ++r) d.ptr[r] = (float4 *)u->ptr[r];
+    }
+    return d;
+}
+
 // Per-segment grid parameters, written on device by grid_plan.
 struct __align__(16) GridSeg {
     float ox, oy, oz, h;

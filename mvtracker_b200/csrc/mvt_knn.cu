@@ -70,6 +70,7 @@ struct CorrParams {
     float *out;
     long long row_stride;
     int *idx_out;
+    const int *idx_hint;   // [n_levels,B,M,k] or null: any k points of the same clouds (e.g. last iteration's neighbours)
     float scale;      // sqrt(C/G)
     int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4)
 };
@@ -193,7 +194,27 @@ __global__ void __launch_bounds__(256, MVT_CORR_MINB) knn_corr_kernel(const Corr
     const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
 
     TopK tk;
-    if (RASTER_ONLY || L.sd.raster) raster_search<GW>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q);
+    // warm start: the largest distance to k known points of this cloud bounds the k-th best -> cap of the search
+    u64 cap = kEmptyKey64;
+    if (p.idx_hint && (RASTER_ONLY || L.sd.raster)) {
+        unsigned bits = 0xffffffffu;
+        if (gl < k) {
+            const int hi = __ldg(p.idx_hint + (((long long)lvl * p.B + b) * p.M + m) * k + gl);
+            if (hi >= 0 && hi < L.sd.N) {
+                const float4 hp = __ldg(L.sd.rv.xyz4 + (size_t)b * L.sd.N + hi);
+                const float hd = dist2(hp.x, hp.y, hp.z, qx, qy, qz);
+                const bool usable = L.sd.rv.skip_invalid ? (hp.w > 0.f) : !(hp.w < 0.f);
+                if (usable && hd == hd) bits = __float_as_uint(hd);
+            }
+        } else {
+            bits = 0u;
+        }
+        // group maximum (all lanes take part)
+#pragma unroll
+        for (int o = GW / 2; o; o >>= 1) bits = max(bits, g.shfl_xor(bits, o));
+        if (bits < 0x7f800000u) cap = ((u64)bits << 32) | 0xffffffffull;
+    }
+    if (RASTER_ONLY || L.sd.raster) raster_search<GW>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap);
     else if (GW == 32) knn_search(L.sd.g, b, qx, qy, qz, k, lane, tk);
     const int bi = key_idx(tk.t);       // group lane j < k: the j-th neighbour
 
@@ -402,7 +423,7 @@ MVT_EXPORT int mvt_knn(const mvt_search *search, int B, const float *query, int 
 
 MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                             const void *targets, const float *coords, int add_offset, int add_xyz,
-                            float *out, long long out_row_stride, int *idx_out, void *stream) {
+                            float *out, long long out_row_stride, const int *idx_hint, int *idx_out, void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(levels && targets && coords && out, "mvt_knn_corr: null pointer");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_corr: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
@@ -413,7 +434,7 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     CorrParams p;
     p.n_levels = n_levels; p.B = B; p.M = M; p.C = C; p.G = G;
     p.add_offset = add_offset ? 1 : 0; p.add_xyz = add_xyz ? 1 : 0;
-    p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride; p.idx_out = idx_out;
+    p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride; p.idx_out = idx_out; p.idx_hint = idx_hint;
     p.scale = sqrtf((float)C / (float)G);
     const int D = G + 3 * p.add_offset + 3 * p.add_xyz;
     bool fast = (C == 128 && G == 1);
@@ -426,7 +447,7 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
         MVT_CHECK_ARG(u.k >= 1 && u.k <= MVT_MAX_K, "mvt_knn_corr: level %d bad k=%d", l, u.k);
         MVT_CHECK_ARG(u.k <= u.search.N, "mvt_knn_corr: k should be less than or equal to N (level %d: k=%d N=%d)", l, u.k,
                       u.search.N);   // mvtracker.py:785
-        MVT_CHECK_ARG(idx_out == nullptr || u.k == levels[0].k, "mvt_knn_corr: idx_out needs the same k on every level");
+        MVT_CHECK_ARG((idx_out == nullptr && idx_hint == nullptr) || u.k == levels[0].k, "mvt_knn_corr: idx_out / idx_hint need the same k on every level");
         int rc = make_search(&u.search, B, p.add_offset || p.add_xyz, p.lv[l].sd, "mvt_knn_corr");
         if (rc) return rc;
         p.lv[l].fvec = u.fvec; p.lv[l].k = u.k; p.lv[l].out_off = u.out_offset;

@@ -31,6 +31,8 @@ struct KeysParams {
     const unsigned char *skip;   // same layout, or null: 1 = leave this query's keys as they are
     const float *query;
     u64 *out;
+    PeersDev idx_peers;          // n != 0: store int32 index lists into idx_all of every rank instead of keys into `out`
+    int out_shard, out_shards;   // ... at track shard out_shard of out_shards
 };
 
 // grid: x = blocks of 8 queries over n_shards*Ms padded tracks, y = frame, z = level
@@ -44,7 +46,7 @@ __global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
     const int b = blockIdx.y, lvl = blockIdx.z, k = p.k;
     const int shard = m / p.Ms, mm = m - shard * p.Ms;
     const size_t qslot = (((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm;
-    u64 *o = p.out + qslot * k;
+    u64 *o = p.out ? p.out + qslot * k : nullptr;
     u64 key = kEmptyKey64;
     if (p.skip && p.skip[qslot]) return;          // warp-uniform
     bool exact = true;
@@ -66,8 +68,20 @@ __global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
         if (key_idx(key) != kNoIdx) key += (u64)p.idx_off[lvl];      // local -> global index (no carry: idx < 2^31)
         else key = kEmptyKey64;
     }
-    if (lane < k) o[lane] = key;
+    if (o && lane < k) o[lane] = key;
     if (p.exact_out && lane == 0) p.exact_out[qslot] = exact ? 1 : 0;
+    if (p.idx_peers.n) {
+        // four indices per 16-byte store; lane j < k/4 stores neighbours 4j..4j+3 to every rank
+        const int i = (key == kEmptyKey64) ? -1 : key_idx(key);
+        const int src = (4 * lane) & 31;
+        const int i0 = __shfl_sync(FULL, i, src), i1 = __shfl_sync(FULL, i, src + 1);
+        const int i2 = __shfl_sync(FULL, i, src + 2), i3 = __shfl_sync(FULL, i, src + 3);
+        if (lane < (k >> 2)) {
+            const size_t slot = (((size_t)p.out_shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm;
+            store_all(p.idx_peers, slot * (size_t)(k >> 2) + lane,
+                      make_float4(__int_as_float(i0), __int_as_float(i1), __int_as_float(i2), __int_as_float(i3)));
+        }
+    }
 }
 
 // one warp per query: merge n_lists sorted lists of k keys
@@ -111,6 +125,8 @@ struct CorrIdxParams {
     float *out;
     long long row_stride;
     float scale;
+    PeersDev out_peers;     // n != 0: records go to `out` of every rank (row_stride in floats, same on every rank)
+    int shard;              // this rank's track shard (it stores the zero records of missing neighbours)
 };
 
 // 16 partial sums per lane -> lane L holds the warp total of neighbour L >> 1 (same network as mvt_knn.cu)
@@ -141,6 +157,14 @@ __global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxPara
     const bool own = gi >= L.lo && gi < L.hi;
     const int row = own ? (int)(gi - L.lo) : -1;       // local row of neighbour `lane`
     const size_t nloc = (size_t)(L.hi - L.lo);
+    if (!__any_sync(FULL, own)) {      // none of this query's neighbours lives here: no target row, no gather
+        if (lane < k) {
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.out_peers.n == 0) *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = z;
+            else if (gi < 0 && shard == p.shard) store_all(p.out_peers, (size_t)((q * p.row_stride + L.out_off) >> 2) + lane, z);
+        }
+        return;
+    }
     float corr_mine;
     if (!BF16) {
         const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + lane);
@@ -196,7 +220,11 @@ __global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxPara
             const float4 n = __ldg(L.xyz4 + (size_t)b * nloc + row);
             rec = make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz);
         }
-        *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = rec;
+        if (p.out_peers.n == 0) {
+            *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = rec;
+        } else if (own || (gi < 0 && shard == p.shard)) {     // exactly one rank stores each record
+            store_all(p.out_peers, (size_t)((q * p.row_stride + L.out_off) >> 2) + lane, rec);
+        }
     }
 }
 
@@ -220,6 +248,7 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     p.query = query; p.out = (u64 *)keys_out;
     MVT_CHECK_ARG(budget >= 0, "mvt_knn_keys: budget=%d", budget);
     p.caps = (const u64 *)cap_keys; p.budget = (unsigned)budget; p.exact_out = exact_out; p.skip = skip;
+    p.idx_peers = peers_dev(nullptr); p.out_shard = 0; p.out_shards = 1;
     for (int l = 0; l < n_levels; ++l) {
         int rc = make_search(&searches[l], B, 0, p.sd[l], "mvt_knn_keys");
         MVT_CHECK_ARG(!(cap_keys || budget) || p.sd[l].raster, "mvt_knn_keys: caps / budget need the raster search");
@@ -250,11 +279,13 @@ MVT_EXPORT int mvt_topk_merge(const unsigned long long *keys_in, int n_lists, lo
     return MVT_OK;
 }
 
-MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
-                                 int n_shards, const int *idx, const void *targets, const float *coords, float *out,
-                                 long long out_row_stride, void *stream) {
+static int corr_from_idx_impl(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                              int n_shards, const int *idx, const void *targets, const float *coords, float *out,
+                              long long out_row_stride, const mvt_peers *out_peers, int shard, void *stream) {
     using namespace mvt;
-    MVT_CHECK_ARG(levels && idx && targets && coords && out, "mvt_corr_from_idx: null pointer");
+    MVT_CHECK_ARG(levels && idx && targets && coords && (out || out_peers), "mvt_corr_from_idx: null pointer");
+    MVT_CHECK_ARG(!out_peers || (out_peers->n >= 1 && out_peers->n <= MVT_MAX_PEERS && shard >= 0 && shard < n_shards),
+                  "mvt_corr_from_idx_shared: bad peers / shard");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_corr_from_idx: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
     MVT_CHECK_ARG(B > 0 && B <= 65535 && M > 0, "mvt_corr_from_idx: bad shape B=%d M=%d", B, M);
     MVT_CHECK_ARG(C == 128, "mvt_corr_from_idx: the sharded path supports C == 128, groups == 1 (got C=%d)", C);
@@ -266,6 +297,7 @@ MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, in
     p.n_levels = n_levels; p.B = B; p.M = M; p.k = k; p.n_shards = n_shards; p.Ms = (M + n_shards - 1) / n_shards;
     p.idx = idx; p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride;
     p.scale = sqrtf((float)C);
+    p.out_peers = peers_dev(out_peers); p.shard = shard;
     for (int l = 0; l < n_levels; ++l) {
         const mvt_owned_level &u = levels[l];
         MVT_CHECK_ARG(u.xyz4 && u.fvec && u.hi > u.lo && u.lo >= 0, "mvt_corr_from_idx: level %d: bad shard", l);
@@ -277,5 +309,46 @@ MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, in
     if (feat_dtype == MVT_BF16) corr_from_idx_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     else corr_from_idx_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("corr_from_idx");
+    return MVT_OK;
+}
+
+MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                                 int n_shards, const int *idx, const void *targets, const float *coords, float *out,
+                                 long long out_row_stride, void *stream) {
+    return corr_from_idx_impl(levels, n_levels, B, M, C, feat_dtype, k, n_shards, idx, targets, coords, out, out_row_stride,
+                              nullptr, 0, stream);
+}
+
+MVT_EXPORT int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                                        int n_shards, int shard, const int *idx, const void *targets, const float *coords,
+                                        const mvt_peers *out, long long out_row_stride, void *stream) {
+    MVT_CHECK_ARG(out, "mvt_corr_from_idx_shared: null out");
+    return corr_from_idx_impl(levels, n_levels, B, M, C, feat_dtype, k, n_shards, idx, targets, coords,
+                              (float *)out->ptr[shard < MVT_MAX_PEERS && shard >= 0 ? shard : 0], out_row_stride, out, shard, stream);
+}
+
+MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int B, const float *query, int Ms, int k,
+                                  int shard, int n_shards, const mvt_peers *idx_all, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(searches && query && idx_all, "mvt_knn_idx_shared: null pointer");
+    MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_idx_shared: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
+    MVT_CHECK_ARG(B > 0 && B <= 65535 && Ms > 0, "mvt_knn_idx_shared: bad shape B=%d Ms=%d", B, Ms);
+    MVT_CHECK_ARG(k >= 4 && k <= MVT_MAX_K && k % 4 == 0, "mvt_knn_idx_shared: k must be a multiple of 4 in 4..%d (got %d)", MVT_MAX_K, k);
+    MVT_CHECK_ARG(idx_all->n >= 1 && idx_all->n <= MVT_MAX_PEERS && shard >= 0 && shard < n_shards, "mvt_knn_idx_shared: bad peers / shard");
+    KeysParams p;
+    p.n_levels = n_levels; p.B = B; p.M = Ms; p.k = k; p.n_shards = 1; p.Ms = Ms;
+    p.query = query; p.out = nullptr;
+    p.caps = nullptr; p.budget = 0u; p.exact_out = nullptr; p.skip = nullptr;
+    p.idx_peers = peers_dev(idx_all); p.out_shard = shard; p.out_shards = n_shards;
+    for (int l = 0; l < n_levels; ++l) {
+        int rc = make_search(&searches[l], B, 0, p.sd[l], "mvt_knn_idx_shared");
+        if (rc) return rc;
+        MVT_CHECK_ARG(p.sd[l].raster, "mvt_knn_idx_shared: needs the raster search");
+        p.idx_off[l] = 0;
+    }
+    for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) { p.sd[l] = p.sd[0]; p.idx_off[l] = 0; }
+    dim3 grid((unsigned)((Ms + 7) / 8), (unsigned)B, (unsigned)n_levels);
+    knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    MVT_CHECK_LAUNCH("knn_idx_shared");
     return MVT_OK;
 }

@@ -29,6 +29,40 @@ import torch
 import torch.distributed as dist
 
 
+class SharedBuffer:
+    """A tensor in symmetric memory (same size on every rank of the node) + the addresses the kernels store through:
+    the NVSwitch multicast address when the allocation has one, and every rank's peer mapping."""
+
+    def __init__(self, shape, dtype, device, group=None):
+        import os
+        import torch.distributed._symmetric_memory as symm
+        from ._lib import Peers
+        self.t = symm.empty(*shape, dtype=dtype, device=device)
+        self.h = symm.rendezvous(self.t, dist.group.WORLD if group is None else group)
+        world, rank = self.h.world_size, self.h.rank
+        ptrs = list(self.h.buffer_ptrs)
+        off = self.t.data_ptr() - ptrs[rank]
+        self.peers = Peers()
+        self.peers.n = world
+        for r in range(world):
+            self.peers.ptr[r] = ptrs[r] + off
+        mc = int(getattr(self.h, "multicast_ptr", 0) or 0)
+        self.multicast = bool(mc) and not os.environ.get("MVT_NO_MULTICAST")
+        self.peers.mc = (mc + off) if self.multicast else None
+
+    def barrier(self):
+        """Cross-rank barrier on the current stream (signal pads): everything stored before it, by any rank, is visible after."""
+        self.h.barrier(channel=0)
+
+
+def symmetric_memory_available() -> bool:
+    try:
+        import torch.distributed._symmetric_memory as symm  # noqa: F401
+        return dist.is_initialized() and dist.get_backend() == "nccl"
+    except Exception:
+        return False
+
+
 def _all_to_all(recv: torch.Tensor, send: torch.Tensor, group=None):
     """Equal-split all-to-all along dim 0.  NCCL: all_to_all_single.  gloo has no all-to-all (CPU tests only):
     all-gather and slice -- same result, plumbing only."""
@@ -85,9 +119,15 @@ class ShardedWindow:
             from . import ops as backend
         if mode is None:
             mode = "tracks" if intrs_all is not None else "views"
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if mode == "p2p" and (world == 1 or V_total < world or not symmetric_memory_available()):
+            mode = "tracks"         # needs >= 2 ranks, a view on every rank and symmetric memory
         Vloc = fmaps_local.shape[0]
         levels = list(levels)
         clouds = []
+        if mode == "p2p":
+            return cls._build_p2p(fmaps_local, depths_local, intrs_local, extrs_local, v0, V_total, stride, levels, k, group,
+                                  backend, reuse, intrs_all, extrs_all)
         if Vloc > 0:
             clouds = backend.cloud_build(fmaps_local, depths_local, intrs_local, extrs_local, stride=stride, levels=levels,
                                          want_spacing=False, reuse=None if reuse is None else reuse.clouds)
@@ -100,6 +140,42 @@ class ShardedWindow:
         elif mode != "views":
             raise ValueError(mode)
         return win
+
+    @classmethod
+    def _build_p2p(cls, fmaps_local, depths_local, intrs_local, extrs_local, v0, V_total, stride, levels, k, group, backend, reuse,
+                   intrs_all, extrs_all):
+        """mode "p2p": cloud_build stores the 16-byte records of its views straight into every rank's replicated cloud
+        (symmetric memory, multicast stores) -- no all-gather, no copy."""
+        be = backend
+        Vloc, S, H, W = fmaps_local.shape[0], fmaps_local.shape[1], fmaps_local.shape[3], fmaps_local.shape[4]
+        dev = fmaps_local.device
+        win = cls([], v0, v0 + Vloc, V_total, k, group, be, n_levels=len(levels))
+        win.mode = "p2p"
+        if reuse is not None and reuse.mode == "p2p":
+            win._bufs = reuse._bufs
+        shared = {}
+        for l in levels:
+            hw = (H >> l) * (W >> l)
+            shared[l] = win._shared(f"full{l}", (S, V_total * hw, 4), torch.float32, dev)
+        first = win._shared("full%d" % levels[0], None, None, None)
+        first.barrier()           # every rank is done reading the previous window's records
+        win.clouds = be.cloud_build(fmaps_local, depths_local, intrs_local, extrs_local, stride=stride, levels=levels,
+                                    want_spacing=False, reuse=None if (reuse is None or not reuse.clouds) else reuse.clouds,
+                                    shared_records={l: shared[l].peers for l in levels}, view_offset=v0, V_total=V_total)
+        first.barrier()           # ... and every rank's records have arrived everywhere
+        cam_all = be.camera_prep(intrs_all, extrs_all)
+        win.full = [be.full_cloud(l, shared[l].t, cam_all, V_total, H >> l, W >> l, float(stride) * (1 << l)) for l in levels]
+        return win
+
+    def _shared(self, name, shape, dtype, device):
+        key = "shared:" + name
+        b = self._bufs.get(key)
+        if shape is None:
+            return b
+        if b is None or tuple(b.t.shape) != tuple(shape) or b.t.dtype != dtype:
+            b = SharedBuffer(shape, dtype, device, self.group)      # collective: every rank allocates the same buffers
+            self._bufs[key] = b
+        return b
 
     def _replicate_records(self, fmaps_local, intrs_all, extrs_all, stride, levels):
         """All-gather the raster records of every level -> self.full[l]: search structure over all V views."""
@@ -155,6 +231,8 @@ class ShardedWindow:
         dev = targets.device
         if self.mode == "tracks":
             return self._corr_tracks(targets, coords, out, mark)
+        if self.mode == "p2p":
+            return self._corr_p2p(targets, coords, out, mark)
         keys = self._buf("keys", (N, L, S, Ms, k), torch.int64, dev)
         recv = self._buf("recv", (N, L, S, Ms, k), torch.int64, dev) if N > 1 else keys
         offs = [self.v0 * c.H * c.W for c in self.clouds]
@@ -241,3 +319,34 @@ class ShardedWindow:
             dist.all_reduce(out, op=dist.ReduceOp.SUM, group=self.group)
         mark()
         return out
+
+    def _corr_p2p(self, targets, coords, out, mark):
+        """mode "p2p": the exchanges are stores into peer memory issued by the producing kernels (multicast when the
+        switch offers it); two ~6 us cross-rank barriers per iteration replace the NCCL collectives."""
+        be, N, k, L, r = self.be, self.world, self.k, self.levels, self.rank
+        S, M, _ = targets.shape
+        Ms = track_shard(N, M)
+        dev = targets.device
+        lo, hi = r * Ms, min((r + 1) * Ms, M)
+        mine = self._buf("coords_mine", (S, Ms, 3), torch.float32, dev)
+        if hi > lo:
+            mine[:, :hi - lo].copy_(coords[:, lo:hi])
+        if hi - lo < Ms:
+            mine[:, max(hi - lo, 0):].copy_(coords[:, :1])
+        idx_all = self._shared("idx_all", (N, L, S, Ms, k), torch.int32, dev)
+        flip = 1 - self._bufs.get("flip", 1)       # two result buffers alternate: a rank may still be reading the last one
+        self._bufs["flip"] = flip
+        res = self._shared(f"out{flip}", (S, M, L * k * 4), torch.float32, dev)
+        be.knn_idx_shared(self.full, mine, k, r, N, idx_all.peers)
+        mark()
+        idx_all.barrier()
+        mark()
+        owned = [(c.xyz4, c.fvec, self.v0 * c.H * c.W, self.v1 * c.H * c.W) for c in self.clouds]
+        be.corr_from_idx_shared(owned, idx_all.t, targets, coords, k, r, res.peers, res.t.stride(1))
+        mark()
+        res.barrier()
+        mark()
+        if out is not None:
+            out.copy_(res.t)
+            return out
+        return res.t

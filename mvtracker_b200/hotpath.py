@@ -21,6 +21,8 @@ class WindowClouds:
         self.k, self.groups, self.add_offset, self.add_xyz = k, groups, add_offset, add_xyz
         self.D = groups + 3 * bool(add_offset) + 3 * bool(add_xyz)
         self.width = len(clouds) * k * self.D
+        self.warm_start = False     # True: iteration i+1 starts its searches from iteration i's neighbours (exact either way; no gain measured when tracks move ~ the k-NN radius per iteration)
+        self._idx = None            # [levels, S, N, k] int32 of the last corr() call on these clouds
 
     @classmethod
     def build(cls, fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0, 1, 2, 3), k=16, groups=1,
@@ -42,8 +44,15 @@ class WindowClouds:
     def corr(self, targets: torch.Tensor, coords: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """targets [S,N,C], coords [S,N,3] -> [S,N,width]."""
         levels = [(sr, c.fvec, self.k) for sr, c in zip(self.searches, self.clouds)]
+        hint = idx = None
+        if self.warm_start and self.grids is None:
+            shape = (len(levels), targets.shape[0], targets.shape[1], self.k)
+            if self._idx is not None and tuple(self._idx.shape) == shape:
+                hint = idx = self._idx
+            else:
+                idx = self._idx = torch.empty(shape, device=targets.device, dtype=torch.int32)
         return ops.knn_corr(levels, targets, coords, groups=self.groups, add_offset=self.add_offset, add_xyz=self.add_xyz,
-                            out=out)
+                            out=out, idx_hint=hint, idx_out=idx)
 
     def feature_init(self, frame: int, query_xyz: torch.Tensor) -> torch.Tensor:
         """Nearest level-0 point's feature for each query of `frame` (mvtracker.py:627-643).  query_xyz [n,3] -> [n,C]."""

@@ -60,10 +60,13 @@ class Cloud:
 
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
                 want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None,
-                reuse: Optional[Sequence["Cloud"]] = None) -> List[Cloud]:
+                reuse: Optional[Sequence["Cloud"]] = None, shared_records=None, view_offset: int = 0,
+                V_total: Optional[int] = None) -> List[Cloud]:
     """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass.
     reuse: Clouds of an earlier call with the same shapes / levels / dtype whose buffers are overwritten in place (no
-    allocation in steady state, e.g. one set of buffers per sliding window)."""
+    allocation in steady state, e.g. one set of buffers per sliding window).
+    shared_records {level: _lib.Peers}: also store the 16-byte records of these views into the replicated
+    [S, V_total*H_l*W_l, 4] buffers of every rank, views view_offset.. (mvt_cloud_build_shared)."""
     _need_cuda(fmaps, "fmaps"); _need_cuda(depths, "depths")
     V, S, Cc, H, W = fmaps.shape
     depths = depths.reshape(V, S, H, W)
@@ -115,8 +118,16 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         mask |= 1 << l
         clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
                             float(stride) * (1 << l)))
-    check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
-                                int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
+    if shared_records is None:
+        check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
+                                    int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
+    else:
+        recs = (_lib.Peers * _lib.MAX_LEVELS)()
+        for l in levels:
+            recs[l] = shared_records[l]
+        check(lib().mvt_cloud_build_shared(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
+                                           int(depth_interp_mode == "avg"), outs, mask, recs, int(view_offset),
+                                           int(V if V_total is None else V_total), _stream()), "mvt_cloud_build_shared")
     return clouds
 
 
@@ -223,10 +234,13 @@ def knn(where, query: torch.Tensor, k: int, idx_dtype=torch.int64, want_dist=Tru
 
 
 def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, groups=1, add_offset=True, add_xyz=False,
-             out: Optional[torch.Tensor] = None, return_idx=False):
+             out: Optional[torch.Tensor] = None, return_idx=False, idx_hint: Optional[torch.Tensor] = None,
+             idx_out: Optional[torch.Tensor] = None):
     """levels: sequence of (where, fvec [B,N,C], k) with where = Grid | Cloud | Search.
     -> out [B, M, sum_l k_l*D] fp32 (level-major columns, the layout of torch.cat(fcorrs, -1) at mvtracker.py:374),
-    D = groups + 3*add_offset + 3*add_xyz."""
+    D = groups + 3*add_offset + 3*add_xyz.
+    idx_hint [L,B,M,k] int32: warm start (any k points per query, e.g. the previous iteration's idx); idx_out: buffer that
+    receives the neighbour indices (may be the same tensor as idx_hint)."""
     _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
     B, M, Cc = targets.shape
     tg = targets.contiguous()
@@ -250,11 +264,14 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
         out = torch.empty(B, M, off, device=tg.device, dtype=torch.float32)
     row_stride = out.stride(1)
     assert out.shape[0] == B and out.shape[1] == M and out.stride(2) == 1 and out.stride(0) == M * row_stride
-    idx = None
-    if return_idx:
+    idx = idx_out
+    if return_idx and idx is None:
         idx = torch.empty(n, B, M, int(levels[0][2]), device=tg.device, dtype=torch.int32)
+    for t in (idx, idx_hint):
+        if t is not None:
+            assert t.dtype == torch.int32 and t.is_contiguous() and t.numel() == n * B * M * int(levels[0][2])
     check(lib().mvt_knn_corr(lv, n, B, M, Cc, int(groups), _feat_dtype(tg), _ptr(tg), _ptr(cq), int(bool(add_offset)),
-                             int(bool(add_xyz)), _ptr(out), row_stride, _ptr(idx), _stream()), "mvt_knn_corr")
+                             int(bool(add_xyz)), _ptr(out), row_stride, _ptr(idx_hint), _ptr(idx), _stream()), "mvt_knn_corr")
     return (out, idx) if return_idx else out
 
 
@@ -351,3 +368,31 @@ def full_cloud(level: int, xyz4: torch.Tensor, cam: torch.Tensor, V: int, H: int
     """Search-only Cloud over replicated raster records [S, V*H*W, 4] (no features): what mvtracker_b200.dist searches
     in "tracks" mode."""
     return Cloud(level, None, None, None, None, xyz4, cam, V, H, W, stride)
+
+
+def knn_idx_shared(searches: Sequence, query: torch.Tensor, k: int, shard: int, n_shards: int, peers) -> None:
+    """Exact kNN of this rank's track shard (query [B, Ms, 3]); index lists stored into idx_all of every rank (peers)."""
+    _need_cuda(query, "query")
+    q = _f32c(query)
+    B, Ms, _ = q.shape
+    srs = [_as_search(s) for s in searches]
+    arr = (_CSearch * len(srs))(*[s.c for s in srs])
+    check(lib().mvt_knn_idx_shared(arr, len(srs), B, _ptr(q), Ms, int(k), int(shard), int(n_shards), C.byref(peers), _stream()),
+          "mvt_knn_idx_shared")
+
+
+def corr_from_idx_shared(owned: Sequence, idx: torch.Tensor, targets: torch.Tensor, coords: torch.Tensor, k: int, shard: int,
+                         peers, row_stride: int) -> None:
+    """corr_from_idx whose records are stored into the [B, M, L*k*4] block of every rank (peers)."""
+    _need_cuda(targets, "targets"); _need_cuda(idx, "idx")
+    B, M, Cc = targets.shape
+    tg, cq = targets.contiguous(), _f32c(coords)
+    L = len(owned)
+    assert idx.dtype == torch.int32 and idx.is_contiguous() and idx.shape[1] == L and idx.shape[2] == B and idx.shape[4] == k
+    lv = (_lib.OwnedLevel * L)()
+    for i, (xyz4, fvec, lo, hi) in enumerate(owned):
+        if fvec.dtype != tg.dtype:
+            raise MvtError(f"targets dtype {tg.dtype} != fvec dtype {fvec.dtype}")
+        lv[i] = _lib.OwnedLevel(xyz4.data_ptr(), fvec.data_ptr(), int(lo), int(hi), i * k * 4)
+    check(lib().mvt_corr_from_idx_shared(lv, L, B, M, Cc, _feat_dtype(tg), int(k), int(idx.shape[0]), int(shard), _ptr(idx),
+                                         _ptr(tg), _ptr(cq), C.byref(peers), int(row_stride), _stream()), "mvt_corr_from_idx_shared")

@@ -232,6 +232,37 @@ def test_corr_half_warp_groups_identical(dtype, k):
     assert (ib[0].cpu().numpy() == oi).all()
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_corr_warm_start_is_exact(dtype):
+    """idx_hint (previous iteration's neighbours, or garbage) only bounds the first radius: outputs must not change."""
+    sc = synth.make_scene(3, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.2, seed=37, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 257, 3, valid=clouds[0].valid[0], dtype=dtype, jitter=0.03)
+    coords[:, :6] += 1.5
+    lv = [(c, c.fvec, 16) for c in clouds]
+    cold, idx0 = ops.knn_corr(lv, targets, coords, return_idx=True)
+    g = torch.Generator(device=DEV).manual_seed(38)
+    moved = coords + 0.02 * torch.randn(coords.shape, device=DEV, generator=g)
+    want, widx = ops.knn_corr(lv, targets, moved, return_idx=True)
+    # (a) hint = last iteration's neighbours, written back in place
+    buf = idx0.clone()
+    got = ops.knn_corr(lv, targets, moved, idx_hint=buf, idx_out=buf)
+    assert torch.equal(got, want) and torch.equal(buf, widx)
+    # (b) a useless hint: random points, some missing (-1), some out of range
+    junk = torch.randint(-5, 400, idx0.shape, device=DEV, generator=g, dtype=torch.int32)
+    junk[0, :, ::3] = 10 ** 9
+    got, gidx = ops.knn_corr(lv, targets, moved, idx_hint=junk, return_idx=True)
+    assert torch.equal(got, want) and torch.equal(gidx, widx)
+    # (c) the window driver warm-starts by itself
+    from mvtracker_b200.hotpath import WindowClouds
+    win = WindowClouds(clouds, None, 16, 1, True, False)
+    win.warm_start = True
+    assert torch.equal(win.corr(targets, coords), cold)
+    assert torch.equal(win.corr(targets, moved), want)
+    win.warm_start = False
+    assert torch.equal(win.corr(targets, moved), want)
+
+
 def test_knn_gather_feature_init():
     sc = synth.make_scene(3, 40 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=24, device=DEV)
     c = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0], want_valid=True)[0]

@@ -36,7 +36,8 @@ for _ in range(3):
 torch.cuda.synchronize(); dist.barrier()
 print(f"rank {rank}: sharded output equals the single-GPU fused kernel: {torch.equal(out, want)}", flush=True)
 names = (["phaseA(keys+a2a+merge+gather)", "knn_keys", "all_to_all", "topk_merge", "all_gather", "corr_from_idx", "all_reduce"] if mode == "views"
-         else ["search", "keys->idx", "all_gather", "corr_from_idx", "all_reduce"])
+         else ["search", "keys->idx", "all_gather", "corr_from_idx", "all_reduce"] if mode == "tracks"
+         else ["search+idx stores", "barrier", "corr_from_idx+record stores", "barrier"])
 acc = [0.0] * len(names)
 R = 10
 for _ in range(R):
