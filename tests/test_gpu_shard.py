@@ -93,3 +93,66 @@ def test_shard_argument_errors():
     idx = torch.zeros(1, 1, 1, 16, 16, dtype=torch.int32, device=DEV)
     with pytest.raises(MvtError, match="C == 128"):
         ops.corr_from_idx([(c.xyz4, c.fvec, 0, c.xyz4.shape[1])], idx, targets, coords, 16)
+
+
+def _peers(tensors):
+    """mvt_peers over plain device buffers of ONE process (no multicast address): every emulated rank's copy."""
+    from mvtracker_b200._lib import Peers
+    p = Peers()
+    p.n = len(tensors)
+    p.mc = None
+    for r, t in enumerate(tensors):
+        p.ptr[r] = t.data_ptr()
+    return p
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_peer_store_kernels_equal_fused(world, dtype):
+    """The "p2p" mode's three kernels (cloud_build_shared, knn_idx_shared, corr_from_idx_shared) with every rank's
+    symmetric buffer emulated by a private buffer in this process: each rank's copy must equal the fused kernel's result."""
+    V, S, M, k, L = 4, 3, 203, 16, 4
+    sc = synth.make_scene(V, 48 * 4, 64 * 4, S=S, C=128, zero_frac=0.1, seed=41, device=DEV, dtype=dtype)
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0]
+    clouds = ops.cloud_build(fm, dp, K, E, levels=range(L), want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], M, S, valid=clouds[0].valid[0], dtype=dtype, jitter=0.04)
+    coords[:, :5] += 2.5
+    fused, fidx = ops.knn_corr([(c, c.fvec, k) for c in clouds], targets, coords, return_idx=True)
+
+    H, W = fm.shape[3], fm.shape[4]
+    recs = [[torch.full((S, V * (H >> l) * (W >> l), 4), float("nan"), device=DEV) for l in range(L)] for _ in range(world)]
+    local = []
+    for r in range(world):
+        v0, v1 = view_range(r, world, V)
+        if v1 > v0:
+            shared = {l: _peers([recs[j][l] for j in range(world)]) for l in range(L)}
+            local.append(ops.cloud_build(fm[v0:v1], dp[v0:v1], K[v0:v1], E[v0:v1], levels=range(L), want_spacing=False,
+                                         shared_records=shared, view_offset=v0, V_total=V))
+        else:
+            local.append([])
+    for r in range(world):
+        for l in range(L):
+            assert torch.equal(recs[r][l], clouds[l].xyz4)          # every rank holds the whole window's records
+
+    cam_all = ops.camera_prep(K, E)
+    Ms = track_shard(world, M)
+    idx_all = [torch.full((world, L, S, Ms, k), -7, dtype=torch.int32, device=DEV) for _ in range(world)]
+    for r in range(world):
+        full = [ops.full_cloud(l, recs[r][l], cam_all, V, H >> l, W >> l, 4.0 * (1 << l)) for l in range(L)]
+        lo, hi = r * Ms, min((r + 1) * Ms, M)
+        mine = coords[:, :1].repeat(1, Ms, 1).float().contiguous()
+        if hi > lo:
+            mine[:, :hi - lo] = coords[:, lo:hi]
+        ops.knn_idx_shared(full, mine, k, r, world, _peers(idx_all))
+    for r in range(world):
+        got = idx_all[r].permute(1, 2, 0, 3, 4).reshape(L, S, world * Ms, k)[:, :, :M]
+        assert torch.equal(got, fidx)
+
+    outs = [torch.full((S, M, L * k * 4), float("nan"), device=DEV) for _ in range(world)]
+    for r in range(world):
+        v0, v1 = view_range(r, world, V)
+        owned = [(c.xyz4, c.fvec, v0 * c.H * c.W, v1 * c.H * c.W) for c in local[r]]
+        if owned:
+            ops.corr_from_idx_shared(owned, idx_all[r], targets, coords, k, r, _peers(outs), outs[r].stride(1))
+    for r in range(world):
+        assert torch.equal(outs[r], fused)
