@@ -148,4 +148,20 @@ __device__ __forceinline__ int cell_coord(float x, float o, float inv_h, int n) 
     return c;
 }
 
+// Grid of a work-drawing kernel (256-thread blocks, `per_block` items in flight per block): one wave of resident blocks
+// (SMs x blocks_per_sm), fewer when there is less work than that.
+__host__ inline unsigned one_wave_grid(long long n_items, int per_block, int blocks_per_sm) {
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (sms[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        sms[dev] = n;
+    }
+    long long wave = (long long)sms[dev] * blocks_per_sm, need = (n_items + per_block - 1) / per_block;
+    return (unsigned)(need < wave ? (need > 0 ? need : 1) : wave);
+}
+
 }  // namespace mvt

@@ -33,17 +33,14 @@ struct KeysParams {
     u64 *out;
     PeersDev idx_peers;          // n != 0: store int32 index lists into idx_all of every rank instead of keys into `out`
     int out_shard, out_shards;   // ... at track shard out_shard of out_shards
+    unsigned n_items;            // n_levels * B * n_shards * Ms
 };
 
-// grid: x = blocks of 8 queries over n_shards*Ms padded tracks, y = frame, z = level
+// one query (level lvl, frame b, padded track m of n_shards*Ms) by one warp
 template <bool RASTER_ONLY>
-__global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
-    __shared__ unsigned char win_tab[32];
-    init_window_table(win_tab);
+__device__ __forceinline__ void keys_item(const KeysParams &p, const unsigned char *win_tab, const int lvl, const int b, const int m) {
     const int lane = threadIdx.x & 31;
-    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (m >= p.n_shards * p.Ms) return;
-    const int b = blockIdx.y, lvl = blockIdx.z, k = p.k;
+    const int k = p.k;
     const int shard = m / p.Ms, mm = m - shard * p.Ms;
     const size_t qslot = (((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm;
     u64 *o = p.out ? p.out + qslot * k : nullptr;
@@ -81,6 +78,29 @@ __global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
             store_all(p.idx_peers, slot * (size_t)(k >> 2) + lane,
                       make_float4(__int_as_float(i0), __int_as_float(i1), __int_as_float(i2), __int_as_float(i3)));
         }
+    }
+}
+
+// Work distribution as in knn_corr_kernel (mvt_knn.cu): one wave of blocks, block j owns items j, j + gridDim.x, ...,
+// its warps draw from that list through a shared counter.
+template <bool RASTER_ONLY>
+__global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
+    __shared__ unsigned char win_tab[32];
+    __shared__ unsigned next_item;
+    if (threadIdx.x == 0) next_item = 0u;
+    init_window_table(win_tab);          // ends with __syncthreads()
+    const int lane = threadIdx.x & 31;
+    const unsigned Mp = (unsigned)(p.n_shards * p.Ms);
+    for (;;) {
+        unsigned i = 0u;
+        if (lane == 0) i = atomicAdd(&next_item, 1u);
+        i = __shfl_sync(FULL, i, 0);
+        const unsigned long long item64 = (unsigned long long)i * gridDim.x + blockIdx.x;
+        if (item64 >= (unsigned long long)p.n_items) break;
+        const unsigned item = (unsigned)item64;
+        const unsigned fr = item / Mp, m = item - fr * Mp;
+        const unsigned lvl = fr / (unsigned)p.B, b = fr - lvl * (unsigned)p.B;
+        keys_item<RASTER_ONLY>(p, win_tab, (int)lvl, (int)b, (int)m);
     }
 }
 
@@ -258,7 +278,10 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     }
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) { p.sd[l] = p.sd[0]; p.idx_off[l] = 0; }
     const int padded = p.n_shards * p.Ms;
-    dim3 grid((unsigned)((padded + 7) / 8), (unsigned)B, (unsigned)n_levels);
+    const long long n_items = (long long)n_levels * B * padded;
+    MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_keys: too many queries (%lld)", n_items);
+    p.n_items = (unsigned)n_items;
+    const unsigned grid = one_wave_grid(n_items, 8, 5);
     bool all_raster = true;
     for (int l = 0; l < n_levels; ++l) all_raster = all_raster && p.sd[l].raster;
     if (all_raster) knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
@@ -347,7 +370,10 @@ MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int 
         p.idx_off[l] = 0;
     }
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) { p.sd[l] = p.sd[0]; p.idx_off[l] = 0; }
-    dim3 grid((unsigned)((Ms + 7) / 8), (unsigned)B, (unsigned)n_levels);
+    const long long n_items = (long long)n_levels * B * Ms;
+    MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_idx_shared: too many queries (%lld)", n_items);
+    p.n_items = (unsigned)n_items;
+    const unsigned grid = one_wave_grid(n_items, 8, 5);
     knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_idx_shared");
     return MVT_OK;
