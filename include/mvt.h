@@ -106,7 +106,19 @@ typedef struct mvt_search {
     int V, H, W;             /* raster mode: rasters of this pyramid level */
     float stride;            /* raster mode: input-image pixels per raster pixel (stride * 2^level) */
     int skip_invalid;        /* raster mode: 1 = points with depth <= 0 are not searchable */
+    const float *tile_z;     /* raster mode, optional: [B, V, ceil(H/8), ceil(W/8), 2] {min, max} view-space depth of the points of
+                                every MVT_TILE x MVT_TILE pixel tile (mvt_tile_depth_build); lets a search whose ball projects onto
+                                a large pixel box skip the tiles whose depth range the ball cannot reach.  NULL: no culling.
+                                Never changes a result. */
 } mvt_search;
+
+#define MVT_TILE 8
+/* Floats in the tile_z table of one raster level. */
+long long mvt_tile_depth_floats(int B, int V, int H, int W);
+/* Fills tile_z_out[i] for n (<= 8) raster-mode descriptors (e.g. the 4 pyramid levels) in one launch.  The tile_z fields
+ * of the descriptors themselves are ignored.  No reference counterpart (the reference's kNN, mvtracker.py:26-90, is brute
+ * force / pointops); this is part of the search structure, like mvt_grid_build. */
+int mvt_tile_depth_build(const mvt_search *searches, int n, int B, float *const *tile_z_out, void *stream);
 
 /* Exact kNN.  query [B,M,3] device fp32.  idx_out [B,M,k] int32 or int64 (idx_is_i64), dist_out [B,M,k] fp32 Euclidean,
  * either may be NULL.  Order: ascending (d2, index) with d2 = fma(dz,dz,fma(dy,dy,dx*dx)) in fp32.

@@ -14,7 +14,8 @@ CAM_STRIDE, MAX_VIEWS = 48, 32
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
            "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
-           "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared")
+           "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
+           "mvt_tile_depth_build")
 
 
 class LevelOut(C.Structure):
@@ -30,7 +31,7 @@ class GridJob(C.Structure):
 class Search(C.Structure):
     _fields_ = [("grid", C.c_void_p), ("xyz", C.c_void_p), ("xyz4", C.c_void_p), ("cam", C.c_void_p),
                 ("cam_view_stride", C.c_int), ("N", C.c_int), ("V", C.c_int), ("H", C.c_int), ("W", C.c_int),
-                ("stride", C.c_float), ("skip_invalid", C.c_int)]
+                ("stride", C.c_float), ("skip_invalid", C.c_int), ("tile_z", C.c_void_p)]
 
 
 class CorrLevel(C.Structure):
@@ -89,9 +90,12 @@ def lib():
     L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll, vp]
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
+    L.mvt_tile_depth_floats.argtypes = [ci, ci, ci, ci]
+    L.mvt_tile_depth_floats.restype = ll
+    L.mvt_tile_depth_build.argtypes = [C.POINTER(Search), ci, ci, C.POINTER(vp), vp]
     for name in SYMBOLS:
         f = getattr(L, name)
-        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count"):
+        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count", "mvt_tile_depth_floats"):
             f.restype = ci
     _lib = L
     return L

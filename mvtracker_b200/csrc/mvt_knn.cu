@@ -22,7 +22,7 @@ __device__ __forceinline__ void search(const SearchDev &sd, const unsigned char 
                                        int k, int lane, float &bd, int &bi, int qtag = 0) {
     TopK tk;
     const Group<32> g(lane);
-    if (RASTER_ONLY || sd.raster) raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, qtag);
+    if (RASTER_ONLY || sd.raster) raster_search<32, true>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, qtag);
     else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
     bd = key_d2(tk.t);
     bi = key_idx(tk.t);
@@ -362,11 +362,100 @@ __global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, con
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// tile depth tables (raster search: depth culling of large pixel boxes, tile_scan in mvt_raster.cuh)
+// ---------------------------------------------------------------------------------------------------------------
+struct TileJob {
+    const float4 *xyz4;     // [B, V*H*W]
+    const float *cam;
+    float2 *out;            // [B, V, TH, TW]
+    int V, S, H, W, TW, TH;
+    long long first;        // first warp of this job
+};
+struct TileParams {
+    TileJob job[8];
+    int n, B;
+    long long warps;
+};
+
+// one warp per 8x8 tile: {min, max} over its points of Z = third row of the view matrix . p, evaluated exactly as the
+// search evaluates the query's Z (same fma chain), so that the cull test compares like with like
+__global__ void __launch_bounds__(256) tile_depth_kernel(const TileParams p) {
+    const int lane = threadIdx.x & 31;
+    const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= p.warps) return;
+    int ji = 0;
+#pragma unroll
+    for (int i = 1; i < 8; ++i)
+        if (i < p.n && w >= p.job[i].first) ji = i;
+    const TileJob &J = p.job[ji];
+    long long t = w - J.first;
+    const int tx = (int)(t % J.TW); t /= J.TW;
+    const int ty = (int)(t % J.TH); t /= J.TH;
+    const int v = (int)(t % J.V);
+    const int b = (int)(t / J.V);
+    const float *cm = J.cam + ((size_t)v * J.S + b) * kCamStride;
+    const float r0 = cm[30], r1 = cm[31], r2 = cm[32], t3 = cm[35];
+    const float4 *vf = J.xyz4 + ((size_t)b * J.V + v) * J.H * J.W;
+    float zmin = INFINITY, zmax = -INFINITY;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int px = tx * kTile + (lane & 7), py = ty * kTile + (lane >> 3) + 4 * h;
+        if (px < J.W && py < J.H) {
+            const float4 q = __ldg(vf + (size_t)py * J.W + px);
+            if (!(q.w < 0.f)) {       // every point any search may return (skip_invalid only narrows this)
+                const float z = fmaf(r0, q.x, fmaf(r1, q.y, fmaf(r2, q.z, t3)));
+                if (z == z) { zmin = fminf(zmin, z); zmax = fmaxf(zmax, z); }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        zmin = fminf(zmin, __shfl_xor_sync(FULL, zmin, o));
+        zmax = fmaxf(zmax, __shfl_xor_sync(FULL, zmax, o));
+    }
+    if (lane == 0) J.out[(((size_t)b * J.V + v) * J.TH + ty) * J.TW + tx] = make_float2(zmin, zmax);
+}
+
 }  // namespace mvt
 
 // ---------------------------------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------------------------------
+MVT_EXPORT long long mvt_tile_depth_floats(int B, int V, int H, int W) {
+    if (B <= 0 || V <= 0 || H <= 0 || W <= 0) return 0;
+    return 2ll * B * V * ((H + MVT_TILE - 1) / MVT_TILE) * ((W + MVT_TILE - 1) / MVT_TILE);
+}
+
+MVT_EXPORT int mvt_tile_depth_build(const mvt_search *searches, int n, int B, float *const *tile_z_out, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(searches && tile_z_out, "mvt_tile_depth_build: null pointer");
+    MVT_CHECK_ARG(n >= 1 && n <= 8 && B > 0, "mvt_tile_depth_build: n must be 1..8, B > 0 (got n=%d B=%d)", n, B);
+    TileParams p;
+    p.n = n; p.B = B;
+    long long warps = 0;
+    for (int i = 0; i < n; ++i) {
+        const mvt_search &u = searches[i];
+        MVT_CHECK_ARG(!u.grid && u.xyz4 && u.cam && tile_z_out[i], "mvt_tile_depth_build: descriptor %d is not a raster search / null output", i);
+        MVT_CHECK_ARG(u.V > 0 && u.V <= MVT_MAX_VIEWS && u.H > 0 && u.W > 0 && (long long)u.V * u.H * u.W == (long long)u.N,
+                      "mvt_tile_depth_build: descriptor %d: bad raster V=%d H=%d W=%d N=%d", i, u.V, u.H, u.W, u.N);
+        MVT_CHECK_ARG(u.cam_view_stride >= B, "mvt_tile_depth_build: descriptor %d: cam_view_stride %d < B", i, u.cam_view_stride);
+        MVT_CHECK_ARG((((uintptr_t)u.xyz4 & 15) | ((uintptr_t)tile_z_out[i] & 7)) == 0, "mvt_tile_depth_build: descriptor %d: alignment", i);
+        TileJob &J = p.job[i];
+        J.xyz4 = (const float4 *)u.xyz4; J.cam = u.cam; J.out = (float2 *)tile_z_out[i];
+        J.V = u.V; J.S = u.cam_view_stride; J.H = u.H; J.W = u.W;
+        J.TW = (u.W + kTile - 1) / kTile; J.TH = (u.H + kTile - 1) / kTile;
+        J.first = warps;
+        warps += (long long)B * u.V * J.TH * J.TW;
+    }
+    for (int i = n; i < 8; ++i) p.job[i] = p.job[0];
+    p.warps = warps;
+    MVT_CHECK_ARG((warps + 7) / 8 < 0x7fffffffLL, "mvt_tile_depth_build: too many tiles");
+    tile_depth_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, (cudaStream_t)stream>>>(p);
+    MVT_CHECK_LAUNCH("tile_depth_build");
+    return MVT_OK;
+}
+
 static inline unsigned warp_blocks(long long warps) { return (unsigned)((warps + 7) / 8); }
 
 namespace mvt {
@@ -397,6 +486,9 @@ int make_search(const mvt_search *u, int B, int need_xyz, SearchDev &sd, const c
         sd.rv.V = u->V; sd.rv.S = u->cam_view_stride; sd.rv.H = u->H; sd.rv.W = u->W;
         sd.rv.stride = u->stride;
         sd.rv.skip_invalid = u->skip_invalid ? 1 : 0;
+        MVT_CHECK_ARG(((uintptr_t)u->tile_z & 7) == 0, "%s: tile_z must be 8-byte aligned", who);
+        sd.rv.ztab = reinterpret_cast<const float2 *>(u->tile_z);
+        sd.rv.TW = (u->W + kTile - 1) / kTile; sd.rv.TH = (u->H + kTile - 1) / kTile;
     }
     return MVT_OK;
 }

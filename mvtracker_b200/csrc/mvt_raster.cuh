@@ -28,7 +28,11 @@ struct RasterView {
     int V, S, H, W;
     float stride;         // input-image pixels per raster pixel (stride * 2^level)
     int skip_invalid;     // 1: points with depth <= 0 are not searchable
+    const float2 *ztab;   // [S, V, TH, TW] {min, max} view-space depth per 8x8 tile, or null (tile_depth_kernel)
+    int TW, TH;
 };
+constexpr int kTile = 8;          // == MVT_TILE
+constexpr int kTileMinPixels = 384;   // a pass that would read this many new pixels of one view goes to tile_search instead
 
 #ifndef MVT_M0
 #define MVT_M0 2
@@ -108,16 +112,156 @@ __device__ __forceinline__ void pix_range(float ulo, float uhi, float inv_st, in
     i1 = (int)fhi + 1;
 }
 
+// Pixel bounding box, in one view, of the ball of radius reff around the view-space point (X, Y, Z): every pixel whose
+// ray can hold a point of the ball.  front: Z > 0 and iz = 1/Z is valid.  Empty ({0,0,0,0}) when the view cannot see it.
+__device__ __forceinline__ Rect ball_box(bool front, float X, float Y, float Z, float iz, float reff, float fx, float sk,
+                                         float cx0, float fy, float cy0, float inv_st, int W, int H) {
+    Rect R = {0, 0, 0, 0};
+    float alo, ahi, blo, bhi;
+    bool vis = true;
+    if (front && Z > 1.01f * reff) {   // the usual case: the ball is strictly in front of the camera
+        tan_range_front(X, Z, iz, reff, alo, ahi);
+        tan_range_front(Y, Z, iz, reff, blo, bhi);
+    } else {
+        vis = tan_range(X, Z, reff, alo, ahi) && tan_range(Y, Z, reff, blo, bhi);
+        if (fmaf(X, X, fmaf(Y, Y, Z * Z)) <= reff * reff) { vis = true; alo = blo = -INFINITY; ahi = bhi = INFINITY; }
+    }
+    if (vis) {
+        float ulo = fmaf(fx, alo, cx0), uhi = fmaf(fx, ahi, cx0);
+        if (sk != 0.f) {
+            float s0 = sk * blo, s1 = sk * bhi;
+            ulo += fminf(s0, s1); uhi += fmaxf(s0, s1);
+        }
+        float vlo = fmaf(fy, blo, cy0), vhi = fmaf(fy, bhi, cy0);
+        pix_range(ulo, uhi, inv_st, W, R.x0, R.x1);
+        pix_range(vlo, vhi, inv_st, H, R.y0, R.y1);
+        if (rect_empty(R)) R = Rect{0, 0, 0, 0};
+    }
+    return R;
+}
+
+// Finishes a query that the window search (raster_windows) gave up on because a pass would have read a large pixel box
+// of some view (a query next to a camera, or one far from every surface).  Same idea one level up: the unit is the 8x8
+// tile, a tile is read only if the depth interval the ball spans in that view, |Z_p - Z_q| <= r * |depth axis|, meets
+// the tile's {min, max} depth (tile_depth_kernel), and tiles are visited in rings around the query's projection, ring
+// rho of every view before ring rho + 1, so that the k-th distance r -- and with it every view's box and depth interval
+// -- tightens after the first few tiles.  Restarts with an empty list capped at the k-th distance found so far: every
+// true neighbour is at most that far and no point can enter twice (each tile of each view is visited at most once).
+// Lane v holds view v.  Exact.  Full warps only.
+static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s, const float qx, const float qy, const float qz,
+                                                const int k, TopK tk, unsigned long long *stats) {
+    const int lane = threadIdx.x & 31;
+    const Group<32> g(lane);
+    const int W = rv.W, H = rv.H, HW = W * H, V = rv.V, TW = rv.TW, TH = rv.TH;
+    const float4 *frame = rv.xyz4 + (size_t)s * V * HW;
+    const float2 *ztab = rv.ztab + (size_t)s * V * TW * TH;
+    const float inv_st = __frcp_rn(rv.stride);
+    const bool skip_invalid = rv.skip_invalid != 0;
+    u64 cap = tk.th | 0xffffffffull;          // tk holds k real points: th is the k-th key, finite
+    if (tk.cap < cap) cap = tk.cap;
+    tk.init(cap);
+    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, zpad = 0.f, nz = 1.f;
+    bool kok = false;
+    const bool mine = lane < V;
+    if (mine) {
+        const float *cm = rv.cam + ((size_t)lane * rv.S + s) * kCamStride;
+        X = fmaf(cm[24], qx, fmaf(cm[25], qy, fmaf(cm[26], qz, cm[33])));
+        Y = fmaf(cm[27], qx, fmaf(cm[28], qy, fmaf(cm[29], qz, cm[34])));
+        Z = fmaf(cm[30], qx, fmaf(cm[31], qy, fmaf(cm[32], qz, cm[35])));
+        fx = cm[36]; sk = cm[37]; cx0 = cm[38]; fy = cm[39]; cy0 = cm[40];
+        kok = cm[41] != 0.f;
+        zpad = 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + fabsf(cm[33]) + fabsf(cm[34]) + fabsf(cm[35]));
+        nz = sqrtf(fmaf(cm[30], cm[30], fmaf(cm[31], cm[31], cm[32] * cm[32])));   // 1 for a rigid view transform
+    }
+    const bool front = kok && Z > 1e-12f;
+    if (front) iz = __frcp_rn(Z);
+    // this view's pixel box for the current threshold (odd intrinsics: the whole raster; depth culling still applies)
+    auto box = [&]() {
+        const float r = sqrtf(key_d2(tk.th));
+        Rect R = {0, 0, 0, 0};
+        if (mine) R = kok ? ball_box(front, X, Y, Z, iz, fmaf(r, 1.0001f, fmaf(4e-6f, r, zpad)), fx, sk, cx0, fy, cy0, inv_st, W, H)
+                          : Rect{0, 0, W, H};
+        return R;
+    };
+    // ring centre: the tile of q's projection, clamped into the first box (its middle when q is behind the camera)
+    int tcx = 0, tcy = 0;
+    {
+        const Rect R = box();
+        int px = (R.x0 + R.x1) >> 1, py = (R.y0 + R.y1) >> 1;
+        if (front && !rect_empty(R)) {
+            const float a = X * iz, b = Y * iz;
+            const float fi = fmaf(fmaf(fx, a, fmaf(sk, b, cx0)) + 0.5f, inv_st, -0.5f);
+            const float fj = fmaf(fmaf(fy, b, cy0) + 0.5f, inv_st, -0.5f);
+            px = (int)fminf(fmaxf(fi, (float)R.x0), (float)(R.x1 - 1));
+            py = (int)fminf(fmaxf(fj, (float)R.y0), (float)(R.y1 - 1));
+        }
+        tcx = px / kTile; tcy = py / kTile;
+    }
+    unsigned tested = 0, kept = 0, st_ins = 0;
+    for (int rho = 0; rho <= max(TW, TH); ++rho) {
+        // views whose current box still reaches ring rho
+        const Rect R = box();
+        const int tx0 = R.x0 / kTile, tx1 = (R.x1 + kTile - 1) / kTile, ty0 = R.y0 / kTile, ty1 = (R.y1 + kTile - 1) / kTile;   // [ , )
+        const bool active = !rect_empty(R) && rho <= max(max(tcx - tx0, tx1 - 1 - tcx), max(tcy - ty0, ty1 - 1 - tcy));
+        const unsigned amask = g.ballot(active);
+        if (amask == 0u) break;
+        const float r = sqrtf(key_d2(tk.th));
+        const float zhalf = fmaf(r, 1.0001f, fmaf(4e-6f, r, zpad)) * nz;
+        const int cnt = rho == 0 ? 1 : 8 * rho;            // tiles of one ring
+        const int total = cnt * __popc(amask);
+        for (int t0 = 0; t0 < total; t0 += 32) {
+            const int t = t0 + lane;
+            const int vi = t / cnt, i = t - vi * cnt;      // vi-th active view, i-th tile of its ring
+            const int v = (t < total) ? (int)__fns(amask, 0, vi + 1) : 0;
+            const int side = rho ? i / (2 * rho) : 0, j = rho ? i - side * 2 * rho : 0;
+            const int dx = side == 0 ? -rho + j : side == 1 ? rho : side == 2 ? rho - j : -rho;
+            const int dy = side == 0 ? -rho : side == 1 ? -rho + j : side == 2 ? rho : rho - j;
+            const int tx = g.shfl(tcx, v) + dx, ty = g.shfl(tcy, v) + dy;
+            const int bx0 = g.shfl(tx0, v), bx1 = g.shfl(tx1, v), by0 = g.shfl(ty0, v), by1 = g.shfl(ty1, v);
+            const float zq = g.shfl(Z, v), zh = g.shfl(zhalf, v);
+            bool keep = t < total && tx >= bx0 && tx < bx1 && ty >= by0 && ty < by1;     // inside the view's box (and the raster)
+            if (keep) {
+                const float2 zr = __ldg(ztab + ((size_t)v * TH + ty) * TW + tx);
+                keep = !(zr.x > zq + zh) && !(zr.y < zq - zh);                           // an empty tile holds {+inf, -inf}
+            }
+            unsigned mask = g.ballot(keep);
+            tested += (unsigned)min(32, total - t0);
+            kept += __popc(mask);
+            while (mask) {
+                const int src = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const int vv = g.shfl(v, src);
+                const int px = g.shfl(tx, src) * kTile + (lane & 7), py0 = g.shfl(ty, src) * kTile + (lane >> 3), py1 = py0 + 4;
+                const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
+                const int i0 = vv * HW + py0 * W + px, i1 = vv * HW + py1 * W + px;
+                const float4 p0 = in0 ? __ldg(frame + i0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 p1 = in1 ? __ldg(frame + i1) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const bool v0 = in0 && (skip_invalid ? (p0.w > 0.f) : !(p0.w < 0.f));
+                const bool v1 = in1 && (skip_invalid ? (p1.w > 0.f) : !(p1.w < 0.f));
+                st_ins += topk_offer(g, tk, v0 ? pack_key(dist2(p0.x, p0.y, p0.z, qx, qy, qz), i0) : kEmptyKey64, k);
+                st_ins += topk_offer(g, tk, v1 ? pack_key(dist2(p1.x, p1.y, p1.z, qx, qy, qz), i1) : kEmptyKey64, k);
+            }
+        }
+    }
+    if (stats && lane == 0) {
+        atomicAdd(stats + 4, 1ull);        // [4]: queries finished here (raster_windows counts only those it finishes)
+        atomicAdd(stats + 5, (unsigned long long)kept * 64ull);
+        atomicAdd(stats + 6, (unsigned long long)st_ins);
+        atomicAdd(stats + 7, (unsigned long long)tested);
+        atomicAdd(stats + 8, (unsigned long long)kept);
+    }
+    return tk;
+}
+
 // win_tab: shared-memory table of init_window_table.
 // cap: only points whose key is below it are wanted (see TopK).  budget != 0: bounded effort, see below.
 // Returns true when the list is the exact answer (always, unless a budget made the search give up).
 // live = false: the group has no query (padding at the end of a frame's track list); it only takes part in the
 // collectives.  Must be called by all 32 lanes.
-template <int GW>
-__device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
-                                              bool live, float qx, float qy, float qz, int k, TopK &tk,
-                                              unsigned long long *stats, int qtag = 0, u64 cap = kEmptyKey64,
-                                              unsigned budget = 0u) {
+template <int GW, bool TILES>
+__device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
+                                               bool live, float qx, float qy, float qz, int k, TopK &tk,
+                                               unsigned long long *stats, int qtag, u64 cap, unsigned budget) {
     tk.init(cap);
     const int gl = g.gl;
     const int W = rv.W, H = rv.H, HW = W * H, V = rv.V;
@@ -207,29 +351,7 @@ __device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterVi
             // pixel bounding box of the ball B(q, r), r = current k-th best distance (an upper bound of the final one)
             float r = sqrtf(key_d2(tk.th));
             float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
-            if (mine && kok) {
-                R = Rect{0, 0, 0, 0};
-                float alo, ahi, blo, bhi;
-                bool vis = true;
-                if (front && Z > 1.01f * reff) {   // the usual case: the ball is strictly in front of the camera
-                    tan_range_front(X, Z, iz, reff, alo, ahi);
-                    tan_range_front(Y, Z, iz, reff, blo, bhi);
-                } else {
-                    vis = tan_range(X, Z, reff, alo, ahi) && tan_range(Y, Z, reff, blo, bhi);
-                    if (fmaf(X, X, fmaf(Y, Y, Z * Z)) <= reff * reff) { vis = true; alo = blo = -INFINITY; ahi = bhi = INFINITY; }
-                }
-                if (vis) {
-                    float ulo = fmaf(fx, alo, cx0), uhi = fmaf(fx, ahi, cx0);
-                    if (sk != 0.f) {
-                        float s0 = sk * blo, s1 = sk * bhi;
-                        ulo += fminf(s0, s1); uhi += fmaxf(s0, s1);
-                    }
-                    float vlo = fmaf(fy, blo, cy0), vhi = fmaf(fy, bhi, cy0);
-                    pix_range(ulo, uhi, inv_st, W, R.x0, R.x1);
-                    pix_range(vlo, vhi, inv_st, H, R.y0, R.y1);
-                    if (rect_empty(R)) R = Rect{0, 0, 0, 0};
-                }
-            }
+            if (mine && kok) R = ball_box(front, X, Y, Z, iz, reff, fx, sk, cx0, fy, cy0, inv_st, W, H);
             covered = !mine || rect_empty(R) || rect_inside(R, A);
         } else {
             // fewer than k searchable points so far; stop only when all rasters are covered
@@ -261,6 +383,11 @@ __device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterVi
         // r only shrinks: if this pass reaches every R, nothing outside can matter afterwards
         const bool reaches_all = g.all(!mine || rect_empty(R) || rect_inside(R, B));
         const bool last = have_k && reaches_all;
+        // a large box of new pixels in some view: give the query to tile_search (depth-culled tiles), see raster_search
+        if (TILES && GW == 32 && rv.ztab != nullptr && budget == 0u) {
+            const int newpx = rect_empty(B) ? 0 : (B.x1 - B.x0) * (B.y1 - B.y0) - (rect_empty(A) ? 0 : (A.x1 - A.x0) * (A.y1 - A.y0));
+            if (g.any(have_k && mine && !done && newpx >= kTileMinPixels)) return false;
+        }
 
         // ---- scan B \ A of every view: four strips per view (top, bottom, left, right), GW/4 views per round ----
         for (int v0 = 0; v0 < V; v0 += GW / 4) {
@@ -331,6 +458,25 @@ __device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterVi
         atomicAdd(stats + 10 + bin, 1ull);
     }
     return true;
+}
+
+// The search: growing windows for the (vast majority of) queries whose neighbourhood is a few hundred pixels and, with
+// TILES (and depth tables in rv), the depth-culled tile scan for those whose ball projects onto a large box in some view
+// (next to a camera, far from every surface): that bounds the time of the slowest query, which is what a kernel with
+// few queries per SM (a track shard of a multi-GPU run) waits for.  The fused single-GPU kernel is throughput-bound
+// and keeps TILES off: the rare large scans cost it less than the registers of the call.  Same result either way.
+// Arguments and return value as raster_windows.
+template <int GW, bool TILES = false>
+__device__ __forceinline__ bool raster_search(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
+                                              bool live, float qx, float qy, float qz, int k, TopK &tk,
+                                              unsigned long long *stats, int qtag = 0, u64 cap = kEmptyKey64,
+                                              unsigned budget = 0u) {
+    bool exact = raster_windows<GW, TILES>(g, rv, win_tab, s, live, qx, qy, qz, k, tk, stats, qtag, cap, budget);
+    if (TILES && GW == 32 && budget == 0u && !exact) {       // (uniform in the warp)
+        tk = tile_search(rv, s, qx, qy, qz, k, tk, stats);
+        exact = true;
+    }
+    return exact;
 }
 
 }  // namespace mvt

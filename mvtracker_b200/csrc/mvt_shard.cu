@@ -59,7 +59,7 @@ __device__ __forceinline__ void keys_item(const KeysParams &p, const unsigned ch
             const u64 c = __ldg(p.caps + qslot);
             if ((c >> 32) < 0x7f800000ull) cap = c | 0xffffffffull;      // finite distance; else no bound is known
         }
-        if (RASTER_ONLY || sd.raster) exact = raster_search<32>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q, cap, p.budget);
+        if (RASTER_ONLY || sd.raster) exact = raster_search<32, true>(g, sd.rv, win_tab, b, true, qx, qy, qz, k, tk, sd.g.stats, (int)q, cap, p.budget);
         else knn_search(sd.g, b, qx, qy, qz, k, lane, tk);
         key = tk.t;
         if (key_idx(key) != kNoIdx) key += (u64)p.idx_off[lvl];      // local -> global index (no carry: idx < 2^31)
@@ -84,7 +84,10 @@ __device__ __forceinline__ void keys_item(const KeysParams &p, const unsigned ch
 // Work distribution as in knn_corr_kernel (mvt_knn.cu): one wave of blocks, block j owns items j, j + gridDim.x, ...,
 // its warps draw from that list through a shared counter.
 template <bool RASTER_ONLY>
-__global__ void __launch_bounds__(256, 5) knn_keys_kernel(const KeysParams p) {
+#ifndef MVT_KEYS_MINB
+#define MVT_KEYS_MINB 4
+#endif
+__global__ void __launch_bounds__(256, MVT_KEYS_MINB) knn_keys_kernel(const KeysParams p) {
     __shared__ unsigned char win_tab[32];
     __shared__ unsigned next_item;
     if (threadIdx.x == 0) next_item = 0u;
@@ -281,7 +284,7 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     const long long n_items = (long long)n_levels * B * padded;
     MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_keys: too many queries (%lld)", n_items);
     p.n_items = (unsigned)n_items;
-    const unsigned grid = one_wave_grid(n_items, 8, 5);
+    const unsigned grid = one_wave_grid(n_items, 8, MVT_KEYS_MINB);
     bool all_raster = true;
     for (int l = 0; l < n_levels; ++l) all_raster = all_raster && p.sd[l].raster;
     if (all_raster) knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
@@ -373,7 +376,7 @@ MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int 
     const long long n_items = (long long)n_levels * B * Ms;
     MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_idx_shared: too many queries (%lld)", n_items);
     p.n_items = (unsigned)n_items;
-    const unsigned grid = one_wave_grid(n_items, 8, 5);
+    const unsigned grid = one_wave_grid(n_items, 8, MVT_KEYS_MINB);
     knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_idx_shared");
     return MVT_OK;

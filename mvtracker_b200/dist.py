@@ -161,10 +161,12 @@ class ShardedWindow:
         first.barrier()           # every rank is done reading the previous window's records
         win.clouds = be.cloud_build(fmaps_local, depths_local, intrs_local, extrs_local, stride=stride, levels=levels,
                                     want_spacing=False, reuse=None if (reuse is None or not reuse.clouds) else reuse.clouds,
-                                    shared_records={l: shared[l].peers for l in levels}, view_offset=v0, V_total=V_total)
+                                    shared_records={l: shared[l].peers for l in levels}, view_offset=v0, V_total=V_total,
+                                    want_tiles=False)
         first.barrier()           # ... and every rank's records have arrived everywhere
         cam_all = be.camera_prep(intrs_all, extrs_all)
         win.full = [be.full_cloud(l, shared[l].t, cam_all, V_total, H >> l, W >> l, float(stride) * (1 << l)) for l in levels]
+        win._tiles()
         return win
 
     def _shared(self, name, shape, dtype, device):
@@ -209,6 +211,17 @@ class ShardedWindow:
                         if b > a:
                             full[:, a * hw:b * hw].copy_(gathered[r, :, :(b - a) * hw])
             self.full.append(be.full_cloud(l, full, cam_all, V, Hl, Wl, float(stride) * (1 << l)))
+        self._tiles()
+
+    def _tiles(self):
+        """Per-tile depth ranges of the replicated clouds (every rank builds its own: one small kernel over the records)."""
+        build = getattr(self.be, "tile_depth_build", None)
+        if build is None:
+            return
+        for c in self.full:
+            shape = (c.xyz4.shape[0], c.V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
+            c.tile_z = self._buf(f"tiles{c.level}", shape, torch.float32, c.xyz4.device)
+        build(self.full)
 
     def _buf(self, name, shape, dtype, device):
         t = self._bufs.get(name)

@@ -1,5 +1,6 @@
 """Torch-facing wrappers over the C ABI (include/mvt.h).  PyTorch is plumbing only here: it owns device memory and the
 current stream; every computation below runs in libmvt.so's sm_100a kernels.  CUDA tensors only -- there is no CPU path."""
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -56,12 +57,35 @@ class Cloud:
     H: int = 0                           # raster height / width of this level
     W: int = 0
     stride: float = 0.0                  # input pixels per raster pixel at this level
+    tile_z: Optional[torch.Tensor] = None  # [S, V, ceil(H/8), ceil(W/8), 2] per-tile depth range (tile_depth_build)
+
+
+def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
+    """Fills cloud.tile_z of every Cloud that has raster records (one launch for all): the per-tile depth ranges that let
+    the raster search skip, inside a large pixel box, the tiles the query's ball cannot reach (mvt_tile_depth_build)."""
+    todo = [c for c in clouds if c.xyz4 is not None and c.cam is not None]
+    if not todo or os.environ.get("MVT_NO_TILES"):       # (debugging knob: searches then read every pixel of a box)
+        return
+    if len(todo) > 8:
+        raise MvtError("tile_depth_build takes at most 8 clouds")
+    S = todo[0].xyz4.shape[0]
+    arr = (_CSearch * len(todo))()
+    outs = (C.c_void_p * len(todo))()
+    for i, c in enumerate(todo):
+        if c.xyz4.shape[0] != S:
+            raise MvtError("tile_depth_build: clouds of one call must have the same number of frames")
+        shape = (S, c.V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
+        if c.tile_z is None or tuple(c.tile_z.shape) != shape:
+            c.tile_z = torch.empty(shape, device=c.xyz4.device, dtype=torch.float32)
+        arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), S, c.xyz4.shape[1], c.V, c.H, c.W, float(c.stride), 0, None)
+        outs[i] = c.tile_z.data_ptr()
+    check(lib().mvt_tile_depth_build(arr, len(todo), S, outs, _stream()), "mvt_tile_depth_build")
 
 
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
                 want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None,
                 reuse: Optional[Sequence["Cloud"]] = None, shared_records=None, view_offset: int = 0,
-                V_total: Optional[int] = None) -> List[Cloud]:
+                V_total: Optional[int] = None, want_tiles=True) -> List[Cloud]:
     """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass.
     reuse: Clouds of an earlier call with the same shapes / levels / dtype whose buffers are overwritten in place (no
     allocation in steady state, e.g. one set of buffers per sliding window).
@@ -117,7 +141,7 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
                            valid.data_ptr() if want_valid else None, spacing.data_ptr() if want_spacing else None)
         mask |= 1 << l
         clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
-                            float(stride) * (1 << l)))
+                            float(stride) * (1 << l), old.tile_z if reuse is not None else None))
     if shared_records is None:
         check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                     int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
@@ -128,6 +152,8 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         check(lib().mvt_cloud_build_shared(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                            int(depth_interp_mode == "avg"), outs, mask, recs, int(view_offset),
                                            int(V if V_total is None else V_total), _stream()), "mvt_cloud_build_shared")
+    if want_tiles and want_xyz4:
+        tile_depth_build(clouds)
     return clouds
 
 
@@ -199,8 +225,13 @@ class Search:
             cam_ptr += frame * _lib.CAM_STRIDE * 4
             B = int(nframes)
             assert 0 <= frame and frame + B <= S
-        c = _CSearch(None, None, x4_ptr, cam_ptr, S, P, cloud.V, cloud.H, cloud.W, float(cloud.stride), int(bool(skip_invalid)))
-        return cls(c, B, P, (x4, cam))
+        tz = cloud.tile_z
+        tz_ptr = None
+        if tz is not None:
+            tz_ptr = tz.data_ptr() + (0 if frame is None else frame * tz[0].numel() * 4)
+        c = _CSearch(None, None, x4_ptr, cam_ptr, S, P, cloud.V, cloud.H, cloud.W, float(cloud.stride), int(bool(skip_invalid)),
+                     tz_ptr)
+        return cls(c, B, P, (x4, cam, tz))
 
 
 def _as_search(obj) -> Search:
@@ -367,7 +398,7 @@ def corr_from_idx(owned: Sequence, idx: torch.Tensor, targets: torch.Tensor, coo
 def full_cloud(level: int, xyz4: torch.Tensor, cam: torch.Tensor, V: int, H: int, W: int, stride: float) -> Cloud:
     """Search-only Cloud over replicated raster records [S, V*H*W, 4] (no features): what mvtracker_b200.dist searches
     in "tracks" mode."""
-    return Cloud(level, None, None, None, None, xyz4, cam, V, H, W, stride)
+    return Cloud(level, None, None, None, None, xyz4, cam, V, H, W, stride)      # tile_z: ops.tile_depth_build([...])
 
 
 def knn_idx_shared(searches: Sequence, query: torch.Tensor, k: int, shard: int, n_shards: int, peers) -> None:

@@ -330,6 +330,75 @@ def test_raster_knn_queries_beside_and_behind_cameras(V):
         check_knn_raster(c, coords, 3, skip_invalid=True)
 
 
+def test_tile_depth_tables_and_culled_search():
+    """The per-tile depth ranges (mvt_tile_depth_build) against numpy, and the searches that use them -- queries next to
+    the cameras and far off the surfaces, whose balls project onto large pixel boxes -- against the oracle and against
+    the same search without tables; the statistics prove the tile path ran and culled."""
+    import ctypes
+    from mvtracker_b200 import _lib
+    V, S = 5, 2
+    sc = synth.make_scene(V, 80 * 4, 96 * 4, S=S, C=4, zero_frac=0.1, seed=90, device=DEV)
+    sc.depths[0, 1, 0, 0, :64, :64] = float("nan")          # a block of NaN depths: never a neighbour, never in a range
+    args = (sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0])
+    clouds = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True)
+    plain = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True, want_tiles=False)
+    for c in clouds:
+        assert c.tile_z is not None and c.tile_z.shape == (S, V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
+        x4 = c.xyz4.view(S, V, c.H, c.W, 4).cpu().numpy().astype(np.float32)
+        cam = c.cam.view(V, S, -1).cpu().numpy()
+        z = np.empty((S, V, c.H, c.W), np.float32)
+        for v in range(V):
+            for s_ in range(S):
+                r = cam[v, s_]
+                # the kernel's fma chain in float32 is not reproducible with numpy products: compare with a tolerance
+                z[s_, v] = (x4[s_, v, ..., 0].astype(np.float64) * r[30] + x4[s_, v, ..., 1].astype(np.float64) * r[31]
+                            + x4[s_, v, ..., 2].astype(np.float64) * r[32] + r[35])
+        z[(x4[..., 3] < 0) | np.isnan(z)] = np.nan
+        TH, TW = (c.H + 7) // 8, (c.W + 7) // 8
+        pad = np.full((S, V, TH * 8, TW * 8), np.nan, np.float32)
+        pad[:, :, :c.H, :c.W] = z
+        tiles = pad.reshape(S, V, TH, 8, TW, 8)
+        with np.errstate(all="ignore"):
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                lo, hi = np.nanmin(tiles, axis=(3, 5)), np.nanmax(tiles, axis=(3, 5))
+        lo[np.isnan(lo)] = np.inf
+        hi[np.isnan(hi)] = -np.inf
+        got = c.tile_z.cpu().numpy()
+        fin = np.isfinite(lo)
+        assert (np.isfinite(got[..., 0]) == fin).all() and (np.isfinite(got[..., 1]) == fin).all()
+        assert np.abs(got[..., 0][fin] - lo[fin]).max() < 1e-4 and np.abs(got[..., 1][fin] - hi[fin]).max() < 1e-4
+        assert (got[..., 0][~fin] == np.inf).all() and (got[..., 1][~fin] == -np.inf).all()
+
+    g = torch.Generator(device=DEV).manual_seed(91)
+    coords = (torch.rand(S, 1200, 3, device=DEV, generator=g) - 0.5) * torch.tensor([12.0, 12.0, 4.0], device=DEV)
+    E = sc.extrs[0, :, 0]
+    centres = -(E[:, :, :3].transpose(1, 2) @ E[:, :, 3:]).squeeze(-1)
+    coords[:, :600] = centres[torch.arange(600, device=DEV) % V] + 0.3 * torch.randn(S, 600, 3, device=DEV, generator=g)
+    surf = clouds[0].xyz[:, torch.randint(0, clouds[0].xyz.shape[1], (300,), device=DEV, generator=g)]
+    coords[:, 900:] = surf + 0.01 * torch.randn(S, 300, 3, device=DEV, generator=g)
+    stats = torch.zeros(16, dtype=torch.int64, device=DEV)
+    L = _lib.lib()
+    for c, c0 in zip(clouds, plain):
+        L.mvt_debug_set_stats(ctypes.c_void_p(stats.data_ptr()))
+        stats.zero_()
+        try:
+            check_knn_raster(c, coords, 16)
+            torch.cuda.synchronize()
+        finally:
+            L.mvt_debug_set_stats(None)
+        tested, kept = int(stats[7]), int(stats[8])
+        assert tested > 0 and kept < tested, (tested, kept)
+        check_knn_raster(c, coords, 5, skip_invalid=True)
+        d1, i1 = ops.knn(ops.Search.from_cloud(c), coords, 16)
+        d0, i0 = ops.knn(ops.Search.from_cloud(c0), coords, 16)
+        assert torch.equal(i0, i1) and torch.equal(d0, d1)
+        # a single frame of the cloud (the reference's per-frame calls): the table is sliced with it
+        d2_, i2_ = ops.knn(ops.Search.from_cloud(c, frame=1), coords[1:2].contiguous(), 16)
+        assert torch.equal(i2_, i1[1:2]) and torch.equal(d2_, d1[1:2])
+
+
 def test_raster_knn_skewed_intrinsics_and_moving_cameras():
     sc = synth.make_scene(3, 40 * 4, 56 * 4, S=3, C=4, zero_frac=0.1, seed=50, device=DEV)
     g = torch.Generator(device=DEV).manual_seed(51)

@@ -38,7 +38,7 @@ def run(tag, levels_of):
         q = max(st[0], 1)
         print(f"{tag} lvl {lvl} N={c.xyz.shape[1]:7d} | ms={e0.elapsed_time(e1):.3f} pass1={st[1] / q:.3f} pass2={st[2] / q:.3f} "
               f"pass3={st[3] / q:.3f} pass4+={st[4] / q:.4f} cand/q={st[5] / q:.0f} ins/q={st[6] / q:.1f} "
-              f"hist(<2,<16,<128,<1k,<8k,>=8k)={st[10:16]}")
+              f"hist(<2,<16,<128,<1k,<8k,>=8k)={st[10:16]} tiles tested/q={st[7] / q:.2f} kept/q={st[8] / q:.2f}")
         worst_c, worst_q = st[9] >> 24, st[9] & 0xFFFFFF
         b, m_ = divmod(worst_q, coords.shape[1])
         qq = coords[b, m_]
