@@ -152,22 +152,18 @@ struct CorrIdxParams {
     int shard;              // this rank's track shard (it stores the zero records of missing neighbours)
 };
 
-// 16 partial sums per lane -> lane L holds the warp total of neighbour L >> 1 (same network as mvt_knn.cu)
-__device__ __forceinline__ float shard_reduce16(float (&pr)[16], int lane) {
-#pragma unroll
-    for (int w = 16, n = 8; n >= 1; w >>= 1, n >>= 1) {
-#pragma unroll
-        for (int i = 0; i < n; ++i) {
-            bool hi = lane & w;
-            float send = hi ? pr[i] : pr[i + n], keep = hi ? pr[i + n] : pr[i];
-            pr[i] = keep + __shfl_xor_sync(FULL, send, w);
-        }
-    }
-    return pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
-}
-
+// One warp per (level, frame, track).  Only the neighbours whose rows live on this rank are gathered, four rows in flight
+// per round (with N view shards a query owns 16 / N of its neighbours on average, often none).  Arithmetic per neighbour
+// is that of knn_corr_kernel -- the same per-lane fma chain and the same butterfly order over the lanes of a row -- so
+// the records are bit-identical to the fused single-GPU kernel's whatever the sharding.
+#ifndef MVT_CIDX_MINB
+#define MVT_CIDX_MINB 8
+#endif
+#ifndef MVT_CIDX_ROUND
+#define MVT_CIDX_ROUND 4       // rows in flight per round (fp32; bf16 rows are half as long: ROUND / 2 pairs)
+#endif
 template <bool BF16>
-__global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxParams p) {
+__global__ void __launch_bounds__(256, MVT_CIDX_MINB) corr_from_idx_kernel(const CorrIdxParams p) {
     const int lane = threadIdx.x & 31;
     const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (m >= p.M) return;
@@ -178,9 +174,10 @@ __global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxPara
     const int *ip = p.idx + ((((size_t)shard * p.n_levels + lvl) * p.B + b) * p.Ms + mm) * k;
     const long long gi = (lane < k) ? (long long)__ldg(ip + lane) : -1ll;
     const bool own = gi >= L.lo && gi < L.hi;
-    const int row = own ? (int)(gi - L.lo) : -1;       // local row of neighbour `lane`
+    const int row = own ? (int)(gi - L.lo) : 0;        // local row of neighbour `lane`
     const size_t nloc = (size_t)(L.hi - L.lo);
-    if (!__any_sync(FULL, own)) {      // none of this query's neighbours lives here: no target row, no gather
+    unsigned om = __ballot_sync(FULL, own);
+    if (om == 0u) {      // none of this query's neighbours lives here: no target row, no gather
         if (lane < k) {
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
             if (p.out_peers.n == 0) *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = z;
@@ -188,61 +185,82 @@ __global__ void __launch_bounds__(256, 4) corr_from_idx_kernel(const CorrIdxPara
         }
         return;
     }
-    float corr_mine;
+    // everything that depends only on the index list is requested before the feature rows: one round trip, not three
+    const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+    float4 n = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (own) n = __ldg(L.xyz4 + (size_t)b * nloc + row);
+    float corr_mine = 0.f;
     if (!BF16) {
         const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + q * 32 + lane);
         const float4 *fv = reinterpret_cast<const float4 *>(L.fvec) + (size_t)b * nloc * 32 + lane;
-        float pr[16];
+        while (om) {
+            int j[MVT_CIDX_ROUND];
+            float4 f[MVT_CIDX_ROUND];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            int rj = __shfl_sync(FULL, row, j);
-            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (rj >= 0) f = __ldg(fv + (size_t)rj * 32);
-            pr[j] = fmaf(tg.w, f.w, fmaf(tg.z, f.z, fmaf(tg.y, f.y, tg.x * f.x)));
+            for (int u = 0; u < MVT_CIDX_ROUND; ++u) {
+                j[u] = om ? __ffs(om) - 1 : -1;
+                om &= om - 1;
+            }
+#pragma unroll
+            for (int u = 0; u < MVT_CIDX_ROUND; ++u) {
+                const int rj = __shfl_sync(FULL, row, j[u] & 31);
+                f[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (j[u] >= 0) f[u] = __ldg(fv + (size_t)rj * 32);
+            }
+#pragma unroll
+            for (int u = 0; u < MVT_CIDX_ROUND; ++u) {
+                if (j[u] < 0) break;
+                float d = fmaf(tg.w, f[u].w, fmaf(tg.z, f[u].z, fmaf(tg.y, f[u].y, tg.x * f[u].x)));
+#pragma unroll
+                for (int o = 16; o; o >>= 1) d += __shfl_xor_sync(FULL, d, o);
+                if (lane == j[u]) corr_mine = d;
+            }
         }
-        float tot = shard_reduce16(pr, lane);
-        corr_mine = __shfl_sync(FULL, tot, (2 * lane) & 31);
     } else {
-        // same summation order as knn_corr_kernel<2, *, 32>: 16 lanes x 8 channels per row, two rows per warp load
+        // 16 lanes x 8 channels per row: each half-warp takes one neighbour of a pair
         const uint4 tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + q * 16 + (lane & 15));
         const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec) + (size_t)b * nloc * 16 + (lane & 15);
         const int half = lane >> 4;
-        float pr[8];
+        while (om) {
+            int ja[MVT_CIDX_ROUND / 2], jb[MVT_CIDX_ROUND / 2];
+            uint4 f[MVT_CIDX_ROUND / 2];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            int rj = __shfl_sync(FULL, row, 2 * i + half);
-            uint4 f = make_uint4(0u, 0u, 0u, 0u);
-            if (rj >= 0) f = __ldg(fv + (size_t)rj * 16);
-            const __nv_bfloat162 *x = reinterpret_cast<const __nv_bfloat162 *>(&tgh);
-            const __nv_bfloat162 *y = reinterpret_cast<const __nv_bfloat162 *>(&f);
-            float acc = 0.f;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                float2 u = __bfloat1622float2(x[e]), v = __bfloat1622float2(y[e]);
-                acc = fmaf(u.x, v.x, acc);
-                acc = fmaf(u.y, v.y, acc);
+            for (int u = 0; u < MVT_CIDX_ROUND / 2; ++u) {
+                ja[u] = om ? __ffs(om) - 1 : -1;
+                om &= om - 1;
+                jb[u] = om ? __ffs(om) - 1 : -1;
+                om &= om - 1;
             }
-            pr[i] = acc;
-        }
 #pragma unroll
-        for (int w = 8, n = 4; n >= 1; w >>= 1, n >>= 1) {
+            for (int u = 0; u < MVT_CIDX_ROUND / 2; ++u) {
+                const int jm = half ? jb[u] : ja[u];
+                const int rj = __shfl_sync(FULL, row, jm & 31);
+                f[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (jm >= 0) f[u] = __ldg(fv + (size_t)rj * 16);
+            }
 #pragma unroll
-            for (int i = 0; i < n; ++i) {
-                bool hi = lane & w;
-                float send = hi ? pr[i] : pr[i + n], keep = hi ? pr[i + n] : pr[i];
-                pr[i] = keep + __shfl_xor_sync(FULL, send, w);
+            for (int u = 0; u < MVT_CIDX_ROUND / 2; ++u) {
+                if (ja[u] < 0) break;
+                const __nv_bfloat162 *x = reinterpret_cast<const __nv_bfloat162 *>(&tgh);
+                const __nv_bfloat162 *y = reinterpret_cast<const __nv_bfloat162 *>(&f[u]);
+                float acc = 0.f;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 uu = __bfloat1622float2(x[e]), vv = __bfloat1622float2(y[e]);
+                    acc = fmaf(uu.x, vv.x, acc);
+                    acc = fmaf(uu.y, vv.y, acc);
+                }
+#pragma unroll
+                for (int o = 8; o; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);
+                const float va = __shfl_sync(FULL, acc, 0), vb = __shfl_sync(FULL, acc, 16);
+                if (lane == ja[u]) corr_mine = va;
+                if (lane == jb[u]) corr_mine = vb;
             }
         }
-        float tot = pr[0] + __shfl_xor_sync(FULL, pr[0], 1);
-        corr_mine = __shfl_sync(FULL, tot, ((lane & 1) << 4) | ((lane >> 1) << 1));
     }
     if (lane < k) {
         float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (own) {
-            const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
-            const float4 n = __ldg(L.xyz4 + (size_t)b * nloc + row);
-            rec = make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz);
-        }
+        if (own) rec = make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz);
         if (p.out_peers.n == 0) {
             *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = rec;
         } else if (own || (gi < 0 && shard == p.shard)) {     // exactly one rank stores each record

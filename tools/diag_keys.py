@@ -25,3 +25,10 @@ for frac in (1, 2, 4, 8):
     c = coords[:, :m].contiguous()
     keys = torch.empty(1, 4, S, m, 16, dtype=torch.int64, device=dev)
     print(f"knn_keys, {S * m * 4} queries (1/{frac}): {t(lambda: ops.knn_keys(full, [0] * 4, c, 16, out=keys)):.3f} ms")
+# corr_from_idx with the ownership of one rank out of n (views 0 .. V/n - 1), all queries
+_, fidx = ops.knn_corr(lv, targets, coords, return_idx=True)
+idx_all = fidx.unsqueeze(0).contiguous()            # [1 shard, L, S, M, k]
+for n in (1, 2, 4, 8):
+    owned = [(c.xyz4[:, :(V // n) * c.H * c.W].contiguous(), c.fvec[:, :(V // n) * c.H * c.W].contiguous(), 0, (V // n) * c.H * c.W) for c in full]
+    res = torch.empty(S, N, 256, device=dev)
+    print(f"corr_from_idx, owner of {V // n}/{V} views: {t(lambda: ops.corr_from_idx(owned, idx_all, targets, coords, 16, out=res)):.3f} ms")
