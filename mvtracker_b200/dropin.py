@@ -149,7 +149,7 @@ def _find_raster(xyz_ref: torch.Tensor):
                 continue
             f0 = off // (P * 12)
             if f0 + Bq <= S:
-                return ops.Search.from_cloud(cloud, frame=int(f0), nframes=int(Bq))
+                return ops.Search.from_cloud(cloud, frame=int(f0), nframes=int(Bq), tiles=True)
     return None
 
 

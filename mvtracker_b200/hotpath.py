@@ -58,7 +58,7 @@ class WindowClouds:
         """Nearest level-0 point's feature for each query of `frame` (mvtracker.py:627-643).  query_xyz [n,3] -> [n,C]."""
         c = self.clouds[0]
         if self.grids is None:
-            sr = ops.Search.from_cloud(c, frame=frame)
+            sr = ops.Search.from_cloud(c, frame=frame, tiles=True)
             return ops.knn_gather(sr, c.fvec[frame:frame + 1], query_xyz[None])[0]
         g = ops.build_grids([(c.xyz[frame:frame + 1], None, c.spacing[frame:frame + 1])], k_hint=1)[0]
         return ops.knn_gather(g, c.fvec[frame:frame + 1], query_xyz[None])[0]

@@ -58,6 +58,7 @@ class Cloud:
     W: int = 0
     stride: float = 0.0                  # input pixels per raster pixel at this level
     tile_z: Optional[torch.Tensor] = None  # [S, V, ceil(H/8), ceil(W/8), 2] per-tile depth range (tile_depth_build)
+    tiles_ready: bool = False              # tile_z describes the current xyz4 (a reused buffer starts out stale)
 
 
 def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
@@ -80,17 +81,21 @@ def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
         arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), S, c.xyz4.shape[1], c.V, c.H, c.W, float(c.stride), 0, None)
         outs[i] = c.tile_z.data_ptr()
     check(lib().mvt_tile_depth_build(arr, len(todo), S, outs, _stream()), "mvt_tile_depth_build")
+    for c in todo:
+        c.tiles_ready = True
 
 
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
                 want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None,
                 reuse: Optional[Sequence["Cloud"]] = None, shared_records=None, view_offset: int = 0,
-                V_total: Optional[int] = None, want_tiles=True) -> List[Cloud]:
+                V_total: Optional[int] = None, want_tiles=False) -> List[Cloud]:
     """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass.
     reuse: Clouds of an earlier call with the same shapes / levels / dtype whose buffers are overwritten in place (no
     allocation in steady state, e.g. one set of buffers per sliding window).
     shared_records {level: _lib.Peers}: also store the 16-byte records of these views into the replicated
-    [S, V_total*H_l*W_l, 4] buffers of every rank, views view_offset.. (mvt_cloud_build_shared)."""
+    [S, V_total*H_l*W_l, 4] buffers of every rank, views view_offset.. (mvt_cloud_build_shared).
+    want_tiles: also build the per-tile depth tables now, in one launch (otherwise the first search-only call on a level
+    builds that level's table; the fused knn_corr kernel does not use them)."""
     _need_cuda(fmaps, "fmaps"); _need_cuda(depths, "depths")
     V, S, Cc, H, W = fmaps.shape
     depths = depths.reshape(V, S, H, W)
@@ -213,8 +218,12 @@ class Search:
         return cls(c, grid.B, grid.N, (grid, x))
 
     @classmethod
-    def from_cloud(cls, cloud: Cloud, skip_invalid=False, frame: Optional[int] = None, nframes: int = 1):
-        """Raster search over a Cloud from cloud_build (no build step).  frame=f restricts to frames f..f+nframes-1."""
+    def from_cloud(cls, cloud: Cloud, skip_invalid=False, frame: Optional[int] = None, nframes: int = 1, tiles=False):
+        """Raster search over a Cloud from cloud_build (no build step).  frame=f restricts to frames f..f+nframes-1.
+        tiles: the consumer is a search-only kernel (knn, knn_gather, knn_keys, knn_idx_shared), which culls large pixel
+        boxes by the per-tile depth tables: build them now if this cloud's are missing or stale."""
+        if tiles and cloud.xyz4 is not None and cloud.cam is not None and not cloud.tiles_ready:
+            tile_depth_build([cloud])
         if cloud.xyz4 is None or cloud.cam is None:
             raise MvtError("this Cloud has no raster records (build it with want_xyz4=True)")
         S, P = cloud.xyz4.shape[0], cloud.xyz4.shape[1]
@@ -225,7 +234,7 @@ class Search:
             cam_ptr += frame * _lib.CAM_STRIDE * 4
             B = int(nframes)
             assert 0 <= frame and frame + B <= S
-        tz = cloud.tile_z
+        tz = cloud.tile_z if cloud.tiles_ready else None
         tz_ptr = None
         if tz is not None:
             tz_ptr = tz.data_ptr() + (0 if frame is None else frame * tz[0].numel() * 4)
@@ -234,13 +243,13 @@ class Search:
         return cls(c, B, P, (x4, cam, tz))
 
 
-def _as_search(obj) -> Search:
+def _as_search(obj, tiles=False) -> Search:
     if isinstance(obj, Search):
         return obj
     if isinstance(obj, Grid):
         return Search.from_grid(obj)
     if isinstance(obj, Cloud):
-        return Search.from_cloud(obj)
+        return Search.from_cloud(obj, tiles=tiles)
     raise MvtError(f"cannot search in {type(obj)}")
 
 
@@ -252,7 +261,7 @@ def knn(where, query: torch.Tensor, k: int, idx_dtype=torch.int64, want_dist=Tru
     """where: Grid | Cloud | Search.  -> (dists [B,M,k] fp32 ascending, idx [B,M,k]); canonical (d2, index) order;
     -1 / inf where fewer than k searchable points exist."""
     _need_cuda(query, "query")
-    sr = _as_search(where)
+    sr = _as_search(where, tiles=True)
     q = _f32c(query)
     B, M, _ = q.shape
     if B != sr.B:
@@ -309,7 +318,7 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
 def knn_gather(where, fvec: torch.Tensor, query: torch.Tensor, return_idx=False):
     """k=1: feature row of the nearest cloud point per query.  fvec [B,N,C] (or the frame's [1,N,C]), query [B,M,3]."""
     _need_cuda(query, "query"); _need_cuda(fvec, "fvec")
-    sr = _as_search(where)
+    sr = _as_search(where, tiles=True)
     q = _f32c(query)
     fv = fvec.contiguous()
     B, M, _ = q.shape
@@ -338,7 +347,7 @@ def knn_keys(searches: Sequence, index_offsets: Sequence[int], query: torch.Tens
     q = _f32c(query)
     B, M, _ = q.shape
     L = len(searches)
-    srs = [_as_search(s) for s in searches]
+    srs = [_as_search(s, tiles=True) for s in searches]
     arr = (_CSearch * L)(*[s.c for s in srs])
     offs = (C.c_longlong * L)(*[int(o) for o in index_offsets])
     Ms = (M + n_shards - 1) // n_shards
@@ -406,7 +415,7 @@ def knn_idx_shared(searches: Sequence, query: torch.Tensor, k: int, shard: int, 
     _need_cuda(query, "query")
     q = _f32c(query)
     B, Ms, _ = q.shape
-    srs = [_as_search(s) for s in searches]
+    srs = [_as_search(s, tiles=True) for s in searches]
     arr = (_CSearch * len(srs))(*[s.c for s in srs])
     check(lib().mvt_knn_idx_shared(arr, len(srs), B, _ptr(q), Ms, int(k), int(shard), int(n_shards), C.byref(peers), _stream()),
           "mvt_knn_idx_shared")

@@ -81,7 +81,7 @@ def check_knn_exact(xyz, q, k, mask=None, spacing=None, cell_scale=0.0, k_hint=N
 
 def check_knn_raster(cloud, q, k, skip_invalid=False):
     """Raster search (no index) against the canonical oracle on the same CUDA-built cloud: bit exact."""
-    dist, idx = ops.knn(ops.Search.from_cloud(cloud, skip_invalid=skip_invalid), q, k, idx_dtype=torch.int32)
+    dist, idx = ops.knn(ops.Search.from_cloud(cloud, skip_invalid=skip_invalid, tiles=True), q, k, idx_dtype=torch.int32)
     mask = cloud.valid.cpu().numpy() if skip_invalid else None
     od, oi = oracle.knn(k, cloud.xyz.cpu().numpy(), q.cpu().numpy(), mask)
     idx, dist = idx.cpu().numpy(), dist.cpu().numpy()
@@ -275,7 +275,7 @@ def test_knn_gather_feature_init():
         expect = torch.gather(c.fvec, 1, idx.long()[..., None].expand(-1, -1, 128))
         assert torch.equal(feat, expect)
     # one frame of the window (what the feature-init loop asks for)
-    feat1 = ops.knn_gather(ops.Search.from_cloud(c, frame=1), c.fvec[1:2], coords[1:2])
+    feat1 = ops.knn_gather(ops.Search.from_cloud(c, frame=1, tiles=True), c.fvec[1:2], coords[1:2])
     assert torch.equal(feat1[0], expect[1])
 
 
@@ -340,8 +340,8 @@ def test_tile_depth_tables_and_culled_search():
     sc = synth.make_scene(V, 80 * 4, 96 * 4, S=S, C=4, zero_frac=0.1, seed=90, device=DEV)
     sc.depths[0, 1, 0, 0, :64, :64] = float("nan")          # a block of NaN depths: never a neighbour, never in a range
     args = (sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0])
-    clouds = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True)
-    plain = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True, want_tiles=False)
+    clouds = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True, want_tiles=True)
+    plain = ops.cloud_build(*args, levels=[0, 1, 2], want_valid=True)
     for c in clouds:
         assert c.tile_z is not None and c.tile_z.shape == (S, V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
         x4 = c.xyz4.view(S, V, c.H, c.W, 4).cpu().numpy().astype(np.float32)
@@ -391,12 +391,21 @@ def test_tile_depth_tables_and_culled_search():
         tested, kept = int(stats[7]), int(stats[8])
         assert tested > 0 and kept < tested, (tested, kept)
         check_knn_raster(c, coords, 5, skip_invalid=True)
-        d1, i1 = ops.knn(ops.Search.from_cloud(c), coords, 16)
-        d0, i0 = ops.knn(ops.Search.from_cloud(c0), coords, 16)
+        d1, i1 = ops.knn(ops.Search.from_cloud(c, tiles=True), coords, 16)
+        d0, i0 = ops.knn(ops.Search.from_cloud(c0), coords, 16)          # no tables: windows only
+        assert c0.tile_z is None
         assert torch.equal(i0, i1) and torch.equal(d0, d1)
         # a single frame of the cloud (the reference's per-frame calls): the table is sliced with it
-        d2_, i2_ = ops.knn(ops.Search.from_cloud(c, frame=1), coords[1:2].contiguous(), 16)
+        d2_, i2_ = ops.knn(ops.Search.from_cloud(c, frame=1, tiles=True), coords[1:2].contiguous(), 16)
         assert torch.equal(i2_, i1[1:2]) and torch.equal(d2_, d1[1:2])
+    # buffers reused in place for the next window: the old tables are stale and must be rebuilt before use
+    sc2 = synth.make_scene(V, 80 * 4, 96 * 4, S=S, C=4, zero_frac=0.1, seed=92, device=DEV)
+    again = ops.cloud_build(sc2.fmaps[0], sc2.depths[0, :, :, 0], sc2.intrs[0], sc2.extrs[0], levels=[0, 1, 2], want_valid=True,
+                            reuse=clouds)
+    assert all(not c.tiles_ready for c in again)
+    for c in again:
+        check_knn_raster(c, coords, 16)
+        assert c.tiles_ready
 
 
 def test_raster_knn_skewed_intrinsics_and_moving_cameras():
