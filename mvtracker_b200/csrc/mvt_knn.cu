@@ -174,10 +174,13 @@ __device__ __forceinline__ float dot8_bf16(const uint4 &a, const uint4 &b) {
 // GW = 32: one warp per query.   GW = 16 (raster search, MODE 1/2, V <= 16): one half warp per query.
 // Grid: x = query blocks of one frame, y = frame b, z = pyramid level.
 #ifndef MVT_CORR_MINB
-#define MVT_CORR_MINB 1
+#define MVT_CORR_MINB 8
+#endif
+#ifndef MVT_CORR_THREADS
+#define MVT_CORR_THREADS 128      // 4 queries per block, 8 blocks per SM: 64 registers per thread (no spills), 32 warps per SM
 #endif
 template <int MODE, bool RASTER_ONLY, int GW>
-__global__ void __launch_bounds__(256, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
+__global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
     __shared__ unsigned char win_tab[32];
     init_window_table(win_tab);
     const int lane = threadIdx.x & 31;
@@ -556,18 +559,18 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     bool half = all_raster && fast && aligned;      // half-warp groups: k <= 16 (part of `fast`) and V <= 16
     for (int l = 0; l < n_levels; ++l) half = half && levels[l].search.V <= 16;
     if (mvt::g_group_width != 16) half = false;
-    const int qpb = half ? 16 : 8;                  // queries per 256-thread block
+    const int qpb = (half ? 2 : 1) * (MVT_CORR_THREADS / 32);      // queries per block
     const dim3 grid((unsigned)((M + qpb - 1) / qpb), (unsigned)B, (unsigned)n_levels);
     if (feat_dtype == MVT_BF16) {
-        if (half) knn_corr_kernel<2, true, 16><<<grid, 256, 0, st>>>(p);
-        else if (all_raster) knn_corr_kernel<2, true, 32><<<grid, 256, 0, st>>>(p);
-        else knn_corr_kernel<2, false, 32><<<grid, 256, 0, st>>>(p);
+        if (half) knn_corr_kernel<2, true, 16><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else if (all_raster) knn_corr_kernel<2, true, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else knn_corr_kernel<2, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     } else if (fast && aligned) {
-        if (half) knn_corr_kernel<1, true, 16><<<grid, 256, 0, st>>>(p);
-        else if (all_raster) knn_corr_kernel<1, true, 32><<<grid, 256, 0, st>>>(p);
-        else knn_corr_kernel<1, false, 32><<<grid, 256, 0, st>>>(p);
+        if (half) knn_corr_kernel<1, true, 16><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else if (all_raster) knn_corr_kernel<1, true, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else knn_corr_kernel<1, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     } else {
-        knn_corr_kernel<0, false, 32><<<grid, 256, 0, st>>>(p);
+        knn_corr_kernel<0, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     }
     MVT_CHECK_LAUNCH("knn_corr");
     return MVT_OK;
