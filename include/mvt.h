@@ -217,10 +217,15 @@ int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int B, const fl
 
 /* mvt_corr_from_idx whose records go to out [B, M, n_levels*k*4] of every rank: a record is stored by the rank that owns
  * the neighbour's features; records of missing neighbours (index < 0) are stored as zeros by rank `shard` for its own
- * track shard.  After the barrier every rank holds the complete block. */
+ * track shard.  After the barrier every rank holds the complete block.
+ * all_xyz4 / n_all (optional, [n_levels]): this rank's replica of every view's records per level ([B, n_all[l], 4], what
+ * mvt_cloud_build_shared filled).  Then each rank writes the three offsets of every neighbour into its own block itself
+ * and only the correlation value of a record (4 of its 16 bytes) is stored to the other ranks: a quarter of the NVLink
+ * traffic, same bits. */
 int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
                              int n_shards, int shard, const int *idx, const void *targets, const float *coords,
-                             const mvt_peers *out, long long out_row_stride, void *stream);
+                             const mvt_peers *out, long long out_row_stride, const float *const *all_xyz4,
+                             const long long *n_all, void *stream);
 
 /* Debug / profiling: per-segment grid parameters copied out for inspection.
  * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */

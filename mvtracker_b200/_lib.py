@@ -87,7 +87,8 @@ def lib():
     L.mvt_knn_keys.argtypes = [C.POINTER(Search), C.POINTER(ll), ci, ci, vp, ci, ci, ci, vp, ci, vp, vp, vp, vp]
     L.mvt_cloud_build_shared.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, C.POINTER(Peers), ci, ci, vp]
     L.mvt_knn_idx_shared.argtypes = [C.POINTER(Search), ci, ci, vp, ci, ci, ci, ci, C.POINTER(Peers), vp]
-    L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll, vp]
+    L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll,
+                                           C.POINTER(vp), C.POINTER(ll), vp]
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
     L.mvt_tile_depth_floats.argtypes = [ci, ci, ci, ci]

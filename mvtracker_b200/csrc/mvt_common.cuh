@@ -57,6 +57,13 @@ __device__ __forceinline__ void store_all(const PeersDev &P, size_t i, float4 v)
         for (int r = 0; r < P.n; ++r) P.ptr[r][i] = v;
     }
 }
+__device__ __forceinline__ void store_all_f32(const PeersDev &P, size_t i, float v) {      // i in floats
+    if (P.mc) {
+        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(reinterpret_cast<float *>(P.mc) + i), "f"(v) : "memory");
+    } else {
+        for (int r = 0; r < P.n; ++r) reinterpret_cast<float *>(P.ptr[r])[i] = v;
+    }
+}
 __host__ inline PeersDev peers_dev(const mvt_peers *u) {
     PeersDev d;
     d.mc = nullptr; d.n = 0;

@@ -87,7 +87,10 @@ template <bool RASTER_ONLY>
 #ifndef MVT_KEYS_MINB
 #define MVT_KEYS_MINB 4
 #endif
-__global__ void __launch_bounds__(256, MVT_KEYS_MINB) knn_keys_kernel(const KeysParams p) {
+#ifndef MVT_KEYS_THREADS
+#define MVT_KEYS_THREADS 256
+#endif
+__global__ void __launch_bounds__(MVT_KEYS_THREADS, MVT_KEYS_MINB) knn_keys_kernel(const KeysParams p) {
     __shared__ unsigned char win_tab[32];
     __shared__ unsigned next_item;
     if (threadIdx.x == 0) next_item = 0u;
@@ -138,6 +141,8 @@ struct OwnedLevel {
     const void *fvec;       // [B, Nloc, 128]
     long long lo, hi;       // owned global index range [lo, hi), Nloc = hi - lo
     long long out_off;
+    const float4 *all_xyz4; // [B, n_all] records of ALL views (this rank's replica), or null -- see corr_from_idx_kernel
+    long long n_all;
 };
 struct CorrIdxParams {
     OwnedLevel lv[MVT_MAX_LEVELS];
@@ -177,7 +182,24 @@ __global__ void __launch_bounds__(256, MVT_CIDX_MINB) corr_from_idx_kernel(const
     const int row = own ? (int)(gi - L.lo) : 0;        // local row of neighbour `lane`
     const size_t nloc = (size_t)(L.hi - L.lo);
     unsigned om = __ballot_sync(FULL, own);
-    if (om == 0u) {      // none of this query's neighbours lives here: no target row, no gather
+    // Split records (shared output + a replica of every view's records on each rank): the offsets of ALL k neighbours are
+    // computed here from the replica and written to this rank's own block with plain stores; only the correlation values
+    // (4 of a record's 16 bytes, known to the rank that holds the feature row) cross NVLink.
+    const bool split = L.all_xyz4 != nullptr && p.out_peers.n != 0;
+    if (split) {
+        if (lane < k) {
+            float *o = p.out + q * p.row_stride + L.out_off + (size_t)lane * 4;
+            if (gi >= 0) {
+                const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+                const float4 n = __ldg(L.all_xyz4 + (size_t)b * L.n_all + gi);
+                o[1] = n.x - qx;
+                *reinterpret_cast<float2 *>(o + 2) = make_float2(n.y - qy, n.z - qz);
+            } else {
+                *reinterpret_cast<float4 *>(o) = make_float4(0.f, 0.f, 0.f, 0.f);      // missing neighbour: nobody owns it
+            }
+        }
+        if (om == 0u) return;
+    } else if (om == 0u) {      // none of this query's neighbours lives here: no target row, no gather
         if (lane < k) {
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
             if (p.out_peers.n == 0) *reinterpret_cast<float4 *>(p.out + q * p.row_stride + L.out_off + (size_t)lane * 4) = z;
@@ -258,6 +280,10 @@ __global__ void __launch_bounds__(256, MVT_CIDX_MINB) corr_from_idx_kernel(const
             }
         }
     }
+    if (split) {
+        if (own) store_all_f32(p.out_peers, (size_t)(q * p.row_stride + L.out_off) + (size_t)lane * 4, __fdiv_rn(corr_mine, p.scale));
+        return;
+    }
     if (lane < k) {
         float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);
         if (own) rec = make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz);
@@ -302,11 +328,11 @@ MVT_EXPORT int mvt_knn_keys(const mvt_search *searches, const long long *index_o
     const long long n_items = (long long)n_levels * B * padded;
     MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_keys: too many queries (%lld)", n_items);
     p.n_items = (unsigned)n_items;
-    const unsigned grid = one_wave_grid(n_items, 8, MVT_KEYS_MINB);
+    const unsigned grid = one_wave_grid(n_items, MVT_KEYS_THREADS / 32, MVT_KEYS_MINB);
     bool all_raster = true;
     for (int l = 0; l < n_levels; ++l) all_raster = all_raster && p.sd[l].raster;
-    if (all_raster) knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
-    else knn_keys_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    if (all_raster) knn_keys_kernel<true><<<grid, MVT_KEYS_THREADS, 0, (cudaStream_t)stream>>>(p);
+    else knn_keys_kernel<false><<<grid, MVT_KEYS_THREADS, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_keys");
     return MVT_OK;
 }
@@ -325,7 +351,8 @@ MVT_EXPORT int mvt_topk_merge(const unsigned long long *keys_in, int n_lists, lo
 
 static int corr_from_idx_impl(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
                               int n_shards, const int *idx, const void *targets, const float *coords, float *out,
-                              long long out_row_stride, const mvt_peers *out_peers, int shard, void *stream) {
+                              long long out_row_stride, const mvt_peers *out_peers, int shard, void *stream,
+                              const float *const *all_xyz4 = nullptr, const long long *n_all = nullptr) {
     using namespace mvt;
     MVT_CHECK_ARG(levels && idx && targets && coords && (out || out_peers), "mvt_corr_from_idx: null pointer");
     MVT_CHECK_ARG(!out_peers || (out_peers->n >= 1 && out_peers->n <= MVT_MAX_PEERS && shard >= 0 && shard < n_shards),
@@ -347,6 +374,11 @@ static int corr_from_idx_impl(const mvt_owned_level *levels, int n_levels, int B
         MVT_CHECK_ARG(u.xyz4 && u.fvec && u.hi > u.lo && u.lo >= 0, "mvt_corr_from_idx: level %d: bad shard", l);
         MVT_CHECK_ARG((((uintptr_t)u.xyz4 | (uintptr_t)u.fvec) & 15) == 0 && u.out_offset % 4 == 0, "mvt_corr_from_idx: level %d: 16-byte alignment", l);
         p.lv[l].xyz4 = (const float4 *)u.xyz4; p.lv[l].fvec = u.fvec; p.lv[l].lo = u.lo; p.lv[l].hi = u.hi; p.lv[l].out_off = u.out_offset;
+        p.lv[l].all_xyz4 = nullptr; p.lv[l].n_all = 0;
+        if (all_xyz4 && all_xyz4[l]) {
+            MVT_CHECK_ARG(n_all && n_all[l] >= u.hi && ((uintptr_t)all_xyz4[l] & 15) == 0, "mvt_corr_from_idx_shared: level %d: bad replica", l);
+            p.lv[l].all_xyz4 = (const float4 *)all_xyz4[l]; p.lv[l].n_all = n_all[l];
+        }
     }
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
     dim3 grid((unsigned)((M + 7) / 8), (unsigned)B, (unsigned)n_levels);
@@ -365,10 +397,12 @@ MVT_EXPORT int mvt_corr_from_idx(const mvt_owned_level *levels, int n_levels, in
 
 MVT_EXPORT int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
                                         int n_shards, int shard, const int *idx, const void *targets, const float *coords,
-                                        const mvt_peers *out, long long out_row_stride, void *stream) {
+                                        const mvt_peers *out, long long out_row_stride, const float *const *all_xyz4,
+                                        const long long *n_all, void *stream) {
     MVT_CHECK_ARG(out, "mvt_corr_from_idx_shared: null out");
     return corr_from_idx_impl(levels, n_levels, B, M, C, feat_dtype, k, n_shards, idx, targets, coords,
-                              (float *)out->ptr[shard < MVT_MAX_PEERS && shard >= 0 ? shard : 0], out_row_stride, out, shard, stream);
+                              (float *)out->ptr[shard < MVT_MAX_PEERS && shard >= 0 ? shard : 0], out_row_stride, out, shard, stream,
+                              all_xyz4, n_all);
 }
 
 MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int B, const float *query, int Ms, int k,
@@ -394,8 +428,8 @@ MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int 
     const long long n_items = (long long)n_levels * B * Ms;
     MVT_CHECK_ARG(n_items < (1ll << 31), "mvt_knn_idx_shared: too many queries (%lld)", n_items);
     p.n_items = (unsigned)n_items;
-    const unsigned grid = one_wave_grid(n_items, 8, MVT_KEYS_MINB);
-    knn_keys_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    const unsigned grid = one_wave_grid(n_items, MVT_KEYS_THREADS / 32, MVT_KEYS_MINB);
+    knn_keys_kernel<true><<<grid, MVT_KEYS_THREADS, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_idx_shared");
     return MVT_OK;
 }

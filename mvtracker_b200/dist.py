@@ -25,6 +25,8 @@ the CPU tests inject a numpy stand-in to exercise the exchanges over gloo.
 """
 from typing import List, Optional, Sequence, Tuple
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -34,7 +36,6 @@ class SharedBuffer:
     the NVSwitch multicast address when the allocation has one, and every rank's peer mapping."""
 
     def __init__(self, shape, dtype, device, group=None):
-        import os
         import torch.distributed._symmetric_memory as symm
         from ._lib import Peers
         self.t = symm.empty(*shape, dtype=dtype, device=device)
@@ -101,6 +102,7 @@ class ShardedWindow:
         self.levels = len(clouds) if n_levels is None else n_levels     # a rank without views still has to know
         self.width = self.levels * k * 4
         self._bufs = {}
+        self.split_records = False   # "p2p": only correlation values cross NVLink, offsets are filled in locally
         # phase-A effort per query: the fixed windows (30 pixels per view) plus about one growth step
         self.budget = 4 * 30 * max(1, v1 - v0)
         self.mode = "views"      # build() switches to "tracks" when it replicates the 16-byte records
@@ -151,6 +153,7 @@ class ShardedWindow:
         dev = fmaps_local.device
         win = cls([], v0, v0 + Vloc, V_total, k, group, be, n_levels=len(levels))
         win.mode = "p2p"
+        win.split_records = not os.environ.get("MVT_FULL_RECORDS")    # (debugging knob: whole 16-byte records cross NVLink)
         if reuse is not None and reuse.mode == "p2p":
             win._bufs = reuse._bufs
         shared = {}
@@ -355,7 +358,8 @@ class ShardedWindow:
         idx_all.barrier()
         mark()
         owned = [(c.xyz4, c.fvec, self.v0 * c.H * c.W, self.v1 * c.H * c.W) for c in self.clouds]
-        be.corr_from_idx_shared(owned, idx_all.t, targets, coords, k, r, res.peers, res.t.stride(1))
+        be.corr_from_idx_shared(owned, idx_all.t, targets, coords, k, r, res.peers, res.t.stride(1),
+                                replicas=[c.xyz4 for c in self.full] if self.split_records else None)
         mark()
         res.barrier()
         mark()

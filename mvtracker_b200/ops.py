@@ -422,8 +422,10 @@ def knn_idx_shared(searches: Sequence, query: torch.Tensor, k: int, shard: int, 
 
 
 def corr_from_idx_shared(owned: Sequence, idx: torch.Tensor, targets: torch.Tensor, coords: torch.Tensor, k: int, shard: int,
-                         peers, row_stride: int) -> None:
-    """corr_from_idx whose records are stored into the [B, M, L*k*4] block of every rank (peers)."""
+                         peers, row_stride: int, replicas: Optional[Sequence[torch.Tensor]] = None) -> None:
+    """corr_from_idx whose records are stored into the [B, M, L*k*4] block of every rank (peers).
+    replicas: per level, this rank's copy of every view's records [B, N_all, 4]; then only correlation values cross
+    NVLink and each rank fills in the offsets itself."""
     _need_cuda(targets, "targets"); _need_cuda(idx, "idx")
     B, M, Cc = targets.shape
     tg, cq = targets.contiguous(), _f32c(coords)
@@ -434,5 +436,11 @@ def corr_from_idx_shared(owned: Sequence, idx: torch.Tensor, targets: torch.Tens
         if fvec.dtype != tg.dtype:
             raise MvtError(f"targets dtype {tg.dtype} != fvec dtype {fvec.dtype}")
         lv[i] = _lib.OwnedLevel(xyz4.data_ptr(), fvec.data_ptr(), int(lo), int(hi), i * k * 4)
+    rp = na = None
+    if replicas is not None:
+        assert len(replicas) == L and all(r.is_contiguous() and r.dtype == torch.float32 and r.shape[0] == B for r in replicas)
+        rp = (C.c_void_p * L)(*[r.data_ptr() for r in replicas])
+        na = (C.c_longlong * L)(*[r.shape[1] for r in replicas])
     check(lib().mvt_corr_from_idx_shared(lv, L, B, M, Cc, _feat_dtype(tg), int(k), int(idx.shape[0]), int(shard), _ptr(idx),
-                                         _ptr(tg), _ptr(cq), C.byref(peers), int(row_stride), _stream()), "mvt_corr_from_idx_shared")
+                                         _ptr(tg), _ptr(cq), C.byref(peers), int(row_stride), rp, na, _stream()),
+          "mvt_corr_from_idx_shared")

@@ -108,7 +108,8 @@ def _peers(tensors):
 
 @pytest.mark.parametrize("world", [1, 2, 3, 8])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_peer_store_kernels_equal_fused(world, dtype):
+@pytest.mark.parametrize("split", [False, True])     # True: only correlation values are stored to the peers
+def test_peer_store_kernels_equal_fused(world, dtype, split):
     """The "p2p" mode's three kernels (cloud_build_shared, knn_idx_shared, corr_from_idx_shared) with every rank's
     symmetric buffer emulated by a private buffer in this process: each rank's copy must equal the fused kernel's result."""
     V, S, M, k, L = 4, 3, 203, 16, 4
@@ -153,6 +154,9 @@ def test_peer_store_kernels_equal_fused(world, dtype):
         v0, v1 = view_range(r, world, V)
         owned = [(c.xyz4, c.fvec, v0 * c.H * c.W, v1 * c.H * c.W) for c in local[r]]
         if owned:
-            ops.corr_from_idx_shared(owned, idx_all[r], targets, coords, k, r, _peers(outs), outs[r].stride(1))
+            ops.corr_from_idx_shared(owned, idx_all[r], targets, coords, k, r, _peers(outs), outs[r].stride(1),
+                                     replicas=recs[r] if split else None)
     for r in range(world):
+        if split and not local[r]:
+            continue            # a rank without views runs no kernel (dist.py's "p2p" mode needs a view on every rank)
         assert torch.equal(outs[r], fused)

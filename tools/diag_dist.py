@@ -49,6 +49,15 @@ for _ in range(R):
     for i, e in enumerate(marks):
         acc[i] += prev.elapsed_time(e); prev = e
 print(f"rank {rank}: " + "  ".join(f"{n}={a / R:.3f}ms" for n, a in zip(names, acc)) + f"  total={sum(acc) / R:.3f}ms", flush=True)
+# back-to-back calls: GPU time per call (events around the loop) and host time per call (how long Python takes to issue one)
+import time
+torch.cuda.synchronize(); dist.barrier()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(); t0 = time.perf_counter()
+for _ in range(40):
+    win.corr(targets, coords)
+t1 = time.perf_counter(); e1.record(); torch.cuda.synchronize()
+print(f"rank {rank}: back-to-back corr: {e0.elapsed_time(e1) / 40:.3f} ms per call on the GPU, {(t1 - t0) / 40 * 1e3:.3f} ms of host time to issue one", flush=True)
 # raw NCCL timings at these sizes
 for name, fn in (("all_reduce 50MB", lambda: dist.all_reduce(out)),):
     for _ in range(3): fn()
