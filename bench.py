@@ -44,6 +44,10 @@ def parse_args():
                     help="raster: search the depth rasters directly (no index build); grid: hashed grid")
     ap.add_argument("--dist-mode", default="p2p", choices=["p2p", "tracks", "views"],
                     help="N > 1: tracks = replicate the 16-byte records, search per track shard; views = search own views, merge candidates")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="N > 1: strong = ONE window sharded over the ranks (views, then tracks; the default, what the path's "
+                         "multi-GPU design is about); weak = every rank tracks its own sequence's window with the single-GPU path "
+                         "(independent replicas, no exchange)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
@@ -172,14 +176,15 @@ def run_reference(args):
     r["value"] = v
     line = {"impl": "reference", "metric": "knn_corr_queries_per_s", "value": v, "unit": "queries/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sorted(secs)[len(secs) // 2],
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_dict(w, args), "cpu_baseline": r,
             "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def config_dict(w, args, world=1):
+def config_dict(w, args, world=1, weak=False):
     return {"parallelism": "1 GPU: fused knn_corr kernel" if world == 1 else
+            f"{world} GPUs: independent replicas, each rank runs the single-GPU path on its own sequence's window (no exchange)" if weak else
             (f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
              f"index lists all-gathered; records of locally owned neighbours all-reduced (NCCL)" if getattr(args, "dist_mode", "tracks") == "tracks" else
              f"{world} GPUs: views sharded for the cloud build (features stay local); point records, index lists and result records are stored by the producing kernels "
@@ -224,10 +229,12 @@ def run_ours(args):
     iters, N, V = args.iters, w["N"], w["V"]
     warmup = max(args.warmup, 3)
     L = _lib.lib()
+    weak = args.scaling == "weak" and world > 1
+    pw = 1 if weak else world          # ranks ONE window is sharded over
 
     # ---- synthetic inputs, identical on every rank (same seed); tracks are sampled from the full level-0 cloud ---------
-    sc = synth.make_scene(V, w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac, seed=72,
-                          device=dev, dtype=fdtype)
+    sc = synth.make_scene(V, w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac,
+                          seed=72 + (rank if weak else 0), device=dev, dtype=fdtype)
     fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
     c0 = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=[0], want_fvec=False, want_spacing=False)[0]
     # tracks follow the surface at their pixel (+ N(0, 2 cm)), i.e. near the cloud in every frame like converged tracks
@@ -239,7 +246,7 @@ def run_ours(args):
     width = LEVELS * K_NN * 4
     outs = [torch.empty(S_WINDOW, N, width, device=dev, dtype=torch.float32) for _ in range(iters)]
     K_all, E_all = K, E
-    if world > 1:
+    if pw > 1:
         v0, v1 = view_range(rank, world, V)
         fm, dp, K, E = fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous()
         del sc
@@ -250,7 +257,7 @@ def run_ours(args):
 
     def step(ev=None):
         if ev is not None: ev[0].record()
-        if world == 1:
+        if pw == 1:
             clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=(args.search == "grid"),
                                      reuse=None if state["win"] is None else state["win"].clouds)
             if ev is not None: ev[1].record()
@@ -304,7 +311,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_step = total_ms / args.steps
-    queries = iters * LEVELS * S_WINDOW * N
+    queries = iters * LEVELS * S_WINDOW * N * (world if weak else 1)
     value = queries / (ms_step * 1e-3)
 
     # ---- per-kernel split (separate, untimed-for-the-metric pass with events between the stages) -------------------------
@@ -326,16 +333,16 @@ def run_ours(args):
     peak, peak_src = _peak()
     v_loc = fm.shape[0]
     q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4          # 9164 B (fp32) / 4812 B (bf16)
-    corr_bytes = LEVELS * S_WINDOW * N * q_bytes / world                              # per rank: its share of the gathers
+    corr_bytes = LEVELS * S_WINDOW * N * q_bytes / pw                                 # per rank: its share of the gathers
     pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * S_WINDOW
     cloud_bytes = fm.numel() * esz + dp.numel() * 4 + pts * (C_FEAT * esz + 12)       # SURVEY.md 8d (xyz4 records not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
-                     "what": "fused knn_corr kernel" if world == 1 else "search kernels + index all-gather + corr_from_idx + all-reduce (per iteration)"},
+                     "what": "fused knn_corr kernel" if pw == 1 else "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6,
-                        "what": "camera_prep + cloud_build (4 levels, one pass)" + ("" if world == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
+                        "what": "camera_prep + cloud_build (4 levels, one pass)" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
     }
-    if args.search == "grid" and world == 1:
+    if args.search == "grid" and pw == 1:
         kern["grid_build"] = {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0}
     step_sum = sum(kv["ms"] * kv["launches_per_step"] if name != "grid_build" else kv["ms"] for name, kv in kern.items())
     for name, kv in kern.items():
@@ -348,13 +355,13 @@ def run_ours(args):
                 "step_frac": (corr_bytes * iters + cloud_bytes) / (ms_step * 1e-3) / 1e9 / peak}
 
     line = {"metric": "knn_corr_queries_per_s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
-            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args, world), "clocks": clocks,
+            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if weak else "strong",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args, world, weak), "clocks": clocks,
             "gpu_launches": int(launches), "roofline": roofline, "kernels": kern}
 
     # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------------
     if not args.no_e2e:
-        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if world > 1 else 0, K_all, E_all)
+        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if pw > 1 else 0, K_all, E_all, weak)
         line["e2e"] = e2e
     state["win"] = None
     if sampler:
@@ -368,7 +375,7 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, K_all, E_all):
+def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, K_all, E_all, weak=False):
     """Each step: this rank's inputs pinned host -> device, the public API (N = 1: the drop-in mirror of the reference seam --
     init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat;
     N > 1: mvtracker_b200.dist.ShardedWindow), then every iteration's correlation block -> pinned host."""
@@ -377,6 +384,7 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, 
     from mvtracker_b200 import dropin
     from mvtracker_b200.dist import ShardedWindow
     iters, N, V = args.iters, w["N"], w["V"]
+    pw = 1 if weak else world
     host_in = [t.cpu().pin_memory() for t in (fm, dp, K, E)]
     host_cam = [t.cpu().pin_memory() for t in (K_all, E_all)]
     host_ct = [(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(coords_it, targets_it)]
@@ -387,7 +395,7 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, 
 
     def step():
         fmd, dpd, Kd, Ed = [t.to(dev, non_blocking=True) for t in host_in]
-        if world == 1:
+        if pw == 1:
             blocks = []
             for lvl in range(LEVELS):
                 xyz, fvec = dropin.init_pointcloud_from_rgbd(fmd[None], dpd[None, :, :, None], Kd[None], Ed[None], stride=STRIDE, level=lvl)
@@ -401,7 +409,7 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, 
         for i in range(iters):
             coords = host_ct[i][0].to(dev, non_blocking=True)
             ffeats = host_ct[i][1].to(dev, non_blocking=True)
-            if world == 1:
+            if pw == 1:
                 fcorrs = [blocks[l].corr_sample(ffeats, coords).reshape(S_WINDOW, N, -1) for l in range(LEVELS)]
                 host_out[i].copy_(torch.cat(fcorrs, dim=-1), non_blocking=True)
             else:
@@ -433,10 +441,10 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, 
         h2d, d2h = int(hb[0].item()), int(hb[1].item())
     ms /= n
     dropin.clear_caches()
-    queries = iters * LEVELS * S_WINDOW * N
+    queries = iters * LEVELS * S_WINDOW * N * (world if weak else 1)
     return {"value": queries / (ms * 1e-3), "unit": "queries/s", "ms_per_step": ms, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": n,
-            "api": ("mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample)" if world == 1 else
+            "api": ("mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample)" if pw == 1 else
                     "mvtracker_b200.dist.ShardedWindow (build / corr)") + ", pinned host buffers, all ranks summed"}
 
 
