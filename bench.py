@@ -26,7 +26,9 @@ S_WINDOW, C_FEAT, K_NN, LEVELS, STRIDE = 12, 128, 16, 4, 4
 DEFAULT_WORKLOAD = "panoptic"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full captures under
 # profiles/ (workload, dtype, kernel) -> bytes; None until that capture exists.
-NCU_TRAFFIC = {}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full captures under profiles/
+NCU_TRAFFIC = {("panoptic", "f32", "knn_corr"): 1434346792, ("panoptic", "f32", "cloud_build"): 15580389000,
+               ("droid", "f32", "knn_corr"): 498648576}
 
 
 def parse_args():
