@@ -178,7 +178,7 @@ def run_reference(args):
     r["value"] = v
     line = {"impl": "reference", "metric": "knn_corr_queries_per_s", "value": v, "unit": "queries/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sorted(secs)[len(secs) // 2],
-            "higher_is_better": True, "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_dict(w, args), "cpu_baseline": r,
             "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
