@@ -18,6 +18,9 @@ def t(fn, n=10):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n
 lv = [(c, c.fvec, 16) for c in full]
+if os.environ.get("MVT_GROUP_WIDTH"):
+    from mvtracker_b200 import _lib
+    _lib.lib().mvt_debug_set_group_width(int(os.environ["MVT_GROUP_WIDTH"]))
 out = torch.empty(S, N, 256, device=dev)
 print(f"fused knn_corr, {S * N * 4} queries: {t(lambda: ops.knn_corr(lv, targets, coords, out=out)):.3f} ms")
 for frac in (1, 2, 4, 8):
