@@ -260,20 +260,44 @@ __global__ void __launch_bounds__(256, MVT_CLOUD_MINB) cloud_build_kernel(const 
     const int yy = tid >> 5, xx = tid & 31;
     const bool inside = (y0 + yy < H) && (x0 + xx < W);
     const size_t pix = (size_t)(y0 + yy) * W + (x0 + xx);
+    const bool pairs = ((W & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.fmaps) & 3) == 0);   // 4-byte pixel pairs are aligned
 
     for (int c0 = 0; c0 < C; c0 += CC) {
         __syncthreads();   // previous chunk's readers of t0..t3 are done
-        // all loads of a batch are issued before the first shared-memory store: MVT_CLOUD_BATCH x 4 B per thread in flight
+        if (sizeof(T) == 2 && pairs) {
+            // 2-byte features: a thread loads TWO adjacent pixels of one channel (4 B), so that a warp instruction moves
+            // 128 B like the fp32 path (half-warps on consecutive rows); threads 128..255 take the odd channels.  All 16
+            // loads of the chunk are in flight before the first shared-memory store.
+            const int hsel = tid >> 7, r2 = (tid >> 4) & 7, pp = tid & 15;
+            const bool in2 = (y0 + r2 < H) && (x0 + 2 * pp < W);
+            const size_t pix2 = (size_t)(y0 + r2) * W + (size_t)(x0 + 2 * pp);
+            const bool swap = (tid >> 4) & 1;          // rows r2, r2+1 of a warp map to the same banks: alternate the order
+            unsigned val[CC / 2];
 #pragma unroll
-        for (int cb = 0; cb < CC; cb += MVT_CLOUD_BATCH) {
-            float val[MVT_CLOUD_BATCH];
-#pragma unroll
-            for (int c = 0; c < MVT_CLOUD_BATCH; ++c) {
-                val[c] = 0.f;
-                if (inside && c0 + cb + c < C) val[c] = to_f<T>(__ldg(fm + (size_t)(c0 + cb + c) * HW + pix));
+            for (int c = 0; c < CC / 2; ++c) {
+                const int ch = c0 + 2 * c + hsel;
+                val[c] = 0u;
+                if (in2 && ch < C) val[c] = __ldg(reinterpret_cast<const unsigned *>(fm + (size_t)ch * HW + pix2));
             }
 #pragma unroll
-            for (int c = 0; c < MVT_CLOUD_BATCH; ++c) t0[(cb + c) * S0 + tid] = val[c];
+            for (int c = 0; c < CC / 2; ++c) {
+                float *d = t0 + (2 * c + hsel) * S0 + r2 * 32 + 2 * pp;
+                const float lo = __uint_as_float(val[c] << 16), hi = __uint_as_float(val[c] & 0xffff0000u);
+                if (swap) { d[1] = hi; d[0] = lo; } else { d[0] = lo; d[1] = hi; }
+            }
+        } else {
+            // all loads of a batch are issued before the first shared-memory store: MVT_CLOUD_BATCH x 4 B per thread in flight
+#pragma unroll
+            for (int cb = 0; cb < CC; cb += MVT_CLOUD_BATCH) {
+                float val[MVT_CLOUD_BATCH];
+#pragma unroll
+                for (int c = 0; c < MVT_CLOUD_BATCH; ++c) {
+                    val[c] = 0.f;
+                    if (inside && c0 + cb + c < C) val[c] = to_f<T>(__ldg(fm + (size_t)(c0 + cb + c) * HW + pix));
+                }
+#pragma unroll
+                for (int c = 0; c < MVT_CLOUD_BATCH; ++c) t0[(cb + c) * S0 + tid] = val[c];
+            }
         }
         __syncthreads();
         if (need1) pool_tile<T>(t0, S0, 32, t1, S1, 16, 64);
