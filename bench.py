@@ -57,8 +57,18 @@ def parse_args():
 
 
 def workload_cfg(name):
+    """A named workload (synth.WORKLOADS), or a point of the scaling sweep: "sweep:V=8,P0=1M,N=16k" (V views, P0 fused
+    level-0 points per frame, N tracks; the raster is 4:5, as the panoptic one)."""
     from mvtracker_b200 import synth
-    w = dict(synth.WORKLOADS[name])
+    if name.startswith("sweep:"):
+        kv = dict(item.split("=") for item in name[6:].split(","))
+        num = lambda t: int(float(t[:-1]) * {"k": 1024, "M": 1024 * 1024}[t[-1]]) if t[-1] in "kM" else int(t)
+        V, P0, N = int(kv["V"]), num(kv["P0"]), num(kv["N"])
+        hs = max(8, int(round((P0 / V / 1.25) ** 0.5 / 8)) * 8)          # level-0 raster rows (multiple of 8: 4 levels)
+        ws = max(8, int(round(P0 / V / hs / 8)) * 8)
+        w = {"V": V, "H": hs * STRIDE, "W": ws * STRIDE, "N": N, "T": 24}
+    else:
+        w = dict(synth.WORKLOADS[name])
     w["name"] = name
     w["Hs"], w["Ws"] = w["H"] // STRIDE, w["W"] // STRIDE
     return w
