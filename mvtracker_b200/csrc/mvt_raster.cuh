@@ -43,22 +43,37 @@ constexpr int kPW = 2 * kM0 + 2, kPH = 2 * kM0 + 1;    // 6 x 5 pixels: x in [fl
 // The first-pass window pixels ordered nearest-first from the query's projection (which lies in [0,1) x [-0.5,0.5]
 // relative to pixel (kM0, kM0) of the window): tab[rank] = wx | wy << 4.  Candidates are then enumerated rank-major,
 // view-minor, so the first batch -- the one that is sorted and sets the first threshold -- holds the pixels nearest
-// to the projection in EVERY view and few later candidates survive it.  Call with all threads of the block.
+// to the projection in EVERY view and few later candidates survive it.
+// The table is a compile-time constant (eight 32-bit immediates); every WARP keeps its own 32-byte copy in shared memory
+// (lane-indexed lookups), so no block-wide barrier is needed before the first search.
 constexpr int kNW = kPW * kPH;
-__device__ __forceinline__ void init_window_table(unsigned char *tab) {
-    const int l = threadIdx.x;
-    if (l < kNW) {
-        const int wy = l / kPW, wx = l - wy * kPW;
-        auto key = [](int x, int y) { int a = 2 * x - (2 * kM0 + 1), b = 2 * (y - kM0); return a * a + b * b; };
-        const int mykey = key(wx, wy);
+static_assert(kNW <= 32 && kPW <= 16 && kPH <= 16, "window table: 32 one-byte entries");
+__host__ __device__ constexpr int win_key(int x, int y) {
+    return (2 * x - (2 * kM0 + 1)) * (2 * x - (2 * kM0 + 1)) + (2 * (y - kM0)) * (2 * (y - kM0));
+}
+// 32-bit word i of the table: entries 4i .. 4i+3 (entry = wx | wy << 4 of the pixel with that nearest-first rank)
+__host__ __device__ constexpr unsigned win_tab_word(int i) {
+    unsigned word = 0;
+    for (int l = 0; l < kNW; ++l) {
+        const int wy = l / kPW, wx = l - wy * kPW, mykey = win_key(wx, wy);
         int rank = 0;
         for (int o = 0; o < kNW; ++o) {
-            const int oy = o / kPW, ox = o - oy * kPW, ok = key(ox, oy);
+            const int oy = o / kPW, ox = o - oy * kPW, ok = win_key(ox, oy);
             rank += (ok < mykey || (ok == mykey && o < l)) ? 1 : 0;
         }
-        tab[rank] = (unsigned char)(wx | (wy << 4));
+        if ((rank >> 2) == i) word |= (unsigned)(wx | (wy << 4)) << (8 * (rank & 3));
     }
-    __syncthreads();
+    return word;
+}
+template <int I> struct WinWord { static constexpr unsigned value = win_tab_word(I); };
+// tab: this warp's 32 bytes of shared memory (4-byte aligned).  Call with all lanes of the warp.
+__device__ __forceinline__ void init_window_table(unsigned char *tab) {
+    const int l = threadIdx.x & 31;
+    const unsigned w = l == 0 ? WinWord<0>::value : l == 1 ? WinWord<1>::value : l == 2 ? WinWord<2>::value
+                     : l == 3 ? WinWord<3>::value : l == 4 ? WinWord<4>::value : l == 5 ? WinWord<5>::value
+                     : l == 6 ? WinWord<6>::value : WinWord<7>::value;
+    if (l < 8) reinterpret_cast<unsigned *>(tab)[l] = w;
+    __syncwarp();
 }
 
 // tan-range [lo, hi] of the directions (in the half plane z > 0) from the origin to the disk of radius r centred at
