@@ -135,7 +135,10 @@ typedef struct mvt_corr_level {
 
 /* Fused kNN + neighbour gather + grouped dot-product correlation + offset encoding for up to 4 levels in one launch.
  * targets [B,M,C] (feature dtype), coords [B,M,3] fp32.
- * out: fp32; row (b,m) starts at out + (b*M+m)*out_row_stride; level l writes k*D floats at its out_offset, neighbour j
+ * out: fp32; row (b,m) starts at out + b*out_frame_stride + m*out_row_stride (out_frame_stride 0 = M*out_row_stride, the
+ * dense [B,M,.] block); with out_frame_stride = D_in, out_row_stride = S*D_in and out pointing at its column the block
+ * lands directly in the [N,S,D_in] transformer input that mvtracker.py:374-384 otherwise assembles with permute + cat.
+ * Level l writes k*D floats at its out_offset, neighbour j
  * at j*D:  [corr_0..corr_{G-1}, dx,dy,dz (add_offset), x,y,z (add_xyz)],  D = G + 3*add_offset + 3*add_xyz,
  * corr_g = <target_g, nbr_g> / sqrt(C/G)  (mvtracker.py:832-846).
  * idx_out: optional [n_levels,B,M,k] int32.
@@ -145,7 +148,8 @@ typedef struct mvt_corr_level {
  * and identical with or without it (entries < 0 or of unsearchable points disable it for that query).  May alias idx_out. */
 int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                  const void *targets, const float *coords, int add_offset, int add_xyz,
-                 float *out, long long out_row_stride, const int *idx_hint, int *idx_out, void *stream);
+                 float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
+                 void *stream);
 
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */

@@ -69,7 +69,7 @@ struct CorrParams {
     const void *targets;
     const float *coords;
     float *out;
-    long long row_stride;
+    long long row_stride, frame_stride;
     int *idx_out;
     const int *idx_hint;   // [n_levels,B,M,k] or null: any k points of the same clouds (e.g. last iteration's neighbours)
     float scale;      // sqrt(C/G)
@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
     if (p.idx_out && live && gl < k) p.idx_out[(((long long)lvl * p.B + b) * p.M + m) * k + gl] = (bi != kNoIdx) ? bi : -1;
 
     const int D = p.G + 3 * p.add_offset + 3 * p.add_xyz;
-    float *orow = p.out + q * p.row_stride + L.out_off;
+    float *orow = p.out + (long long)b * p.frame_stride + (long long)m * p.row_stride + L.out_off;
     const size_t seg = (size_t)b * L.sd.N;
     float corr_mine = 0.f;   // MODE 1/2: correlation of neighbour `gl` (GW == 16) / `lane` (GW == 32)
 
@@ -521,7 +521,8 @@ MVT_EXPORT int mvt_knn(const mvt_search *search, int B, const float *query, int 
 
 MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                             const void *targets, const float *coords, int add_offset, int add_xyz,
-                            float *out, long long out_row_stride, const int *idx_hint, int *idx_out, void *stream) {
+                            float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
+                            void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(levels && targets && coords && out, "mvt_knn_corr: null pointer");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_corr: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
@@ -532,11 +533,12 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     CorrParams p;
     p.n_levels = n_levels; p.B = B; p.M = M; p.C = C; p.G = G;
     p.add_offset = add_offset ? 1 : 0; p.add_xyz = add_xyz ? 1 : 0;
-    p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride; p.idx_out = idx_out; p.idx_hint = idx_hint;
+    p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride;
+    p.frame_stride = out_frame_stride ? out_frame_stride : (long long)M * out_row_stride; p.idx_out = idx_out; p.idx_hint = idx_hint;
     p.scale = sqrtf((float)C / (float)G);
     const int D = G + 3 * p.add_offset + 3 * p.add_xyz;
     bool fast = (C == 128 && G == 1);
-    bool vec = (D == 4) && (((uintptr_t)out & 15) == 0) && (out_row_stride % 4 == 0);
+    bool vec = (D == 4) && (((uintptr_t)out & 15) == 0) && (out_row_stride % 4 == 0) && (out_frame_stride % 4 == 0);
     bool aligned = (((uintptr_t)targets & 15) == 0);
     bool all_raster = true;
     for (int l = 0; l < n_levels; ++l) {

@@ -302,8 +302,11 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
         off += int(k) * D
     if out is None:
         out = torch.empty(B, M, off, device=tg.device, dtype=torch.float32)
-    row_stride = out.stride(1)
-    assert out.shape[0] == B and out.shape[1] == M and out.stride(2) == 1 and out.stride(0) == M * row_stride
+    # out may be any [B, M, width] view with unit stride along the last axis, e.g. the column slice
+    # tin.permute(1, 0, 2)[:, :, c0:c0 + width] of a [M, B, D_in] transformer-input buffer
+    row_stride, frame_stride = out.stride(1), out.stride(0)
+    assert out.shape[0] == B and out.shape[1] == M and out.shape[2] >= off and (out.stride(2) == 1 or out.shape[2] == 1)
+    assert out.dtype == torch.float32
     idx = idx_out
     if return_idx and idx is None:
         idx = torch.empty(n, B, M, int(levels[0][2]), device=tg.device, dtype=torch.int32)
@@ -311,7 +314,7 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
         if t is not None:
             assert t.dtype == torch.int32 and t.is_contiguous() and t.numel() == n * B * M * int(levels[0][2])
     check(lib().mvt_knn_corr(lv, n, B, M, Cc, int(groups), _feat_dtype(tg), _ptr(tg), _ptr(cq), int(bool(add_offset)),
-                             int(bool(add_xyz)), _ptr(out), row_stride, _ptr(idx_hint), _ptr(idx), _stream()), "mvt_knn_corr")
+                             int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _stream()), "mvt_knn_corr")
     return (out, idx) if return_idx else out
 
 

@@ -191,6 +191,25 @@ def test_corr_bf16():
     check_corr(c.xyz, c.fvec, targets, coords, 16, tol=2e-2, cloud=c)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c0", [195, 192])     # 195: the reference's column (after the 195 flow-embedding floats); 192: aligned
+def test_corr_written_into_transformer_input_layout(dtype, c0):
+    """Row f1: the [S, N, 256] block written straight into a [N, S, 581] transformer-input buffer at its column offset
+    (mvtracker.py:374-384 builds that with permute + cat): frame / track strides of the output are free."""
+    S, N, K = 3, 157, 16
+    sc = synth.make_scene(3, 40 * 4, 56 * 4, S=S, C=128, zero_frac=0.1, seed=81, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], N, S, valid=clouds[0].valid[0], dtype=dtype)
+    lv = [(c, c.fvec, K) for c in clouds]
+    dense = ops.knn_corr(lv, targets, coords)
+    tin = torch.full((N, S, 581), -7.0, device=DEV)
+    view = tin.permute(1, 0, 2)[:, :, c0:c0 + 256]
+    got = ops.knn_corr(lv, targets, coords, out=view)
+    assert got.data_ptr() == view.data_ptr()
+    assert torch.equal(tin[:, :, c0:c0 + 256], dense.permute(1, 0, 2))
+    assert (tin[:, :, :c0] == -7.0).all() and (tin[:, :, c0 + 256:] == -7.0).all()      # nothing else is touched
+
+
 def test_corr_fused_levels_equal_separate_launches():
     sc = synth.make_scene(3, 48 * 4, 64 * 4, S=4, C=128, zero_frac=0.05, seed=23, device=DEV)
     clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True)
