@@ -16,6 +16,8 @@
  *        mvtracker/models/core/mvtracker/mvtracker.py:800-846 (and the level loop :355-369)
  *   mvt_knn_gather                      <- feature init, k = 1
  *        mvtracker/models/core/mvtracker/mvtracker.py:627-643
+ *   mvt_track_input                     <- assembly of the update transformer's input around the correlation block
+ *        mvtracker/models/core/mvtracker/mvtracker.py:374-386, mvtracker/models/core/embeddings.py:134-161
  */
 #ifndef MVT_H_
 #define MVT_H_
@@ -155,6 +157,18 @@ int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
 int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, int B, int C,
                    const float *query, int M, void *feat_out, int *idx_out, void *stream);
+
+/* Update-transformer input rows (mvtracker.py:374-386 builds them with permute + cat + two adds):
+ *   x[n, s, :] = cat( get_3d_embedding(coords[s,n] - coords[0,n], E) (3E sin/cos columns, then the 3 flow components;
+ *                     embeddings.py:134-161), the Lc correlation columns, ffeats[s,n,:] (C), track_mask[s,n], vis[s,n] )
+ *                + pos_embed[n,:] + time_embed[s,:]                      D = 3E + 3 + Lc + C + 2 columns
+ * coords [S,N,3] fp32; ffeats [S,N,C] feature dtype; track_mask, vis [S,N] fp32; pos_embed [N,D], time_embed [S,D] fp32
+ * (either may be NULL = not added).  x: row (n, s) at x + n*track_stride + s*frame_stride (floats), unit column stride.
+ * corr_mode 1: the correlation columns already hold what mvt_knn_corr wrote there (out = x + 3E+3, row stride =
+ * track_stride, frame stride = frame_stride) and get the two embeddings added in place; 0: they are left untouched. */
+int mvt_track_input(const float *coords, const void *ffeats, int feat_dtype, const float *track_mask, const float *vis,
+                    const float *pos_embed, const float *time_embed, int S, int N, int C, int E, int Lc, float *x,
+                    long long track_stride, long long frame_stride, int corr_mode, void *stream);
 
 /* ---- view-sharded kNN correlation across GPUs (mvtracker_b200/csrc/mvt_shard.cu; driven by mvtracker_b200/dist.py) --------
  * Each rank keeps only the clouds of the views it unprojected; 8-byte (d2, index) keys and 16-byte result records are

@@ -1,0 +1,94 @@
+// Update-transformer input rows: everything around the correlation block that
+// MVTracker.forward_iteration assembles with permute + cat + two broadcast adds
+// (mvtracker/models/core/mvtracker/mvtracker.py:374-386; flow embedding: mvtracker/models/core/embeddings.py:134-161).
+//
+//   x[n, s, :] = cat( sincos(flow), flow,          3E + 3 columns,  flow = coords[s, n] - coords[0, n]
+//                     corr block,                  Lc columns, written beforehand by mvt_knn_corr through its strides
+//                     track features ffeats[s, n], C columns
+//                     track_mask[s, n], vis[s, n] )
+//                + pos_embed[n, :] + time_embed[s, :]
+//
+// One block per track, one pass: every column of the [N, S, D] buffer is written exactly once (the correlation columns
+// are read-modify-written in place: + pos + time), instead of the reference's cat (read all parts, write D) followed by
+// two out-of-place adds (read D, write D, twice).  Bound: HBM; algorithmic bytes per row = D*4 written + (C*e + 12 + 8)
+// read + Lc*4 re-read; the embedding tables (N*D and S*D floats) are read once per track / stay in L2.
+// Arithmetic follows the reference's order in fp32: div_j = float(2j) * float(1000/E); sin / cos (full-precision
+// sinf / cosf) of flow * div_j at columns axis*E + 2j / + 2j + 1; x = (row + pos) + time.
+#include "mvt_common.cuh"
+
+namespace mvt {
+
+struct InputParams {
+    const float *coords;       // [S, N, 3]
+    const void *ffeats;        // [S, N, C]
+    const float *track_mask;   // [S, N]
+    const float *vis;          // [S, N]
+    const float *pos;          // [N, D] or null
+    const float *tim;          // [S, D] or null
+    float *x;                  // row (n, s) at n * track_stride + s * frame_stride
+    long long track_stride, frame_stride;
+    int S, N, C, E, Lc, D;
+    float div_scale;           // float(1000 / E)
+    int corr_mode;             // 0: leave the correlation columns alone, 1: add the embeddings to them in place
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
+    const int n = blockIdx.x;
+    const int E3 = 3 * p.E, c_corr = E3 + 3, c_feat = c_corr + p.Lc, c_mask = c_feat + p.C;
+    const float x0 = __ldg(p.coords + (size_t)n * 3), y0 = __ldg(p.coords + (size_t)n * 3 + 1), z0 = __ldg(p.coords + (size_t)n * 3 + 2);
+    const float *pos = p.pos ? p.pos + (size_t)n * p.D : nullptr;
+    const T *ff = reinterpret_cast<const T *>(p.ffeats);
+    for (int s = 0; s < p.S; ++s) {
+        const size_t q = (size_t)s * p.N + n;
+        const float fx = __fsub_rn(__ldg(p.coords + q * 3), x0), fy = __fsub_rn(__ldg(p.coords + q * 3 + 1), y0),
+                    fz = __fsub_rn(__ldg(p.coords + q * 3 + 2), z0);
+        float *row = p.x + (long long)n * p.track_stride + (long long)s * p.frame_stride;
+        const float *tim = p.tim ? p.tim + (size_t)s * p.D : nullptr;
+        for (int c = threadIdx.x; c < p.D; c += blockDim.x) {
+            float v;
+            if (c < E3) {
+                const int axis = c / p.E, j = c - axis * p.E;
+                const float f = axis == 0 ? fx : (axis == 1 ? fy : fz);
+                const float a = __fmul_rn(f, __fmul_rn((float)(j & ~1), p.div_scale));
+                v = (j & 1) ? cosf(a) : sinf(a);
+            } else if (c < c_corr) {
+                v = c == E3 ? fx : (c == E3 + 1 ? fy : fz);
+            } else if (c < c_feat) {
+                if (p.corr_mode == 0) continue;
+                v = row[c];
+            } else if (c < c_mask) {
+                v = (float)ff[q * p.C + (c - c_feat)];
+            } else {
+                v = c == c_mask ? __ldg(p.track_mask + q) : __ldg(p.vis + q);
+            }
+            if (pos) v = __fadd_rn(v, __ldg(pos + c));
+            if (tim) v = __fadd_rn(v, __ldg(tim + c));
+            row[c] = v;
+        }
+    }
+}
+
+}  // namespace mvt
+
+MVT_EXPORT int mvt_track_input(const float *coords, const void *ffeats, int feat_dtype, const float *track_mask, const float *vis,
+                               const float *pos_embed, const float *time_embed, int S, int N, int C, int E, int Lc, float *x,
+                               long long track_stride, long long frame_stride, int corr_mode, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(coords && ffeats && track_mask && vis && x, "mvt_track_input: null pointer");
+    MVT_CHECK_ARG(S > 0 && N > 0 && C > 0 && Lc >= 0, "mvt_track_input: bad sizes S=%d N=%d C=%d Lc=%d", S, N, C, Lc);
+    MVT_CHECK_ARG(E > 0 && (E & 1) == 0, "mvt_track_input: flow embedding size must be even (got %d)", E);
+    MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_track_input: feat_dtype %d", feat_dtype);
+    MVT_CHECK_ARG(corr_mode == 0 || corr_mode == 1, "mvt_track_input: corr_mode %d", corr_mode);
+    InputParams p;
+    p.coords = coords; p.ffeats = ffeats; p.track_mask = track_mask; p.vis = vis; p.pos = pos_embed; p.tim = time_embed;
+    p.x = x; p.track_stride = track_stride; p.frame_stride = frame_stride;
+    p.S = S; p.N = N; p.C = C; p.E = E; p.Lc = Lc; p.D = 3 * E + 3 + Lc + C + 2;
+    p.div_scale = (float)(1000.0 / (double)E);
+    p.corr_mode = corr_mode;
+    MVT_CHECK_ARG(track_stride >= p.D || N == 1, "mvt_track_input: track stride %lld < row width %d", track_stride, p.D);
+    if (feat_dtype == MVT_F32) track_input_kernel<float><<<N, 256, 0, (cudaStream_t)stream>>>(p);
+    else track_input_kernel<__nv_bfloat16><<<N, 256, 0, (cudaStream_t)stream>>>(p);
+    MVT_CHECK_LAUNCH("track_input_kernel");
+    return MVT_OK;
+}

@@ -34,9 +34,7 @@ __device__ __forceinline__ void search(const SearchDev &sd, const unsigned char 
 __global__ void __launch_bounds__(256) knn_kernel(const SearchDev sd, int B, int M, const float *__restrict__ query, int k,
                                                   int *__restrict__ idx32, long long *__restrict__ idx64,
                                                   float *__restrict__ dist) {
-    __shared__ __align__(4) unsigned char win_tabs[32][32];     // one copy per warp of the block
-    unsigned char *win_tab = win_tabs[threadIdx.x >> 5];
-    init_window_table(win_tab);
+    MVT_WARP_SCRATCH(win_tab, 32);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;
@@ -182,9 +180,7 @@ __device__ __forceinline__ float dot8_bf16(const uint4 &a, const uint4 &b) {
 #endif
 template <int MODE, bool RASTER_ONLY, int GW>
 __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
-    __shared__ __align__(4) unsigned char win_tabs[32][32];     // one copy per warp of the block
-    unsigned char *win_tab = win_tabs[threadIdx.x >> 5];
-    init_window_table(win_tab);
+    MVT_WARP_SCRATCH(win_tab, MVT_CORR_THREADS / 32);
     const int lane = threadIdx.x & 31;
     const Group<GW> g(lane);
     const int gl = g.gl;
@@ -343,9 +339,7 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
 __global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, const void *__restrict__ fvec, int elem_bytes,
                                                          int B, int M, int C, const float *__restrict__ query,
                                                          void *__restrict__ feat_out, int *__restrict__ idx_out) {
-    __shared__ __align__(4) unsigned char win_tabs[32][32];     // one copy per warp of the block
-    unsigned char *win_tab = win_tabs[threadIdx.x >> 5];
-    init_window_table(win_tab);
+    MVT_WARP_SCRATCH(win_tab, 32);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;

@@ -72,22 +72,85 @@ __device__ __forceinline__ u64 group_sort(const Group<GW> &g, u64 v) {
 // entry); th = the k-th best, uniform across the group; empty = nothing has been offered yet (uniform).
 // cap: an optional a-priori bound -- only keys below it are ever accepted (th = min(k-th best, cap)); a search that
 // is given the cap of a wider search (other views, an earlier iteration) stops as early as that wider search would.
+// pend / np (buffered update, see topk_offer<GW, true>): candidates that beat th wait in this warp's 32-entry shared
+// memory buffer and are merged into the list as ONE sorted batch (topk_flush); t and th lag behind until then.
 struct TopK {
     u64 t, th, cap;
+    u64 *pend;
+    int np;
     bool empty;
-    __device__ __forceinline__ void init(u64 cap_key = kEmptyKey64) { t = kEmptyKey64; th = cap_key; cap = cap_key; empty = true; }
+    __device__ __forceinline__ void init(u64 cap_key = kEmptyKey64) { t = kEmptyKey64; th = cap_key; cap = cap_key; empty = true; np = 0; }
     __device__ __forceinline__ bool have_k() const { return th != kEmptyKey64; }
 };
+
+#ifndef MVT_FLUSH_AT
+#define MVT_FLUSH_AT 32
+#endif
+#ifndef MVT_FLUSH_INLINE
+#define MVT_FLUSH_INLINE __noinline__
+#endif
+// Sorted merge of the np pending keys (this warp's buffer) into the sorted list t: sort the batch (bitonic, only the
+// stages np needs: lanes >= np hold the empty key), min with the reversed batch = the 32 smallest of both as a bitonic
+// sequence, 5 merge stages.  Full warps only.
+static __device__ MVT_FLUSH_INLINE u64 topk_merge_pending(u64 t, const u64 *pend, int np) {
+    const int lane = threadIdx.x & 31;
+    __syncwarp();
+    u64 b = lane < np ? pend[lane] : kEmptyKey64;
+    __syncwarp();
+#pragma unroll
+    for (int k2 = 2; k2 <= 32; k2 <<= 1) {
+        if ((k2 >> 1) >= np) break;        // (uniform) blocks of k2/2 lanes are sorted and block 0 holds every key
+#pragma unroll
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            u64 o = __shfl_xor_sync(FULL, b, j);
+            bool take_min = ((lane & k2) == 0) == ((lane & j) == 0);
+            b = ((o < b) == take_min) ? o : b;
+        }
+    }
+    u64 r = __shfl_sync(FULL, b, 31 - lane);
+    u64 v = r < t ? r : t;
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        u64 o = __shfl_xor_sync(FULL, v, j);
+        bool take_min = (lane & j) == 0;
+        v = ((o < v) == take_min) ? o : v;
+    }
+    return v;
+}
+// Brings t and th up to date (no-op without pending keys).  Call before reading tk.t / tk.th / have_k() for a decision
+// that needs the current k-th best; a stale th is still a valid upper bound.
+__device__ __forceinline__ void topk_flush(TopK &tk, int k) {
+    if (tk.np == 0) return;
+    tk.t = topk_merge_pending(tk.t, tk.pend, tk.np);
+    tk.np = 0;
+    const u64 kth = __shfl_sync(FULL, tk.t, k - 1);
+    tk.th = kth < tk.cap ? kth : tk.cap;
+}
 
 // Offer one candidate key per lane (kEmptyKey64 for "no candidate").  Returns the number of candidates that beat the
 // k-th best at entry.  The first non-empty batch is sorted as a whole; later ones are inserted one by one (few survive
 // the threshold).  Within a batch the threshold is not refreshed: a candidate that no longer makes the top k after an
 // earlier insertion of the same batch lands at a position >= k, which is harmless.
 // Must be called by all 32 lanes (see Group).
-template <int GW>
+// BUF (GW == 32, tk.pend set): after the first batch the survivors are appended to the pending buffer instead and merged
+// as a sorted batch when it fills up or when the caller flushes (topk_flush).
+template <int GW, bool BUF = false>
 __device__ __forceinline__ int topk_offer(const Group<GW> &g, TopK &tk, u64 key, int k) {
     unsigned m = g.ballot(key < tk.th);
     if (!Group<GW>::wany(m != 0u)) return 0;
+    if (BUF && GW == 32 && !tk.empty) {
+        if (tk.np + __popc(m) > 32) {
+            topk_flush(tk, k);
+            m = __ballot_sync(FULL, key < tk.th);
+            if (m == 0u) return 0;
+        }
+        const int nb = __popc(m);
+        const unsigned below = m & ((1u << (threadIdx.x & 31)) - 1u);
+        if (key < tk.th) tk.pend[tk.np + __popc(below)] = key;
+        tk.np += nb;
+        if (MVT_FLUSH_AT < 32 && tk.np >= MVT_FLUSH_AT) topk_flush(tk, k);
+        return nb;
+    }
     const int n = __popc(m);
     const bool do_sort = tk.empty && m != 0u;
     if (Group<GW>::wany(do_sort)) {

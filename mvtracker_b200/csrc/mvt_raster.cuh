@@ -31,6 +31,9 @@ struct RasterView {
     const float2 *ztab;   // [S, V, TH, TW] {min, max} view-space depth per 8x8 tile, or null (tile_depth_kernel)
     int TW, TH;
 };
+#ifndef MVT_TOPK_BUF
+#define MVT_TOPK_BUF 0
+#endif
 constexpr int kTile = 8;          // == MVT_TILE
 constexpr int kTileMinPixels = 384;   // a pass that would read this many new pixels of one view goes to tile_search instead
 
@@ -66,6 +69,16 @@ __host__ __device__ constexpr unsigned win_tab_word(int i) {
     return word;
 }
 template <int I> struct WinWord { static constexpr unsigned value = win_tab_word(I); };
+// Per-warp shared memory of the search: the window table and, right behind it, the pending buffer of the top-k list.
+struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; };
+// declares the block's scratch (one per warp), hands this warp its table pointer `name` and fills the table
+#define MVT_WARP_SCRATCH(name, nwarps)                                   \
+    __shared__ mvt::WarpScratch name##_all[nwarps];                      \
+    unsigned char *name = name##_all[threadIdx.x >> 5].tab;              \
+    mvt::init_window_table(name)
+__device__ __forceinline__ u64 *scratch_pend(const unsigned char *win_tab) {
+    return reinterpret_cast<u64 *>(const_cast<unsigned char *>(win_tab) + 32);
+}
 // tab: this warp's 32 bytes of shared memory (4-byte aligned).  Call with all lanes of the warp.
 __device__ __forceinline__ void init_window_table(unsigned char *tab) {
     const int l = threadIdx.x & 31;
@@ -214,6 +227,7 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
     }
     unsigned tested = 0, kept = 0, st_ins = 0;
     for (int rho = 0; rho <= max(TW, TH); ++rho) {
+        topk_flush(tk, k);
         // views whose current box still reaches ring rho
         const Rect R = box();
         const int tx0 = R.x0 / kTile, tx1 = (R.x1 + kTile - 1) / kTile, ty0 = R.y0 / kTile, ty1 = (R.y1 + kTile - 1) / kTile;   // [ , )
@@ -253,11 +267,12 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
                 const float4 p1 = in1 ? __ldg(frame + i1) : make_float4(0.f, 0.f, 0.f, 0.f);
                 const bool v0 = in0 && (skip_invalid ? (p0.w > 0.f) : !(p0.w < 0.f));
                 const bool v1 = in1 && (skip_invalid ? (p1.w > 0.f) : !(p1.w < 0.f));
-                st_ins += topk_offer(g, tk, v0 ? pack_key(dist2(p0.x, p0.y, p0.z, qx, qy, qz), i0) : kEmptyKey64, k);
-                st_ins += topk_offer(g, tk, v1 ? pack_key(dist2(p1.x, p1.y, p1.z, qx, qy, qz), i1) : kEmptyKey64, k);
+                st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, v0 ? pack_key(dist2(p0.x, p0.y, p0.z, qx, qy, qz), i0) : kEmptyKey64, k);
+                st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, v1 ? pack_key(dist2(p1.x, p1.y, p1.z, qx, qy, qz), i1) : kEmptyKey64, k);
             }
         }
     }
+    topk_flush(tk, k);
     if (stats && lane == 0) {
         atomicAdd(stats + 4, 1ull);        // [4]: queries finished here (raster_windows counts only those it finishes)
         atomicAdd(stats + 5, (unsigned long long)kept * 64ull);
@@ -278,6 +293,8 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                                                bool live, float qx, float qy, float qz, int k, TopK &tk,
                                                unsigned long long *stats, int qtag, u64 cap, unsigned budget) {
     tk.init(cap);
+    constexpr bool BUF = GW == 32 && MVT_TOPK_BUF != 0;
+    tk.pend = scratch_pend(win_tab);
     const int gl = g.gl;
     const int W = rv.W, H = rv.H, HW = W * H, V = rv.V;
     const float4 *frame = rv.xyz4 + (size_t)s * V * HW;
@@ -354,7 +371,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 const int nc = min(kCB, (total - t0 + GW - 1) / GW);
 #pragma unroll 1
                 for (int c = 0; c < nc; ++c) {
-                    st_ins += topk_offer(g, tk, key[0], k);
+                    st_ins += topk_offer<GW, BUF>(g, tk, key[0], k);
 #pragma unroll
                     for (int r = 0; r + 1 < kCB; ++r) key[r] = key[r + 1];
                 }
@@ -364,11 +381,12 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                     if (t0 + c * GW >= total) break;
                     bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < 0.f));
                     float d2 = dist2(p[c].x, p[c].y, p[c].z, qx, qy, qz);
-                    st_ins += topk_offer(g, tk, valid ? pack_key(d2, id[c]) : kEmptyKey64, k);
+                    st_ins += topk_offer<GW, BUF>(g, tk, valid ? pack_key(d2, id[c]) : kEmptyKey64, k);
                 }
             }
         }
         st_cand += kNW * __popc(front_mask);
+        if (BUF) topk_flush(tk, k);
     }
     Rect A = window(kM0);     // scanned so far (per view)
     int m = kM0;
@@ -445,7 +463,10 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
             st_cand += total;
             for (unsigned i0 = 0; Group<GW>::wany(i0 < total); i0 += GW) {
                 // bounded effort: a single pass can be large (a view behind the query gets its whole box at once)
-                if (budget != 0u && i0 >= budget && Group<GW>::wall(tk.have_k())) return false;
+                if (budget != 0u && i0 >= budget && Group<GW>::wall(tk.have_k())) {
+                    if (BUF) topk_flush(tk, k);
+                    return false;
+                }
                 const unsigned t = i0 + gl;
                 bool valid = t < total;
                 int j = 0;
@@ -471,9 +492,10 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 float4 p = valid ? __ldg(frame + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
                 valid = valid && (skip_invalid ? (p.w > 0.f) : !(p.w < 0.f));
                 float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
-                st_ins += topk_offer(g, tk, valid ? pack_key(d2, idx) : kEmptyKey64, k);
+                st_ins += topk_offer<GW, BUF>(g, tk, valid ? pack_key(d2, idx) : kEmptyKey64, k);
             }
         }
+        if (BUF) topk_flush(tk, k);
         if (!rect_empty(B)) A = B;
         if (!done) ++st_pass;
         done = done || last;

@@ -91,11 +91,9 @@ template <bool RASTER_ONLY>
 #define MVT_KEYS_THREADS 256
 #endif
 __global__ void __launch_bounds__(MVT_KEYS_THREADS, MVT_KEYS_MINB) knn_keys_kernel(const KeysParams p) {
-    __shared__ __align__(4) unsigned char win_tabs[32][32];     // one copy per warp of the block
     __shared__ unsigned next_item;
-    unsigned char *win_tab = win_tabs[threadIdx.x >> 5];
     if (threadIdx.x == 0) next_item = 0u;
-    init_window_table(win_tab);
+    MVT_WARP_SCRATCH(win_tab, MVT_KEYS_THREADS / 32);
     __syncthreads();                     // next_item
     const int lane = threadIdx.x & 31;
     const unsigned Mp = (unsigned)(p.n_shards * p.Ms);

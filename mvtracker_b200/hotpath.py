@@ -54,6 +54,23 @@ class WindowClouds:
         return ops.knn_corr(levels, targets, coords, groups=self.groups, add_offset=self.add_offset, add_xyz=self.add_xyz,
                             out=out, idx_hint=hint, idx_out=idx)
 
+    def transformer_input(self, ffeats: torch.Tensor, coords: torch.Tensor, track_mask: torch.Tensor, vis: torch.Tensor,
+                          pos_embed: Optional[torch.Tensor], time_embed: Optional[torch.Tensor], flow_embed_dim: int = 64,
+                          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One refinement iteration's transformer input x [N, S, D] (mvtracker.py:350-386) in two launches: the fused kNN
+        correlation of all levels writes its block straight into x's correlation columns, mvt_track_input writes the
+        flow embedding, the track features and the two masks and adds pos / time embeddings -- every byte of x is
+        written once.  ffeats [S,N,C], coords [S,N,3], track_mask / vis [S,N]."""
+        S, N, C = ffeats.shape
+        D_n = self.groups + 3 * bool(self.add_offset) + 3 * bool(self.add_xyz)
+        width = len(self.clouds) * self.k * D_n
+        D = 3 * flow_embed_dim + 3 + width + C + 2
+        if out is None:
+            out = torch.empty(N, S, D, device=ffeats.device, dtype=torch.float32)
+        self.corr(ffeats, coords, out=ops.corr_columns(out, flow_embed_dim, width))
+        return ops.track_input(coords, ffeats, track_mask, vis, pos_embed, time_embed, flow_embed_dim, width, out=out,
+                               corr_in_out=True)
+
     def feature_init(self, frame: int, query_xyz: torch.Tensor) -> torch.Tensor:
         """Nearest level-0 point's feature for each query of `frame` (mvtracker.py:627-643).  query_xyz [n,3] -> [n,C]."""
         c = self.clouds[0]

@@ -318,6 +318,37 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     return (out, idx) if return_idx else out
 
 
+def track_input(coords: torch.Tensor, ffeats: torch.Tensor, track_mask: torch.Tensor, vis: torch.Tensor,
+                pos_embed: Optional[torch.Tensor], time_embed: Optional[torch.Tensor], flow_embed_dim: int = 64,
+                corr_width: int = 256, out: Optional[torch.Tensor] = None, corr_in_out: bool = False) -> torch.Tensor:
+    """Row f1: the update transformer's input x [N, S, D] (mvtracker.py:374-386), D = 3E+3 + corr_width + C + 2.
+    coords [S,N,3], ffeats [S,N,C], track_mask / vis [S,N] (or [S,N,1]), pos_embed [N,D] (or [N,1,D]), time_embed [S,D]
+    (or [1,S,D]).  corr_in_out: `out` already holds the correlation block in columns [3E+3, 3E+3+corr_width) (written by
+    knn_corr(out=corr_columns(out))) and gets the embeddings added there in place; otherwise those columns are untouched."""
+    _need_cuda(coords, "coords"); _need_cuda(ffeats, "ffeats")
+    S, N, C = ffeats.shape
+    E = int(flow_embed_dim)
+    D = 3 * E + 3 + int(corr_width) + C + 2
+    cq, ff = _f32c(coords.reshape(S, N, 3)), ffeats.contiguous()
+    tm, vs = _f32c(track_mask.reshape(S, N)), _f32c(vis.reshape(S, N))
+    pe = _f32c(pos_embed.reshape(N, D)) if pos_embed is not None else None
+    te = _f32c(time_embed.reshape(S, D)) if time_embed is not None else None
+    if out is None:
+        assert not corr_in_out
+        out = torch.empty(N, S, D, device=ff.device, dtype=torch.float32)
+    assert out.dtype == torch.float32 and out.shape == (N, S, D) and out.stride(2) == 1
+    check(lib().mvt_track_input(_ptr(cq), _ptr(ff), _feat_dtype(ff), _ptr(tm), _ptr(vs), _ptr(pe), _ptr(te), S, N, C, E,
+                                int(corr_width), _ptr(out), out.stride(0), out.stride(1), int(bool(corr_in_out)), _stream()),
+          "mvt_track_input")
+    return out
+
+
+def corr_columns(x: torch.Tensor, flow_embed_dim: int = 64, corr_width: int = 256) -> torch.Tensor:
+    """The [S, N, corr_width] view of a [N, S, D] transformer-input buffer that knn_corr(out=...) writes into."""
+    c0 = 3 * int(flow_embed_dim) + 3
+    return x.permute(1, 0, 2)[:, :, c0:c0 + corr_width]
+
+
 def knn_gather(where, fvec: torch.Tensor, query: torch.Tensor, return_idx=False):
     """k=1: feature row of the nearest cloud point per query.  fvec [B,N,C] (or the frame's [1,N,C]), query [B,M,3]."""
     _need_cuda(query, "query"); _need_cuda(fvec, "fvec")

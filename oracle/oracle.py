@@ -117,3 +117,30 @@ def dist2_f64(ref, q):
     out = np.empty((ref.shape[0],), np.float64)
     lib().orc_dist2_f64(_p(ref), _p(q), ref.shape[0], _p(out))
     return out
+
+
+def transformer_input(coords, fcorrs, ffeats, track_mask, vis, pos_embed=None, time_embed=None, flow_embed_dim=64):
+    """numpy restatement of the assembly of the update transformer's input:
+    mvtracker/models/core/mvtracker/mvtracker.py:374-386 with get_3d_embedding (mvtracker/models/core/embeddings.py:134-161).
+    coords [S,N,3], fcorrs [S,N,Lc], ffeats [S,N,C], track_mask / vis [S,N], pos_embed [N,D], time_embed [S,D]
+    -> x [N,S,D] fp32, D = 3E+3 + Lc + C + 2.  All arithmetic in fp32, in the reference's order."""
+    f32 = np.float32
+    coords = np.asarray(coords, f32)
+    S, N, _ = coords.shape
+    E = int(flow_embed_dim)
+    flows = (coords - coords[0:1]).transpose(1, 0, 2)                                  # [N,S,3]  (:379)
+    div = np.arange(0, E, 2, dtype=f32) * f32(1000.0 / E)                              # embeddings.py:141-143
+    pe = np.zeros((N, S, 3, E), f32)
+    arg = flows[..., None] * div[None, None, None, :]                                  # fp32 products
+    pe[..., 0::2] = np.sin(arg.astype(np.float64)).astype(f32)                         # correctly rounded sin / cos of the fp32 argument
+    pe[..., 1::2] = np.cos(arg.astype(np.float64)).astype(f32)
+    emb = np.concatenate([pe.reshape(N, S, 3 * E), flows], axis=2)                     # cat_coords=True: pe first (:159-160)
+    tm = np.asarray(track_mask).reshape(S, N).astype(f32).T[..., None]
+    vs = np.asarray(vis, f32).reshape(S, N).T[..., None]
+    x = np.concatenate([emb, np.asarray(fcorrs, f32).transpose(1, 0, 2), np.asarray(ffeats).astype(f32).transpose(1, 0, 2), tm, vs],
+                       axis=2)                                                         # (:384)
+    if pos_embed is not None:
+        x = x + np.asarray(pos_embed, f32).reshape(N, 1, -1)                           # (:386) x = (input + pos) + time
+    if time_embed is not None:
+        x = x + np.asarray(time_embed, f32).reshape(1, S, -1)
+    return x.astype(f32)

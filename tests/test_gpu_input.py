@@ -1,0 +1,95 @@
+"""GPU parity of mvt_track_input: the update transformer's input rows, against the golden vectors made
+with the reference's own embedding functions and against the oracle on fresh inputs; fused with knn_corr's strided
+output so that the [N, S, 581] buffer is written once."""
+import numpy as np
+import pytest
+import torch
+
+from mvtracker_b200 import ops, synth
+from oracle import oracle
+from parity import golden
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+# fp32 sin / cos of arguments up to ~1e3 * |flow|: CUDA's sinf / cosf are within 2 ulp of the correctly rounded value
+TOL_TRIG = 5e-7
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+@pytest.mark.parametrize("name,g", golden("input"))
+def test_track_input_matches_reference_golden(name, g):
+    E = int(g["flow_embed_dim"])
+    S, N, Lc = g["fcorrs"].shape
+    D = g["x"].shape[-1]
+    x = torch.empty(N, S, D, device=DEV)
+    ops.corr_columns(x, E, Lc).copy_(_t(g["fcorrs"]))
+    got = ops.track_input(_t(g["coords"]), _t(g["ffeats"]), _t(g["track_mask"]), _t(g["vis"]), _t(g["pos_embed"]),
+                          _t(g["time_embed"]), E, Lc, out=x, corr_in_out=True).cpu().numpy()
+    assert np.abs(got - g["x"]).max() <= 2 * TOL_TRIG
+    # without the embeddings every copied column is bit-exact and the correlation columns are left alone
+    x.fill_(-3.0)
+    raw = ops.track_input(_t(g["coords"]), _t(g["ffeats"]), _t(g["track_mask"]), _t(g["vis"]), None, None, E, Lc, out=x).cpu().numpy()
+    c0 = 3 * E + 3
+    assert (raw[:, :, c0:c0 + Lc] == -3.0).all()
+    ref = g["x_noembed"]
+    assert np.array_equal(raw[:, :, 3 * E:c0], ref[:, :, 3 * E:c0]) and np.array_equal(raw[:, :, c0 + Lc:], ref[:, :, c0 + Lc:])
+    assert np.abs(raw[:, :, :3 * E] - ref[:, :, :3 * E]).max() <= TOL_TRIG
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_corr_and_input_written_once(dtype):
+    """knn_corr writes its block into the [N, S, 581] buffer, track_input fills the rest and adds the embeddings: equal to
+    the oracle's cat of (oracle embedding, the CUDA correlation block, features, masks) + pos + time."""
+    S, N, K, E = 4, 203, 16, 64
+    sc = synth.make_scene(3, 40 * 4, 56 * 4, S=S, C=128, zero_frac=0.1, seed=91, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(4), want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], N, S, valid=clouds[0].valid[0], dtype=dtype)
+    lv = [(c, c.fvec, K) for c in clouds]
+    dense = ops.knn_corr(lv, targets, coords)
+    g = torch.Generator().manual_seed(3)
+    D = 3 * E + 3 + 256 + 128 + 2
+    pos, tim = torch.randn(N, D, generator=g).to(DEV), torch.randn(S, D, generator=g).to(DEV)
+    mask = (torch.rand(S, N, generator=g) > 0.4).to(DEV)
+    vis = torch.rand(S, N, generator=g).to(DEV)
+    x = torch.full((N, S, D), float("nan"), device=DEV)
+    ops.knn_corr(lv, targets, coords, out=ops.corr_columns(x, E, 256))
+    ops.track_input(coords, targets, mask, vis, pos, tim, E, 256, out=x, corr_in_out=True)
+    ref = oracle.transformer_input(coords.cpu().numpy(), dense.cpu().numpy(), targets.float().cpu().numpy(), mask.cpu().numpy(),
+                                   vis.cpu().numpy(), pos.cpu().numpy(), tim.cpu().numpy(), E)
+    got = x.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.array_equal(got[:, :, 3 * E:], ref[:, :, 3 * E:])             # flow, corr, features, masks (+ embeddings): bit-exact
+    assert np.abs(got[:, :, :3 * E] - ref[:, :, :3 * E]).max() <= 2 * TOL_TRIG
+
+
+def test_track_input_full_size_properties():
+    """Panoptic-size rows (4096 tracks x 12 frames x 581): frame 0 has zero flow (sin 0 = 0, cos 0 = 1 columns), the op is
+    linear in the two embeddings, and a strided (padded) output buffer receives the same rows."""
+    S, N, E, Lc, C = 12, 4096, 64, 256, 128
+    g = torch.Generator().manual_seed(11)
+    coords = (torch.randn(1, N, 3, generator=g) + 0.05 * torch.randn(S, N, 3, generator=g)).to(DEV)
+    ff = torch.randn(S, N, C, generator=g).to(DEV)
+    mask, vis = (torch.rand(S, N, generator=g) > 0.5).to(DEV), torch.rand(S, N, generator=g).to(DEV)
+    D = 3 * E + 3 + Lc + C + 2
+    pos, tim = torch.randn(N, D, generator=g).to(DEV), torch.randn(S, D, generator=g).to(DEV)
+    x0 = torch.zeros(N, S, D, device=DEV)
+    ops.track_input(coords, ff, mask, vis, None, None, E, Lc, out=x0)
+    assert (x0[:, 0, 0:3 * E:2] == 0).all() and (x0[:, 0, 1:3 * E:2] == 1).all() and (x0[:, 0, 3 * E:3 * E + 3] == 0).all()
+    assert torch.equal(x0[:, :, 3 * E + 3 + Lc:3 * E + 3 + Lc + C], ff.permute(1, 0, 2))
+    assert torch.equal(x0[:, :, -2], mask.float().T) and torch.equal(x0[:, :, -1], vis.T)
+    x1 = torch.zeros(N, S, D, device=DEV)
+    ops.track_input(coords, ff, mask, vis, pos, tim, E, Lc, out=x1, corr_in_out=True)
+    assert torch.equal(x1, (x0 + pos[:, None, :]) + tim[None, :, :])
+    big = torch.zeros(N, S + 1, D + 3, device=DEV)
+    view = big[:, :S, :D]
+    ops.track_input(coords, ff, mask, vis, pos, tim, E, Lc, out=view, corr_in_out=True)
+    assert torch.equal(view, x1) and (big[:, S] == 0).all() and (big[:, :, D:] == 0).all()
+
+
+def test_track_input_rejects_cpu_tensors():
+    from mvtracker_b200._lib import MvtError
+    with pytest.raises(MvtError):
+        ops.track_input(torch.zeros(2, 3, 3), torch.zeros(2, 3, 128), torch.zeros(2, 3), torch.zeros(2, 3), None, None)

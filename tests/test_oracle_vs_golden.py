@@ -52,3 +52,16 @@ def test_corr_sample_matches_reference(name, g):
         sb = qb[np.lexsort(qb.T[::-1])]
         assert np.allclose(sa, sb, rtol=1e-4, atol=1e-5), name
     assert exact_rows >= 0.95 * len(a), f"{name}: only {exact_rows}/{len(a)} queries match positionally"
+
+
+@pytest.mark.parametrize("name,g", golden("input"))
+def test_transformer_input_matches_reference(name, g):
+    """Row f1: the oracle's assembly of the update transformer's input against the reference's own embedding functions
+    joined as mvtracker.py:374-386 does (tests/golden/make_golden_input.py)."""
+    E = int(g["flow_embed_dim"])
+    x = oracle.transformer_input(g["coords"], g["fcorrs"], g["ffeats"], g["track_mask"], g["vis"], g["pos_embed"], g["time_embed"], E)
+    assert x.shape == g["x"].shape
+    assert np.abs(x - g["x"]).max() <= 5e-7                        # sin / cos columns: 1 ulp of values <= 1 (+ two adds)
+    raw = oracle.transformer_input(g["coords"], g["fcorrs"], g["ffeats"], g["track_mask"], g["vis"], None, None, E)
+    assert np.array_equal(raw[:, :, 3 * E:], g["x_noembed"][:, :, 3 * E:])       # copied columns: bit-exact
+    assert np.abs(raw[:, :, :3 * E] - g["x_noembed"][:, :, :3 * E]).max() <= 1.2e-7
