@@ -16,6 +16,7 @@
  *        mvtracker/models/core/mvtracker/mvtracker.py:800-846 (and the level loop :355-369)
  *   mvt_knn_gather                      <- feature init, k = 1
  *        mvtracker/models/core/mvtracker/mvtracker.py:627-643
+ *   mvt_knn_corr_backward, mvt_cloud_build_backward  <- torch autograd through the two functions above (training)
  *   mvt_track_input                     <- assembly of the update transformer's input around the correlation block
  *        mvtracker/models/core/mvtracker/mvtracker.py:374-386, mvtracker/models/core/embeddings.py:134-161
  */
@@ -169,6 +170,24 @@ int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, i
 int mvt_track_input(const float *coords, const void *ffeats, int feat_dtype, const float *track_mask, const float *vis,
                     const float *pos_embed, const float *time_embed, int S, int N, int C, int E, int Lc, float *x,
                     long long track_stride, long long frame_stride, int corr_mode, void *stream);
+
+/* ---- backward of the path (training, train.py:119-163) ---------------------------------------------
+ * What autograd computes through corr_sample's gather + einsum / sqrt(C/G) (mvtracker.py:827-835) for ONE level, given the
+ * neighbour lists of the forward pass (mvt_knn_corr's idx_out, [B,M,k] int32, -1 = none):
+ *   grad_targets[b,m,c] (+)= sum_j gs * fvec[b, idx_j, c]      gs = grad_out[b,m,j,group(c)] / sqrt(C/G)
+ *   grad_fvec[b,idx_j,c]  += gs * targets[b,m,c]               (vector reductions; accumulation order is not fixed)
+ * grad_out entry (b,m,j,g) at grad_out[b*grad_frame_stride + m*grad_row_stride + j*D + g] (the level's block of the
+ * forward output; offset / xyz columns carry no gradient).  grad_targets [B,M,C] fp32 (accumulate_targets 1: added to,
+ * for the further levels of the same targets), grad_fvec [B,N,C] fp32, zeroed by the caller.  C/G % 4 == 0. */
+int mvt_knn_corr_backward(const void *fvec, const void *targets, int feat_dtype, const int *idx, const float *grad_out,
+                          long long grad_row_stride, long long grad_frame_stride, int B, int N, int M, int C, int G,
+                          int k, int D, float *grad_targets, int accumulate_targets, float *grad_fvec, void *stream);
+
+/* Feature branch of init_pointcloud_from_rgbd backwards (model_utils.py:439-441 chained avg_pool2d, :475-476 permute):
+ *   grad_fmaps[v,s,c,y,x] (+)= grad_fvec[s, v*Hl*Wl + (y>>level)*Wl + (x>>level), c] / 4^level, 0 outside the pooled area.
+ * grad_fvec [S, V*Hl*Wl, C] fp32 (Hl = H>>level); grad_fmaps [V,S,C,H,W] fp32. */
+int mvt_cloud_build_backward(const float *grad_fvec, int V, int S, int C, int H, int W, int level, float *grad_fmaps,
+                             int accumulate, void *stream);
 
 /* ---- view-sharded kNN correlation across GPUs (mvtracker_b200/csrc/mvt_shard.cu; driven by mvtracker_b200/dist.py) --------
  * Each rank keeps only the clouds of the views it unprojected; 8-byte (d2, index) keys and 16-byte result records are

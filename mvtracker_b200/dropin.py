@@ -111,10 +111,52 @@ def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, de
             del _pyramid_cache[2:]
     cloud = pyr.clouds[level]
     xyz, fvec = cloud.xyz, cloud.fvec
+    if torch.is_grad_enabled() and fmaps.requires_grad:
+        # training (row f2): the cloud's features are a function of fmaps (chained avg_pool2d + permute); depths, cameras
+        # and therefore xyz carry no gradient in the reference either (they come from the data loader)
+        fvec = _FeatureCloudFn.apply(fmaps, fvec, level)
     xyz._mvt = (weakref.ref(pyr), level)   # lets PointcloudCorrBlock find the footprint hint and its sibling levels
     if return_validity_mask:
         return xyz, fvec, cloud.valid
     return xyz, fvec
+
+
+class _FeatureCloudFn(torch.autograd.Function):
+    """fvec of one pyramid level as a differentiable function of fmaps (model_utils.py:439-441, 475-476); the forward
+    value is the cloud that mvt_cloud_build already produced, the backward is mvt_cloud_build_backward."""
+
+    @staticmethod
+    def forward(ctx, fmaps, fvec_built, level):
+        ctx.level, ctx.shape, ctx.dtype = level, tuple(fmaps.shape), fmaps.dtype
+        return fvec_built.view_as(fvec_built)
+
+    @staticmethod
+    def backward(ctx, grad_fvec):
+        B, V, S, C, H, W = ctx.shape
+        g = grad_fvec.reshape(B, S, -1, C)
+        out = torch.stack([ops.cloud_build_backward(g[b], V, H, W, ctx.level) for b in range(B)])
+        return out.to(ctx.dtype), None, None
+
+
+class _CorrSampleFn(torch.autograd.Function):
+    """corr_sample of ONE level with gradients w.r.t. targets and fvec (mvtracker.py:827-835); the neighbour search, the
+    offsets and the positions are not differentiable (coords are detached in the reference, mvtracker.py:351)."""
+
+    @staticmethod
+    def forward(ctx, targets, fvec, block, coords):
+        out, idx = ops.knn_corr([(block._search(), block._fvec_c.detach(), block.k)], targets.detach(), coords.detach(),
+                                groups=block.groups, add_offset=block.corr_add_neighbor_offset,
+                                add_xyz=block.corr_add_neighbor_xyz, return_idx=True)
+        ctx.save_for_backward(targets, fvec, idx[0])
+        ctx.groups = block.groups
+        D = block.groups + 3 * bool(block.corr_add_neighbor_offset) + 3 * bool(block.corr_add_neighbor_xyz)
+        return out.reshape(targets.shape[0], targets.shape[1], block.k, D)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        targets, fvec, idx = ctx.saved_tensors
+        gt, gf = ops.knn_corr_backward(fvec.detach(), targets.detach(), idx, grad_out, groups=ctx.groups)
+        return gt.to(targets.dtype), gf.to(fvec.dtype), None, None
 
 
 def knn(k: int, xyz_ref: torch.Tensor, xyz_query: torch.Tensor):
@@ -249,11 +291,12 @@ class PointcloudCorrBlock:
         assert coords_world_xyz.shape == (self.B, M, 3)
         if save_debug_logs or save_rerun_logs:
             raise MvtError("debug / rerun logging lives in the reference implementation only")
-        if torch.is_grad_enabled() and (targets.requires_grad or self.fvec.requires_grad):
-            raise MvtError("mvtracker_b200 corr_sample is forward-only; run under torch.no_grad()")
         D = self.groups + 3 * bool(self.corr_add_neighbor_offset) + 3 * bool(self.corr_add_neighbor_xyz)
         if targets.dtype != self.fvec.dtype:
             targets = targets.to(self.fvec.dtype)
+        if torch.is_grad_enabled() and (targets.requires_grad or self.fvec.requires_grad):
+            # training (row f2): one level per call, neighbour lists kept for mvt_knn_corr_backward
+            return _CorrSampleFn.apply(targets, self.fvec, self, coords_world_xyz)
 
         sib = self._siblings()
         ckey = (_key(targets), _key(coords_world_xyz))

@@ -318,6 +318,52 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     return (out, idx) if return_idx else out
 
 
+def knn_corr_backward(fvec: torch.Tensor, targets: torch.Tensor, idx: torch.Tensor, grad_out: torch.Tensor, groups: int = 1,
+                      grad_targets: Optional[torch.Tensor] = None, grad_fvec: Optional[torch.Tensor] = None):
+    """Row f2: backward of one level of corr_sample (mvtracker.py:827-835) given the forward pass's neighbour lists.
+    fvec [B,N,C], targets [B,M,C] (same dtype), idx [B,M,k] int32, grad_out [B,M,k,D] fp32 (any strides with a unit
+    last one, e.g. the level's slice of the fused block's gradient) -> (grad_targets [B,M,C], grad_fvec [B,N,C]) fp32.
+    Passing grad_targets / grad_fvec accumulates into them (further levels of the same targets / a shared cloud)."""
+    _need_cuda(fvec, "fvec"); _need_cuda(targets, "targets"); _need_cuda(grad_out, "grad_out")
+    B, N, C = fvec.shape
+    _, M, k, D = grad_out.shape
+    assert targets.shape == (B, M, C) and idx.shape == (B, M, k) and idx.dtype == torch.int32
+    if fvec.dtype != targets.dtype:
+        raise MvtError(f"targets dtype {targets.dtype} != fvec dtype {fvec.dtype}")
+    fv, tg, ix = fvec.contiguous(), targets.contiguous(), idx.contiguous()
+    go = grad_out if grad_out.dtype == torch.float32 else grad_out.float()
+    if go.stride(3) != 1 or go.stride(2) != D:
+        go = go.contiguous()
+    acc = grad_targets is not None
+    if grad_targets is None:
+        grad_targets = torch.empty(B, M, C, device=fv.device, dtype=torch.float32)
+    if grad_fvec is None:
+        grad_fvec = torch.zeros(B, N, C, device=fv.device, dtype=torch.float32)
+    for t in (grad_targets, grad_fvec):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    check(lib().mvt_knn_corr_backward(_ptr(fv), _ptr(tg), _feat_dtype(fv), _ptr(ix), _ptr(go), go.stride(1), go.stride(0), B, N, M, C,
+                                      int(groups), k, D, _ptr(grad_targets), int(acc), _ptr(grad_fvec), _stream()),
+          "mvt_knn_corr_backward")
+    return grad_targets, grad_fvec
+
+
+def cloud_build_backward(grad_fvec: torch.Tensor, V: int, H: int, W: int, level: int,
+                         grad_fmaps: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Row f2: feature branch of init_pointcloud_from_rgbd backwards (model_utils.py:439-441, 475-476).
+    grad_fvec [S, V*(H>>level)*(W>>level), C] -> grad_fmaps [V,S,C,H,W] fp32 (accumulated into when given)."""
+    _need_cuda(grad_fvec, "grad_fvec")
+    S, P, C = grad_fvec.shape
+    assert P == V * (H >> level) * (W >> level), "grad_fvec does not match the level's cloud size"
+    g = _f32c(grad_fvec)
+    acc = grad_fmaps is not None
+    if grad_fmaps is None:
+        grad_fmaps = torch.empty(V, S, C, H, W, device=g.device, dtype=torch.float32)
+    assert grad_fmaps.dtype == torch.float32 and grad_fmaps.is_contiguous() and grad_fmaps.shape == (V, S, C, H, W)
+    check(lib().mvt_cloud_build_backward(_ptr(g), V, S, C, H, W, int(level), _ptr(grad_fmaps), int(acc), _stream()),
+          "mvt_cloud_build_backward")
+    return grad_fmaps
+
+
 def track_input(coords: torch.Tensor, ffeats: torch.Tensor, track_mask: torch.Tensor, vis: torch.Tensor,
                 pos_embed: Optional[torch.Tensor], time_embed: Optional[torch.Tensor], flow_embed_dim: int = 64,
                 corr_width: int = 256, out: Optional[torch.Tensor] = None, corr_in_out: bool = False) -> torch.Tensor:

@@ -144,3 +144,40 @@ def transformer_input(coords, fcorrs, ffeats, track_mask, vis, pos_embed=None, t
     if time_embed is not None:
         x = x + np.asarray(time_embed, f32).reshape(1, S, -1)
     return x.astype(f32)
+
+
+def corr_backward(fvec, targets, idx, grad_out, groups=1):
+    """numpy restatement of what autograd computes through corr_sample's gather + einsum / sqrt(C/G)
+    (mvtracker/models/core/mvtracker/mvtracker.py:827-835) given the neighbour lists.
+    fvec [B,N,C], targets [B,M,C], idx [B,M,k] (-1 = none), grad_out [B,M,k,D] -> (grad_targets [B,M,C], grad_fvec [B,N,C]),
+    accumulated in float64 and rounded once (the CUDA reductions add in an unspecified order)."""
+    fvec, targets, g = np.asarray(fvec, np.float64), np.asarray(targets, np.float64), np.asarray(grad_out, np.float64)
+    B, N, Cc = fvec.shape
+    M, k = idx.shape[1], idx.shape[2]
+    G = int(groups)
+    Cg = Cc // G
+    gs = g[..., :G] / np.float64(np.sqrt(np.float32(Cg)))                     # [B,M,k,G]
+    gs = np.repeat(gs, Cg, axis=-1)                                           # per channel [B,M,k,C]
+    gt = np.zeros((B, M, Cc))
+    gf = np.zeros((B, N, Cc))
+    for b in range(B):
+        for j in range(k):
+            ij = idx[b, :, j]
+            ok = ij >= 0
+            gt[b, ok] += gs[b, ok, j] * fvec[b, ij[ok]]
+            np.add.at(gf[b], ij[ok], gs[b, ok, j] * targets[b, ok])
+    return gt.astype(np.float32), gf.astype(np.float32)
+
+
+def unproject_backward(grad_fvec, V, H, W, level):
+    """Feature branch of init_pointcloud_from_rgbd backwards (mvtracker/models/core/model_utils.py:439-441 chained
+    avg_pool2d(2, 2), :475-476 permute + reshape): grad_fvec [S, V*Hl*Wl, C] -> grad_fmaps [V,S,C,H,W]."""
+    g = np.asarray(grad_fvec, np.float32)
+    S, P, Cc = g.shape
+    Hl, Wl = H >> level, W >> level
+    assert P == V * Hl * Wl
+    gl = g.reshape(S, V, Hl, Wl, Cc).transpose(1, 0, 4, 2, 3) * np.float32(1.0 / (1 << (2 * level)))     # [V,S,C,Hl,Wl]
+    out = np.zeros((V, S, Cc, H, W), np.float32)
+    f = 1 << level
+    out[:, :, :, :Hl * f, :Wl * f] = np.repeat(np.repeat(gl, f, axis=3), f, axis=4)
+    return out

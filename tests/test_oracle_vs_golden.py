@@ -65,3 +65,20 @@ def test_transformer_input_matches_reference(name, g):
     raw = oracle.transformer_input(g["coords"], g["fcorrs"], g["ffeats"], g["track_mask"], g["vis"], None, None, E)
     assert np.array_equal(raw[:, :, 3 * E:], g["x_noembed"][:, :, 3 * E:])       # copied columns: bit-exact
     assert np.abs(raw[:, :, :3 * E] - g["x_noembed"][:, :, :3 * E]).max() <= 1.2e-7
+
+
+@pytest.mark.parametrize("name,g", golden("bwdcorr"))
+def test_corr_backward_matches_reference_autograd(name, g):
+    """Row f2: analytic gradients of corr_sample against torch autograd through the reference (make_golden_backward.py)."""
+    k, G = int(g["k"]), int(g["groups"])
+    out, idx, _ = oracle.corr_sample(k, g["xyz"], g["fvec"], g["targets"], g["coords"], G, True, bool(g["add_xyz"]), return_idx=True)
+    assert_close(out, g["out"], 1e-4, name)
+    gt, gf = oracle.corr_backward(g["fvec"], g["targets"], idx, g["w"], G)
+    assert_close(gt, g["grad_targets"], 1e-5, f"{name} grad_targets")
+    assert_close(gf, g["grad_fvec"], 1e-5, f"{name} grad_fvec")
+
+
+@pytest.mark.parametrize("name,g", golden("bwdcloud"))
+def test_unproject_backward_matches_reference_autograd(name, g):
+    o = oracle.unproject_backward(g["w"], int(g["V"]), int(g["H"]), int(g["W"]), int(g["level"]))
+    assert np.array_equal(o, g["grad_fmaps"])
