@@ -93,3 +93,20 @@ def test_track_input_rejects_cpu_tensors():
     from mvtracker_b200._lib import MvtError
     with pytest.raises(MvtError):
         ops.track_input(torch.zeros(2, 3, 3), torch.zeros(2, 3, 128), torch.zeros(2, 3), torch.zeros(2, 3), None, None)
+
+
+def test_window_stream_delivers_padded_windows():
+    """Row f4: pinned-host streaming of a sequence's windows (copy of window w+1 overlaps the work on window w); the last
+    window repeats the final frame (mvtracker.py:561-566)."""
+    from mvtracker_b200 import io as mio
+    V, T, S = 2, 27, 12
+    seq = {"fmaps": torch.randn(V, T, 4, 5, 6), "depths": torch.rand(V, T, 1, 5, 6)}
+    seen = []
+    for start, win in mio.WindowStream(seq, S=S, device=DEV):
+        seen.append(start)
+        for k, t in win.items():
+            n = min(S, T - start)
+            assert t.shape[1] == S and torch.equal(t[:, :n].cpu(), seq[k][:, start:start + n])
+            if n < S:
+                assert torch.equal(t[:, n:].cpu(), seq[k][:, T - 1:T].expand(-1, S - n, *seq[k].shape[2:]))
+    assert seen == mio.window_starts(T, S) == [0, 6, 12, 18]
