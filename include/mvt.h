@@ -17,6 +17,8 @@
  *   mvt_knn_gather                      <- feature init, k = 1
  *        mvtracker/models/core/mvtracker/mvtracker.py:627-643
  *   mvt_knn_corr_backward, mvt_cloud_build_backward  <- torch autograd through the two functions above (training)
+ *   mvt_lift_pixels                     <- support-grid unprojection of EvaluationPredictor.forward
+ *        mvtracker/models/evaluation_predictor_3dpt.py:99-116 (bilinear_sample2d: model_utils.py:81-165)
  *   mvt_track_input                     <- assembly of the update transformer's input around the correlation block
  *        mvtracker/models/core/mvtracker/mvtracker.py:374-386, mvtracker/models/core/embeddings.py:134-161
  */
@@ -170,6 +172,14 @@ int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, i
 int mvt_track_input(const float *coords, const void *ffeats, int feat_dtype, const float *track_mask, const float *vis,
                     const float *pos_embed, const float *time_embed, int S, int N, int C, int E, int Lc, float *x,
                     long long track_stride, long long frame_stride, int corr_mode, void *stream);
+
+/* Pixels of ONE depth map lifted to world space (the support grid of EvaluationPredictor.forward,
+ * mvtracker/models/evaluation_predictor_3dpt.py:99-116): z = bilinear_sample2d(depth, x, y) (model_utils.py:81-165), then
+ * world = Einv * [Kinv * [x, y, 1] * z, 1] with the camera record of mvt_camera_prep.
+ * depth [H,W] device fp32; cam [MVT_CAM_STRIDE] (one record); pixels_xy [n,2] (x, y) in pixels of this map.
+ * out [n,3] (with_t 0) or [n,4] = (t_value, x, y, z) (with_t 1: the query / support point layout). */
+int mvt_lift_pixels(const float *depth, int H, int W, const float *cam, const float *pixels_xy, int n, int with_t,
+                    float t_value, float *out, void *stream);
 
 /* ---- backward of the path (training, train.py:119-163) ---------------------------------------------
  * What autograd computes through corr_sample's gather + einsum / sqrt(C/G) (mvtracker.py:827-835) for ONE level, given the

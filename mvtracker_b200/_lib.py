@@ -16,7 +16,7 @@ SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build"
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
            "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
            "mvt_tile_depth_build", "mvt_track_input", "mvt_knn_corr_backward",
-           "mvt_cloud_build_backward")
+           "mvt_cloud_build_backward", "mvt_lift_pixels")
 
 
 class LevelOut(C.Structure):
@@ -97,6 +97,7 @@ def lib():
     L.mvt_tile_depth_build.argtypes = [C.POINTER(Search), ci, ci, C.POINTER(vp), vp]
     L.mvt_track_input.argtypes = [vp, vp, ci, vp, vp, vp, vp, ci, ci, ci, ci, ci, vp, ll, ll, ci, vp]
     L.mvt_knn_corr_backward.argtypes = [vp, vp, ci, vp, vp, ll, ll, ci, ci, ci, ci, ci, ci, ci, vp, ci, vp, vp]
+    L.mvt_lift_pixels.argtypes = [vp, ci, ci, vp, vp, ci, ci, cf, vp, vp]
     L.mvt_cloud_build_backward.argtypes = [vp, ci, ci, ci, ci, ci, ci, vp, ci, vp]
     for name in SYMBOLS:
         f = getattr(L, name)

@@ -69,7 +69,51 @@ __global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
     }
 }
 
+// Lifts pixels of one depth map to world space: bilinear_sample2d of the depth at (x, y)
+// (mvtracker/models/core/model_utils.py:81-165: floor / +1 corners clamped into the image, weights from the unclamped
+// corners) followed by the same unprojection as the cloud build, camera = Kinv * [x, y, 1] * z, world = Einv * [camera, 1]
+// (mvtracker/models/evaluation_predictor_3dpt.py:103-116).  One thread per pixel.
+__global__ void __launch_bounds__(256) lift_pixels_kernel(const float *__restrict__ depth, int H, int W, const float *__restrict__ cam,
+                                                          const float *__restrict__ pix, int n, float t_value,
+                                                          float *__restrict__ out, int out_stride, int out_off) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = __ldg(pix + 2 * i), y = __ldg(pix + 2 * i + 1);
+    const float xf = floorf(x), yf = floorf(y);
+    const float x0f = fminf(fmaxf(xf, -2.0e9f), 2.0e9f), y0f = fminf(fmaxf(yf, -2.0e9f), 2.0e9f);
+    const int x0 = (int)x0f, y0 = (int)y0f;
+    const int x0c = min(max(x0, 0), W - 1), x1c = min(max(x0 + 1, 0), W - 1);
+    const int y0c = min(max(y0, 0), H - 1), y1c = min(max(y0 + 1, 0), H - 1);
+    const float x1f = xf + 1.f, y1f = yf + 1.f;
+    const float w00 = __fmul_rn(x1f - x, y1f - y), w01 = __fmul_rn(x - xf, y1f - y);
+    const float w10 = __fmul_rn(x1f - x, y - yf), w11 = __fmul_rn(x - xf, y - yf);
+    const float d00 = __ldg(depth + (size_t)y0c * W + x0c), d01 = __ldg(depth + (size_t)y0c * W + x1c);
+    const float d10 = __ldg(depth + (size_t)y1c * W + x0c), d11 = __ldg(depth + (size_t)y1c * W + x1c);
+    // (w00*i00 + w01*i01 + w10*i10 + w11*i11), left to right, products rounded (model_utils.py:149)
+    const float z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(w00, d00), __fmul_rn(w01, d01)), __fmul_rn(w10, d10)), __fmul_rn(w11, d11));
+    const float rx = fmaf(cam[0], x, fmaf(cam[1], y, cam[2])), ry = fmaf(cam[3], x, fmaf(cam[4], y, cam[5])),
+                rz = fmaf(cam[6], x, fmaf(cam[7], y, cam[8]));
+    const float cx = rx * z, cy = ry * z, cz = rz * z;
+    float *o = out + (size_t)i * out_stride + out_off;
+    if (out_off > 0) o[-1] = t_value;
+    o[0] = fmaf(cam[9], cx, fmaf(cam[10], cy, fmaf(cam[11], cz, cam[12])));
+    o[1] = fmaf(cam[13], cx, fmaf(cam[14], cy, fmaf(cam[15], cz, cam[16])));
+    o[2] = fmaf(cam[17], cx, fmaf(cam[18], cy, fmaf(cam[19], cz, cam[20])));
+}
+
 }  // namespace mvt
+
+MVT_EXPORT int mvt_lift_pixels(const float *depth, int H, int W, const float *cam, const float *pixels_xy, int n, int with_t,
+                               float t_value, float *out, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(depth && cam && pixels_xy && out, "mvt_lift_pixels: null pointer");
+    MVT_CHECK_ARG(H > 0 && W > 0 && n >= 0, "mvt_lift_pixels: bad sizes H=%d W=%d n=%d", H, W, n);
+    if (n == 0) return MVT_OK;
+    lift_pixels_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(depth, H, W, cam, pixels_xy, n, t_value, out,
+                                                                           with_t ? 4 : 3, with_t ? 1 : 0);
+    MVT_CHECK_LAUNCH("lift_pixels_kernel");
+    return MVT_OK;
+}
 
 MVT_EXPORT int mvt_track_input(const float *coords, const void *ffeats, int feat_dtype, const float *track_mask, const float *vis,
                                const float *pos_embed, const float *time_embed, int S, int N, int C, int E, int Lc, float *x,

@@ -364,6 +364,19 @@ def cloud_build_backward(grad_fvec: torch.Tensor, V: int, H: int, W: int, level:
     return grad_fmaps
 
 
+def lift_pixels(depth: torch.Tensor, cam_record: torch.Tensor, pixels_xy: torch.Tensor, t: Optional[float] = None) -> torch.Tensor:
+    """Row f3: depth [H,W] fp32, cam_record [CAM_STRIDE] (camera_prep), pixels_xy [n,2] -> world points [n,3], or
+    [n,4] = (t, x, y, z) when t is given (evaluation_predictor_3dpt.py:99-116)."""
+    _need_cuda(depth, "depth"); _need_cuda(pixels_xy, "pixels_xy"); _need_cuda(cam_record, "cam_record")
+    H, W = depth.shape
+    d, px, cm = _f32c(depth), _f32c(pixels_xy.reshape(-1, 2)), _f32c(cam_record.reshape(-1))
+    assert cm.numel() == _lib.CAM_STRIDE
+    out = torch.empty(px.shape[0], 3 if t is None else 4, device=d.device, dtype=torch.float32)
+    check(lib().mvt_lift_pixels(_ptr(d), H, W, _ptr(cm), _ptr(px), px.shape[0], int(t is not None), float(t or 0.0), _ptr(out),
+                                _stream()), "mvt_lift_pixels")
+    return out
+
+
 def track_input(coords: torch.Tensor, ffeats: torch.Tensor, track_mask: torch.Tensor, vis: torch.Tensor,
                 pos_embed: Optional[torch.Tensor], time_embed: Optional[torch.Tensor], flow_embed_dim: int = 64,
                 corr_width: int = 256, out: Optional[torch.Tensor] = None, corr_in_out: bool = False) -> torch.Tensor:

@@ -181,3 +181,26 @@ def unproject_backward(grad_fvec, V, H, W, level):
     f = 1 << level
     out[:, :, :, :Hl * f, :Wl * f] = np.repeat(np.repeat(gl, f, axis=3), f, axis=4)
     return out
+
+
+def lift_pixels(depth, K, E, pixels_xy):
+    """numpy restatement of the support-grid unprojection: bilinear_sample2d of the depth
+    (mvtracker/models/core/model_utils.py:81-165) and camera = Kinv [x,y,1] z, world = Einv [camera,1]
+    (mvtracker/models/evaluation_predictor_3dpt.py:103-116).  depth [H,W], K [3,3], E [3,4], pixels_xy [n,2] -> [n,3]."""
+    f32 = np.float32
+    d = np.asarray(depth, f32)
+    H, W = d.shape
+    x, y = np.asarray(pixels_xy, f32)[:, 0], np.asarray(pixels_xy, f32)[:, 1]
+    x0, y0 = np.floor(x), np.floor(y)
+    x1, y1 = x0 + 1, y0 + 1
+    xi0, xi1 = np.clip(x0.astype(np.int64), 0, W - 1), np.clip(x1.astype(np.int64), 0, W - 1)
+    yi0, yi1 = np.clip(y0.astype(np.int64), 0, H - 1), np.clip(y1.astype(np.int64), 0, H - 1)
+    z = ((x1 - x) * (y1 - y)) * d[yi0, xi0] + ((x - x0) * (y1 - y)) * d[yi0, xi1] + ((x1 - x) * (y - y0)) * d[yi1, xi0] \
+        + ((x - x0) * (y - y0)) * d[yi1, xi1]
+    Kinv = np.linalg.inv(np.asarray(K, np.float64))
+    E4 = np.eye(4)
+    E4[:3] = np.asarray(E, np.float64)
+    Einv = np.linalg.inv(E4)
+    cam = (Kinv @ np.stack([x, y, np.ones_like(x)]).astype(np.float64)) * z.astype(np.float64)
+    world = Einv @ np.concatenate([cam, np.ones((1, cam.shape[1]))])
+    return (world[:3] / world[3:]).T.astype(f32)

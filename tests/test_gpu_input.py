@@ -110,3 +110,36 @@ def test_window_stream_delivers_padded_windows():
             if n < S:
                 assert torch.equal(t[:, n:].cpu(), seq[k][:, T - 1:T].expand(-1, S - n, *seq[k].shape[2:]))
     assert seen == mio.window_starts(T, S) == [0, 6, 12, 18]
+
+
+@pytest.mark.parametrize("name,g", golden("predictor"))
+def test_predictor_preprocessing_matches_reference_golden(name, g):
+    """Row f3: resize + intrinsics rescale + support grid (mvt_lift_pixels) against the reference's own code."""
+    from mvtracker_b200 import predictor
+    H, W = (int(v) for v in g["interp_shape"])
+    rgbs, depths, intrs = predictor.resize_inputs(_t(g["rgbs"])[None], _t(g["depths"])[None], _t(g["intrs"])[None], (H, W))
+    assert np.array_equal(rgbs[0].cpu().numpy(), g["rgbs_resized"]) and np.array_equal(depths[0].cpu().numpy(), g["depths_resized"])
+    assert np.allclose(intrs[0].cpu().numpy(), g["intrs_resized"], rtol=1e-6)
+    assert np.allclose(predictor.grid_pixels(int(g["grid_size"]), (H, W), DEV).cpu().numpy(), g["pixel_xy"], atol=1e-5)
+    pts = predictor.support_grid_points(depths, intrs, _t(g["extrs"])[None], int(g["grid_size"]), int(g["n_grids_per_view"]))
+    ref = g["support_points"]
+    assert tuple(pts.shape) == (1,) + ref.shape
+    assert np.array_equal(pts[0, :, 0].cpu().numpy(), ref[:, 0])
+    err = np.abs(pts[0, :, 1:].cpu().numpy() - ref[:, 1:]).max()
+    assert err <= 1e-4 * np.abs(ref[:, 1:]).max(), err
+
+
+def test_lift_pixels_edges_vs_oracle():
+    """Pixels outside the image (clamped corners, extrapolating weights), on integer positions, zero depth."""
+    from mvtracker_b200 import ops as _ops
+    sc = synth.make_scene(1, 20, 28, S=1, C=1, stride=1, zero_frac=0.2, seed=43, device=DEV)
+    depth = sc.depths[0, 0, 0, 0]
+    g = torch.Generator().manual_seed(4)
+    pix = torch.cat([torch.rand(200, 2, generator=g) * torch.tensor([34.0, 26.0]) - 3.0,
+                     torch.tensor([[0.0, 0.0], [27.0, 19.0], [27.5, 19.5], [-0.5, -0.5], [13.0, 7.0]])]).to(DEV)
+    cam = _ops.camera_prep(sc.intrs[0, 0], sc.extrs[0, 0])[0]
+    got = _ops.lift_pixels(depth, cam, pix).cpu().numpy()
+    ref = oracle.lift_pixels(depth.cpu().numpy(), sc.intrs[0, 0, 0].cpu().numpy(), sc.extrs[0, 0, 0].cpu().numpy(), pix.cpu().numpy())
+    assert np.abs(got - ref).max() <= 1e-4 * max(1.0, np.abs(ref).max())
+    with_t = _ops.lift_pixels(depth, cam, pix, t=3.0).cpu().numpy()
+    assert (with_t[:, 0] == 3.0).all() and np.array_equal(with_t[:, 1:], got)

@@ -82,3 +82,15 @@ def test_corr_backward_matches_reference_autograd(name, g):
 def test_unproject_backward_matches_reference_autograd(name, g):
     o = oracle.unproject_backward(g["w"], int(g["V"]), int(g["H"]), int(g["W"]), int(g["level"]))
     assert np.array_equal(o, g["grad_fmaps"])
+
+
+@pytest.mark.parametrize("name,g", golden("predictor"))
+def test_support_grid_matches_reference(name, g):
+    """Row f3: the oracle's pixel lift against the reference's support-grid code (make_golden_predictor.py)."""
+    V, T = g["depths"].shape[:2]
+    pts = []
+    for t in range(0, T, max(1, T // int(g["n_grids_per_view"]))):
+        for v in range(V):
+            w = oracle.lift_pixels(g["depths_resized"][v, t, 0], g["intrs_resized"][v, t], g["extrs"][v, t], g["pixel_xy"])
+            pts.append(np.concatenate([np.full((len(w), 1), t, np.float32), w], 1))
+    assert_close(np.concatenate(pts), g["support_points"], 1e-5, name)
