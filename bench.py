@@ -52,6 +52,7 @@ def parse_args():
                          "(independent replicas, no exchange)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-adjacent", action="store_true", help="skip the timings of the adjacent kernels (rows f1 / f2)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     return ap.parse_args()
 
@@ -371,6 +372,10 @@ def run_ours(args):
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": config_dict(w, args, world, weak), "clocks": clocks,
             "gpu_launches": int(launches), "roofline": roofline, "kernels": kern}
 
+    # ---- adjacent kernels, timed outside the step: not part of `value` -----------------------------
+    if world == 1 and not args.no_adjacent and args.search == "raster":
+        line["adjacent_kernels"] = time_adjacent(ops, state["win"], targets_it[0], coords_it[0], w, esz, peak, dev)
+
     # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------------
     if not args.no_e2e:
         e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if pw > 1 else 0, K_all, E_all, weak)
@@ -385,6 +390,54 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def time_adjacent(ops, win, targets, coords, w, esz, peak, dev, reps=5):
+    """track_input (row f1) on the window's [N, S, 581] buffer; knn_corr_backward + cloud_build_backward (row f2) at level 0.
+    CUDA events on the current stream, 2 warm-up + `reps` timed launches each; algorithmic bytes as in DESIGN.md."""
+    import torch
+    N, S, C, E, V, Hs, Ws = w["N"], S_WINDOW, C_FEAT, 64, w["V"], w["Hs"], w["Ws"]
+    width = LEVELS * K_NN * 4
+    D = 3 * E + 3 + width + C + 2
+
+    def timed(fn, prep=None):
+        for _ in range(2):
+            if prep: prep()
+            fn()
+        ms = 0.0
+        for _ in range(reps):
+            if prep: prep()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            ms += a.elapsed_time(b)
+        return ms / reps
+
+    out = {}
+    g = torch.Generator(device=dev).manual_seed(75)
+    x = torch.empty(N, S, D, device=dev)
+    pos, tim = torch.randn(N, D, device=dev, generator=g), torch.randn(S, D, device=dev, generator=g)
+    mask, vis = torch.ones(S, N, device=dev), torch.rand(S, N, device=dev, generator=g)
+    win.corr(targets, coords, out=ops.corr_columns(x, E, width))
+    ms = timed(lambda: ops.track_input(coords, targets, mask, vis, pos, tim, E, width, out=x, corr_in_out=True))
+    b = N * S * (D * 4 + width * 4 + C * esz + 12 + 8) + (N + S) * D * 4
+    out["track_input"] = {"ms": ms, "alg_bytes": b, "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak,
+                          "what": f"[{N},{S},{D}] transformer input rows written once (corr columns + pos + time in place)"}
+    c0 = win.clouds[0]
+    _, idx = ops.knn_corr([(c0, c0.fvec, K_NN)], targets, coords, return_idx=True)
+    gout = torch.randn(S, N, K_NN, 4, device=dev, generator=g)
+    gfv = torch.zeros(c0.fvec.shape, device=dev, dtype=torch.float32)
+    gtg = torch.zeros(S, N, C, device=dev)
+    ms = timed(lambda: ops.knn_corr_backward(c0.fvec, targets, idx[0], gout, grad_targets=gtg, grad_fvec=gfv))
+    b = S * N * (C * esz + K_NN * C * esz + K_NN * C * 4 + C * 4 + K_NN * 4 + K_NN * 4)
+    out["knn_corr_backward"] = {"ms": ms, "alg_bytes": b, "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak,
+                                "what": "level 0: gather of the neighbour rows + one 16-byte vector reduction per lane and neighbour"}
+    gfm = torch.empty(V, S, C, Hs, Ws, device=dev)
+    ms = timed(lambda: ops.cloud_build_backward(gfv, V, Hs, Ws, 0, grad_fmaps=gfm))
+    b = 2 * gfm.numel() * 4 + gfm.numel() * 4      # accumulate mode: read grad_fvec, read + write grad_fmaps
+    out["cloud_build_backward"] = {"ms": ms, "alg_bytes": b, "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak,
+                                   "what": "level 0 un-pool + transpose, accumulating into grad_fmaps"}
+    return out
 
 
 def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, K_all, E_all, weak=False):
