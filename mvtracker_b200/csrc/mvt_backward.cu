@@ -79,32 +79,41 @@ struct UnpoolParams {
     int accumulate;
 };
 
-// block: 32 level-0 pixels of one row y of one (v, s) plane x all channels (chunks of 32); grid (ceil(W/32), H, V*S)
+// block: 32 level-0 pixels of one row y of one (v, s) plane x all channels, 128 channels per barrier pair (16 loads in
+// flight per thread); grid (ceil(W/32), H, V*S)
+constexpr int kUnpoolCC = 128;
 __global__ void __launch_bounds__(256) feature_unpool_kernel(const UnpoolParams p) {
-    __shared__ float tile[32][33];
+    __shared__ float tile[kUnpoolCC][33];                        // [channel][pixel]
     const int x0 = blockIdx.x * 32, y = blockIdx.y, vs = blockIdx.z;
     const int v = vs / p.S, s = vs - v * p.S;
     const int l = p.level;
     const int yl = y >> l;
     const bool row_in = yl < p.Hl;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 8 rows of 32 threads
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 8 warps
     const size_t frame = ((size_t)s * p.V + v) * (size_t)p.Hl * p.Wl;
-    for (int c0 = 0; c0 < p.C; c0 += 32) {
-        // load: pixel (x0 + i), channels c0 .. c0+31 -- one coalesced 128-byte piece of a point's row per warp
-        for (int i = ty; i < 32; i += 8) {
-            const int x = x0 + i, xl = x >> l;
-            float g = 0.f;
-            if (row_in && x < p.W && xl < p.Wl && c0 + tx < p.C)
-                g = __ldg(p.grad_fvec + (frame + (size_t)yl * p.Wl + xl) * p.C + c0 + tx) * p.weight;
-            tile[i][tx] = g;
+    for (int c0 = 0; c0 < p.C; c0 += kUnpoolCC) {
+        // load: warp ty takes pixels ty, ty+8, ...; a pixel's 128 channels = 4 coalesced 128-byte pieces
+#pragma unroll
+        for (int ii = 0; ii < 4; ++ii) {
+            const int i = ty + 8 * ii, x = x0 + i, xl = x >> l;
+            const bool in = row_in && x < p.W && xl < p.Wl;
+            const float *src = p.grad_fvec + (frame + (size_t)yl * p.Wl + (in ? xl : 0)) * p.C + c0;
+#pragma unroll
+            for (int cc = 0; cc < kUnpoolCC; cc += 32) {
+                float g = 0.f;
+                if (in && c0 + cc + tx < p.C) g = __ldg(src + cc + tx) * p.weight;
+                tile[cc + tx][i] = g;
+            }
         }
         __syncthreads();
-        // store: channel (c0 + i), pixels x0 .. x0+31 of row y
-        for (int i = ty; i < 32; i += 8) {
-            const int c = c0 + i, x = x0 + tx;
+        // store: warp ty takes channels ty, ty+8, ...: 32 consecutive pixels of row y per warp instruction
+        const int x = x0 + tx;
+#pragma unroll 4
+        for (int i = ty; i < kUnpoolCC; i += 8) {
+            const int c = c0 + i;
             if (c < p.C && x < p.W) {
                 float *o = p.grad_fmaps + ((((size_t)v * p.S + s) * p.C + c) * p.H + y) * p.W + x;
-                *o = p.accumulate ? *o + tile[tx][i] : tile[tx][i];
+                *o = p.accumulate ? *o + tile[i][tx] : tile[i][tx];
             }
         }
         __syncthreads();

@@ -32,40 +32,48 @@ struct InputParams {
     int corr_mode;             // 0: leave the correlation columns alone, 1: add the embeddings to them in place
 };
 
+constexpr int kInputMaxS = 64;      // frames per window the kernel keeps flows for (the model uses S = 12)
+
+// One block per track.  The S*D elements of the track's rows are independent: thread t takes elements t, t + 256, ...
+// (four per loop trip, so that their loads are in flight together); the S flow vectors are computed once into shared memory.
 template <typename T>
 __global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
+    __shared__ float flow[3 * kInputMaxS];
     const int n = blockIdx.x;
-    const int E3 = 3 * p.E, c_corr = E3 + 3, c_feat = c_corr + p.Lc, c_mask = c_feat + p.C;
-    const float x0 = __ldg(p.coords + (size_t)n * 3), y0 = __ldg(p.coords + (size_t)n * 3 + 1), z0 = __ldg(p.coords + (size_t)n * 3 + 2);
-    const float *pos = p.pos ? p.pos + (size_t)n * p.D : nullptr;
+    const int E3 = 3 * p.E, c_corr = E3 + 3, c_feat = c_corr + p.Lc, c_mask = c_feat + p.C, D = p.D;
+    if (threadIdx.x < 3 * p.S) {
+        const int s = threadIdx.x / 3, a = threadIdx.x - 3 * s;
+        flow[threadIdx.x] = __fsub_rn(__ldg(p.coords + ((size_t)s * p.N + n) * 3 + a), __ldg(p.coords + (size_t)n * 3 + a));
+    }
+    __syncthreads();
+    const float *pos = p.pos ? p.pos + (size_t)n * D : nullptr;
     const T *ff = reinterpret_cast<const T *>(p.ffeats);
-    for (int s = 0; s < p.S; ++s) {
+    float *base = p.x + (long long)n * p.track_stride;
+    const int total = p.S * D;
+    const unsigned magic = (unsigned)((0x100000000ull + (unsigned)D - 1) / (unsigned)D);      // e / D == (e * magic) >> 32 while e * D < 2^32 (checked on the host)
+#pragma unroll 4
+    for (int e = threadIdx.x; e < total; e += 256) {
+        const int s = (int)(((unsigned long long)(unsigned)e * magic) >> 32), c = e - s * D;
         const size_t q = (size_t)s * p.N + n;
-        const float fx = __fsub_rn(__ldg(p.coords + q * 3), x0), fy = __fsub_rn(__ldg(p.coords + q * 3 + 1), y0),
-                    fz = __fsub_rn(__ldg(p.coords + q * 3 + 2), z0);
-        float *row = p.x + (long long)n * p.track_stride + (long long)s * p.frame_stride;
-        const float *tim = p.tim ? p.tim + (size_t)s * p.D : nullptr;
-        for (int c = threadIdx.x; c < p.D; c += blockDim.x) {
-            float v;
-            if (c < E3) {
-                const int axis = c / p.E, j = c - axis * p.E;
-                const float f = axis == 0 ? fx : (axis == 1 ? fy : fz);
-                const float a = __fmul_rn(f, __fmul_rn((float)(j & ~1), p.div_scale));
-                v = (j & 1) ? cosf(a) : sinf(a);
-            } else if (c < c_corr) {
-                v = c == E3 ? fx : (c == E3 + 1 ? fy : fz);
-            } else if (c < c_feat) {
-                if (p.corr_mode == 0) continue;
-                v = row[c];
-            } else if (c < c_mask) {
-                v = (float)ff[q * p.C + (c - c_feat)];
-            } else {
-                v = c == c_mask ? __ldg(p.track_mask + q) : __ldg(p.vis + q);
-            }
-            if (pos) v = __fadd_rn(v, __ldg(pos + c));
-            if (tim) v = __fadd_rn(v, __ldg(tim + c));
-            row[c] = v;
+        float *row = base + (long long)s * p.frame_stride;
+        float v;
+        if (c < E3) {
+            const int axis = c / p.E, j = c - axis * p.E;
+            const float a = __fmul_rn(flow[3 * s + axis], __fmul_rn((float)(j & ~1), p.div_scale));
+            v = (j & 1) ? cosf(a) : sinf(a);
+        } else if (c < c_corr) {
+            v = flow[3 * s + (c - E3)];
+        } else if (c < c_feat) {
+            if (p.corr_mode == 0) continue;
+            v = row[c];
+        } else if (c < c_mask) {
+            v = (float)ff[q * p.C + (c - c_feat)];
+        } else {
+            v = c == c_mask ? __ldg(p.track_mask + q) : __ldg(p.vis + q);
         }
+        if (pos) v = __fadd_rn(v, __ldg(pos + c));
+        if (p.tim) v = __fadd_rn(v, __ldg(p.tim + (size_t)s * D + c));
+        row[c] = v;
     }
 }
 
@@ -121,6 +129,7 @@ MVT_EXPORT int mvt_track_input(const float *coords, const void *ffeats, int feat
     using namespace mvt;
     MVT_CHECK_ARG(coords && ffeats && track_mask && vis && x, "mvt_track_input: null pointer");
     MVT_CHECK_ARG(S > 0 && N > 0 && C > 0 && Lc >= 0, "mvt_track_input: bad sizes S=%d N=%d C=%d Lc=%d", S, N, C, Lc);
+    MVT_CHECK_ARG(S <= kInputMaxS, "mvt_track_input: at most %d frames per window (got %d)", kInputMaxS, S);
     MVT_CHECK_ARG(E > 0 && (E & 1) == 0, "mvt_track_input: flow embedding size must be even (got %d)", E);
     MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_track_input: feat_dtype %d", feat_dtype);
     MVT_CHECK_ARG(corr_mode == 0 || corr_mode == 1, "mvt_track_input: corr_mode %d", corr_mode);
@@ -130,6 +139,7 @@ MVT_EXPORT int mvt_track_input(const float *coords, const void *ffeats, int feat
     p.S = S; p.N = N; p.C = C; p.E = E; p.Lc = Lc; p.D = 3 * E + 3 + Lc + C + 2;
     p.div_scale = (float)(1000.0 / (double)E);
     p.corr_mode = corr_mode;
+    MVT_CHECK_ARG((long long)S * p.D * p.D < (1ll << 32), "mvt_track_input: S*D*D = %lld too large", (long long)S * p.D * p.D);
     MVT_CHECK_ARG(track_stride >= p.D || N == 1, "mvt_track_input: track stride %lld < row width %d", track_stride, p.D);
     if (feat_dtype == MVT_F32) track_input_kernel<float><<<N, 256, 0, (cudaStream_t)stream>>>(p);
     else track_input_kernel<__nv_bfloat16><<<N, 256, 0, (cudaStream_t)stream>>>(p);

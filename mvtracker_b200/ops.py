@@ -348,15 +348,16 @@ def knn_corr_backward(fvec: torch.Tensor, targets: torch.Tensor, idx: torch.Tens
 
 
 def cloud_build_backward(grad_fvec: torch.Tensor, V: int, H: int, W: int, level: int,
-                         grad_fmaps: Optional[torch.Tensor] = None) -> torch.Tensor:
+                         grad_fmaps: Optional[torch.Tensor] = None, accumulate: Optional[bool] = None) -> torch.Tensor:
     """Row f2: feature branch of init_pointcloud_from_rgbd backwards (model_utils.py:439-441, 475-476).
     grad_fvec [S, V*(H>>level)*(W>>level), C] -> grad_fmaps [V,S,C,H,W] fp32 (accumulated into when given)."""
     _need_cuda(grad_fvec, "grad_fvec")
     S, P, C = grad_fvec.shape
     assert P == V * (H >> level) * (W >> level), "grad_fvec does not match the level's cloud size"
     g = _f32c(grad_fvec)
-    acc = grad_fmaps is not None
+    acc = (grad_fmaps is not None) if accumulate is None else bool(accumulate)
     if grad_fmaps is None:
+        assert not acc
         grad_fmaps = torch.empty(V, S, C, H, W, device=g.device, dtype=torch.float32)
     assert grad_fmaps.dtype == torch.float32 and grad_fmaps.is_contiguous() and grad_fmaps.shape == (V, S, C, H, W)
     check(lib().mvt_cloud_build_backward(_ptr(g), V, S, C, H, W, int(level), _ptr(grad_fmaps), int(acc), _stream()),
