@@ -111,3 +111,22 @@ def test_install_rebinds_reference_seam():
     finally:
         undo()
     assert (ref.mvt.init_pointcloud_from_rgbd, ref.mvt.knn, ref.mvt.PointcloudCorrBlock) == saved
+
+
+def test_adjacent_entry_points_check_arguments_without_a_gpu():
+    """Rows f1-f3: the new entry points reject bad arguments before any device work (code -1 + message)."""
+    L = _lib.lib()
+    d = ctypes.c_void_p(256)
+    assert L.mvt_track_input(d, d, 0, d, d, None, None, 12, 4, 128, 63, 256, d, 581 * 12, 581, 1, None) == -1       # odd E
+    assert b"even" in L.mvt_last_error()
+    assert L.mvt_track_input(d, d, 0, d, d, None, None, 65, 4, 128, 64, 256, d, 581 * 65, 581, 1, None) == -1       # S > 64
+    assert L.mvt_track_input(d, None, 0, d, d, None, None, 12, 4, 128, 64, 256, d, 581 * 12, 581, 1, None) == -1
+    assert b"null" in L.mvt_last_error()
+    assert L.mvt_knn_corr_backward(d, d, 0, d, d, 64, 0, 1, 10, 5, 6, 1, 4, 4, d, 0, d, None) == -1                  # C % 4
+    assert b"multiple of 4" in L.mvt_last_error()
+    assert L.mvt_knn_corr_backward(d, d, 0, d, d, 64, 0, 1, 10, 5, 8, 1, 64, 4, d, 0, d, None) == -1                 # k > 32
+    assert L.mvt_cloud_build_backward(d, 2, 2, 8, 16, 16, 4, d, 0, None) == -1                                      # level > 3
+    assert L.mvt_cloud_build_backward(d, 2, 2, 8, 4, 16, 3, d, 0, None) == -1                                       # empty level
+    assert b"empty" in L.mvt_last_error()
+    assert L.mvt_lift_pixels(None, 4, 4, d, d, 3, 0, 0.0, d, None) == -1
+    assert L.mvt_lift_pixels(d, 4, 4, d, d, 0, 0, 0.0, d, None) == 0                                                 # nothing to do
