@@ -58,9 +58,12 @@ __global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
         float *row = base + (long long)s * p.frame_stride;
         float v;
         if (c < E3) {
+            // even / odd columns of a pair share the angle: one sincosf (one range reduction) instead of a divergent sinf | cosf
             const int axis = c / p.E, j = c - axis * p.E;
             const float a = __fmul_rn(flow[3 * s + axis], __fmul_rn((float)(j & ~1), p.div_scale));
-            v = (j & 1) ? cosf(a) : sinf(a);
+            float sv, cv;
+            sincosf(a, &sv, &cv);
+            v = (j & 1) ? cv : sv;
         } else if (c < c_corr) {
             v = flow[3 * s + (c - E3)];
         } else if (c < c_feat) {
