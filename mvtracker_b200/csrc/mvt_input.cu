@@ -35,7 +35,7 @@ struct InputParams {
 constexpr int kInputMaxS = 64;      // frames per window the kernel keeps flows for (the model uses S = 12)
 
 // One block per track.  The S*D elements of the track's rows are independent: thread t takes elements t, t + 256, ...
-// (four per loop trip, so that their loads are in flight together); the S flow vectors are computed once into shared memory.
+// (several per loop trip, so that their loads are in flight together); the S flow vectors are computed once into shared memory.
 template <typename T>
 __global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
     __shared__ float flow[3 * kInputMaxS];
@@ -49,34 +49,51 @@ __global__ void __launch_bounds__(256) track_input_kernel(const InputParams p) {
     const float *pos = p.pos ? p.pos + (size_t)n * D : nullptr;
     const T *ff = reinterpret_cast<const T *>(p.ffeats);
     float *base = p.x + (long long)n * p.track_stride;
-    const int total = p.S * D;
-    const unsigned magic = (unsigned)((0x100000000ull + (unsigned)D - 1) / (unsigned)D);      // e / D == (e * magic) >> 32 while e * D < 2^32 (checked on the host)
-#pragma unroll 4
-    for (int e = threadIdx.x; e < total; e += 256) {
-        const int s = (int)(((unsigned long long)(unsigned)e * magic) >> 32), c = e - s * D;
-        const size_t q = (size_t)s * p.N + n;
-        float *row = base + (long long)s * p.frame_stride;
-        float v;
-        if (c < E3) {
-            // even / odd columns of a pair share the angle: one sincosf (one range reduction) instead of a divergent sinf | cosf
-            const int axis = c / p.E, j = c - axis * p.E;
-            const float a = __fmul_rn(flow[3 * s + axis], __fmul_rn((float)(j & ~1), p.div_scale));
+    auto magic_of = [](int d) { return (unsigned)((0x100000000ull + (unsigned)d - 1) / (unsigned)d); };   // e / d == (e * magic) >> 32 while e * d < 2^32 (checked on the host)
+    auto div_by = [](int e, unsigned magic) { return (int)(((unsigned long long)(unsigned)e * magic) >> 32); };
+    // (a) the sin / cos pairs: columns axis*E + 2i (sin) and + 2i + 1 (cos) share the angle -> one sincosf per pair
+    {
+        const int half = p.E >> 1, ppr = 3 * half, total = p.S * ppr;        // pairs per row
+        const unsigned m_row = magic_of(ppr), m_axis = magic_of(half);
+#pragma unroll 2
+        for (int e = threadIdx.x; e < total; e += 256) {
+            const int s = div_by(e, m_row), pr = e - s * ppr;
+            const int axis = div_by(pr, m_axis), i = pr - axis * half;
+            const int c = axis * p.E + 2 * i;
+            const float a = __fmul_rn(flow[3 * s + axis], __fmul_rn((float)(2 * i), p.div_scale));
             float sv, cv;
             sincosf(a, &sv, &cv);
-            v = (j & 1) ? cv : sv;
-        } else if (c < c_corr) {
-            v = flow[3 * s + (c - E3)];
-        } else if (c < c_feat) {
-            if (p.corr_mode == 0) continue;
-            v = row[c];
-        } else if (c < c_mask) {
-            v = (float)ff[q * p.C + (c - c_feat)];
-        } else {
-            v = c == c_mask ? __ldg(p.track_mask + q) : __ldg(p.vis + q);
+            if (pos) { sv = __fadd_rn(sv, __ldg(pos + c)); cv = __fadd_rn(cv, __ldg(pos + c + 1)); }
+            if (p.tim) { sv = __fadd_rn(sv, __ldg(p.tim + (size_t)s * D + c)); cv = __fadd_rn(cv, __ldg(p.tim + (size_t)s * D + c + 1)); }
+            float *row = base + (long long)s * p.frame_stride;
+            row[c] = sv;
+            row[c + 1] = cv;
         }
-        if (pos) v = __fadd_rn(v, __ldg(pos + c));
-        if (p.tim) v = __fadd_rn(v, __ldg(p.tim + (size_t)s * D + c));
-        row[c] = v;
+    }
+    // (b) the copied columns [3E, D): flow, correlation block (in place), track features, masks
+    {
+        const int w = D - E3, total = p.S * w;
+        const unsigned m_row = magic_of(w);
+#pragma unroll 4
+        for (int e = threadIdx.x; e < total; e += 256) {
+            const int s = div_by(e, m_row), c = E3 + (e - s * w);
+            const size_t q = (size_t)s * p.N + n;
+            float *row = base + (long long)s * p.frame_stride;
+            float v;
+            if (c < c_corr) {
+                v = flow[3 * s + (c - E3)];
+            } else if (c < c_feat) {
+                if (p.corr_mode == 0) continue;
+                v = row[c];
+            } else if (c < c_mask) {
+                v = (float)ff[q * p.C + (c - c_feat)];
+            } else {
+                v = c == c_mask ? __ldg(p.track_mask + q) : __ldg(p.vis + q);
+            }
+            if (pos) v = __fadd_rn(v, __ldg(pos + c));
+            if (p.tim) v = __fadd_rn(v, __ldg(p.tim + (size_t)s * D + c));
+            row[c] = v;
+        }
     }
 }
 
