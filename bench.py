@@ -51,6 +51,9 @@ def parse_args():
                          "multi-GPU design is about); weak = every rank tracks its own sequence's window with the single-GPU path "
                          "(independent replicas, no exchange)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--warm-start", action="store_true",
+                    help="N = 1: iterations 2..4 of a window start their searches from the previous iteration's neighbours "
+                         "(exact; off by default so that every timed iteration does the full cold search)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-adjacent", action="store_true", help="skip the timings of the adjacent kernels (rows f1 / f2)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
@@ -204,7 +207,7 @@ def config_dict(w, args, world=1, weak=False):
              f"straight into every rank's buffers (symmetric memory, NVSwitch multicast stores), two signal-pad barriers per iteration, no NCCL on the data path" if args.dist_mode == "p2p" else
              f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard (two bounded phases), merged indices all-gathered, result records all-reduced (NCCL)"),"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
-            "levels": LEVELS, "k": K_NN, "iters": args.iters, "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
+            "levels": LEVELS, "k": K_NN, "iters": args.iters, "warm_start": bool(getattr(args, "warm_start", False)), "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
             "l2": "inputs_exceed_l2 (feature maps and clouds are > 126 MB and are rewritten every step)"}
 
@@ -278,6 +281,7 @@ def run_ours(args):
             if args.search == "grid":
                 grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
             win = WindowClouds(clouds, grids, K_NN, 1, True, False)
+            win.warm_start = bool(args.warm_start)
         else:
             win = ShardedWindow.build(fm, dp, K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
                                       intrs_all=K_all, extrs_all=E_all, mode=args.dist_mode)

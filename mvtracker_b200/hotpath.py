@@ -21,7 +21,10 @@ class WindowClouds:
         self.k, self.groups, self.add_offset, self.add_xyz = k, groups, add_offset, add_xyz
         self.D = groups + 3 * bool(add_offset) + 3 * bool(add_xyz)
         self.width = len(clouds) * k * self.D
-        self.warm_start = False     # True: iteration i+1 starts its searches from iteration i's neighbours (exact either way; no gain measured when tracks move ~ the k-NN radius per iteration)
+        # True: iteration i+1 starts its searches from iteration i's neighbours (their largest distance caps the k-th best;
+        # exact either way).  Panoptic window, tracks moving N(0, 1 cm) per iteration: 0.697 -> 0.667 ms per warm iteration
+        # (tools/diag_warm.py).  Off by default: bench.py times every iteration cold unless --warm-start is given.
+        self.warm_start = False
         self._idx = None            # [levels, S, N, k] int32 of the last corr() call on these clouds
 
     @classmethod
