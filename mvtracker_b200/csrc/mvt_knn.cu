@@ -34,7 +34,7 @@ __device__ __forceinline__ void search(const SearchDev &sd, const unsigned char 
 __global__ void __launch_bounds__(256) knn_kernel(const SearchDev sd, int B, int M, const float *__restrict__ query, int k,
                                                   int *__restrict__ idx32, long long *__restrict__ idx64,
                                                   float *__restrict__ dist) {
-    MVT_WARP_SCRATCH(win_tab, 32);
+    MVT_WARP_SCRATCH(win_tab, 8);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;
@@ -172,14 +172,16 @@ __device__ __forceinline__ float dot8_bf16(const uint4 &a, const uint4 &b) {
 // MODE 0: generic fp32 (any C, G).   MODE 1: fp32, C == 128, G == 1, k <= 16.   MODE 2: bf16, C == 128, G == 1, k <= 16.
 // GW = 32: one warp per query.   GW = 16 (raster search, MODE 1/2, V <= 16): one half warp per query.
 // Grid: x = query blocks of one frame, y = frame b, z = pyramid level.
-// One warp (one query) per block, 32 blocks per SM: 64 registers per thread, 32 warps per SM as with larger blocks, but a
-// warp slot is handed to the next query the moment ITS query is done instead of when the slowest of the block's queries
-// is (measured 128 x 8: 0.734 ms, 64 x 16: 0.718, 32 x 32: 0.699 on the panoptic window; 256 x 4: 0.802).
+// Two warps (two queries) per block, 18 blocks per SM: 56 registers per thread, 36 warps per SM.  Small blocks hand a warp
+// slot to the next query as soon as its own query is done (128 x 8: 0.734 ms on the panoptic window, 64 x 16: 0.718,
+// 32 x 32: 0.699; 256 x 4: 0.802); with the per-view projection constants parked in shared memory between passes
+// (MVT_CAM_SMEM, mvt_raster.cuh) 56 registers spill 12 bytes and 36 resident warps beat 32: 32 x 32 -> 0.689, 64 x 18 -> 0.681,
+// 64 x 20 (48 registers, 40 warps) -> 0.726.
 #ifndef MVT_CORR_MINB
-#define MVT_CORR_MINB 32
+#define MVT_CORR_MINB 18
 #endif
 #ifndef MVT_CORR_THREADS
-#define MVT_CORR_THREADS 32
+#define MVT_CORR_THREADS 64
 #endif
 template <int MODE, bool RASTER_ONLY, int GW>
 __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
@@ -342,7 +344,7 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
 __global__ void __launch_bounds__(256) knn_gather_kernel(const SearchDev sd, const void *__restrict__ fvec, int elem_bytes,
                                                          int B, int M, int C, const float *__restrict__ query,
                                                          void *__restrict__ feat_out, int *__restrict__ idx_out) {
-    MVT_WARP_SCRATCH(win_tab, 32);
+    MVT_WARP_SCRATCH(win_tab, 8);
     const int lane = threadIdx.x & 31;
     const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (w >= (long long)B * M) return;

@@ -70,7 +70,16 @@ __host__ __device__ constexpr unsigned win_tab_word(int i) {
 }
 template <int I> struct WinWord { static constexpr unsigned value = win_tab_word(I); };
 // Per-warp shared memory of the search: the window table and, right behind it, the pending buffer of the top-k list.
+#ifndef MVT_CAM_SMEM
+#define MVT_CAM_SMEM 1
+#endif
+#if MVT_CAM_SMEM
+// cam[i][lane]: the lane's (= its view's) projection constants, read back once per pass for the ball's pixel box --
+// ten registers per thread that need not stay live across the scans
+struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; float cam[10][32]; };
+#else
 struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; };
+#endif
 // declares the block's scratch (one per warp), hands this warp its table pointer `name` and fills the table
 #define MVT_WARP_SCRATCH(name, nwarps)                                   \
     __shared__ mvt::WarpScratch name##_all[nwarps];                      \
@@ -325,6 +334,14 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         ci = (int)fminf(fmaxf(floorf(fi), -1.0e8f), 1.0e8f);
         cj = (int)fminf(fmaxf(rintf(fj), -1.0e8f), 1.0e8f);
     }
+#if MVT_CAM_SMEM
+    {
+        float (*cs)[32] = reinterpret_cast<float (*)[32]>(const_cast<unsigned char *>(win_tab) + 32 + 32 * sizeof(u64));
+        const int ln = threadIdx.x & 31;
+        cs[0][ln] = X; cs[1][ln] = Y; cs[2][ln] = Z; cs[3][ln] = iz; cs[4][ln] = fx; cs[5][ln] = sk; cs[6][ln] = cx0;
+        cs[7][ln] = fy; cs[8][ln] = cy0; cs[9][ln] = tnorm;
+    }
+#endif
     const Rect whole = {0, 0, W, H};
     auto window = [&](int mm) {
         Rect r = {0, 0, 0, 0};
@@ -402,8 +419,18 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         if (have_k) {
             // pixel bounding box of the ball B(q, r), r = current k-th best distance (an upper bound of the final one)
             float r = sqrtf(key_d2(tk.th));
+#if MVT_CAM_SMEM
+            {
+                float (*cs)[32] = reinterpret_cast<float (*)[32]>(const_cast<unsigned char *>(win_tab) + 32 + 32 * sizeof(u64));
+                const int ln = threadIdx.x & 31;
+                const float X_ = cs[0][ln], Y_ = cs[1][ln], Z_ = cs[2][ln];
+                float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X_) + fabsf(Y_) + fabsf(Z_) + cs[9][ln] + r));
+                if (mine && kok) R = ball_box(front, X_, Y_, Z_, cs[3][ln], reff, cs[4][ln], cs[5][ln], cs[6][ln], cs[7][ln], cs[8][ln], inv_st, W, H);
+            }
+#else
             float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
             if (mine && kok) R = ball_box(front, X, Y, Z, iz, reff, fx, sk, cx0, fy, cy0, inv_st, W, H);
+#endif
             covered = !mine || rect_empty(R) || rect_inside(R, A);
         } else {
             // fewer than k searchable points so far; stop only when all rasters are covered
