@@ -137,6 +137,9 @@ def cpu_sample(w, iters, budget_s, zero_frac, seed=72):
     from mvtracker_b200 import synth
     from oracle import oracle
 
+    # all the host threads this process may use -- set explicitly: torchrun exports OMP_NUM_THREADS=1 to its workers,
+    # which would time the CPU arm on one core
+    oracle.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     cores = oracle.num_threads()
     ck = (w["name"], zero_frac, seed)
     if _scene_cache.get("key") != ck:       # inputs are generated once; only the oracle calls are timed
