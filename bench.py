@@ -24,11 +24,17 @@ S_WINDOW, C_FEAT, K_NN, LEVELS, STRIDE = 12, 128, 16, 4, 4
 # The workload every N runs by default: the 8-view / ~1M-point window north_star quotes its 1-GPU roofline and 8-GPU scaling
 # targets on (BASELINE.json configs[2]); it fits one GPU (~17 GB), so the 1/2/4/8-GPU series is one fixed job (strong scaling).
 DEFAULT_WORKLOAD = "panoptic"
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full captures under
-# profiles/ (workload, dtype, kernel) -> bytes; None until that capture exists.
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full captures under profiles/
-NCU_TRAFFIC = {("panoptic", "f32", "knn_corr"): 1448518168, ("panoptic", "f32", "cloud_build"): 15580389000,
-               ("droid", "f32", "knn_corr"): 498648576}
+
+
+def ncu_traffic(workload, dtype, kernel, n_gpus):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the ncu --set full capture that
+    tools/ncu_summary.py recorded in profiles/traffic.json ("workload/dtype/kernel/nN" -> {bytes, capture}); None when that
+    kernel has no capture at this N (a number measured on another kernel or another N is not this kernel's traffic)."""
+    try:
+        tab = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return tab.get(f"{workload}/{dtype}/{kernel}/n{n_gpus}", {}).get("bytes")
+    except Exception:
+        return None
 
 
 def parse_args():
@@ -55,6 +61,11 @@ def parse_args():
                     help="N = 1: iterations 2..4 of a window start their searches from the previous iteration's neighbours "
                          "(exact; off by default so that every timed iteration does the full cold search)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-verify", action="store_true", help="skip the sampled check of the last step's output against the oracle")
+    ap.add_argument("--no-distributions", action="store_true",
+                    help="skip the extra timed track distributions (static init, 40 %% invalid depth); N = 1 only")
+    ap.add_argument("--no-model", action="store_true", help="skip the MVTracker.forward frames/s legs (N = 1 only)")
+    ap.add_argument("--model-workloads", default="kubric,droid", help="configs of the MVTracker.forward legs")
     ap.add_argument("--no-adjacent", action="store_true", help="skip the timings of the adjacent kernels (rows f1 / f2)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     return ap.parse_args()
@@ -177,26 +188,94 @@ def cpu_sample(w, iters, budget_s, zero_frac, seed=72):
             "step_seconds_extrapolated": step_cpu, "sample_seconds": t_build + t_small + t_corr * reps}
 
 
+def ref_sample(w, iters, budget_s, zero_frac, seed=72):
+    """The reference's OWN CPU path (oracle/ref_import.py: /root/reference, or the unmodified copy staged under oracle/_ref):
+    init_pointcloud_from_rgbd x4 levels (model_utils.py:420-482) and PointcloudCorrBlock.corr_sample -> _knn_torch
+    (mvtracker.py:75-79, 800-846) x4 levels x `iters`, on ONE frame of the workload and a track subsample sized to the budget
+    (_knn_torch materialises [S, M, P] fp32 -- 201 GB at the panoptic level 0 -- so it is run per frame and per
+    track chunk; its cost is exactly linear in both).  Everything reported under sample_* is measured; `value` scales the
+    measured per-frame build and per-track correlation times to the window (S frames, N tracks)."""
+    import numpy as np
+    import torch
+    from mvtracker_b200 import synth
+    from oracle import ref_import
+    ref = ref_import.load()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(cores)
+    ck = (w["name"], zero_frac, seed, "ref")
+    if _scene_cache.get("key") != ck:
+        sc = synth.make_scene(w["V"], w["H"], w["W"], S=1, C=C_FEAT, stride=STRIDE, zero_frac=zero_frac, seed=seed)
+        _scene_cache.clear()
+        _scene_cache.update(key=ck, scene=sc)
+    sc = _scene_cache["scene"]
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        blocks = []
+        for lvl in range(LEVELS):
+            xyz, fvec = ref.init_pointcloud_from_rgbd(fmaps=sc.fmaps, depths=sc.depths, intrs=sc.intrs, extrs=sc.extrs,
+                                                      stride=STRIDE, level=lvl)
+            blocks.append(ref.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
+                                                  corr_add_neighbor_xyz=False))
+        t_build = time.perf_counter() - t0
+        coords, targets = synth.make_tracks(blocks[0].xyz[0], w["N"], 1, C=C_FEAT)
+        P0 = blocks[0].xyz.shape[1]
+        chunk = int(max(16, min(w["N"], (2 << 30) // (4 * P0))))      # <= 2 GB distance matrix per call
+
+        def run(m):
+            t = time.perf_counter()
+            for a in range(0, m, chunk):
+                b = min(m, a + chunk)
+                for blk in blocks:
+                    blk.corr_sample(targets[:, a:b], coords[:, a:b])
+            return time.perf_counter() - t
+
+        m = min(w["N"], 16)
+        t_small = run(m)
+        per_track = t_small / m
+        m_big = int(max(m, min(w["N"], (budget_s - t_build - t_small) / max(per_track * iters, 1e-9))))
+        t_corr = sum(run(m_big) for _ in range(iters))         # `iters` refinement iterations on the same clouds
+    t_q = t_corr / (iters * m_big)                              # seconds per track per frame per iteration, all 4 levels
+    step_cpu = S_WINDOW * t_build + iters * S_WINDOW * w["N"] * t_q
+    queries = iters * LEVELS * S_WINDOW * w["N"]
+    sample_s = t_build + t_corr
+    return {"value": queries / step_cpu, "unit": "queries/s", "cores": cores, "kind": "reference",
+            "source": f"{ref.kind}: {'oracle/_ref (unmodified files staged by oracle/make_ref.py)' if ref.kind == 'staged' else ref.root}",
+            "sample": (f"the reference's own init_pointcloud_from_rgbd x{LEVELS} levels ({t_build:.2f}s) + PointcloudCorrBlock.corr_sample "
+                       f"(_knn_torch) x{LEVELS} levels x{iters} iterations on {m_big} of {w['N']} tracks ({t_corr:.2f}s), 1 of {S_WINDOW} frames, "
+                       f"{cores} torch threads; value = window queries / (S*t_build + S*N/m*t_corr)"),
+            "sample_queries": iters * LEVELS * m_big, "sample_seconds": sample_s,
+            "sample_value": iters * LEVELS * m_big / sample_s, "step_seconds_extrapolated": step_cpu}
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port, all host threads), rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path on the box's host cores (its own PyTorch code when
+    oracle/_ref or /root/reference is there, else the oracle port), rank 0 only.  A STEP of this arm is one bounded sample."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import ref_import
     w = workload_cfg(args.workload or DEFAULT_WORKLOAD)
     budget = max(2.0, min(args.cpu_budget, 150.0 / max(1, args.steps + args.warmup)))
-    for _ in range(args.warmup):
-        cpu_sample(w, args.iters, budget, args.zero_frac)
-    vals, secs = [], []
+    sample = ref_sample if ref_import.available() else cpu_sample
+    for _ in range(min(args.warmup, 1)):
+        sample(w, args.iters, budget, args.zero_frac)
+    vals, secs, wall = [], [], []
     for _ in range(args.steps):
-        r = cpu_sample(w, args.iters, budget, args.zero_frac)
-        vals.append(r["value"]); secs.append(r["step_seconds_extrapolated"])
+        t0 = time.perf_counter()
+        r = sample(w, args.iters, budget, args.zero_frac)
+        wall.append(time.perf_counter() - t0)
+        vals.append(r["value"]); secs.append(r["sample_seconds"])
     vals.sort()
     v = vals[len(vals) // 2]
     r["value"] = v
+    cfg = config_dict(w, args)
+    cfg["parallelism"] = f"CPU: {r['cores']} host threads, {'the reference PyTorch path (_knn_torch)' if r['kind'] == 'reference' else 'C/OpenMP port of the reference path'}"
+    cfg["search"] = "brute force (torch.cdist + topk)" if r["kind"] == "reference" else "brute force"
     line = {"impl": "reference", "metric": "knn_corr_queries_per_s", "value": v, "unit": "queries/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sorted(secs)[len(secs) // 2],
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * sorted(wall)[len(wall) // 2],
+            "step_is": "one bounded sample (1 frame, a track subsample); see cpu_baseline.sample",
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(w, args), "cpu_baseline": r,
+            "config": cfg, "cpu_baseline": r,
             "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -293,7 +372,7 @@ def run_ours(args):
         for i in range(iters):
             # "p2p": the result block is returned where the ranks' kernels stored it (symmetric memory; valid until the
             # next-but-one corr call), as the fused kernel writes into the caller's buffer at N = 1 -- no extra copy
-            win.corr(targets_it[i], coords_it[i], out=None if getattr(win, "mode", "") == "p2p" else outs[i])
+            state["out"] = win.corr(targets_it[i], coords_it[i], out=None if getattr(win, "mode", "") == "p2p" else outs[i])
             if ev is not None: ev[3 + i].record()
         state["win"] = win
 
@@ -370,7 +449,7 @@ def run_ours(args):
         kv["share_of_step"] = (kv["ms"] * kv["launches_per_step"] if name != "grid_build" else kv["ms"]) / step_sum
     dom = "knn_corr" if t_corr * iters >= t_cloud else "cloud_build"
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["gbs"], "peak": peak, "peak_source": peak_src,
-                "unit": "GB/s", "frac": kern[dom]["gbs"] / peak, "traffic": NCU_TRAFFIC.get((w["name"], args.dtype, dom)),
+                "unit": "GB/s", "frac": kern[dom]["gbs"] / peak, "traffic": ncu_traffic(w["name"], args.dtype, dom, world),
                 "alg_bytes_per_launch": kern[dom]["alg_bytes"], "ms_per_launch": kern[dom]["ms"],
                 "step_frac": (corr_bytes * iters + cloud_bytes) / (ms_step * 1e-3) / 1e9 / peak}
 
@@ -385,6 +464,15 @@ def run_ours(args):
     line["hot_path_frames_per_s"] = {"value": w["T"] / (n_win * ms_step * 1e-3), "frames": w["T"], "windows": n_win,
                                      "what": "T / (windows x step): hot path only, not MVTracker.forward end to end"}
 
+    # ---- the timed step's output, sampled against the oracle (every N) ----------------------------------------------------------
+    if not args.no_verify and not weak:
+        line.update(verify_output(state["win"], state["out"], targets_it[iters - 1], coords_it[iters - 1], world, rank,
+                                  args.dtype == "bf16"))
+
+    # ---- two more track distributions on the same window (cold search each), N = 1 ---------------------------------------------
+    if world == 1 and not args.no_distributions and args.search == "raster":
+        kern.update(time_distributions(args, w, ops, synth, WindowClouds, state["win"], fm, dp, K, E, targets_it[0], dev, peak, esz))
+
     # ---- adjacent kernels, timed outside the step: not part of `value` -----------------------------
     if world == 1 and not args.no_adjacent and args.search == "raster":
         line["adjacent_kernels"] = time_adjacent(ops, state["win"], targets_it[0], coords_it[0], w, esz, peak, dev)
@@ -394,11 +482,21 @@ def run_ours(args):
         e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if pw > 1 else 0, K_all, E_all, weak)
         line["e2e"] = e2e
     state["win"] = None
+    state["out"] = None
     if sampler:
         sampler.stop()
+    if world == 1 and not args.no_model:
+        # BASELINE.json metric (ii): MVTracker.forward end to end, reference seam vs drop-in, on this GPU
+        del fm, dp, sc, outs, coords_it, targets_it, base_coords, base_targets
+        torch.cuda.empty_cache()
+        try:
+            line["e2e_frames_per_s"] = model_frames_per_s([n for n in args.model_workloads.split(",") if n], dev, iters)
+        except Exception as e:      # the legs use the reference's model code; a failure there must not void the bench line
+            line["e2e_frames_per_s"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0:
         if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_sample(w, iters, args.cpu_budget, args.zero_frac)
+            from oracle import ref_import
+            line["cpu_baseline"] = (ref_sample if ref_import.available() else cpu_sample)(w, iters, args.cpu_budget, args.zero_frac)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -450,6 +548,135 @@ def time_adjacent(ops, win, targets, coords, w, esz, peak, dev, reps=5):
     b = 2 * gfm.numel() * 4                        # read grad_fvec, write grad_fmaps
     out["cloud_build_backward"] = {"ms": ms, "alg_bytes": b, "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak,
                                    "what": "level 0 un-pool + transpose (point-major rows -> channel-major planes)"}
+    return out
+
+
+def verify_output(win, out, targets, coords, world, rank, bf16, n_tracks=64, frames=(0, S_WINDOW - 1)):
+    """Samples the LAST timed step's output: n_tracks tracks x `frames` x every level against oracle.corr_sample (brute
+    force, canonical (d2, index) order) on the clouds the step built.  Offsets must be bit-equal (same neighbour sets in the
+    same order); correlations within 1e-4 (fp32) / 2e-2 (bf16) of the level's largest |corr|.  N > 1: every rank checks the
+    replicated result block; the feature rows of the sampled frames are all-gathered for the check only."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle
+    S, N, _ = out.shape
+    sel = torch.linspace(0, N - 1, min(n_tracks, N), device=out.device).long()
+    worst, bad_sets, checked = 0.0, 0, 0
+    sharded = hasattr(win, "full") and getattr(win, "full", None) is not None
+    n_levels = len(win.full) if sharded else len(win.clouds)
+    for l in range(n_levels):
+        for f in frames:
+            if sharded:
+                xyz = win.full[l].xyz4[f, :, :3].contiguous()
+                mine = win.clouds[l].fvec[f].contiguous()
+                parts = [torch.empty_like(mine) for _ in range(world)]
+                dist.all_gather(parts, mine)
+                fvec = torch.cat(parts, 0)
+            else:
+                xyz, fvec = win.clouds[l].xyz[f], win.clouds[l].fvec[f]
+            ref = oracle.corr_sample(K_NN, xyz[None].cpu().numpy(), fvec[None].float().cpu().numpy(),
+                                     targets[f:f + 1, sel].float().cpu().numpy(), coords[f:f + 1, sel].cpu().numpy())[0]
+            got = out[f, sel, l * K_NN * 4:(l + 1) * K_NN * 4].reshape(-1, K_NN, 4).cpu().numpy()
+            bad_sets += int((got[..., 1:] != ref[..., 1:]).any(-1).any(-1).sum())
+            err = float(np.abs(got[..., 0] - ref[..., 0]).max() / max(1.0, float(np.abs(ref[..., 0]).max())))
+            worst = max(worst, err)
+            checked += got.shape[0]
+    tol = 2e-2 if bf16 else 1e-4
+    ok = bad_sets == 0 and worst <= tol
+    if world > 1:
+        t = torch.tensor([float(bad_sets), worst, float(not ok)], device=out.device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        bad_sets, worst, ok = int(t[0].item()), float(t[1].item()), t[2].item() == 0.0
+    return {"verified": bool(ok), "queries_checked": checked, "neighbour_set_mismatches": bad_sets, "max_corr_err": worst,
+            "tolerance": tol, "against": "oracle.corr_sample (brute force) on the clouds of the last timed step, every rank" if world > 1
+            else "oracle.corr_sample (brute force) on the clouds of the last timed step"}
+
+
+def time_distributions(args, w, ops, synth, WindowClouds, win, fm, dp, K, E, base_targets, dev, peak, esz, reps=5):
+    """The raster search's cost depends on where the tracks are (SURVEY.md 8d asks 0 / 5 / 40 % invalid depth; the reference
+    starts every window with the SAME 3-D point in all S frames, mvtracker.py:510).  Times one fused knn_corr launch (cold
+    search) for two more distributions on the benched window: `static` = frame 0's surface point repeated in all frames
+    (+ N(0, 2 cm)): tracks of moving objects end up in free space in later frames; `zero40` = the same scene with 40 % of the
+    depth pixels invalid.  Not part of `value`."""
+    import torch
+    N = w["N"]
+    q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4
+    alg = LEVELS * S_WINDOW * N * q_bytes
+    out_buf = torch.empty(S_WINDOW, N, LEVELS * K_NN * 4, device=dev, dtype=torch.float32)
+
+    def timed(wn, coords):
+        for _ in range(2):
+            wn.corr(base_targets, coords, out=out_buf)
+        ms = 0.0
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); wn.corr(base_targets, coords, out=out_buf); b.record()
+            torch.cuda.synchronize()
+            ms += a.elapsed_time(b)
+        ms /= reps
+        return {"ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak}
+
+    res = {}
+    c0 = win.clouds[0]
+    valid0 = c0.xyz4[0, :, 3] > 0
+    static_coords, _ = synth.make_tracks(c0.xyz[0], N, S_WINDOW, C=C_FEAT, seed=76, valid=valid0)
+    res["knn_corr_static"] = dict(timed(win, static_coords), what="same 3-D point in all 12 frames (frame 0's surface + N(0, 2 cm)), "
+                                  "the reference's window initialisation (mvtracker.py:510)")
+    # 40 % invalid depth: rebuild the window's clouds in place from the same feature maps
+    g = torch.Generator(device=dev).manual_seed(77)
+    dp40 = torch.where(torch.rand(dp.shape, device=dev, generator=g) < (0.4 - args.zero_frac) / max(1e-6, 1.0 - args.zero_frac),
+                       torch.zeros_like(dp), dp)
+    clouds = ops.cloud_build(fm, dp40, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds)
+    w40 = WindowClouds(clouds, None, K_NN, 1, True, False)
+    coords40, _ = synth.make_tracks(clouds[0].xyz, N, S_WINDOW, C=C_FEAT, seed=73, valid=clouds[0].xyz4[..., 3] > 0)
+    res["knn_corr_zero40"] = dict(timed(w40, coords40), what="tracks follow the surface, 40 % of the depth pixels invalid (0)")
+    ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds)     # restore
+    return res
+
+
+def model_frames_per_s(names, dev, iters):
+    """BASELINE.json metric (ii): end-to-end tracked frames/s = T / wall time of the reference's own MVTracker.forward
+    (evaluator_3dpt.py:514-521), random-init weights of configs/model/mvtracker.yaml, host inputs copied to the device
+    inside the timed region -- once with the reference's stock seam (its torch kNN / gather / einsum path ON THIS B200: the
+    GPU bar BASELINE.md names) and once with mvtracker_b200.dropin.install().  Needs oracle/_ref (oracle/make_ref.py)."""
+    import torch
+    from mvtracker_b200 import synth
+    from oracle import model_harness as mh
+    from oracle import ref_import
+    if not ref_import.available():
+        return {"unavailable": "reference model not staged: run python oracle/make_ref.py where /root/reference exists"}
+    out = {}
+    model = mh.build_model(seed=72, device=dev, use_flash_attention=True)
+    for name in names:
+        wl = synth.WORKLOADS[name]
+        seq_host = mh.make_sequence(wl["V"], wl["T"], wl["H"], wl["W"], wl["N"], seed=72, device="cpu", staggered=False)
+        pinned = {k: getattr(seq_host, k).pin_memory() for k in ("rgbs", "depths", "intrs", "extrs", "query_points")}
+        res = {"frames": wl["T"], "views": wl["V"], "tracks": wl["N"], "resolution": [wl["H"], wl["W"]], "iters": iters}
+        # _knn_torch materialises [S, N, P0] fp32 per level-0 call; skip the stock arm where that cannot fit
+        need = 4 * 12 * wl["N"] * wl["V"] * (wl["H"] // STRIDE) * (wl["W"] // STRIDE) * 2.5
+        arms = ["dropin"] + (["stock"] if need < 0.6 * torch.cuda.mem_get_info(dev)[0] else [])
+        outs = {}
+        for seam in arms:
+            best = None
+            for rep in range(2):                                    # first repetition = warm-up (cuDNN autotune, allocator)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                seq = type(seq_host)(**{**vars(seq_host), **{k: v.to(dev, non_blocking=True) for k, v in pinned.items()}})
+                o, _ = mh.forward(model, seq, iters=iters, seam=seam)
+                traj = o["traj_e"].cpu()
+                dt = time.perf_counter() - t0
+                best = dt if best is None or rep > 0 else best
+            outs[seam] = traj
+            res[seam] = {"frames_per_s": wl["T"] / best, "seconds": best}
+            del seq, o
+            torch.cuda.empty_cache()
+        if "stock" in res:
+            res["speedup"] = res["dropin"]["frames_per_s"] / res["stock"]["frames_per_s"]
+            res["max_traj_diff"] = float((outs["dropin"] - outs["stock"]).abs().max())
+        else:
+            res["stock"] = {"unavailable": "_knn_torch's [S, N, P] distance tensor does not fit this GPU at this config"}
+        out[name] = res
     return out
 
 

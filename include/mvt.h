@@ -56,7 +56,9 @@ unsigned long long mvt_launch_count(void);
 /* Inverse camera matrices, fp64 on device, rounded to fp32 (model_utils.py:454-457).
  * intrs [n,3,3], extrs [n,3,4] (world->camera), device fp32, n = V*S.
  * cam   [n,MVT_CAM_STRIDE] device fp32:  [0..8] Kinv | [9..20] Einv rows 0..2 (3x4) | [24..32] R | [33..35] t |
- *       [36..40] fx, skew, cx, fy, cy | [41] 1 if K is upper triangular with K22 == 1 (raster search usable). */
+ *       [36..40] fx, skew, cx, fy, cy | [41] 1 if K is upper triangular with K22 == 1 (raster search usable) |
+ *       [42] upper bound of the largest singular value of extrs[:, :3] (1 for a rigid transform; similarity-scaled
+ *       extrinsics as datasets/utils.py:403-415 produces them are searched exactly). */
 int mvt_camera_prep(const float *intrs, const float *extrs, int n, float *cam, void *stream);
 
 /* One pyramid level's outputs of the cloud build.  Any pointer may be NULL (skip that output). */
@@ -68,6 +70,10 @@ typedef struct mvt_level_out {
     unsigned char *valid;   /* [S, P_l]   depth > 0 (model_utils.py:478-480) */
     float *spacing;         /* [S, 2]     sum and count of the pixel footprint depth*stride_l/fx over valid points
                                           (kNN cell-size hint; accumulated, zeroed by the call) */
+    int *neg_depth;         /* [S]        set to 1 when frame s of this level holds a point with depth < 0 (zeroed by the
+                                          call).  Such points lie BEHIND their camera on the pixel's line; the reference's
+                                          kNN (mvtracker.py:816, filter_invalid=False) still returns them, so a raster
+                                          search that is handed this array scans those frames' rasters exhaustively */
 } mvt_level_out;
 
 /* Fused unprojection + view fusion + feature pyramid, all requested levels in ONE pass over fmaps.
@@ -115,6 +121,8 @@ typedef struct mvt_search {
                                 every MVT_TILE x MVT_TILE pixel tile (mvt_tile_depth_build); lets a search whose ball projects onto
                                 a large pixel box skip the tiles whose depth range the ball cannot reach.  NULL: no culling.
                                 Never changes a result. */
+    const int *neg_depth;    /* raster mode, optional: [B] flags of mvt_level_out.neg_depth.  NULL: the caller promises that
+                                no searchable point has depth < 0 (such points would not be found) */
 } mvt_search;
 
 #define MVT_TILE 8

@@ -21,7 +21,7 @@ SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build"
 
 class LevelOut(C.Structure):
     _fields_ = [("xyz", C.c_void_p), ("xyz4", C.c_void_p), ("fvec", C.c_void_p), ("valid", C.c_void_p),
-                ("spacing", C.c_void_p)]
+                ("spacing", C.c_void_p), ("neg_depth", C.c_void_p)]
 
 
 class GridJob(C.Structure):
@@ -32,7 +32,7 @@ class GridJob(C.Structure):
 class Search(C.Structure):
     _fields_ = [("grid", C.c_void_p), ("xyz", C.c_void_p), ("xyz4", C.c_void_p), ("cam", C.c_void_p),
                 ("cam_view_stride", C.c_int), ("N", C.c_int), ("V", C.c_int), ("H", C.c_int), ("W", C.c_int),
-                ("stride", C.c_float), ("skip_invalid", C.c_int), ("tile_z", C.c_void_p)]
+                ("stride", C.c_float), ("skip_invalid", C.c_int), ("tile_z", C.c_void_p), ("neg_depth", C.c_void_p)]
 
 
 class CorrLevel(C.Structure):

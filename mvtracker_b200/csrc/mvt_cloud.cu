@@ -49,7 +49,18 @@ __global__ void camera_prep_kernel(const float *__restrict__ intrs, const float 
     bool ok = intrs[i * 9 + 3] == 0.f && intrs[i * 9 + 6] == 0.f && intrs[i * 9 + 7] == 0.f && intrs[i * 9 + 8] == 1.f &&
               intrs[i * 9 + 0] > 0.f && intrs[i * 9 + 4] > 0.f;
     o[41] = ok ? 1.f : 0.f;
-    for (int j = 42; j < kCamStride; ++j) o[j] = 0.f;
+    // [42]: an upper bound of the largest singular value of the 3x3 block of extrs (1 for a rigid transform; the
+    // reference also feeds similarity-scaled blocks, datasets/utils.py:403-415): the raster search projects a WORLD ball
+    // of radius r as a VIEW-space ball of radius [42] * r.  sqrt of the Gershgorin bound of A^T A, in fp64, rounded up.
+    double smax2 = 0.0;
+    for (int r = 0; r < 3; ++r) {
+        double row = 0.0;
+        for (int c = 0; c < 3; ++c) row += fabs(A[0 * 3 + r] * A[0 * 3 + c] + A[1 * 3 + r] * A[1 * 3 + c] + A[2 * 3 + r] * A[2 * 3 + c]);
+        smax2 = fmax(smax2, row);
+    }
+    const double smax = sqrt(smax2) * (1.0 + 1e-6);
+    o[42] = (smax == smax && smax < 3.0e38) ? __double2float_ru(smax) : 3.0e38f;
+    for (int j = 43; j < kCamStride; ++j) o[j] = 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -80,6 +91,7 @@ struct CloudParams {
     void *fvec[4];
     unsigned char *valid[4];
     float *spacing[4];
+    int *neg[4];
     PeersDev rec[4];       // replicated record buffers [S, V_total*H_l*W_l] of every rank (n == 0: not shared)
     int view_off, V_total;
 };
@@ -166,6 +178,7 @@ __device__ __forceinline__ void emit_point(const CloudParams &p, const float *cm
         store_all(p.rec[lvl], ((size_t)s * p.V_total + (size_t)(p.view_off + v)) * Hl * Wl + (size_t)gy * Wl + gx,
                   make_float4(X, Y, Z, depth));
     bool ok = depth > 0.f;
+    if (depth < 0.f && p.neg[lvl]) p.neg[lvl][s] = 1;      // (benign race: every writer stores the same value)
     if (p.valid[lvl]) p.valid[lvl][pt] = ok ? 1 : 0;
     if (ok && depth < 3.0e38f) {
         sp_sum += depth * st * fabsf(cm[0]);
@@ -371,6 +384,7 @@ static int cloud_build_impl(const void *fmaps, int feat_dtype, const float *dept
         p.fvec[l] = on ? levels[l].fvec : nullptr;
         p.valid[l] = on ? levels[l].valid : nullptr;
         p.spacing[l] = on ? levels[l].spacing : nullptr;
+        p.neg[l] = on ? levels[l].neg_depth : nullptr;
         if (on) {
             MVT_CHECK_ARG((H >> l) > 0 && (W >> l) > 0, "mvt_cloud_build: level %d is empty for %dx%d", l, H, W);
             any_f |= p.fvec[l] != nullptr;
@@ -391,6 +405,11 @@ static int cloud_build_impl(const void *fmaps, int feat_dtype, const float *dept
         }
     }
     cudaStream_t st = (cudaStream_t)stream;
+    for (int l = 0; l < 4; ++l)
+        if (p.neg[l] && cudaMemsetAsync(p.neg[l], 0, sizeof(int) * (size_t)S, st) != cudaSuccess) {
+            mvt::set_error("mvt_cloud_build: cudaMemsetAsync(neg_depth[%d]) failed", l);
+            return MVT_E_CUDA;
+        }
     if (any_sp) {
         int n = S * 2;
         zero_spacing_kernel<<<(n + 127) / 128, 128, 0, st>>>(p.spacing[0], p.spacing[1], p.spacing[2], p.spacing[3], n);

@@ -204,9 +204,15 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
     u64 cap = kEmptyKey64;
     if (p.idx_hint && (RASTER_ONLY || L.sd.raster)) {
         unsigned bits = 0xffffffffu;
+        // plain (coherent) load: idx_hint may alias idx_out, which this launch writes -- each query reads its own k
+        // entries before it writes them, but ld.global.nc promises that NOBODY writes the location during the kernel
+        int hi = -1 - gl;                       // distinct dummies for the lanes beyond k
+        if (gl < k) hi = p.idx_hint[(((long long)lvl * p.B + b) * p.M + m) * k + gl];
+        // the cap is the largest distance to k DISTINCT points; a repeated index would make it too small: no cap then
+        const unsigned same = __match_any_sync(FULL, GW == 32 ? hi : (hi ^ ((lane & 16) << 26)));
+        const bool dup = gl < k && hi >= 0 && (same & (same - 1u)) != 0u;
         if (gl < k) {
-            const int hi = __ldg(p.idx_hint + (((long long)lvl * p.B + b) * p.M + m) * k + gl);
-            if (hi >= 0 && hi < L.sd.N) {
+            if (hi >= 0 && hi < L.sd.N && !dup) {
                 const float4 hp = __ldg(L.sd.rv.xyz4 + (size_t)b * L.sd.N + hi);
                 const float hd = dist2(hp.x, hp.y, hp.z, qx, qy, qz);
                 const bool usable = L.sd.rv.skip_invalid ? (hp.w > 0.f) : !(hp.w < 0.f);
@@ -494,6 +500,7 @@ int make_search(const mvt_search *u, int B, int need_xyz, SearchDev &sd, const c
         MVT_CHECK_ARG(((uintptr_t)u->tile_z & 7) == 0, "%s: tile_z must be 8-byte aligned", who);
         sd.rv.ztab = reinterpret_cast<const float2 *>(u->tile_z);
         sd.rv.TW = (u->W + kTile - 1) / kTile; sd.rv.TH = (u->H + kTile - 1) / kTile;
+        sd.rv.neg = u->neg_depth;
     }
     return MVT_OK;
 }

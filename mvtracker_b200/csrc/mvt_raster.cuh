@@ -30,6 +30,7 @@ struct RasterView {
     int skip_invalid;     // 1: points with depth <= 0 are not searchable
     const float2 *ztab;   // [S, V, TH, TW] {min, max} view-space depth per 8x8 tile, or null (tile_depth_kernel)
     int TW, TH;
+    const int *neg;       // [S] frame holds points with depth < 0 (behind the camera on their pixel's line), or null
 };
 #ifndef MVT_TOPK_BUF
 #define MVT_TOPK_BUF 0
@@ -76,7 +77,7 @@ template <int I> struct WinWord { static constexpr unsigned value = win_tab_word
 #if MVT_CAM_SMEM
 // cam[i][lane]: the lane's (= its view's) projection constants, read back once per pass for the ball's pixel box --
 // ten registers per thread that need not stay live across the scans
-struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; float cam[10][32]; };
+struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; float cam[11][32]; };
 #else
 struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; };
 #endif
@@ -197,11 +198,12 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
     u64 cap = tk.th | 0xffffffffull;          // tk holds k real points: th is the k-th key, finite
     if (tk.cap < cap) cap = tk.cap;
     tk.init(cap);
-    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, zpad = 0.f, nz = 1.f;
+    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, zpad = 0.f, nz = 1.f, smax = 1.f;
     bool kok = false;
     const bool mine = lane < V;
     if (mine) {
         const float *cm = rv.cam + ((size_t)lane * rv.S + s) * kCamStride;
+        smax = cm[42];
         X = fmaf(cm[24], qx, fmaf(cm[25], qy, fmaf(cm[26], qz, cm[33])));
         Y = fmaf(cm[27], qx, fmaf(cm[28], qy, fmaf(cm[29], qz, cm[34])));
         Z = fmaf(cm[30], qx, fmaf(cm[31], qy, fmaf(cm[32], qz, cm[35])));
@@ -216,7 +218,7 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
     auto box = [&]() {
         const float r = sqrtf(key_d2(tk.th));
         Rect R = {0, 0, 0, 0};
-        if (mine) R = kok ? ball_box(front, X, Y, Z, iz, fmaf(r, 1.0001f, fmaf(4e-6f, r, zpad)), fx, sk, cx0, fy, cy0, inv_st, W, H)
+        if (mine) R = kok ? ball_box(front, X, Y, Z, iz, fmaf(r, 1.0001f, fmaf(4e-6f, r, zpad)) * smax, fx, sk, cx0, fy, cy0, inv_st, W, H)
                           : Rect{0, 0, W, H};
         return R;
     };
@@ -310,17 +312,22 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
     const bool mine = live && gl < V;
     const float inv_st = __frcp_rn(rv.stride);
     const bool skip_invalid = rv.skip_invalid != 0;
+    // points with depth < 0 are not on the forward ray of their pixel: a frame that holds some (and must return them) has
+    // no usable pixel box -- every view is scanned whole, once, like a view with odd intrinsics (uniform in the warp)
+    const bool negf = !skip_invalid && rv.neg != nullptr && __ldg(rv.neg + s) != 0;
+    const float wmin = negf ? -INFINITY : 0.f;          // searchable: !(depth < wmin)
 
     // per-lane (= per-view) camera and projection of q
-    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, tnorm = 0.f;
+    float X = 0.f, Y = 0.f, Z = -1.f, iz = 0.f, fx = 1.f, sk = 0.f, cx0 = 0.f, fy = 1.f, cy0 = 0.f, tnorm = 0.f, smax = 1.f;
     bool kok = false;
     if (mine) {
         const float *cm = rv.cam + ((size_t)gl * rv.S + s) * kCamStride;
+        smax = cm[42];      // view-space radius of a unit world ball (1 for a rigid view transform)
         X = fmaf(cm[24], qx, fmaf(cm[25], qy, fmaf(cm[26], qz, cm[33])));
         Y = fmaf(cm[27], qx, fmaf(cm[28], qy, fmaf(cm[29], qz, cm[34])));
         Z = fmaf(cm[30], qx, fmaf(cm[31], qy, fmaf(cm[32], qz, cm[35])));
         fx = cm[36]; sk = cm[37]; cx0 = cm[38]; fy = cm[39]; cy0 = cm[40];
-        kok = cm[41] != 0.f;
+        kok = cm[41] != 0.f && !negf;
         tnorm = fabsf(cm[33]) + fabsf(cm[34]) + fabsf(cm[35]);
     }
     const bool front = mine && kok && Z > 1e-12f;
@@ -339,7 +346,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         float (*cs)[32] = reinterpret_cast<float (*)[32]>(const_cast<unsigned char *>(win_tab) + 32 + 32 * sizeof(u64));
         const int ln = threadIdx.x & 31;
         cs[0][ln] = X; cs[1][ln] = Y; cs[2][ln] = Z; cs[3][ln] = iz; cs[4][ln] = fx; cs[5][ln] = sk; cs[6][ln] = cx0;
-        cs[7][ln] = fy; cs[8][ln] = cy0; cs[9][ln] = tnorm;
+        cs[7][ln] = fy; cs[8][ln] = cy0; cs[9][ln] = tnorm; cs[10][ln] = smax;
     }
 #endif
     const Rect whole = {0, 0, W, H};
@@ -382,7 +389,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 u64 key[kCB];
 #pragma unroll
                 for (int c = 0; c < kCB; ++c) {
-                    const bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < 0.f));
+                    const bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < wmin));
                     key[c] = valid ? pack_key(dist2(p[c].x, p[c].y, p[c].z, qx, qy, qz), id[c]) : kEmptyKey64;
                 }
                 const int nc = min(kCB, (total - t0 + GW - 1) / GW);
@@ -396,7 +403,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
 #pragma unroll
                 for (int c = 0; c < kCB; ++c) {
                     if (t0 + c * GW >= total) break;
-                    bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < 0.f));
+                    bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < wmin));
                     float d2 = dist2(p[c].x, p[c].y, p[c].z, qx, qy, qz);
                     st_ins += topk_offer<GW, BUF>(g, tk, valid ? pack_key(d2, id[c]) : kEmptyKey64, k);
                 }
@@ -424,11 +431,11 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 float (*cs)[32] = reinterpret_cast<float (*)[32]>(const_cast<unsigned char *>(win_tab) + 32 + 32 * sizeof(u64));
                 const int ln = threadIdx.x & 31;
                 const float X_ = cs[0][ln], Y_ = cs[1][ln], Z_ = cs[2][ln];
-                float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X_) + fabsf(Y_) + fabsf(Z_) + cs[9][ln] + r));
+                float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X_) + fabsf(Y_) + fabsf(Z_) + cs[9][ln] + r)) * cs[10][ln];
                 if (mine && kok) R = ball_box(front, X_, Y_, Z_, cs[3][ln], reff, cs[4][ln], cs[5][ln], cs[6][ln], cs[7][ln], cs[8][ln], inv_st, W, H);
             }
 #else
-            float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r));
+            float reff = fmaf(r, 1.0001f, 4e-6f * (fabsf(X) + fabsf(Y) + fabsf(Z) + tnorm + r)) * smax;
             if (mine && kok) R = ball_box(front, X, Y, Z, iz, reff, fx, sk, cx0, fy, cy0, inv_st, W, H);
 #endif
             covered = !mine || rect_empty(R) || rect_inside(R, A);
@@ -463,7 +470,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         const bool reaches_all = g.all(!mine || rect_empty(R) || rect_inside(R, B));
         const bool last = have_k && reaches_all;
         // a large box of new pixels in some view: give the query to tile_search (depth-culled tiles), see raster_search
-        if (TILES && GW == 32 && rv.ztab != nullptr && budget == 0u) {
+        if (TILES && GW == 32 && rv.ztab != nullptr && budget == 0u && !negf) {
             const int newpx = rect_empty(B) ? 0 : (B.x1 - B.x0) * (B.y1 - B.y0) - (rect_empty(A) ? 0 : (A.x1 - A.x0) * (A.y1 - A.y0));
             if (g.any(have_k && mine && !done && newpx >= kTileMinPixels)) return false;
         }
@@ -517,7 +524,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 if (col < 0) { --row; col += wj; } else if (col >= wj) { ++row; col -= wj; }
                 const int idx = (v0 + (j >> 2)) * HW + (yj + (int)row) * W + xj + col;
                 float4 p = valid ? __ldg(frame + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-                valid = valid && (skip_invalid ? (p.w > 0.f) : !(p.w < 0.f));
+                valid = valid && (skip_invalid ? (p.w > 0.f) : !(p.w < wmin));
                 float d2 = dist2(p.x, p.y, p.z, qx, qy, qz);
                 st_ins += topk_offer<GW, BUF>(g, tk, valid ? pack_key(d2, idx) : kEmptyKey64, k);
             }

@@ -39,8 +39,24 @@ settings = SimpleNamespace(
 )
 
 
+def _version(t: torch.Tensor):
+    """In-place edit counter, or None for inference tensors (torch.inference_mode(): 'Inference tensors do not track
+    version counter')."""
+    try:
+        return t._version
+    except RuntimeError:
+        return None
+
+
 def _key(t: torch.Tensor):
-    return (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()), t.dtype)
+    return (t.data_ptr(), _version(t), tuple(t.shape), tuple(t.stride()), t.dtype)
+
+
+def _untouched(t: torch.Tensor) -> bool:
+    """One of OUR output tensors has not been written since it was made.  Inference tensors have no counter; they are
+    immutable outside inference mode and the model never edits the clouds (mvtracker.py:296-376), so they pass."""
+    v = _version(t)
+    return v is None or v == 0
 
 
 class _Pyramid:
@@ -52,6 +68,8 @@ class _Pyramid:
         self.clouds = clouds            # level -> ops.Cloud
         self.blocks = weakref.WeakValueDictionary()   # level -> PointcloudCorrBlock registered on these clouds
         self.corr_cache = None          # (key, {level: tensor})
+        self.served = set()             # levels already handed out (see init_pointcloud_from_rgbd)
+        self.versioned = all(k[1] is not None for k in key[:4])
 
 
 _pyramid_cache = []     # most recent first, at most 2 entries (feature-init call + forward_iteration call per window)
@@ -78,12 +96,20 @@ def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, de
             raise NotImplementedError
     if level >= MAX_LEVELS:
         raise MvtError(f"pyramid level {level} not supported (0..{MAX_LEVELS - 1})")
+    out_dtype = fmaps.dtype
+    if fmaps.dtype not in (torch.float32, torch.bfloat16):
+        # fp16 / fp64 feature maps (fp16: autocast on pre-Ampere devices, demo.py:833-837): the kernels take fp32 or bf16
+        # features; such maps go through the fp32 kernels and the cloud's features are returned in the caller's dtype
+        fmaps = fmaps.float()
 
     key = (_key(fmaps), _key(depths), _key(intrs), _key(extrs), float(stride), depth_interp_mode)
     pyr = None
     if settings.pyramid_cache:
         for e in _pyramid_cache:
-            if e.key == key and level in e.clouds:
+            # inference tensors carry no version counter, so an in-place edit of the inputs cannot be seen: an entry built
+            # from them serves every level ONCE (the four per-level calls of one window, mvtracker.py:297-306); a second
+            # request for a level means a new window in the same buffers and is rebuilt
+            if e.key == key and level in e.clouds and (e.versioned or level not in e.served):
                 pyr = e
                 break
     if pyr is None:
@@ -107,14 +133,16 @@ def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, de
                                       torch.cat([c.valid for c in cs]), torch.cat([c.spacing for c in cs]))
         pyr = _Pyramid(key, (fmaps, depths, intrs, extrs), clouds)
         if settings.pyramid_cache:
-            _pyramid_cache.insert(0, pyr)
-            del _pyramid_cache[2:]
+            _pyramid_cache[:] = [pyr] + [e for e in _pyramid_cache if e.key != key][:1]
+    pyr.served.add(level)
     cloud = pyr.clouds[level]
     xyz, fvec = cloud.xyz, cloud.fvec
     if torch.is_grad_enabled() and fmaps.requires_grad:
         # training (row f2): the cloud's features are a function of fmaps (chained avg_pool2d + permute); depths, cameras
         # and therefore xyz carry no gradient in the reference either (they come from the data loader)
         fvec = _FeatureCloudFn.apply(fmaps, fvec, level)
+    if fvec.dtype != out_dtype:
+        fvec = fvec.to(out_dtype)
     xyz._mvt = (weakref.ref(pyr), level)   # lets PointcloudCorrBlock find the footprint hint and its sibling levels
     if return_validity_mask:
         return xyz, fvec, cloud.valid
@@ -184,7 +212,7 @@ def _find_raster(xyz_ref: torch.Tensor):
         for cloud in pyr.clouds.values():
             S, P = cloud.xyz.shape[0], cloud.xyz.shape[1]
             base = cloud.xyz.data_ptr()
-            if cloud.xyz4 is None or P != N or cloud.xyz._version != 0 or cloud.xyz4._version != 0:
+            if cloud.xyz4 is None or P != N or not _untouched(cloud.xyz) or not _untouched(cloud.xyz4):
                 continue
             off = ptr - base
             if off < 0 or off % (P * 12) != 0:
@@ -232,15 +260,19 @@ class PointcloudCorrBlock:
         self.rerun_fmap_coloring_fn = rerun_fmap_coloring_fn
 
         self._xyz_c = xyz if (xyz.dtype == torch.float32 and xyz.is_contiguous()) else xyz.float().contiguous()
-        self._fvec_c = fvec.contiguous()
         self._grid = None
         self._pyr, self._level, self._spacing, self._cloud = None, None, None, None
         tag = getattr(xyz, "_mvt", None)
-        if tag is not None and tag[0]() is not None and xyz._version == 0:
+        if tag is not None and tag[0]() is not None and _untouched(xyz):
             self._pyr, self._level = tag[0](), tag[1]
             self._cloud = self._pyr.clouds[self._level]
             self._spacing = self._cloud.spacing
             self._pyr.blocks[self._level] = self
+        if self._cloud is not None and self._cloud.fvec is not None and self._cloud.fvec.shape == fvec.shape and _untouched(fvec) \
+                and (fvec.dtype == self._cloud.fvec.dtype or fvec.dtype not in (torch.float32, torch.bfloat16)):
+            self._fvec_c = self._cloud.fvec          # the rows the kernels built (fp32 for fp16 / fp64 callers)
+        else:
+            self._fvec_c = fvec.contiguous() if fvec.dtype in (torch.float32, torch.bfloat16) else fvec.float().contiguous()
         self._raster = (settings.search == "raster" and self._cloud is not None and self._cloud.xyz4 is not None
                         and not (filter_invalid and settings.filter_invalid_mode == "reference"))
         if not self._raster:
@@ -292,18 +324,23 @@ class PointcloudCorrBlock:
         if save_debug_logs or save_rerun_logs:
             raise MvtError("debug / rerun logging lives in the reference implementation only")
         D = self.groups + 3 * bool(self.corr_add_neighbor_offset) + 3 * bool(self.corr_add_neighbor_xyz)
-        if targets.dtype != self.fvec.dtype:
-            targets = targets.to(self.fvec.dtype)
+        out_dtype = torch.promote_types(targets.dtype, self.fvec.dtype)
+        if self.corr_add_neighbor_offset or self.corr_add_neighbor_xyz:     # torch.cat promotion at mvtracker.py:842-846
+            out_dtype = torch.promote_types(out_dtype, torch.promote_types(self.xyz.dtype, coords_world_xyz.dtype))
+        ckey = (_key(targets), _key(coords_world_xyz))      # of the caller's tensors: the siblings are called with the same ones
+        keep = (targets, coords_world_xyz)
+        if targets.dtype != self._fvec_c.dtype:
+            targets = targets.to(self._fvec_c.dtype)
         if torch.is_grad_enabled() and (targets.requires_grad or self.fvec.requires_grad):
             # training (row f2): one level per call, neighbour lists kept for mvt_knn_corr_backward
             return _CorrSampleFn.apply(targets, self.fvec, self, coords_world_xyz)
 
         sib = self._siblings()
-        ckey = (_key(targets), _key(coords_world_xyz))
         if len(sib) > 1:
             cache = self._pyr.corr_cache
             if cache is not None and cache[0] == ckey and id(self) in cache[1]:
-                return cache[1].pop(id(self))
+                hit = cache[1].pop(id(self))
+                return hit if hit.dtype == out_dtype else hit.to(out_dtype)
         levels = [(b._search(), b._fvec_c, b.k) for b in sib]
         out = ops.knn_corr(levels, targets, coords_world_xyz, groups=self.groups, add_offset=self.corr_add_neighbor_offset,
                            add_xyz=self.corr_add_neighbor_xyz)
@@ -315,8 +352,8 @@ class PointcloudCorrBlock:
         mine = res.pop(id(self))
         if len(sib) > 1:
             # (targets, coords) are referenced by the key tensors' storages for the lifetime of this entry
-            self._pyr.corr_cache = (ckey, res, (targets, coords_world_xyz))
-        return mine
+            self._pyr.corr_cache = (ckey, res, keep, out_dtype)
+        return mine if mine.dtype == out_dtype else mine.to(out_dtype)
 
 
 def install(ref_module=None):

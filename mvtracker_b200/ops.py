@@ -59,6 +59,7 @@ class Cloud:
     stride: float = 0.0                  # input pixels per raster pixel at this level
     tile_z: Optional[torch.Tensor] = None  # [S, V, ceil(H/8), ceil(W/8), 2] per-tile depth range (tile_depth_build)
     tiles_ready: bool = False              # tile_z describes the current xyz4 (a reused buffer starts out stale)
+    neg: Optional[torch.Tensor] = None     # [S] int32: frame holds points with depth < 0 (mvt_level_out.neg_depth)
 
 
 def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
@@ -78,7 +79,7 @@ def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
         shape = (S, c.V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
         if c.tile_z is None or tuple(c.tile_z.shape) != shape:
             c.tile_z = torch.empty(shape, device=c.xyz4.device, dtype=torch.float32)
-        arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), S, c.xyz4.shape[1], c.V, c.H, c.W, float(c.stride), 0, None)
+        arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), S, c.xyz4.shape[1], c.V, c.H, c.W, float(c.stride), 0, None, None)
         outs[i] = c.tile_z.data_ptr()
     check(lib().mvt_tile_depth_build(arr, len(todo), S, outs, _stream()), "mvt_tile_depth_build")
     for c in todo:
@@ -134,6 +135,7 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
             valid = old.valid.view(torch.uint8) if (want_valid and old.valid is not None) else None
             spacing = old.spacing if want_spacing else None
             xyz4 = old.xyz4 if want_xyz4 else None
+            neg = old.neg if (want_xyz4 and old.neg is not None) else (torch.empty(S, device=dev, dtype=torch.int32) if want_xyz4 else None)
             if (want_valid and valid is None) or (want_spacing and spacing is None) or (want_xyz4 and xyz4 is None):
                 raise MvtError(f"reuse: level {l} lacks a requested output buffer")
         else:
@@ -142,11 +144,13 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
             valid = torch.empty(S, P, device=dev, dtype=torch.uint8) if want_valid else None
             spacing = torch.empty(S, 2, device=dev, dtype=torch.float32) if want_spacing else None
             xyz4 = torch.empty(S, P, 4, device=dev, dtype=torch.float32) if want_xyz4 else None
+            neg = torch.empty(S, device=dev, dtype=torch.int32) if want_xyz4 else None
         outs[l] = LevelOut(xyz.data_ptr(), xyz4.data_ptr() if want_xyz4 else None, fvec.data_ptr() if want_fvec else None,
-                           valid.data_ptr() if want_valid else None, spacing.data_ptr() if want_spacing else None)
+                           valid.data_ptr() if want_valid else None, spacing.data_ptr() if want_spacing else None,
+                           neg.data_ptr() if neg is not None else None)
         mask |= 1 << l
         clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
-                            float(stride) * (1 << l), old.tile_z if reuse is not None else None))
+                            float(stride) * (1 << l), old.tile_z if reuse is not None else None, False, neg))
     if shared_records is None:
         check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                     int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
@@ -214,7 +218,7 @@ class Search:
     @classmethod
     def from_grid(cls, grid: Grid, xyz: Optional[torch.Tensor] = None):
         x = grid.xyz if xyz is None else xyz
-        c = _CSearch(grid.ptr, x.data_ptr(), None, None, 0, grid.N, 0, 0, 0, 0.0, 0)
+        c = _CSearch(grid.ptr, x.data_ptr(), None, None, 0, grid.N, 0, 0, 0, 0.0, 0, None, None)
         return cls(c, grid.B, grid.N, (grid, x))
 
     @classmethod
@@ -238,9 +242,12 @@ class Search:
         tz_ptr = None
         if tz is not None:
             tz_ptr = tz.data_ptr() + (0 if frame is None else frame * tz[0].numel() * 4)
+        neg_ptr = None
+        if cloud.neg is not None:
+            neg_ptr = cloud.neg.data_ptr() + (0 if frame is None else frame * 4)
         c = _CSearch(None, None, x4_ptr, cam_ptr, S, P, cloud.V, cloud.H, cloud.W, float(cloud.stride), int(bool(skip_invalid)),
-                     tz_ptr)
-        return cls(c, B, P, (x4, cam, tz))
+                     tz_ptr, neg_ptr)
+        return cls(c, B, P, (x4, cam, tz, cloud.neg))
 
 
 def _as_search(obj, tiles=False) -> Search:

@@ -1,48 +1,75 @@
-"""Import the REAL reference (read-only, /root/reference) in the build container.
+"""Import the REAL reference: from /root/reference in the build container, else from the unmodified files that
+oracle/make_ref.py staged into oracle/_ref/ (git-ignored; travels to the GPU box like the built .so files).
 
-TEST INFRASTRUCTURE ONLY; used by tests/golden/make_golden.py to produce the
-committed golden vectors, and by CPU tests that are skipped when
-/root/reference is absent (it never exists on the GPU box).
+TEST / BASELINE INFRASTRUCTURE ONLY; used by tests/golden/make_golden*.py to produce the committed golden vectors, by the
+CPU tests that rebind the seam on the real module, by tests/test_gpu_model.py (reference forward vs drop-in forward on
+the B200) and by bench.py's reference arm / end-to-end frames-per-second leg.  Never imported by mvtracker_b200/.
 
-Stubs: `easydict` (model_utils.py:10) and `png` (datasets/utils.py:14) are not
-installed; `mvtracker.datasets/__init__.py` pulls matplotlib, so a bare package
-object with only __path__ stands in for it.  Nothing of the reference is copied.
+Stubs: `easydict` (model_utils.py:10) and `png` (datasets/utils.py:14) are not installed; `mvtracker.datasets/__init__.py`
+pulls matplotlib, so a bare package object with only __path__ stands in for it.
 """
 import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("MVT_REFERENCE_ROOT", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+STAGED = os.path.join(HERE, "_ref")
+
+
+def root():
+    """Directory that holds the reference's `mvtracker` package, or None."""
+    env = os.environ.get("MVT_REFERENCE_ROOT")
+    for cand in ([env] if env else []) + ["/root/reference", STAGED]:
+        if cand and os.path.isfile(os.path.join(cand, "mvtracker", "models", "core", "mvtracker", "mvtracker.py")):
+            return cand
+    return None
+
+
+REF_ROOT = root() or "/root/reference"
 
 
 def available():
-    return os.path.isdir(os.path.join(REF_ROOT, "mvtracker"))
+    return root() is not None
+
+
+def kind():
+    """'reference' for /root/reference, 'staged' for oracle/_ref (the same files, copied unmodified by make_ref.py)."""
+    r = root()
+    return None if r is None else ("staged" if os.path.abspath(r) == os.path.abspath(STAGED) else "reference")
 
 
 _cached = None
 
 
 def load():
-    """-> namespace with .mvt (the mvtracker.py module), .init_pointcloud_from_rgbd, .knn, .PointcloudCorrBlock"""
+    """-> namespace with .mvt (the mvtracker.py module), .init_pointcloud_from_rgbd, .knn, .PointcloudCorrBlock, .MVTracker"""
     global _cached
     if _cached is not None:
         return _cached
-    if not available():
-        raise RuntimeError(f"reference not found under {REF_ROOT}")
+    r = root()
+    if r is None:
+        raise RuntimeError("reference not found (neither /root/reference nor oracle/_ref; run `python oracle/make_ref.py` "
+                           "where /root/reference exists)")
     sys.dont_write_bytecode = True
-    if REF_ROOT not in sys.path:
-        sys.path.insert(0, REF_ROOT)
+    if r not in sys.path:
+        sys.path.insert(0, r)
     if "easydict" not in sys.modules:
-        m = types.ModuleType("easydict")
+        try:
+            import easydict  # noqa: F401
+        except Exception:
+            m = types.ModuleType("easydict")
 
-        class EasyDict(dict):
-            __getattr__ = dict.get
-            __setattr__ = dict.__setitem__
+            class EasyDict(dict):
+                __getattr__ = dict.get
+                __setattr__ = dict.__setitem__
 
-        m.EasyDict = EasyDict
-        sys.modules["easydict"] = m
+            m.EasyDict = EasyDict
+            sys.modules["easydict"] = m
     if "png" not in sys.modules:
-        sys.modules["png"] = types.ModuleType("png")
+        try:
+            import png  # noqa: F401
+        except Exception:
+            sys.modules["png"] = types.ModuleType("png")
     import mvtracker  # noqa: the reference package
 
     if "mvtracker.datasets" not in sys.modules:
@@ -59,6 +86,6 @@ def load():
         logging.disable(logging.NOTSET)
     ns = types.SimpleNamespace(mvt=mvt, init_pointcloud_from_rgbd=init_pointcloud_from_rgbd, knn=mvt.knn,
                                knn_torch=mvt._knn_torch, PointcloudCorrBlock=mvt.PointcloudCorrBlock,
-                               MVTracker=mvt.MVTracker)
+                               MVTracker=mvt.MVTracker, root=r, kind=kind())
     _cached = ns
     return ns

@@ -1,5 +1,7 @@
-"""Full-size checks (BASELINE.json's DROID window: 3 views 720x1280, stride 4 -> 180x320, 12 frames, 2048 tracks, 4 levels,
-k = 16) through properties that do not need an oracle pass over the whole problem:
+"""Full-size checks on the windows BASELINE.json names and bench.py times -- DROID (3 views 720x1280, 2048 tracks), the
+Panoptic-shaped window (8 views 1280x1600 -> 1 024 000 fused points per frame, 4096 tracks: the BENCH / SCALE workload) and
+the DexYCB-shaped one (8 views 480x640, 16 384 tracks); stride 4, 12 frames, 4 levels, k = 16 -- through properties that do
+not need an oracle pass over the whole problem:
 
 * the oracle on a SAMPLE of queries against the whole 172 800-point frames (bit exact),
 * two independent search structures -- the raster search and the hashed grid -- agree on every index of every query,
@@ -17,17 +19,23 @@ from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
-V, H, W, S, N, K, L = 3, 720, 1280, 12, 2048, 16, 4
+S, K, L = 12, 16, 4
+V = H = W = N = None        # set per workload by the fixture
 
 
-@pytest.fixture(scope="module")
-def window():
+@pytest.fixture(scope="module", params=["droid", "panoptic", "dexycb"])
+def window(request):
+    global V, H, W, N
+    wl = synth.WORKLOADS[request.param]
+    V, H, W, N = wl["V"], wl["H"], wl["W"], wl["N"]
     sc = synth.make_scene(V, H, W, S=S, C=128, zero_frac=0.05, seed=172, device=DEV)
     clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=range(L), want_valid=True)
     coords, targets = synth.make_tracks(clouds[0].xyz, N, S, seed=173, valid=clouds[0].valid)
     out, idx = ops.knn_corr([(c, c.fvec, K) for c in clouds], targets, coords, return_idx=True)
     torch.cuda.synchronize()
-    return sc, clouds, coords, targets, out, idx
+    yield sc, clouds, coords, targets, out, idx
+    del sc, clouds, coords, targets, out, idx
+    torch.cuda.empty_cache()
 
 
 def test_cloud_against_torch_fp32(window):
@@ -109,3 +117,35 @@ def test_track_permutation_and_target_linearity(window):
     assert torch.equal(a[..., 1:], b[..., 1:]) and torch.equal(a[..., 1:], c12[..., 1:])      # offsets do not depend on features
     lin = (c12[..., 0] - (a[..., 0] + b[..., 0])).abs().max().item()
     assert lin <= 1e-4 * max(1.0, c12[..., 0].abs().max().item()), lin
+
+
+@pytest.mark.parametrize("dist", ["static", "zero40"])
+def test_other_track_distributions_sampled_against_oracle(window, dist):
+    """The search cost -- and the code paths taken -- depend on where the tracks are.  `static`: the reference starts every
+    window with the SAME 3-D point in all S frames (mvtracker.py:510), so tracks of moving objects float in free space in later
+    frames; `zero40`: 40 % of the depth pixels invalid.  Sampled oracle check as above (the timed variants are
+    bench.py's kernels.knn_corr_static / knn_corr_zero40)."""
+    sc, clouds, coords, targets, _, _ = window
+    if dist == "static":
+        cl = clouds
+        crd, _ = synth.make_tracks(cl[0].xyz[0], N, S, seed=176, valid=cl[0].valid[0])
+    else:
+        g = torch.Generator(device=DEV).manual_seed(177)
+        dp = sc.depths[0, :, :, 0]
+        dp40 = torch.where(torch.rand(dp.shape, device=DEV, generator=g) < 0.37, torch.zeros_like(dp), dp)
+        cl = ops.cloud_build(sc.fmaps[0], dp40, sc.intrs[0], sc.extrs[0], levels=range(L), want_valid=True)
+        crd, _ = synth.make_tracks(cl[0].xyz, N, S, seed=173, valid=cl[0].valid)
+    out, idx = ops.knn_corr([(c, c.fvec, K) for c in cl], targets, crd, return_idx=True)
+    rng = np.random.default_rng(8)
+    for li in (0, 3):
+        c = cl[li]
+        for fr in (0, S - 1):
+            pick = np.sort(rng.choice(N, 48, replace=False))
+            q = crd[fr, pick].cpu().numpy()[None]
+            _, oi = oracle.knn(K, c.xyz[fr].cpu().numpy()[None], q)
+            assert (idx[li, fr, pick].cpu().numpy() == oi[0]).all(), (dist, li, fr)
+            ref = oracle.corr_sample(K, c.xyz[fr].cpu().numpy()[None], c.fvec[fr].cpu().numpy()[None],
+                                     targets[fr, pick].cpu().numpy()[None], q)
+            got = out[fr, pick, li * K * 4:(li + 1) * K * 4].reshape(1, len(pick), K, 4).cpu().numpy()
+            assert (got[..., 1:] == ref[..., 1:]).all()
+            assert np.abs(got[..., 0] - ref[..., 0]).max() <= 1e-4 * max(1.0, np.abs(ref[..., 0]).max())

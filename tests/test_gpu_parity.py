@@ -453,3 +453,67 @@ def test_raster_knn_fewer_points_than_k_and_nan_depth():
     check_knn_raster(c[0], q, 16)
     dist, idx = ops.knn(c[1], q, 8)                # level 3 has 2 points only
     assert c[1].xyz.shape[1] == 2 and (idx[..., 2:] == -1).all() and (idx[..., 0] >= 0).all()
+
+
+@pytest.mark.parametrize("scale", [1.3, 1.0 / 1.3, "shear"])
+def test_raster_knn_non_rigid_extrinsics(scale):
+    """the reference feeds similarity-scaled rotation blocks (apply_sim3_to_extrinsics writes R_inv / s,
+    datasets/utils.py:403-415) and tolerates 1e-3 non-orthonormality.  A world ball of radius r is then a view-space
+    ellipsoid inside a ball of radius sigma_max(R) * r: camera_prep stores that bound (cam[42]) and the pixel boxes use it."""
+    sc = synth.make_scene(3, 45 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=70, device=DEV)
+    if scale == "shear":
+        A = torch.tensor([[1.0, 0.2, 0.0], [0.0, 0.9, 0.1], [0.05, 0.0, 1.15]], device=DEV)
+        sc.extrs[..., :3, :3] = sc.extrs[..., :3, :3] @ A
+    else:
+        sc.extrs[..., :3, :3] *= scale
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 3], want_valid=True)
+    cam = clouds[0].cam.cpu().numpy()
+    smax = np.linalg.svd(sc.extrs[0, :, 0, :3, :3].cpu().numpy().astype(np.float64), compute_uv=False).max(-1)
+    assert (cam.reshape(3, 2, -1)[:, 0, 42] >= smax).all() and (cam.reshape(3, 2, -1)[:, 0, 42] <= smax * 1.75).all()
+    coords = _edge_queries(clouds[0], sc)
+    coords2, targets = synth.make_tracks(clouds[0].xyz[0], 200, 2, valid=clouds[0].valid[0], jitter=0.05)
+    for c in clouds:
+        check_knn_raster(c, coords, 16)
+        check_knn_raster(c, coords2, 16)
+        check_knn_raster(c, coords, 3, skip_invalid=True)
+    check_corr(clouds[0].xyz, clouds[0].fvec, targets, coords2, 16, cloud=clouds[0])
+
+
+def test_raster_knn_negative_depths_are_found():
+    """the reference's knn (filter_invalid=False, mvtracker.py:816) considers EVERY unprojected point, also those
+    with depth < 0 (behind their camera, on the backward half of the pixel's line).  cloud_build flags the frames that hold
+    such points (mvt_level_out.neg_depth) and the raster search scans those frames exhaustively: still bit exact."""
+    sc = synth.make_scene(2, 24 * 4, 32 * 4, S=3, C=128, zero_frac=0.1, seed=71, device=DEV)
+    dp = sc.depths[0, :, :, 0].clone()
+    dp[0, 1, 3:9, 5:20] *= -1.0                     # frame 1 of view 0: a patch of negative depths
+    dp[1, 1, 0, 0] = -0.5
+    clouds = ops.cloud_build(sc.fmaps[0], dp, sc.intrs[0], sc.extrs[0], levels=[0, 1], want_valid=True)
+    assert clouds[0].neg.cpu().tolist() == [0, 1, 0]
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 150, 3, valid=clouds[0].valid[0], jitter=0.05)
+    neg_pts = clouds[0].xyz[1][(clouds[0].xyz4[1, :, 3] < 0)]
+    coords[1, :40] = neg_pts[:40] + 0.01            # queries next to the points behind the camera
+    for c in clouds:
+        check_knn_raster(c, coords, 16)
+        check_knn_raster(c, coords, 16, skip_invalid=True)      # "intended" filtering: depth <= 0 is not searchable
+    check_corr(clouds[0].xyz, clouds[0].fvec, targets, coords, 16, cloud=clouds[0])
+    # the next window in the same buffers has none: the flags are reset by the build
+    again = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1], want_valid=True, reuse=clouds)
+    assert again[0].neg.cpu().tolist() == [0, 0, 0]
+
+
+def test_corr_warm_start_with_repeated_hint_indices():
+    """the cap taken from idx_hint is the largest distance to k DISTINCT points; a hint that repeats an index
+    (not something mvt_knn_corr ever writes, but the ABI accepts any int32) must not make the search inexact."""
+    sc = synth.make_scene(3, 48 * 4, 64 * 4, S=2, C=128, zero_frac=0.1, seed=39, device=DEV)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 2], want_valid=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 257, 2, valid=clouds[0].valid[0], jitter=0.03)
+    lv = [(c, c.fvec, 16) for c in clouds]
+    want, widx = ops.knn_corr(lv, targets, coords, return_idx=True)
+    dup = widx.clone()
+    dup[..., 1:] = dup[..., :1]                     # the nearest neighbour sixteen times: its distance is NOT a bound
+    got, gidx = ops.knn_corr(lv, targets, coords, idx_hint=dup, return_idx=True)
+    assert torch.equal(got, want) and torch.equal(gidx, widx)
+    dup = widx.clone()
+    dup[..., 15] = dup[..., 0]                      # one repeat
+    got, gidx = ops.knn_corr(lv, targets, coords, idx_hint=dup, return_idx=True)
+    assert torch.equal(got, want) and torch.equal(gidx, widx)

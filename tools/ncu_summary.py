@@ -1,6 +1,9 @@
-"""Text summary of an .ncu-rep (raw page) for profiles/: python tools/ncu_summary.py REPORT.ncu-rep > profiles/NAME.txt"""
-import csv, subprocess, sys
+"""Text summary of an .ncu-rep (raw page) for profiles/: python tools/ncu_summary.py REPORT.ncu-rep [KEY] > profiles/NAME.txt
+KEY ("workload/dtype/kernel/nN", e.g. panoptic/f32/knn_corr/n1): also record the capture's DRAM traffic per launch under
+that key in profiles/traffic.json -- the table bench.py's roofline.traffic is read from."""
+import csv, json, os, subprocess, sys
 rep = sys.argv[1]
+key = sys.argv[2] if len(sys.argv) > 2 else None
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 h, u = rows[0], rows[1]
@@ -25,6 +28,12 @@ for r in rows[2:]:
         ur, uw = u[h.index('dram__bytes_read.sum')], u[h.index('dram__bytes_write.sum')]
         sc = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         print(f"{'traffic = dram read + write':90s} {rd * sc[ur] + wr * sc[uw]:.0f} byte")
+        if key:
+            tj = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
+            tab = json.load(open(tj)) if os.path.exists(tj) else {}
+            tab[key] = {"bytes": int(rd * sc[ur] + wr * sc[uw]), "capture": rep.split("/")[-1], "kernel": r[h.index("Kernel Name")][:80]}
+            json.dump(tab, open(tj, "w"), indent=1, sort_keys=True)
+            key = None
     except Exception as e:
         print("traffic: n/a", e)
     print("-" * 60)
