@@ -357,7 +357,8 @@ def run_ours(args):
         if ev is not None: ev[0].record()
         if pw == 1:
             clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=(args.search == "grid"),
-                                     reuse=None if state["win"] is None else state["win"].clouds)
+                                     reuse=None if state["win"] is None else state["win"].clouds,
+                                     want_tiles=(args.search == "raster"))
             if ev is not None: ev[1].record()
             grids = None
             if args.search == "grid":
@@ -439,7 +440,7 @@ def run_ours(args):
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
                      "what": "fused knn_corr kernel" if pw == 1 else "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6,
-                        "what": "camera_prep + cloud_build (4 levels, one pass)" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
+                        "what": "camera_prep + cloud_build (4 levels, one pass) + tile depth tables" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
     }
     if args.search == "grid" and pw == 1:
         kern["grid_build"] = {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0}
@@ -627,11 +628,11 @@ def time_distributions(args, w, ops, synth, WindowClouds, win, fm, dp, K, E, bas
     g = torch.Generator(device=dev).manual_seed(77)
     dp40 = torch.where(torch.rand(dp.shape, device=dev, generator=g) < (0.4 - args.zero_frac) / max(1e-6, 1.0 - args.zero_frac),
                        torch.zeros_like(dp), dp)
-    clouds = ops.cloud_build(fm, dp40, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds)
+    clouds = ops.cloud_build(fm, dp40, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds, want_tiles=True)
     w40 = WindowClouds(clouds, None, K_NN, 1, True, False)
     coords40, _ = synth.make_tracks(clouds[0].xyz, N, S_WINDOW, C=C_FEAT, seed=73, valid=clouds[0].xyz4[..., 3] > 0)
     res["knn_corr_zero40"] = dict(timed(w40, coords40), what="tracks follow the surface, 40 % of the depth pixels invalid (0)")
-    ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds)     # restore
+    ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, reuse=win.clouds, want_tiles=True)     # restore
     return res
 
 

@@ -85,6 +85,17 @@ int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, cons
                     int V, int S, int C, int H, int W, float stride, int depth_avg,
                     const mvt_level_out *levels, int level_mask, void *stream);
 
+/* mvt_cloud_build for a RUN OF FRAMES inside larger arrays -- what a sliding window needs when the clouds of the frames it
+ * shares with the previous window are kept (the reference rebuilds all S frames of every window although S/2 of them
+ * overlap, mvtracker.py:297-306 vs :549-555): fmaps / depths are frame runs of views that are fmaps_view_stride /
+ * depths_view_stride ELEMENTS apart (e.g. frames 6..11 of a [V,12,C,H,W] tensor: pointer at frame 6, view stride 12*C*H*W),
+ * the camera record of (view v, frame s) is cam + (v*cam_view_stride + s)*MVT_CAM_STRIDE, and the output pointers of
+ * `levels` point at the first frame to write inside the caller's per-frame arrays.  0 strides = dense. */
+int mvt_cloud_build_frames(const void *fmaps, long long fmaps_view_stride, int feat_dtype, const float *depths,
+                           long long depths_view_stride, const float *cam, int cam_view_stride,
+                           int V, int S, int C, int H, int W, float stride, int depth_avg,
+                           const mvt_level_out *levels, int level_mask, void *stream);
+
 /* Hashed uniform grid over B independent clouds ("segments", one per frame) of N points each. */
 size_t mvt_grid_workspace_bytes(int B, int N);
 
@@ -158,11 +169,19 @@ typedef struct mvt_corr_level {
  * idx_hint: optional [n_levels,B,M,k] int32 -- ANY k points of the same clouds per query, typically the idx_out of the
  * previous refinement iteration (tracks move by centimetres between iterations, mvtracker.py:392): the largest distance
  * to them bounds the k-th best, so the raster search starts with a tight radius.  A warm start only: results are exact
- * and identical with or without it (entries < 0 or of unsearchable points disable it for that query).  May alias idx_out. */
+ * and identical with or without it (entries < 0, repeated entries or entries of unsearchable points disable it for that
+ * query).  May alias idx_out.
+ * workspace: optional device scratch of >= mvt_knn_corr_workspace_bytes(n_levels, B, M) bytes, 16-byte aligned.  With it
+ * (and tile_z tables in every level's search descriptor, C == 128, G == 1, k <= 16) the fused kernel hands the queries whose
+ * ball projects onto a large pixel box -- tracks floating in free space, far from every surface: the reference starts each
+ * window with the same 3-D point in all frames (mvtracker.py:510), so tracks of moving objects do -- to a second kernel
+ * that finishes them with the depth-culled tile search; the results are identical, the slow queries no longer hold the
+ * fused kernel's warps.  NULL: one kernel does everything. */
+size_t mvt_knn_corr_workspace_bytes(int n_levels, int B, int M);
 int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                  const void *targets, const float *coords, int add_offset, int add_xyz,
                  float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
-                 void *stream);
+                 void *workspace, void *stream);
 
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */

@@ -11,8 +11,8 @@ MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
 CAM_STRIDE, MAX_VIEWS = 48, 32
 
-SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
+SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_cloud_build_frames", "mvt_grid_workspace_bytes",
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_corr_workspace_bytes", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
            "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
            "mvt_tile_depth_build", "mvt_track_input", "mvt_knn_corr_backward",
@@ -76,11 +76,14 @@ def lib():
     L.mvt_launch_count.restype = C.c_ulonglong
     L.mvt_camera_prep.argtypes = [vp, vp, ci, vp, vp]
     L.mvt_cloud_build.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
+    L.mvt_cloud_build_frames.argtypes = [vp, ll, ci, vp, ll, vp, ci, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
     L.mvt_grid_workspace_bytes.argtypes = [ci, ci]
     L.mvt_grid_workspace_bytes.restype = C.c_size_t
     L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
     L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
-    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp]
+    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp, vp]
+    L.mvt_knn_corr_workspace_bytes.argtypes = [ci, ci, ci]
+    L.mvt_knn_corr_workspace_bytes.restype = C.c_size_t
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]
     L.mvt_debug_set_stats.argtypes = [vp]
@@ -101,7 +104,8 @@ def lib():
     L.mvt_cloud_build_backward.argtypes = [vp, ci, ci, ci, ci, ci, ci, vp, ci, vp]
     for name in SYMBOLS:
         f = getattr(L, name)
-        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count", "mvt_tile_depth_floats"):
+        if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count", "mvt_tile_depth_floats",
+                        "mvt_knn_corr_workspace_bytes"):
             f.restype = ci
     _lib = L
     return L

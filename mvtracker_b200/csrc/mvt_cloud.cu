@@ -94,6 +94,8 @@ struct CloudParams {
     int *neg[4];
     PeersDev rec[4];       // replicated record buffers [S, V_total*H_l*W_l] of every rank (n == 0: not shared)
     int view_off, V_total;
+    long long fm_vstride, dp_vstride;   // elements between consecutive views of fmaps / depths (dense: S*C*H*W, S*H*W)
+    int cam_vstride;                    // camera records between consecutive views (dense: S)
 };
 
 template <typename T> __device__ __forceinline__ float to_f(T v);
@@ -204,12 +206,12 @@ __global__ void __launch_bounds__(256, MVT_CLOUD_MINB) cloud_build_kernel(const 
     const int H = p.H, W = p.W, C = p.C;
     const size_t HW = (size_t)H * W;
 
-    if (tid < 24) cm[tid] = p.cam[(size_t)vs * kCamStride + tid];
+    if (tid < 24) cm[tid] = p.cam[((size_t)v * p.cam_vstride + s) * kCamStride + tid];
     // depth pyramid of the tile
     {
         int yy = tid >> 5, xx = tid & 31;
         int gy = y0 + yy, gx = x0 + xx;
-        dep[tid] = (gy < H && gx < W) ? p.depths[(size_t)vs * HW + (size_t)gy * W + gx] : 0.f;
+        dep[tid] = (gy < H && gx < W) ? p.depths[(size_t)v * p.dp_vstride + (size_t)s * HW + (size_t)gy * W + gx] : 0.f;
     }
     __syncthreads();
     float *d1 = dep + 256, *d2 = d1 + 64, *d3 = d2 + 16;
@@ -268,12 +270,12 @@ __global__ void __launch_bounds__(256, MVT_CLOUD_MINB) cloud_build_kernel(const 
     const bool any_f = p.fvec[0] || p.fvec[1] || p.fvec[2] || p.fvec[3];
     if (!any_f) return;
     const bool vec = (C % 4) == 0;
-    const T *fm = reinterpret_cast<const T *>(p.fmaps) + (size_t)vs * C * HW;
+    const T *fm = reinterpret_cast<const T *>(p.fmaps) + (size_t)v * p.fm_vstride + (size_t)s * C * HW;
     const bool need1 = (p.level_mask & 0xE) != 0, need2 = (p.level_mask & 0xC) != 0, need3 = (p.level_mask & 0x8) != 0;
     const int yy = tid >> 5, xx = tid & 31;
     const bool inside = (y0 + yy < H) && (x0 + xx < W);
     const size_t pix = (size_t)(y0 + yy) * W + (x0 + xx);
-    const bool pairs = ((W & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.fmaps) & 3) == 0);   // 4-byte pixel pairs are aligned
+    const bool pairs = ((W & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.fmaps) & 3) == 0) && ((p.fm_vstride & 1) == 0);   // 4-byte pixel pairs are aligned
 
     for (int c0 = 0; c0 < C; c0 += CC) {
         __syncthreads();   // previous chunk's readers of t0..t3 are done
@@ -365,7 +367,7 @@ MVT_EXPORT int mvt_camera_prep(const float *intrs, const float *extrs, int n, fl
 static int cloud_build_impl(const void *fmaps, int feat_dtype, const float *depths, const float *cam,
                             int V, int S, int C, int H, int W, float stride, int depth_avg,
                             const mvt_level_out *levels, int level_mask, const mvt_peers *records, int view_offset,
-                            int V_total, void *stream) {
+                            int V_total, void *stream, long long fm_vstride = 0, long long dp_vstride = 0, int cam_vstride = 0) {
     using namespace mvt;
     MVT_CHECK_ARG(depths && cam && levels, "mvt_cloud_build: null pointer");
     MVT_CHECK_ARG(V > 0 && S > 0 && C > 0 && H > 0 && W > 0, "mvt_cloud_build: bad shape V=%d S=%d C=%d H=%d W=%d", V, S, C, H, W);
@@ -375,6 +377,11 @@ static int cloud_build_impl(const void *fmaps, int feat_dtype, const float *dept
     CloudParams p;
     p.fmaps = fmaps; p.depths = depths; p.cam = cam;
     p.V = V; p.S = S; p.C = C; p.H = H; p.W = W;
+    p.fm_vstride = fm_vstride ? fm_vstride : (long long)S * C * H * W;
+    p.dp_vstride = dp_vstride ? dp_vstride : (long long)S * H * W;
+    p.cam_vstride = cam_vstride ? cam_vstride : S;
+    MVT_CHECK_ARG(p.fm_vstride >= (long long)S * C * H * W && p.dp_vstride >= (long long)S * H * W && p.cam_vstride >= S,
+                  "mvt_cloud_build: view strides smaller than one view's frames");
     p.stride = stride; p.depth_avg = depth_avg; p.level_mask = level_mask;
     bool any_f = false, any_sp = false;
     for (int l = 0; l < 4; ++l) {
@@ -429,6 +436,14 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
                                const mvt_level_out *levels, int level_mask, void *stream) {
     return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, nullptr, 0, V,
                             stream);
+}
+
+MVT_EXPORT int mvt_cloud_build_frames(const void *fmaps, long long fmaps_view_stride, int feat_dtype, const float *depths,
+                                      long long depths_view_stride, const float *cam, int cam_view_stride,
+                                      int V, int S, int C, int H, int W, float stride, int depth_avg,
+                                      const mvt_level_out *levels, int level_mask, void *stream) {
+    return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, nullptr, 0, V,
+                            stream, fmaps_view_stride, depths_view_stride, cam_view_stride);
 }
 
 MVT_EXPORT int mvt_cloud_build_shared(const void *fmaps, int feat_dtype, const float *depths, const float *cam,

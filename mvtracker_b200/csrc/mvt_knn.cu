@@ -72,7 +72,16 @@ struct CorrParams {
     const int *idx_hint;   // [n_levels,B,M,k] or null: any k points of the same clouds (e.g. last iteration's neighbours)
     float scale;      // sqrt(C/G)
     int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4)
+    unsigned *hard;   // deferred queries (see knn_corr_hard_kernel): [0] count, [1] cursor, entries (uint4) from byte 256; or null
 };
+
+// A query whose ball projects onto a large pixel box in some view (it floats in free space, far from every surface --
+// e.g. a track of a moving object in the frames where the object has moved on: the reference starts every window with the
+// same 3-D point in all frames, mvtracker.py:510 -- or sits next to a camera) would keep its warp scanning thousands of
+// pixels.  The fused kernel gives such a query up as soon as a pass would read kTileMinPixels new pixels of one view and
+// appends it here with the k-th distance it has found so far; knn_corr_hard_kernel finishes it with the depth-culled tile
+// search (mvt_raster.cuh: tile_search) and the same gather / correlation code.  Costs the fused kernel no registers.
+struct HardEntry { unsigned qid, pad; u64 cap; };
 
 // 16 partial sums per lane (one per neighbour) -> lane L ends with the warp total of neighbour L>>1 (16 shuffles).
 __device__ __forceinline__ float transpose_reduce16(float (&pr)[16], int lane) {
@@ -180,55 +189,24 @@ __device__ __forceinline__ float dot8_bf16(const uint4 &a, const uint4 &b) {
 #ifndef MVT_CORR_MINB
 #define MVT_CORR_MINB 18
 #endif
+#ifndef MVT_CORR_TILES_INLINE
+#define MVT_CORR_TILES_INLINE 0     // 1 (A/B): the fused kernel finishes its own large-box queries with tile_search
+#endif
+#ifndef MVT_HARD_MINB
+#define MVT_HARD_MINB 8             // resident 64-thread blocks per SM of knn_corr_hard_kernel
+#endif
 #ifndef MVT_CORR_THREADS
 #define MVT_CORR_THREADS 64
 #endif
+// Everything after the search: neighbour lists out, gather of the k feature rows, correlation, offsets, store.
+// tkt: the group's sorted result list (group lane j holds the j-th neighbour's key).
 template <int MODE, bool RASTER_ONLY, int GW>
-__global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
-    MVT_WARP_SCRATCH(win_tab, MVT_CORR_THREADS / 32);
-    const int lane = threadIdx.x & 31;
-    const Group<GW> g(lane);
+__device__ __forceinline__ void corr_epilogue(const CorrParams &p, const CorrLevelDev &L, const Group<GW> &g, const int lane, const bool live,
+                                              const int b, const int m, const int lvl, const long long q, const float qx, const float qy,
+                                              const float qz, const u64 tkt) {
     const int gl = g.gl;
-    const int m_raw = (int)((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 / GW)) + (GW == 32 ? 0 : (lane >> 4));
-    const bool live = m_raw < p.M;       // half-warp groups: the last group of a frame may be padding
-    if (GW == 32 && !live) return;
-    const int m = live ? m_raw : p.M - 1;
-    const int b = blockIdx.y, lvl = blockIdx.z;
-    const long long q = (long long)b * p.M + m;
-    const CorrLevelDev &L = p.lv[lvl];
     const int k = L.k, C = p.C;
-    const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
-
-    TopK tk;
-    // warm start: the largest distance to k known points of this cloud bounds the k-th best -> cap of the search
-    u64 cap = kEmptyKey64;
-    if (p.idx_hint && (RASTER_ONLY || L.sd.raster)) {
-        unsigned bits = 0xffffffffu;
-        // plain (coherent) load: idx_hint may alias idx_out, which this launch writes -- each query reads its own k
-        // entries before it writes them, but ld.global.nc promises that NOBODY writes the location during the kernel
-        int hi = -1 - gl;                       // distinct dummies for the lanes beyond k
-        if (gl < k) hi = p.idx_hint[(((long long)lvl * p.B + b) * p.M + m) * k + gl];
-        // the cap is the largest distance to k DISTINCT points; a repeated index would make it too small: no cap then
-        const unsigned same = __match_any_sync(FULL, GW == 32 ? hi : (hi ^ ((lane & 16) << 26)));
-        const bool dup = gl < k && hi >= 0 && (same & (same - 1u)) != 0u;
-        if (gl < k) {
-            if (hi >= 0 && hi < L.sd.N && !dup) {
-                const float4 hp = __ldg(L.sd.rv.xyz4 + (size_t)b * L.sd.N + hi);
-                const float hd = dist2(hp.x, hp.y, hp.z, qx, qy, qz);
-                const bool usable = L.sd.rv.skip_invalid ? (hp.w > 0.f) : !(hp.w < 0.f);
-                if (usable && hd == hd) bits = __float_as_uint(hd);
-            }
-        } else {
-            bits = 0u;
-        }
-        // group maximum (all lanes take part)
-#pragma unroll
-        for (int o = GW / 2; o; o >>= 1) bits = max(bits, g.shfl_xor(bits, o));
-        if (bits < 0x7f800000u) cap = ((u64)bits << 32) | 0xffffffffull;
-    }
-    if (RASTER_ONLY || L.sd.raster) raster_search<GW>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap);
-    else if (GW == 32) knn_search(L.sd.g, b, qx, qy, qz, k, lane, tk);
-    const int bi = key_idx(tk.t);       // group lane j < k: the j-th neighbour
+    const int bi = key_idx(tkt);        // group lane j < k: the j-th neighbour
 
     if (p.idx_out && live && gl < k) p.idx_out[(((long long)lvl * p.B + b) * p.M + m) * k + gl] = (bi != kNoIdx) ? bi : -1;
 
@@ -341,6 +319,103 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
                 if (p.add_xyz) o[wpos + lane] = pv;
             }
         }
+    }
+}
+
+template <int MODE, bool RASTER_ONLY, int GW, bool DEFER = false>
+__global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kernel(const CorrParams p) {
+    MVT_WARP_SCRATCH(win_tab, MVT_CORR_THREADS / 32);
+    const int lane = threadIdx.x & 31;
+    const Group<GW> g(lane);
+    const int gl = g.gl;
+    const int m_raw = (int)((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 / GW)) + (GW == 32 ? 0 : (lane >> 4));
+    const bool live = m_raw < p.M;       // half-warp groups: the last group of a frame may be padding
+    if (GW == 32 && !live) return;
+    const int m = live ? m_raw : p.M - 1;
+    const int b = blockIdx.y, lvl = blockIdx.z;
+    const long long q = (long long)b * p.M + m;
+    const CorrLevelDev &L = p.lv[lvl];
+    const int k = L.k;
+    const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+
+    TopK tk;
+    // warm start: the largest distance to k known points of this cloud bounds the k-th best -> cap of the search
+    u64 cap = kEmptyKey64;
+    if (p.idx_hint && (RASTER_ONLY || L.sd.raster)) {
+        unsigned bits = 0xffffffffu;
+        // plain (coherent) load: idx_hint may alias idx_out, which this launch writes -- each query reads its own k
+        // entries before it writes them, but ld.global.nc promises that NOBODY writes the location during the kernel
+        int hi = -1 - gl;                       // distinct dummies for the lanes beyond k
+        if (gl < k) hi = p.idx_hint[(((long long)lvl * p.B + b) * p.M + m) * k + gl];
+        // the cap is the largest distance to k DISTINCT points; a repeated index would make it too small: no cap then
+        const unsigned same = __match_any_sync(FULL, GW == 32 ? hi : (hi ^ ((lane & 16) << 26)));
+        const bool dup = gl < k && hi >= 0 && (same & (same - 1u)) != 0u;
+        if (gl < k) {
+            if (hi >= 0 && hi < L.sd.N && !dup) {
+                const float4 hp = __ldg(L.sd.rv.xyz4 + (size_t)b * L.sd.N + hi);
+                const float hd = dist2(hp.x, hp.y, hp.z, qx, qy, qz);
+                const bool usable = L.sd.rv.skip_invalid ? (hp.w > 0.f) : !(hp.w < 0.f);
+                if (usable && hd == hd) bits = __float_as_uint(hd);
+            }
+        } else {
+            bits = 0u;
+        }
+        // group maximum (all lanes take part)
+#pragma unroll
+        for (int o = GW / 2; o; o >>= 1) bits = max(bits, g.shfl_xor(bits, o));
+        if (bits < 0x7f800000u) cap = ((u64)bits << 32) | 0xffffffffull;
+    }
+    if (RASTER_ONLY || L.sd.raster) {
+        if constexpr (DEFER) {
+            // windows only; the search gives up on a large pixel box (the level has tile tables, rv.ztab != null)
+            const bool exact = raster_windows<32, true>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap, 0u);
+#if MVT_CORR_TILES_INLINE
+            if (!exact) tk = tile_search(L.sd.rv, b, qx, qy, qz, k, tk, L.sd.g.stats);      // (A/B variant: finish it here)
+#else
+            if (!exact) {       // (uniform) -> knn_corr_hard_kernel
+                if (lane == 0) {
+                    const unsigned i = atomicAdd(p.hard, 1u);
+                    HardEntry e;
+                    e.qid = (unsigned)(((long long)lvl * p.B + b) * p.M + m); e.pad = 0u;
+                    e.cap = tk.th | 0xffffffffull;
+                    reinterpret_cast<HardEntry *>(reinterpret_cast<unsigned char *>(p.hard) + 256)[i] = e;
+                }
+                return;
+            }
+#endif
+        } else {
+            raster_search<GW>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap);
+        }
+    } else if (GW == 32) {
+        knn_search(L.sd.g, b, qx, qy, qz, k, lane, tk);
+    }
+    corr_epilogue<MODE, RASTER_ONLY, GW>(p, L, g, lane, live, b, m, lvl, q, qx, qy, qz, tk.t);
+}
+
+// The deferred queries of knn_corr_kernel: one wave of blocks, every warp draws entries until the list is empty.
+template <int MODE>
+__global__ void __launch_bounds__(64, MVT_HARD_MINB) knn_corr_hard_kernel(const CorrParams p) {
+    const int lane = threadIdx.x & 31;
+    const Group<32> g(lane);
+    const unsigned count = p.hard[0];
+    const HardEntry *list = reinterpret_cast<const HardEntry *>(reinterpret_cast<const unsigned char *>(p.hard) + 256);
+    for (;;) {
+        unsigned i = 0u;
+        if (lane == 0) i = atomicAdd(p.hard + 1, 1u);
+        i = __shfl_sync(FULL, i, 0);
+        if (i >= count) return;
+        const HardEntry e = list[i];
+        const int m = (int)(e.qid % (unsigned)p.M);
+        const unsigned fr = e.qid / (unsigned)p.M;
+        const int b = (int)(fr % (unsigned)p.B), lvl = (int)(fr / (unsigned)p.B);
+        const long long q = (long long)b * p.M + m;
+        const CorrLevelDev &L = p.lv[lvl];
+        const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+        TopK tk;
+        tk.init();
+        tk.th = e.cap;
+        tk = tile_search(L.sd.rv, b, qx, qy, qz, L.k, tk, L.sd.g.stats);
+        corr_epilogue<MODE, true, 32>(p, L, g, lane, true, b, m, lvl, q, qx, qy, qz, tk.t);
     }
 }
 
@@ -525,10 +600,15 @@ MVT_EXPORT int mvt_knn(const mvt_search *search, int B, const float *query, int 
     return MVT_OK;
 }
 
+MVT_EXPORT size_t mvt_knn_corr_workspace_bytes(int n_levels, int B, int M) {
+    if (n_levels <= 0 || B <= 0 || M <= 0) return 0;
+    return 256 + sizeof(mvt::HardEntry) * (size_t)n_levels * (size_t)B * (size_t)M;
+}
+
 MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                             const void *targets, const float *coords, int add_offset, int add_xyz,
                             float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
-                            void *stream) {
+                            void *workspace, void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(levels && targets && coords && out, "mvt_knn_corr: null pointer");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_corr: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
@@ -572,18 +652,38 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     if (mvt::g_group_width != 16) half = false;
     const int qpb = (half ? 2 : 1) * (MVT_CORR_THREADS / 32);      // queries per block
     const dim3 grid((unsigned)((M + qpb - 1) / qpb), (unsigned)B, (unsigned)n_levels);
+    // deferral of the queries with large pixel boxes: needs the caller's scratch and every level's tile tables
+    bool defer = workspace != nullptr && all_raster && fast && aligned && !half && (long long)n_levels * B * M < (1ll << 31);
+    for (int l = 0; l < n_levels; ++l) defer = defer && levels[l].search.tile_z != nullptr;
+    p.hard = nullptr;
+    if (defer) {
+        MVT_CHECK_ARG(((uintptr_t)workspace & 15) == 0, "mvt_knn_corr: workspace must be 16-byte aligned");
+        p.hard = (unsigned *)workspace;
+        if (cudaMemsetAsync(workspace, 0, 16, st) != cudaSuccess) {
+            set_error("mvt_knn_corr: cudaMemsetAsync(workspace) failed");
+            return MVT_E_CUDA;
+        }
+    }
     if (feat_dtype == MVT_BF16) {
         if (half) knn_corr_kernel<2, true, 16><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else if (defer) knn_corr_kernel<2, true, 32, true><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
         else if (all_raster) knn_corr_kernel<2, true, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
         else knn_corr_kernel<2, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     } else if (fast && aligned) {
         if (half) knn_corr_kernel<1, true, 16><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
+        else if (defer) knn_corr_kernel<1, true, 32, true><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
         else if (all_raster) knn_corr_kernel<1, true, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
         else knn_corr_kernel<1, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     } else {
         knn_corr_kernel<0, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     }
     MVT_CHECK_LAUNCH("knn_corr");
+    if (defer) {
+        const unsigned hgrid = one_wave_grid((long long)n_levels * B * M, 2, MVT_HARD_MINB);
+        if (feat_dtype == MVT_BF16) knn_corr_hard_kernel<2><<<hgrid, 64, 0, st>>>(p);
+        else knn_corr_hard_kernel<1><<<hgrid, 64, 0, st>>>(p);
+        MVT_CHECK_LAUNCH("knn_corr_hard");
+    }
     return MVT_OK;
 }
 

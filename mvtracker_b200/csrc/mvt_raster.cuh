@@ -74,10 +74,20 @@ template <int I> struct WinWord { static constexpr unsigned value = win_tab_word
 #ifndef MVT_CAM_SMEM
 #define MVT_CAM_SMEM 1
 #endif
+#ifndef MVT_TOURNAMENT
+#define MVT_TOURNAMENT 1
+#endif
+constexpr int kTQ = 8;            // first-pass candidates per lane that go through the tournament (kTQ * 32 in all)
 #if MVT_CAM_SMEM
 // cam[i][lane]: the lane's (= its view's) projection constants, read back once per pass for the ball's pixel box --
 // ten registers per thread that need not stay live across the scans
+// queue[i - 1][lane]: the lane's i-th best first-pass candidate (tournament selection, see tournament_select), which
+// hands out its winners through pend[]
+#if MVT_TOURNAMENT
+struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; float cam[11][32]; u64 queue[kTQ - 1][32]; };
+#else
 struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; float cam[11][32]; };
+#endif
 #else
 struct __align__(16) WarpScratch { unsigned char tab[32]; u64 pend[32]; };
 #endif
@@ -132,6 +142,65 @@ __device__ __forceinline__ void tan_range_front(float ca, float cz, float icz, f
     lo = (dl > 0.f) ? __fdividef(t0 - ta, dl) : -INFINITY;
     hi = (dh > 0.f) ? __fdividef(t0 + ta, dh) : INFINITY;
 }
+
+#if MVT_TOURNAMENT && MVT_CAM_SMEM
+__device__ __forceinline__ void cswap(u64 &a, u64 &b) {
+    const bool sw = b < a;
+    const u64 lo = sw ? b : a, hi = sw ? a : b;
+    a = lo; b = hi;
+}
+// The k smallest of the warp's 32 * kTQ first-pass keys, in canonical (d2, index) order, WITHOUT a warp-wide sort and
+// without one-by-one insertion: every lane sorts its own kTQ keys in registers (a 19-exchange network, no shuffles) and
+// parks them in its shared-memory queue; then k rounds of "the smallest head wins": one REDUX.MIN over the heads' distance
+// bits, a vote, and -- only when two heads tie on the distance -- a second REDUX.MIN over their indices.  The winner writes
+// its key to sel[round] and advances its queue.  ~11 warp instructions per round, against ~20 per insertion (and ~28
+// insertions after a 200-instruction bitonic sort) of the list update it replaces.  Keys >= kEmptyKey64 (no candidate, NaN
+// distance) never win before a real point.  Returns with lane j < k holding the j-th best key (kEmptyKey64 if fewer).
+__device__ __forceinline__ u64 tournament_select(u64 (&key)[kTQ], int n_used, unsigned char *win_tab, int k) {
+    const int lane = threadIdx.x & 31;
+    u64 *sel = reinterpret_cast<u64 *>(win_tab + 32);
+    u64 (*queue)[32] = reinterpret_cast<u64 (*)[32]>(win_tab + 32 + 32 * sizeof(u64) + 11 * 32 * sizeof(float));
+    if (n_used > 4) {       // (uniform) optimal 8-input network, 19 exchanges
+        cswap(key[0], key[1]); cswap(key[2], key[3]); cswap(key[4], key[5]); cswap(key[6], key[7]);
+        cswap(key[0], key[2]); cswap(key[1], key[3]); cswap(key[4], key[6]); cswap(key[5], key[7]);
+        cswap(key[1], key[2]); cswap(key[5], key[6]); cswap(key[0], key[4]); cswap(key[3], key[7]);
+        cswap(key[1], key[5]); cswap(key[2], key[6]);
+        cswap(key[1], key[4]); cswap(key[3], key[6]);
+        cswap(key[2], key[4]); cswap(key[3], key[5]);
+        cswap(key[3], key[4]);
+    } else {                // keys 4..7 are empty: 4-input network, 5 exchanges
+        cswap(key[0], key[1]); cswap(key[2], key[3]); cswap(key[0], key[2]); cswap(key[1], key[3]); cswap(key[1], key[2]);
+    }
+#pragma unroll
+    for (int i = 1; i < kTQ; ++i) queue[i - 1][lane] = key[i];
+    u64 cur = key[0];
+    int head = 0, nsel = 0;
+    __syncwarp();
+    for (int j = 0; j < k; ++j, ++nsel) {
+        const unsigned hi = (unsigned)(cur >> 32);
+        const unsigned m = __reduce_min_sync(FULL, hi);
+        if (m > 0x7f800000u) break;                     // (uniform) only NaN distances are left
+        bool win = hi == m;
+        unsigned bal = __ballot_sync(FULL, win);
+        if (bal & (bal - 1u)) {                         // (uniform) several heads at this distance: the smallest index wins
+            const unsigned lo = win ? (unsigned)cur : 0xffffffffu;
+            const unsigned ml = __reduce_min_sync(FULL, lo);
+            win = win && lo == ml;
+            bal = __ballot_sync(FULL, win);
+            if (bal & (bal - 1u)) win = lane == __ffs(bal) - 1;     // the same key twice (all queues empty): any one
+        }
+        if (win) {
+            sel[j] = cur;
+            cur = head < kTQ - 1 ? queue[head][lane] : kEmptyKey64;
+            ++head;
+        }
+    }
+    __syncwarp();
+    const u64 mine = lane < nsel ? sel[lane] : kEmptyKey64;
+    __syncwarp();
+    return mine;
+}
+#endif
 
 struct Rect { int x0, y0, x1, y1; };   // [x0,x1) x [y0,y1); empty when x1 <= x0 or y1 <= y0
 __device__ __forceinline__ bool rect_empty(const Rect &r) { return r.x1 <= r.x0 || r.y1 <= r.y0; }
@@ -368,7 +437,48 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         const int total = kNW * V;
         const unsigned magic = (65536u + (unsigned)V - 1u) / (unsigned)V;     // t / V == (t * magic) >> 16 for t < 960
         const int x00 = ci - kM0, y00 = cj - kM0;
-        for (int t0 = 0; t0 < total; t0 += kCB * GW) {
+        int t_first = 0;
+#if MVT_TOURNAMENT && MVT_CAM_SMEM
+        if (GW == 32) {
+            // the first 32 * kTQ candidates (all of them for V <= 8): tournament selection instead of sort + insertions
+            u64 key[kTQ];
+#pragma unroll
+            for (int h = 0; h < kTQ / kCB; ++h) {
+                float4 p[kCB];
+                int id[kCB];
+                bool ok[kCB];
+#pragma unroll
+                for (int c = 0; c < kCB; ++c) {
+                    const int t = (h * kCB + c) * 32 + gl;
+                    const int rk = (int)(((unsigned)t * magic) >> 16), v = t - rk * V;
+                    const unsigned wo = win_tab[min(rk, kNW - 1)];
+                    const int px = g.shfl(x00, v) + (int)(wo & 15u), py = g.shfl(y00, v) + (int)(wo >> 4);
+                    ok[c] = t < total && ((front_mask >> v) & 1u) && (unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H;
+                    id[c] = (int)((unsigned)v * (unsigned)HW + (unsigned)py * (unsigned)W + (unsigned)px);
+                    p[c] = ok[c] ? __ldg(frame + id[c]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int c = 0; c < kCB; ++c) {
+                    const float d2 = dist2(p[c].x, p[c].y, p[c].z, qx, qy, qz);
+                    const bool valid = ok[c] && (skip_invalid ? (p[c].w > 0.f) : !(p[c].w < wmin)) && d2 == d2;
+                    u64 kk = valid ? pack_key(d2, id[c]) : kEmptyKey64;
+                    if (cap != kEmptyKey64 && !(kk < cap)) kk = kEmptyKey64;
+                    key[h * kCB + c] = kk;
+                }
+                if (h == 0 && total <= kCB * 32) {          // (uniform) few views: the second half is empty
+#pragma unroll
+                    for (int c = kCB; c < kTQ; ++c) key[c] = kEmptyKey64;
+                    break;
+                }
+            }
+            tk.t = tournament_select(key, (total + 31) >> 5, const_cast<unsigned char *>(win_tab), k);
+            tk.empty = false;
+            const u64 kth = g.shfl(tk.t, k - 1);
+            tk.th = kth < tk.cap ? kth : tk.cap;
+            t_first = kTQ * 32;
+        }
+#endif
+        for (int t0 = t_first; t0 < total; t0 += kCB * GW) {
             float4 p[kCB];
             int id[kCB];
             bool ok[kCB];

@@ -36,6 +36,14 @@ settings = SimpleNamespace(
     # 'raster': clouds that came from init_pointcloud_from_rgbd are searched directly in their depth rasters (no index
     # to build); 'grid': always build the hashed grid.  Clouds of unknown origin always use the grid.
     search="raster",
+    # Per-frame cloud cache across the overlapping windows of one sequence (hotpath.WindowSequence / ops.CloudArena): the
+    # clouds of the S/2 frames a window shares with the previous one are kept instead of rebuilt.  Needs the provenance that
+    # the smart_cat wrapper of install() records (a window's tensors are `cat(previous[:, :, S/2:], new)`,
+    # mvtracker.py:549-575) -- it is proven, never guessed; anything unproven is rebuilt.  The tensors returned for such a
+    # window are views of the arena: valid until a few windows later, which is all the model needs (mvtracker.py:296-376).
+    frame_cache=False,
+    window=12,                  # the model's sliding_window_len: calls with this many frames get the full pyramid
+    arena_slots=None,           # frames of arena per sequence shape (default: up to 4 windows, a third of the free memory)
 )
 
 
@@ -70,14 +78,106 @@ class _Pyramid:
         self.corr_cache = None          # (key, {level: tensor})
         self.served = set()             # levels already handed out (see init_pointcloud_from_rgbd)
         self.versioned = all(k[1] is not None for k in key[:4])
+        self.seq = None                 # frame cache: the WindowSequence (arena) these clouds are views of
 
 
 _pyramid_cache = []     # most recent first, at most 2 entries (feature-init call + forward_iteration call per window)
+_arenas = {}            # (V, H, W, C, dtype, device, stride, mode) -> hotpath.WindowSequence, kept across forward calls
+_ref_smart_cat = None   # the reference's own smart_cat (model_utils.py), wrapped by install()
 
 
-def clear_caches():
+def clear_caches(arenas: bool = False):
     _pyramid_cache.clear()
     _pending_blocks.clear()
+    for seq in _arenas.values():
+        seq.slot0 = None
+    if arenas:
+        _arenas.clear()
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# frame cache: provenance of a rolled window
+# ----------------------------------------------------------------------------------------------------------------------
+def _is_tail_of(t1: torch.Tensor, base: torch.Tensor, hop: int) -> bool:
+    """t1 is exactly base[:, :, hop:] (same storage, same strides) of a [B, V, S, ...] tensor."""
+    if base is None or t1.dim() != base.dim() or t1.dim() < 3 or t1.dtype != base.dtype:
+        return False
+    shape = list(base.shape)
+    shape[2] -= hop
+    # (`base` is alive, so its storage is: an equal storage pointer is the same storage, not a recycled address)
+    return (t1.untyped_storage().data_ptr() == base.untyped_storage().data_ptr() and list(t1.shape) == shape
+            and t1.stride() == base.stride() and t1.storage_offset() == base.storage_offset() + hop * base.stride(2))
+
+
+def smart_cat(tensor1, tensor2, dim):
+    """The reference's smart_cat (model_utils.py) with the provenance of a rolled window attached to its result: when
+    tensor1 is the last S - hop frames of the tensor the CURRENT arena window was built from, the result's first S - hop
+    frames are frames whose clouds are already in the arena.  The result itself is the reference's, untouched."""
+    out = _ref_smart_cat(tensor1, tensor2, dim)
+    try:
+        if settings.frame_cache and tensor1 is not None and dim == 2 and out is not tensor2 and _pyramid_cache:
+            cur = _pyramid_cache[0]
+            if cur.seq is not None and cur.seq.current is cur:
+                hop = out.shape[2] - tensor1.shape[2]
+                for which, base in (("f", cur.fm), ("d", cur.dp)):
+                    if base is not None and _version(base) == cur.versions[which] and _is_tail_of(tensor1, base, hop):
+                        out._mvt_roll = (weakref.ref(cur), which, hop)
+    except Exception:       # provenance is an optimisation: never let it break the model's own cat
+        pass
+    return out
+
+
+def _same_camera_tail(new: torch.Tensor, old: torch.Tensor, old_version, hop: int) -> bool:
+    """new[:, :, :S-hop] is old[:, :, hop:] -- both are slices of one untouched tensor (mvtracker.py:547-548)."""
+    try:
+        return (new.shape == old.shape and new.stride() == old.stride() and new.dtype == old.dtype
+                and new.untyped_storage().data_ptr() == old.untyped_storage().data_ptr()
+                and new.storage_offset() == old.storage_offset() + hop * old.stride(2)
+                and _version(new) is not None and _version(new) == old_version)
+    except Exception:
+        return False
+
+
+def _arena_for(fmaps, stride, mode):
+    from .hotpath import WindowSequence
+    _, V, S, C, H, W = fmaps.shape
+    key = (V, H, W, C, fmaps.dtype, fmaps.device, float(stride), mode, S)
+    seq = _arenas.get(key)
+    if seq is None:
+        seq = WindowSequence(V, H, W, C, fmaps.dtype, fmaps.device, S=S, hop=S // 2, stride=stride, slots=settings.arena_slots,
+                             want_valid=True, depth_interp_mode=mode)
+        seq.current = None
+        _arenas[key] = seq
+    return seq
+
+
+def _build_in_arena(fmaps, depths, intrs, extrs, stride, mode, key):
+    """Window of `settings.window` frames, B == 1, raster search: through the per-frame cache.  -> _Pyramid"""
+    S = fmaps.shape[2]
+    seq = _arena_for(fmaps, stride, mode)
+    rf, rd = getattr(fmaps, "_mvt_roll", None), getattr(depths, "_mvt_roll", None)
+    prev = rf[0]() if rf is not None else None
+    hop = rf[2] if rf is not None else 0
+    rolled = (prev is not None and rd is not None and rd[0]() is prev and rf[1] == "f" and rd[1] == "d" and rd[2] == hop
+              and prev.seq is seq and seq.current is prev and seq.slot0 is not None and hop == seq.hop
+              and _version(fmaps) == 0 and _version(depths) == 0            # the cat results have not been written since
+              and _same_camera_tail(intrs, prev.cams[0], prev.versions["K"], hop)
+              and _same_camera_tail(extrs, prev.cams[1], prev.versions["E"], hop))
+    if rolled:
+        win = seq.push(fmaps[0][:, S - hop:], depths[0][:, S - hop:, 0], intrs[0], extrs[0])
+    else:
+        seq.slot0 = None                                                    # a new sequence (or nothing could be proven)
+        win = seq.push(fmaps[0], depths[0][:, :, 0], intrs[0], extrs[0])
+    pyr = _Pyramid(key, None, {c.level: c for c in win.clouds})
+    # The window's input tensors are held until the next window replaces this entry: that is when the model lets go of them
+    # too (its next window is cat(this[:, :, S/2:], new), mvtracker.py:549-575), so the peak memory is the reference's; they
+    # make the provenance of the next window checkable (same storage, alive, unwritten).
+    pyr.seq, pyr.fm, pyr.dp = seq, fmaps, depths
+    pyr.cams = (intrs, extrs)
+    pyr.versions = {"f": _version(fmaps), "d": _version(depths), "K": _version(intrs), "E": _version(extrs)}
+    pyr.rolled = rolled
+    seq.current = pyr
+    return pyr
 
 
 def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, depth_interp_mode="nearest",
@@ -97,12 +197,15 @@ def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, de
     if level >= MAX_LEVELS:
         raise MvtError(f"pyramid level {level} not supported (0..{MAX_LEVELS - 1})")
     out_dtype = fmaps.dtype
+    key = (_key(fmaps), _key(depths), _key(intrs), _key(extrs), float(stride), depth_interp_mode)
     if fmaps.dtype not in (torch.float32, torch.bfloat16):
         # fp16 / fp64 feature maps (fp16: autocast on pre-Ampere devices, demo.py:833-837): the kernels take fp32 or bf16
         # features; such maps go through the fp32 kernels and the cloud's features are returned in the caller's dtype
-        fmaps = fmaps.float()
-
-    key = (_key(fmaps), _key(depths), _key(intrs), _key(extrs), float(stride), depth_interp_mode)
+        fmaps_cast = fmaps.float()
+        for name in ("_mvt_roll",):
+            if hasattr(fmaps, name):
+                setattr(fmaps_cast, name, getattr(fmaps, name))
+        fmaps = fmaps_cast
     pyr = None
     if settings.pyramid_cache:
         for e in _pyramid_cache:
@@ -112,17 +215,26 @@ def init_pointcloud_from_rgbd(fmaps, depths, intrs, extrs, stride=4, level=0, de
             if e.key == key and level in e.clouds and (e.versioned or level not in e.served):
                 pyr = e
                 break
+    use_arena = (pyr is None and settings.frame_cache and settings.pyramid_cache and settings.search == "raster" and B == 1
+                 and S == settings.window and S % 2 == 0 and (H >> (MAX_LEVELS - 1)) > 0 and (W >> (MAX_LEVELS - 1)) > 0
+                 and all(k[1] is not None for k in key[:4]) and not (torch.is_grad_enabled() and fmaps.requires_grad))
+    if use_arena:
+        pyr = _build_in_arena(fmaps, depths, intrs, extrs, stride, depth_interp_mode, key)
+        _pyramid_cache[:] = [pyr] + [e for e in _pyramid_cache if e.key != key and e.seq is not pyr.seq][:1]
     if pyr is None:
-        if settings.pyramid_cache:
+        if settings.pyramid_cache and (S == settings.window or not settings.frame_cache):
             levels = [l for l in range(MAX_LEVELS) if (H >> l) > 0 and (W >> l) > 0]
             if level not in levels:
                 levels = [level]
         else:
+            # (frame cache on: a call with another number of frames is the feature-init call on the new frames,
+            # mvtracker.py:606-613, which only ever asks for level 0 -- build what is asked for)
             levels = [level]
         per_b = []
         for b in range(B):
             per_b.append(ops.cloud_build(fmaps[b], depths[b, :, :, 0], intrs[b], extrs[b], stride=stride, levels=levels,
-                                         depth_interp_mode=depth_interp_mode, want_valid=True))
+                                         depth_interp_mode=depth_interp_mode, want_valid=True,
+                                         want_tiles=(settings.search == "raster" and B == 1)))
         clouds = {}
         for i, l in enumerate(levels):
             if B == 1:
@@ -356,19 +468,35 @@ class PointcloudCorrBlock:
         return mine if mine.dtype == out_dtype else mine.to(out_dtype)
 
 
-def install(ref_module=None):
-    """Rebind the reference's three seam names to this implementation.  Returns a callable that restores them."""
+def install(ref_module=None, frame_cache: bool = True, window: Optional[int] = 12):
+    """Rebind the reference's three seam names to this implementation.  Returns a callable that restores them.
+    frame_cache: also wrap the module's `smart_cat` (it keeps returning the reference's result) so that the clouds of the
+    frames consecutive windows share are built once (settings.frame_cache); window: the model's sliding_window_len."""
     if ref_module is None:
         import importlib
         ref_module = importlib.import_module("mvtracker.models.core.mvtracker.mvtracker")
-    saved = {n: getattr(ref_module, n) for n in ("init_pointcloud_from_rgbd", "knn", "PointcloudCorrBlock")}
+    global _ref_smart_cat
+    names = ["init_pointcloud_from_rgbd", "knn", "PointcloudCorrBlock"]
+    if frame_cache and hasattr(ref_module, "smart_cat"):
+        names.append("smart_cat")
+    saved = {n: getattr(ref_module, n) for n in names}
+    saved_settings = (settings.frame_cache, settings.window)
     ref_module.init_pointcloud_from_rgbd = init_pointcloud_from_rgbd
     ref_module.knn = knn
     ref_module.PointcloudCorrBlock = PointcloudCorrBlock
+    if "smart_cat" in saved:
+        # a fourth, passive name: the wrapper returns the reference's own result and only records where it came from
+        if saved["smart_cat"] is not smart_cat:
+            _ref_smart_cat = saved["smart_cat"]
+        ref_module.smart_cat = smart_cat
+        settings.frame_cache = True
+        if window is not None:
+            settings.window = int(window)
 
     def uninstall():
         for n, v in saved.items():
             setattr(ref_module, n, v)
+        settings.frame_cache, settings.window = saved_settings
         clear_caches()
 
     return uninstall

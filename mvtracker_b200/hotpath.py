@@ -36,7 +36,7 @@ class WindowClouds:
             assert fmaps.shape[0] == 1, "B must be 1 (mvtracker.py:275)"
             fmaps, depths, intrs, extrs = fmaps[0], depths[0], intrs[0], extrs[0]
         clouds = ops.cloud_build(fmaps, depths, intrs, extrs, stride=stride, levels=levels,
-                                 depth_interp_mode=depth_interp_mode)
+                                 depth_interp_mode=depth_interp_mode, want_tiles=(search == "raster"))
         grids = None
         if search == "grid":
             grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=k, cell_scale=cell_scale)
@@ -82,3 +82,58 @@ class WindowClouds:
             return ops.knn_gather(sr, c.fvec[frame:frame + 1], query_xyz[None])[0]
         g = ops.build_grids([(c.xyz[frame:frame + 1], None, c.spacing[frame:frame + 1])], k_hint=1)[0]
         return ops.knn_gather(g, c.fvec[frame:frame + 1], query_xyz[None])[0]
+
+
+class WindowSequence:
+    """The sliding windows of ONE sequence with a per-frame cloud cache (exact): window w covers frames hop*w .. hop*w+S-1
+    (mvtracker.py:522-566: S = 12, hop = S // 2) and shares S - hop frames with window w-1, whose clouds are kept in a
+    CloudArena instead of being rebuilt (the reference rebuilds all S frames of every window, mvtracker.py:297-306).
+
+        seq = WindowSequence(V, H', W', C, dtype, device)
+        win = seq.push(fmaps_new, depths_new, intrs_win, extrs_win)      # first call: S frames; then `hop` new frames each
+        fcorrs = win.corr(ffeats, coords)                                # a WindowClouds over the arena's current run
+
+    Each push returns the WindowClouds of the new window; the one returned before stays valid until the run wraps around
+    (slots / hop - 1 pushes later at the latest)."""
+
+    def __init__(self, V: int, H: int, W: int, C: int, dtype, device, S: int = 12, hop: Optional[int] = None, stride=4,
+                 levels: Sequence[int] = (0, 1, 2, 3), k=16, groups=1, add_offset=True, add_xyz=False, slots: Optional[int] = None,
+                 want_valid: bool = False, depth_interp_mode="nearest"):
+        self.S, self.hop = int(S), int(hop or S // 2)
+        assert 0 < self.hop <= self.S
+        if slots is None:       # up to four windows' worth of frames, within a third of the free memory
+            per = ops.CloudArena.bytes_per_frame(V, H, W, C, torch.empty(0, dtype=dtype).element_size(), levels)
+            free = torch.cuda.mem_get_info(device)[0]
+            slots = int(max(self.S + self.hop, min(4 * self.S, (free // 3) // max(per, 1))))
+        if slots < self.S + self.hop:
+            raise ValueError(f"a sliding window of {self.S} frames advancing by {self.hop} needs at least {self.S + self.hop} slots")
+        self.arena = ops.CloudArena(V, H, W, C, dtype, device, levels, slots, stride, want_valid=want_valid)
+        self.args = (k, groups, add_offset, add_xyz)
+        self.mode = depth_interp_mode
+        self.slot0 = None           # first slot of the current window's run
+        self.windows = 0
+        self.frames_built = 0
+
+    def push(self, fmaps_new, depths_new, intrs_win, extrs_win) -> WindowClouds:
+        """fmaps_new [V, n, C, H', W'] / depths_new [V, n, H', W'] (or [V, n, 1, H', W']): the frames this window adds -- all S
+        of the first window, `hop` afterwards (frame runs of larger tensors are taken as they are, no copy).
+        intrs_win [V, S, 3, 3], extrs_win [V, S, 3, 4]: the cameras of the WHOLE window."""
+        n, S, hop, ar = fmaps_new.shape[1], self.S, self.hop, self.arena
+        if self.slot0 is None:
+            if n != S:
+                raise ValueError(f"the first window needs all {S} frames, got {n}")
+            self.slot0, first_new = 0, 0
+        else:
+            if n != hop:
+                raise ValueError(f"a later window adds {hop} frames, got {n}")
+            self.slot0 += hop
+            if self.slot0 + S > ar.slots:                      # wrap: keep the S - hop shared frames, at the front
+                ar.move(self.slot0, 0, S - hop)
+                self.slot0 = 0
+            first_new = S - hop
+        cam = ops.camera_prep(intrs_win, extrs_win)             # [V*S, CAM_STRIDE], record v*S + s
+        cam_run = cam.reshape(-1)[first_new * cam.shape[1]:]
+        ar.build(self.slot0 + first_new, fmaps_new, depths_new, cam_run, S, self.mode)
+        self.windows += 1
+        self.frames_built += n
+        return WindowClouds(ar.run(self.slot0, S, cam), None, *self.args)

@@ -62,7 +62,7 @@ class Cloud:
     neg: Optional[torch.Tensor] = None     # [S] int32: frame holds points with depth < 0 (mvt_level_out.neg_depth)
 
 
-def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
+def tile_depth_build(clouds: Sequence["Cloud"], cam_view_stride: int = 0) -> None:
     """Fills cloud.tile_z of every Cloud that has raster records (one launch for all): the per-tile depth ranges that let
     the raster search skip, inside a large pixel box, the tiles the query's ball cannot reach (mvt_tile_depth_build)."""
     todo = [c for c in clouds if c.xyz4 is not None and c.cam is not None]
@@ -79,34 +79,56 @@ def tile_depth_build(clouds: Sequence["Cloud"]) -> None:
         shape = (S, c.V, (c.H + 7) // 8, (c.W + 7) // 8, 2)
         if c.tile_z is None or tuple(c.tile_z.shape) != shape:
             c.tile_z = torch.empty(shape, device=c.xyz4.device, dtype=torch.float32)
-        arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), S, c.xyz4.shape[1], c.V, c.H, c.W, float(c.stride), 0, None, None)
+        arr[i] = _CSearch(None, None, c.xyz4.data_ptr(), c.cam.data_ptr(), int(cam_view_stride) or S, c.xyz4.shape[1], c.V, c.H, c.W,
+                          float(c.stride), 0, None, None)
         outs[i] = c.tile_z.data_ptr()
     check(lib().mvt_tile_depth_build(arr, len(todo), S, outs, _stream()), "mvt_tile_depth_build")
     for c in todo:
         c.tiles_ready = True
 
 
+def _view_strided(t: torch.Tensor, inner: int):
+    """t [V, S, ...] whose views are whole contiguous runs of S frames (inner elements per frame), any distance apart -- e.g.
+    frames 6..11 of a [V,12,C,H,W] tensor.  -> (tensor to pass, elements between views); copies only when the layout is not that."""
+    V, S = t.shape[0], t.shape[1]
+    want = [inner]
+    for d in range(t.dim() - 1, 1, -1):
+        want.append(want[-1] // t.shape[d] if t.shape[d] else 0)
+    ok = t.stride(1) == inner and (V == 1 or t.stride(0) >= S * inner)
+    st, run = 1, True
+    for d in range(t.dim() - 1, 1, -1):
+        run = run and (t.shape[d] == 1 or t.stride(d) == st)
+        st *= t.shape[d]
+    if ok and run:
+        return t, (t.stride(0) if V > 1 else S * inner)
+    t = t.contiguous()
+    return t, S * inner
+
+
 def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (0,), depth_interp_mode="nearest",
                 want_valid=False, want_fvec=True, want_xyz4=True, want_spacing=True, cam=None,
                 reuse: Optional[Sequence["Cloud"]] = None, shared_records=None, view_offset: int = 0,
-                V_total: Optional[int] = None, want_tiles=False) -> List[Cloud]:
+                V_total: Optional[int] = None, want_tiles=False, cam_view_stride: int = 0) -> List[Cloud]:
     """fmaps [V,S,C,H,W], depths [V,S,H,W] (or [V,S,1,H,W]) -> one Cloud per requested level, built in ONE kernel pass.
+    fmaps / depths may be frame runs of larger tensors (views any distance apart, e.g. x[:, 6:]): no copy is made.
     reuse: Clouds of an earlier call with the same shapes / levels / dtype whose buffers are overwritten in place (no
-    allocation in steady state, e.g. one set of buffers per sliding window).
+    allocation in steady state, e.g. one set of buffers per sliding window; CloudArena hands out frame runs of its slots).
+    cam + cam_view_stride: camera records of a longer window, cam pointing at this run's first frame (records of
+    consecutive views cam_view_stride apart); default: the records are made here from intrs / extrs.
     shared_records {level: _lib.Peers}: also store the 16-byte records of these views into the replicated
     [S, V_total*H_l*W_l, 4] buffers of every rank, views view_offset.. (mvt_cloud_build_shared).
     want_tiles: also build the per-tile depth tables now, in one launch (otherwise the first search-only call on a level
-    builds that level's table; the fused knn_corr kernel does not use them)."""
+    builds that level's table; the fused knn_corr kernel uses them to hand its large-box queries to the tile search)."""
     _need_cuda(fmaps, "fmaps"); _need_cuda(depths, "depths")
     V, S, Cc, H, W = fmaps.shape
-    depths = depths.reshape(V, S, H, W)
+    depths = depths.reshape(V, S, H, W) if depths.dim() == 4 or depths.is_contiguous() else depths[:, :, 0]
     if depth_interp_mode not in ("nearest", "avg"):
         raise NotImplementedError(depth_interp_mode)
     levels = sorted(set(int(l) for l in levels))
     if not levels or levels[0] < 0 or levels[-1] >= _lib.MAX_LEVELS:
         raise MvtError(f"levels {levels} outside 0..{_lib.MAX_LEVELS - 1}")
-    fm = fmaps.contiguous()
-    dp = depths.float().contiguous()
+    fm, fm_vs = _view_strided(fmaps, Cc * H * W)
+    dp, dp_vs = _view_strided(depths if depths.dtype == torch.float32 else depths.float(), H * W)
     if reuse is not None:
         reuse = {c.level: c for c in reuse}
         if cam is None:
@@ -151,10 +173,17 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         mask |= 1 << l
         clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
                             float(stride) * (1 << l), old.tile_z if reuse is not None else None, False, neg))
-    if shared_records is None:
+    dense = fm_vs == S * Cc * H * W and dp_vs == S * H * W and not cam_view_stride
+    if shared_records is None and dense:
         check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                     int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
+    elif shared_records is None:
+        check(lib().mvt_cloud_build_frames(_ptr(fm), int(fm_vs), _feat_dtype(fm), _ptr(dp), int(dp_vs), _ptr(cam),
+                                           int(cam_view_stride), V, S, Cc, H, W, float(stride), int(depth_interp_mode == "avg"),
+                                           outs, mask, _stream()), "mvt_cloud_build_frames")
     else:
+        if not dense:
+            fm, dp = fm.contiguous(), dp.contiguous()
         recs = (_lib.Peers * _lib.MAX_LEVELS)()
         for l in levels:
             recs[l] = shared_records[l]
@@ -162,8 +191,74 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
                                            int(depth_interp_mode == "avg"), outs, mask, recs, int(view_offset),
                                            int(V if V_total is None else V_total), _stream()), "mvt_cloud_build_shared")
     if want_tiles and want_xyz4:
-        tile_depth_build(clouds)
+        tile_depth_build(clouds, cam_view_stride=cam_view_stride)
     return clouds
+
+
+class CloudArena:
+    """Per-level cloud arrays with room for `slots` frames of ONE sequence: the per-frame cloud cache of sliding windows.
+
+    The reference rebuilds all S = 12 frames of every window although consecutive windows share S/2 of them
+    (mvtracker.py:297-306 vs :549-555).  Here a window is a contiguous run of S slots; advancing by `hop` frames builds only
+    the new frames into the slots right behind the run (mvt_cloud_build_frames), so every window's clouds are plain
+    contiguous views [S, P, .] -- the kernels need no indirection.  When the run reaches the end of the arena the S - hop
+    frames it keeps are copied to the front (once every (slots - S) / hop + 1 windows).  HBM is what pays for it: a
+    panoptic frame (1.36 M points, fp32 features) is 0.74 GB, the default 4 windows' worth of slots 35 GB of the 180."""
+
+    def __init__(self, V: int, H: int, W: int, C: int, dtype, device, levels: Sequence[int] = (0, 1, 2, 3), slots: int = 48,
+                 stride: float = 4.0, want_valid: bool = True, want_xyz: bool = True):
+        self.V, self.H, self.W, self.C, self.dtype, self.device = V, H, W, C, dtype, device
+        self.levels, self.slots, self.stride = [int(l) for l in levels], int(slots), float(stride)
+        self.buf = {}
+        for l in self.levels:
+            Hl, Wl = H >> l, W >> l
+            P = V * Hl * Wl
+            self.buf[l] = dict(
+                xyz=torch.empty(slots, P, 3, device=device, dtype=torch.float32) if want_xyz else None,
+                xyz4=torch.empty(slots, P, 4, device=device, dtype=torch.float32),
+                fvec=torch.empty(slots, P, C, device=device, dtype=dtype),
+                valid=torch.empty(slots, P, device=device, dtype=torch.uint8) if want_valid else None,
+                neg=torch.zeros(slots, device=device, dtype=torch.int32),
+                tile_z=torch.empty(slots, V, (Hl + 7) // 8, (Wl + 7) // 8, 2, device=device, dtype=torch.float32))
+
+    @staticmethod
+    def bytes_per_frame(V, H, W, C, esize, levels=(0, 1, 2, 3)) -> int:
+        return sum(V * (H >> l) * (W >> l) * (12 + 16 + C * esize + 1) + 8 * V * (((H >> l) + 7) // 8) * (((W >> l) + 7) // 8)
+                   for l in levels)
+
+    def run(self, slot0: int, n: int, cam: Optional[torch.Tensor] = None, tiles_ready: bool = True) -> List[Cloud]:
+        """Clouds over slots slot0 .. slot0+n-1 (views of the arena; cam: the camera records [V*n, CAM_STRIDE] of that run)."""
+        assert 0 <= slot0 and slot0 + n <= self.slots
+        out = []
+        for l in self.levels:
+            b = self.buf[l]
+            sl = slice(slot0, slot0 + n)
+            out.append(Cloud(l, b["xyz"][sl] if b["xyz"] is not None else None, b["fvec"][sl],
+                             b["valid"][sl].view(torch.bool) if b["valid"] is not None else None, None, b["xyz4"][sl], cam,
+                             self.V, self.H >> l, self.W >> l, self.stride * (1 << l), b["tile_z"][sl], tiles_ready, b["neg"][sl]))
+        return out
+
+    def build(self, slot0: int, fmaps: torch.Tensor, depths: torch.Tensor, cam_run: torch.Tensor, cam_view_stride: int,
+              depth_interp_mode="nearest") -> None:
+        """Builds the frames of fmaps [V, n, C, H, W] (a frame run of any tensor) into slots slot0 .. slot0+n-1, all levels and
+        their tile tables.  cam_run: the window's camera records starting at this run's first frame (a view into the
+        window's [V*S, CAM_STRIDE] record array), consecutive views cam_view_stride records apart."""
+        n = fmaps.shape[1]
+        tgt = self.run(slot0, n, cam_run, tiles_ready=False)
+        for c in tgt:
+            if c.xyz is None:           # cloud_build always writes xyz; an arena without it hands out the xyz4 records only
+                raise MvtError("CloudArena(want_xyz=False) cannot be built into: the kernels write xyz")
+        cloud_build(fmaps, depths, None, None, stride=self.stride, levels=self.levels, depth_interp_mode=depth_interp_mode,
+                    want_valid=self.buf[self.levels[0]]["valid"] is not None, want_spacing=False, cam=cam_run, reuse=tgt,
+                    want_tiles=True, cam_view_stride=cam_view_stride)
+
+    def move(self, src: int, dst: int, n: int) -> None:
+        """Copies n frames' clouds from slot src to slot dst (non-overlapping; the wrap-around of a sliding window)."""
+        assert src >= dst + n or dst >= src + n
+        for b in self.buf.values():
+            for t in b.values():
+                if t is not None:
+                    t[dst:dst + n].copy_(t[src:src + n])
 
 
 class Grid:
@@ -280,14 +375,29 @@ def knn(where, query: torch.Tensor, k: int, idx_dtype=torch.int64, want_dist=Tru
     return dist, idx
 
 
+_corr_ws = {}       # device index -> uint8 scratch of mvt_knn_corr (deferred-query list); grown on demand, reused by every call
+
+
+def _corr_workspace(dev: torch.device, n_levels: int, B: int, M: int) -> torch.Tensor:
+    need = int(lib().mvt_knn_corr_workspace_bytes(n_levels, B, M))
+    ws = _corr_ws.get(dev.index)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need + (need >> 2), device=dev, dtype=torch.uint8)      # calls of one device run on one stream at a time
+        _corr_ws[dev.index] = ws
+    return ws
+
+
 def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, groups=1, add_offset=True, add_xyz=False,
              out: Optional[torch.Tensor] = None, return_idx=False, idx_hint: Optional[torch.Tensor] = None,
-             idx_out: Optional[torch.Tensor] = None):
+             idx_out: Optional[torch.Tensor] = None, defer: bool = True):
     """levels: sequence of (where, fvec [B,N,C], k) with where = Grid | Cloud | Search.
     -> out [B, M, sum_l k_l*D] fp32 (level-major columns, the layout of torch.cat(fcorrs, -1) at mvtracker.py:374),
     D = groups + 3*add_offset + 3*add_xyz.
     idx_hint [L,B,M,k] int32: warm start (any k points per query, e.g. the previous iteration's idx); idx_out: buffer that
-    receives the neighbour indices (may be the same tensor as idx_hint)."""
+    receives the neighbour indices (may be the same tensor as idx_hint).
+    defer: hand the library its scratch so that queries with large pixel boxes (tracks in free space) are finished by the
+    tile-search kernel instead of holding the fused kernel's warps (needs tile tables on every level: cloud_build(...,
+    want_tiles=True) or tile_depth_build; same results either way)."""
     _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
     B, M, Cc = targets.shape
     tg = targets.contiguous()
@@ -320,8 +430,12 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     for t in (idx, idx_hint):
         if t is not None:
             assert t.dtype == torch.int32 and t.is_contiguous() and t.numel() == n * B * M * int(levels[0][2])
+    ws = None
+    if defer and not os.environ.get("MVT_NO_DEFER") and all(sr.c.tile_z for sr in keep):
+        ws = _corr_workspace(tg.device, n, B, M)
     check(lib().mvt_knn_corr(lv, n, B, M, Cc, int(groups), _feat_dtype(tg), _ptr(tg), _ptr(cq), int(bool(add_offset)),
-                             int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _stream()), "mvt_knn_corr")
+                             int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _ptr(ws),
+                             _stream()), "mvt_knn_corr")
     return (out, idx) if return_idx else out
 
 

@@ -125,8 +125,13 @@ def forward(model, seq, iters=4, seam="stock", autocast=None):
 
 
 def compare(a, b):
-    """max abs differences of two forward() results."""
-    return {"traj": float((a["traj_e"].float() - b["traj_e"].float()).abs().max()),
-            "vis": float((a["vis_e"].float() - b["vis_e"].float()).abs().max()),
-            "feat_rows_equal": float((a["feat_init"].float() == b["feat_init"].float()).all(-1).float().mean()),
-            "scale": float(a["traj_e"].float().abs().max())}
+    """Differences of two forward() results.  feat_init[:, :, n] is the feature row of the cloud point nearest to query n
+    (k = 1, mvtracker.py:627-645): where two kNN implementations pick different points for a (near-)tie the whole track
+    starts from another feature vector, so visibilities are compared on the tracks whose rows agree (`vis`), and over all
+    tracks (`vis_all`)."""
+    same = (a["feat_init"].float() == b["feat_init"].float()).all(-1).all(1)[0]           # [N]
+    dv = (a["vis_e"].float() - b["vis_e"].float()).abs()[0]                                # [T, N]
+    dt = (a["traj_e"].float() - b["traj_e"].float()).abs()[0].amax(-1)                     # [T, N]
+    return {"traj": float(dt[:, same].max()) if same.any() else 0.0, "traj_all": float(dt.max()),
+            "vis": float(dv[:, same].max()) if same.any() else 0.0, "vis_all": float(dv.max()),
+            "feat_rows_equal": float(same.float().mean()), "scale": float(a["traj_e"].float().abs().max())}

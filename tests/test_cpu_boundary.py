@@ -56,9 +56,9 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert b"V*H*W" in L.mvt_last_error()
     lv = (_lib.CorrLevel * 4)()
     lv[0] = _lib.CorrLevel(_lib.Search(256, 256, None, None, 0, 8, 0, 0, 0, 0.0, 0), 256, 16, 0)
-    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None)
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, None)
     assert rc == -1 and b"k should be less than or equal to N" in L.mvt_last_error()   # mvtracker.py:785
-    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None)
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, None)
     assert rc == -1 and b"groups" in L.mvt_last_error()                                 # mvtracker.py:786-787
     outs = (_lib.LevelOut * 4)()
     assert L.mvt_cloud_build(dummy, 0, dummy, dummy, 2, 2, 8, 16, 16, 4.0, 0, outs, 0x10, None) == -1   # level 4
@@ -130,3 +130,27 @@ def test_adjacent_entry_points_check_arguments_without_a_gpu():
     assert b"empty" in L.mvt_last_error()
     assert L.mvt_lift_pixels(None, 4, 4, d, d, 3, 0, 0.0, d, None) == -1
     assert L.mvt_lift_pixels(d, 4, 4, d, d, 0, 0, 0.0, d, None) == 0                                                 # nothing to do
+
+
+def test_torch_library_ops_have_fake_kernels_and_no_cpu_kernel():
+    """torch.ops.mvt.* (mvtracker_b200/torch_ops.py): shapes / dtypes from the fake kernels (what torch.compile / export
+    trace with); CPU tensors are refused by the dispatcher -- no CPU implementation exists."""
+    import pytest
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    import mvtracker_b200.torch_ops  # noqa: F401  (registers the ops)
+    with FakeTensorMode():
+        fm, dp = torch.empty(3, 12, 128, 40, 56, device="cuda"), torch.empty(3, 12, 40, 56, device="cuda")
+        K, E = torch.empty(3, 12, 3, 3, device="cuda"), torch.empty(3, 12, 3, 4, device="cuda")
+        outs = torch.ops.mvt.cloud_build(fm, dp, K, E, 4.0, [0, 1, 2, 3], False)
+        assert [tuple(o.shape) for o in outs[:3]] == [(12, 6720, 3), (12, 6720, 128), (12, 6720, 4)] and outs[-1].shape == (36, 48)
+        q, t = torch.empty(12, 100, 3, device="cuda"), torch.empty(12, 100, 128, device="cuda")
+        d, i = torch.ops.mvt.knn(outs[2], outs[-1], q, 16, 3, 40, 56, 4.0)
+        assert d.shape == (12, 100, 16) and i.dtype == torch.int64
+        c = torch.ops.mvt.knn_corr(outs[2::3][:4], outs[1::3][:4], outs[-1], t, q, 16, 3, 40, 56, 4.0)
+        assert c.shape == (12, 100, 256) and c.dtype == torch.float32
+        x = torch.ops.mvt.track_input(q, t, torch.empty(12, 100, device="cuda"), torch.empty(12, 100, device="cuda"),
+                                      torch.empty(100, 581, device="cuda"), torch.empty(12, 581, device="cuda"), c, 64)
+        assert x.shape == (100, 12, 581)
+    with pytest.raises(NotImplementedError):
+        torch.ops.mvt.knn(torch.zeros(1, 10, 4), torch.zeros(1, 48), torch.zeros(1, 2, 3), 1, 1, 2, 5, 4.0)

@@ -143,3 +143,37 @@ def test_filter_invalid(mode):
             _, idx = oracle.knn(8, x[b][None], coords[b][None].cpu().numpy(), mask=v[b][None])
         o = oracle.corr_from_idx(x[b][None], f[b][None], targets[b][None].cpu().numpy(), coords[b][None].cpu().numpy(), idx)
         assert_close(out[b][None], o, 1e-4, f"{mode} frame {b}")
+
+
+def test_pointops_shaped_knn_query_with_unequal_segments():
+    """mvtracker_b200.pointops_compat.knn_query(k, xyz, offset, new_xyz, new_offset): the signature of the reference's native
+    precedent (pointops.knn_query, mvtracker.py:55-65) -- flattened points, cumulative offsets, GLOBAL int32 indices -- with
+    segments of DIFFERENT sizes, against the canonical oracle per segment; and the reference's own un-offset arithmetic
+    (mvtracker.py:68-69) on an equal-sized call."""
+    from mvtracker_b200.pointops_compat import knn_query
+    g = torch.Generator(device=DEV).manual_seed(11)
+    sizes, qsizes, k = [5000, 37, 1200, 9], [300, 11, 1, 25], 16
+    xyz = torch.rand(sum(sizes), 3, device=DEV, generator=g) * 3
+    new = torch.rand(sum(qsizes), 3, device=DEV, generator=g) * 3
+    off = torch.tensor(np.cumsum(sizes), device=DEV, dtype=torch.int32)
+    noff = torch.tensor(np.cumsum(qsizes), device=DEV, dtype=torch.int32)
+    idx, dist = knn_query(k, xyz, off, new, noff)
+    assert idx.dtype == torch.int32 and idx.shape == (sum(qsizes), k) and dist.shape == idx.shape
+    a = qa = 0
+    for n, m in zip(sizes, qsizes):
+        od, oi = oracle.knn(min(k, 32), xyz[a:a + n][None].cpu().numpy(), new[qa:qa + m][None].cpu().numpy())
+        got = idx[qa:qa + m].cpu().numpy()
+        want = np.where(oi[0] >= 0, oi[0] + a, -1)
+        assert (got == want).all(), (n, m)
+        assert (dist[qa:qa + m].cpu().numpy()[want >= 0] == od[0][want >= 0]).all()
+        assert (got[:, n:] == -1).all()                    # fewer than k points in the segment
+        a, qa = a + n, qa + m
+    # the call the reference makes: B equal segments, then idx - b*N  (mvtracker.py:60-69)
+    B, N, M = 3, 700, 40
+    ref, qry = torch.rand(B, N, 3, device=DEV, generator=g), torch.rand(B, M, 3, device=DEV, generator=g)
+    offset = torch.arange(1, B + 1, device=DEV) * N
+    new_offset = torch.arange(1, B + 1, device=DEV) * M
+    idx, dist = knn_query(k, ref.view(B * N, 3), offset, qry.view(B * M, 3), new_offset)
+    idx = idx.view(B, M, k) - (torch.arange(B, device=DEV).view(B, 1, 1) * N)
+    od, oi = oracle.knn(k, ref.cpu().numpy(), qry.cpu().numpy())
+    assert (idx.cpu().numpy() == oi).all() and (dist.view(B, M, k).cpu().numpy() == od).all()

@@ -98,8 +98,17 @@ def test_raster_and_grid_searches_agree_everywhere(window):
         assert torch.equal(ir, idx[li]) and torch.equal(dr, dg)
         # canonical order: distances ascending, ties by index; all indices distinct and in range
         assert (dr[..., 1:] >= dr[..., :-1]).all()
+        # (dr is the square ROOT of the canonical d2: two different d2 may round to the same root, so a tie in dr binds the
+        # index order only where the squared distances themselves are equal -- recomputed here in float64)
         tie = dr[..., 1:] == dr[..., :-1]
-        assert (ir[..., 1:][tie] > ir[..., :-1][tie]).all()
+        if tie.any():
+            fr, tr, j = torch.nonzero(tie, as_tuple=True)
+            pa = c.xyz[fr, ir[fr, tr, j].long()].double() - coords[fr, tr].double()
+            pb = c.xyz[fr, ir[fr, tr, j + 1].long()].double() - coords[fr, tr].double()
+            da, db = (pa * pa).sum(-1), (pb * pb).sum(-1)
+            real = da == db
+            assert (ir[fr, tr, j + 1][real] > ir[fr, tr, j][real]).all()
+            assert (db >= da * (1 - 1e-6)).all()
         assert ir.min().item() >= 0 and ir.max().item() < c.xyz.shape[1]
         assert (torch.sort(ir, -1).values.diff(dim=-1) > 0).all()
 

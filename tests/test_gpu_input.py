@@ -143,3 +143,96 @@ def test_lift_pixels_edges_vs_oracle():
     assert np.abs(got - ref).max() <= 1e-4 * max(1.0, np.abs(ref).max())
     with_t = _ops.lift_pixels(depth, cam, pix, t=3.0).cpu().numpy()
     assert (with_t[:, 0] == 3.0).all() and np.array_equal(with_t[:, 1:], got)
+
+
+@pytest.mark.parametrize("slots,dtype", [(18, torch.float32), (24, torch.float32), (30, torch.bfloat16)])
+def test_window_sequence_frame_cache_equals_full_rebuild(slots, dtype):
+    """Per-frame cloud cache across overlapping windows (the reference rebuilds all 12 frames of every window
+    although 6 overlap, mvtracker.py:297-306 vs :549-555): WindowSequence.push builds only the 6 new frames into the arena;
+    clouds, neighbour lists and correlation blocks of every window must equal a full rebuild bit for bit -- also across the
+    wrap-around of a small arena, and with per-frame cameras (the kept frames keep THEIR cameras)."""
+    from mvtracker_b200.hotpath import WindowClouds, WindowSequence
+    V, Hs, Ws, T, S, hop = 3, 40, 56, 36, 12, 6
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=T, C=128, zero_frac=0.1, seed=101, device=DEV, dtype=dtype)
+    g = torch.Generator(device=DEV).manual_seed(102)
+    sc.extrs[..., 3] += 0.02 * torch.randn(sc.extrs[..., 3].shape, device=DEV, generator=g)        # moving cameras
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0], sc.intrs[0], sc.extrs[0]
+    seq = WindowSequence(V, Hs, Ws, 128, dtype, torch.device(DEV), slots=slots, want_valid=True)
+    for w in range((T - S) // hop + 1):
+        f0 = w * hop
+        new = slice(f0, f0 + S) if w == 0 else slice(f0 + S - hop, f0 + S)
+        win = seq.push(fm[:, new], dp[:, new], K[:, f0:f0 + S], E[:, f0:f0 + S])
+        ref = WindowClouds.build(fm[:, f0:f0 + S], dp[:, f0:f0 + S], K[:, f0:f0 + S], E[:, f0:f0 + S])
+        for a, b in zip(win.clouds, ref.clouds):
+            assert torch.equal(a.xyz, b.xyz) and torch.equal(a.fvec, b.fvec) and torch.equal(a.xyz4, b.xyz4), (w, a.level)
+            assert torch.equal(a.tile_z, b.tile_z) and a.neg.sum().item() == 0
+        coords, targets = synth.make_tracks(ref.clouds[0].xyz, 200, S, seed=103 + w, dtype=dtype, valid=ref.clouds[0].xyz4[..., 3] > 0)
+        coords[:, :20] += 0.4                                       # some free-space queries (deferred to the tile search)
+        assert torch.equal(win.corr(targets, coords), ref.corr(targets, coords)), w
+        assert torch.equal(win.feature_init(3, coords[3, :50]), ref.feature_init(3, coords[3, :50]))
+    assert seq.frames_built == S + hop * ((T - S) // hop)
+
+
+def test_torch_library_ops_equal_the_ctypes_path_and_trace_without_graph_breaks():
+    """torch.ops.mvt.* give the tensors of mvtracker_b200.ops bit for bit, and a function around them compiles with
+    fullgraph=True (no graph break at the custom ops; the "eager" backend keeps the test independent of a code generator)."""
+    import mvtracker_b200.torch_ops  # noqa: F401
+    V, Hs, Ws, S, N, K = 3, 40, 56, 3, 157, 16
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=S, C=128, zero_frac=0.1, seed=81, device=DEV)
+    fm, dp, Ki, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
+    clouds = ops.cloud_build(fm, dp, Ki, E, levels=range(4))
+    outs = torch.ops.mvt.cloud_build(fm, dp, Ki, E, 4.0, [0, 1, 2, 3], False)
+    for i, c in enumerate(clouds):
+        assert torch.equal(outs[3 * i], c.xyz) and torch.equal(outs[3 * i + 1], c.fvec) and torch.equal(outs[3 * i + 2], c.xyz4)
+    cam = outs[-1]
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], N, S)
+    want = ops.knn_corr([(c, c.fvec, K) for c in clouds], targets, coords)
+
+    def f(x4, fv, cam, t, q):
+        corr = torch.ops.mvt.knn_corr(x4, fv, cam, t * 1.0, q + 0.0, K, V, Hs, Ws, 4.0)
+        d, i = torch.ops.mvt.knn(x4[0], cam, q, 4, V, Hs, Ws, 4.0)
+        return corr * 2.0, d, i
+
+    x4, fv = list(outs[2::3][:4]), list(outs[1::3][:4])
+    got, d, i = torch.compile(f, backend="eager", fullgraph=True)(x4, fv, cam, targets, coords)
+    assert torch.equal(got, want * 2.0)
+    d0, i0 = ops.knn(clouds[0], coords, 4)
+    assert torch.equal(d, d0) and torch.equal(i, i0)
+
+
+def test_refinement_iteration_in_a_cuda_graph():
+    """the C ABI only enqueues on the current stream, so one refinement iteration's hot path -- the fused
+    kNN correlation of all levels written into the transformer-input buffer + mvt_track_input -- is captured in a
+    torch.cuda.CUDAGraph and replayed with new track positions / features; every replay must equal the eager result.
+    (The reference's loop has a host sync per iteration, `torch.isnan(coords).any()` at mvtracker.py:401; INTEGRATION.md
+    shows how a captured loop defers that check.)"""
+    from mvtracker_b200.hotpath import WindowClouds
+    V, Hs, Ws, S, N = 3, 40, 56, 4, 200
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=S, C=128, zero_frac=0.1, seed=83, device=DEV)
+    win = WindowClouds.build(sc.fmaps, sc.depths, sc.intrs, sc.extrs)
+    D = 581
+    g = torch.Generator(device=DEV).manual_seed(84)
+    pos, tim = torch.randn(N, D, device=DEV, generator=g), torch.randn(S, D, device=DEV, generator=g)
+    mask, vis = torch.ones(S, N, device=DEV), torch.rand(S, N, device=DEV, generator=g)
+    # static input / output buffers of the captured graph
+    coords_b, feats_b = torch.empty(S, N, 3, device=DEV), torch.empty(S, N, 128, device=DEV)
+    x_b = torch.empty(N, S, D, device=DEV)
+    sets = []
+    for i in range(4):
+        c, t = synth.make_tracks(win.clouds[0].xyz[0], N, S, seed=85 + i, jitter=0.02 + 0.1 * i)      # incl. free-space queries
+        sets.append((c, t))
+    coords_b.copy_(sets[0][0]); feats_b.copy_(sets[0][1])
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):                       # warm-up on the capture stream (allocations, workspace)
+        win.transformer_input(feats_b, coords_b, mask, vis, pos, tim, out=x_b)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        win.transformer_input(feats_b, coords_b, mask, vis, pos, tim, out=x_b)
+    for c, t in sets[1:] + sets[:1]:
+        coords_b.copy_(c); feats_b.copy_(t)
+        graph.replay()
+        torch.cuda.synchronize()
+        want = win.transformer_input(t, c, mask, vis, pos, tim)
+        assert torch.equal(x_b, want)

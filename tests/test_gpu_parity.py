@@ -517,3 +517,31 @@ def test_corr_warm_start_with_repeated_hint_indices():
     dup[..., 15] = dup[..., 0]                      # one repeat
     got, gidx = ops.knn_corr(lv, targets, coords, idx_hint=dup, return_idx=True)
     assert torch.equal(got, want) and torch.equal(gidx, widx)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_corr_deferred_free_space_queries_identical(dtype):
+    """Queries far from every surface (large pixel boxes) are handed by the fused kernel to knn_corr_hard_kernel (tile search,
+    same gather / correlation code): outputs and neighbour lists must equal the one-kernel path bit for bit, and the list
+    must really have been used."""
+    sc = synth.make_scene(4, 80 * 4, 96 * 4, S=3, C=128, zero_frac=0.1, seed=95, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_valid=True,
+                             want_tiles=True)
+    coords, targets = synth.make_tracks(clouds[0].xyz[0], 600, 3, valid=clouds[0].valid[0], dtype=dtype)
+    g = torch.Generator(device=DEV).manual_seed(96)
+    coords[:, :300] += 0.4 * torch.randn(3, 300, 3, device=DEV, generator=g)       # floating in free space
+    E = sc.extrs[0, :, 0]
+    centres = -(E[:, :, :3].transpose(1, 2) @ E[:, :, 3:]).squeeze(-1)
+    coords[:, 300:340] = centres[torch.arange(40, device=DEV) % 4] + 0.2 * torch.randn(3, 40, 3, device=DEV, generator=g)
+    lv = [(c, c.fvec, 16) for c in clouds]
+    a, ia = ops.knn_corr(lv, targets, coords, return_idx=True, defer=False)
+    b, ib = ops.knn_corr(lv, targets, coords, return_idx=True, defer=True)
+    torch.cuda.synchronize()
+    counters = ops._corr_ws[torch.cuda.current_device()][:8].view(torch.int32).cpu().tolist()
+    assert counters[0] > 100 and counters[1] >= counters[0], counters      # deferred queries, all of them drawn
+    assert torch.equal(ia, ib) and torch.equal(a, b)
+    _, oi = oracle.knn(16, clouds[0].xyz.cpu().numpy(), coords.cpu().numpy())
+    assert (ib[0].cpu().numpy() == oi).all()
+    # warm start + deferral (the cap travels with the deferred query)
+    c, ic = ops.knn_corr(lv, targets, coords, return_idx=True, idx_hint=ia.clone(), defer=True)
+    assert torch.equal(ic, ia) and torch.equal(c, a)
