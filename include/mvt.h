@@ -176,12 +176,15 @@ typedef struct mvt_corr_level {
  * ball projects onto a large pixel box -- tracks floating in free space, far from every surface: the reference starts each
  * window with the same 3-D point in all frames (mvtracker.py:510), so tracks of moving objects do -- to a second kernel
  * that finishes them with the depth-culled tile search; the results are identical, the slow queries no longer hold the
- * fused kernel's warps.  NULL: one kernel does everything. */
+ * fused kernel's warps (hard_query_mode 1).  hard_query_mode 2: one kernel does everything, but the queries that mode 1 would
+ * have handed over are counted; either way the count is left in the first 4 bytes of the workspace (a caller can read it back
+ * asynchronously and pick the mode of its next call: deferral pays when several per cent of the queries are such, it costs
+ * a little when there are only a few).  NULL / mode 0: one kernel, nothing counted. */
 size_t mvt_knn_corr_workspace_bytes(int n_levels, int B, int M);
 int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                  const void *targets, const float *coords, int add_offset, int add_xyz,
                  float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
-                 void *workspace, void *stream);
+                 void *workspace, int hard_query_mode, void *stream);
 
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */

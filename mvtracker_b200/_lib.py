@@ -81,7 +81,7 @@ def lib():
     L.mvt_grid_workspace_bytes.restype = C.c_size_t
     L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
     L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
-    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp, vp]
+    L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp, ci, vp]
     L.mvt_knn_corr_workspace_bytes.argtypes = [ci, ci, ci]
     L.mvt_knn_corr_workspace_bytes.restype = C.c_size_t
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]

@@ -73,6 +73,7 @@ struct CorrParams {
     float scale;      // sqrt(C/G)
     int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4)
     unsigned *hard;   // deferred queries (see knn_corr_hard_kernel): [0] count, [1] cursor, entries (uint4) from byte 256; or null
+    int hard_mode;    // 1: defer the large-box queries; 2: only count them in hard[0] and finish them in place
 };
 
 // A query whose ball projects onto a large pixel box in some view (it floats in free space, far from every surface --
@@ -368,7 +369,8 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
     if (RASTER_ONLY || L.sd.raster) {
         if constexpr (DEFER) {
             // windows only; the search gives up on a large pixel box (the level has tile tables, rv.ztab != null)
-            const bool exact = raster_windows<32, true>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap, 0u);
+            const bool exact = raster_windows<32, true>(g, L.sd.rv, win_tab, b, live, qx, qy, qz, k, tk, L.sd.g.stats, (int)q, cap, 0u,
+                                                        p.hard_mode == 2 ? p.hard : nullptr);
 #if MVT_CORR_TILES_INLINE
             if (!exact) tk = tile_search(L.sd.rv, b, qx, qy, qz, k, tk, L.sd.g.stats);      // (A/B variant: finish it here)
 #else
@@ -608,7 +610,7 @@ MVT_EXPORT size_t mvt_knn_corr_workspace_bytes(int n_levels, int B, int M) {
 MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
                             const void *targets, const float *coords, int add_offset, int add_xyz,
                             float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
-                            void *workspace, void *stream) {
+                            void *workspace, int hard_query_mode, void *stream) {
     using namespace mvt;
     MVT_CHECK_ARG(levels && targets && coords && out, "mvt_knn_corr: null pointer");
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_corr: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
@@ -653,9 +655,11 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     const int qpb = (half ? 2 : 1) * (MVT_CORR_THREADS / 32);      // queries per block
     const dim3 grid((unsigned)((M + qpb - 1) / qpb), (unsigned)B, (unsigned)n_levels);
     // deferral of the queries with large pixel boxes: needs the caller's scratch and every level's tile tables
-    bool defer = workspace != nullptr && all_raster && fast && aligned && !half && (long long)n_levels * B * M < (1ll << 31);
+    MVT_CHECK_ARG(hard_query_mode >= 0 && hard_query_mode <= 2, "mvt_knn_corr: hard_query_mode %d", hard_query_mode);
+    bool defer = workspace != nullptr && hard_query_mode != 0 && all_raster && fast && aligned && !half && (long long)n_levels * B * M < (1ll << 31);
     for (int l = 0; l < n_levels; ++l) defer = defer && levels[l].search.tile_z != nullptr;
     p.hard = nullptr;
+    p.hard_mode = hard_query_mode;
     if (defer) {
         MVT_CHECK_ARG(((uintptr_t)workspace & 15) == 0, "mvt_knn_corr: workspace must be 16-byte aligned");
         p.hard = (unsigned *)workspace;
@@ -678,7 +682,7 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
         knn_corr_kernel<0, false, 32><<<grid, MVT_CORR_THREADS, 0, st>>>(p);
     }
     MVT_CHECK_LAUNCH("knn_corr");
-    if (defer) {
+    if (defer && hard_query_mode == 1) {
         const unsigned hgrid = one_wave_grid((long long)n_levels * B * M, 2, MVT_HARD_MINB);
         if (feat_dtype == MVT_BF16) knn_corr_hard_kernel<2><<<hgrid, 64, 0, st>>>(p);
         else knn_corr_hard_kernel<1><<<hgrid, 64, 0, st>>>(p);

@@ -336,19 +336,33 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
             unsigned mask = g.ballot(keep);
             tested += (unsigned)min(32, total - t0);
             kept += __popc(mask);
+            // the kept tiles, kTB at a time: all 2 * kTB record loads of a round are in flight before the first list update
+            // (a query that ends up here is latency-bound: hundreds of dependent load rounds otherwise)
+            constexpr int kTB = 4;
             while (mask) {
-                const int src = __ffs(mask) - 1;
-                mask &= mask - 1;
-                const int vv = g.shfl(v, src);
-                const int px = g.shfl(tx, src) * kTile + (lane & 7), py0 = g.shfl(ty, src) * kTile + (lane >> 3), py1 = py0 + 4;
-                const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
-                const int i0 = vv * HW + py0 * W + px, i1 = vv * HW + py1 * W + px;
-                const float4 p0 = in0 ? __ldg(frame + i0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                const float4 p1 = in1 ? __ldg(frame + i1) : make_float4(0.f, 0.f, 0.f, 0.f);
-                const bool v0 = in0 && (skip_invalid ? (p0.w > 0.f) : !(p0.w < 0.f));
-                const bool v1 = in1 && (skip_invalid ? (p1.w > 0.f) : !(p1.w < 0.f));
-                st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, v0 ? pack_key(dist2(p0.x, p0.y, p0.z, qx, qy, qz), i0) : kEmptyKey64, k);
-                st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, v1 ? pack_key(dist2(p1.x, p1.y, p1.z, qx, qy, qz), i1) : kEmptyKey64, k);
+                float4 p0[kTB], p1[kTB];
+                int i0[kTB], i1[kTB];
+                bool v0[kTB], v1[kTB];
+#pragma unroll
+                for (int u = 0; u < kTB; ++u) {
+                    const bool on = mask != 0u;
+                    const int src = on ? __ffs(mask) - 1 : 0;
+                    mask &= mask - 1;
+                    const int vv = g.shfl(v, src);
+                    const int px = g.shfl(tx, src) * kTile + (lane & 7), py0 = g.shfl(ty, src) * kTile + (lane >> 3), py1 = py0 + 4;
+                    const bool in0 = on && px < W && py0 < H, in1 = on && px < W && py1 < H;
+                    i0[u] = vv * HW + py0 * W + px; i1[u] = vv * HW + py1 * W + px;
+                    p0[u] = in0 ? __ldg(frame + i0[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    p1[u] = in1 ? __ldg(frame + i1[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v0[u] = in0; v1[u] = in1;
+                }
+#pragma unroll
+                for (int u = 0; u < kTB; ++u) {
+                    const bool a0 = v0[u] && (skip_invalid ? (p0[u].w > 0.f) : !(p0[u].w < 0.f));
+                    const bool a1 = v1[u] && (skip_invalid ? (p1[u].w > 0.f) : !(p1[u].w < 0.f));
+                    st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, a0 ? pack_key(dist2(p0[u].x, p0[u].y, p0[u].z, qx, qy, qz), i0[u]) : kEmptyKey64, k);
+                    st_ins += topk_offer<32, MVT_TOPK_BUF != 0>(g, tk, a1 ? pack_key(dist2(p1[u].x, p1[u].y, p1[u].z, qx, qy, qz), i1[u]) : kEmptyKey64, k);
+                }
             }
         }
     }
@@ -368,10 +382,12 @@ static __device__ __noinline__ TopK tile_search(const RasterView rv, const int s
 // Returns true when the list is the exact answer (always, unless a budget made the search give up).
 // live = false: the group has no query (padding at the end of a frame's track list); it only takes part in the
 // collectives.  Must be called by all 32 lanes.
+// soft_count (TILES only): instead of giving a large-box query up, count it there (once) and carry on with the windows.
 template <int GW, bool TILES>
 __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterView &rv, const unsigned char *win_tab, int s,
                                                bool live, float qx, float qy, float qz, int k, TopK &tk,
-                                               unsigned long long *stats, int qtag, u64 cap, unsigned budget) {
+                                               unsigned long long *stats, int qtag, u64 cap, unsigned budget,
+                                               unsigned *soft_count = nullptr) {
     tk.init(cap);
     constexpr bool BUF = GW == 32 && MVT_TOPK_BUF != 0;
     tk.pend = scratch_pend(win_tab);
@@ -429,6 +445,7 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
     };
     unsigned st_cand = 0, st_ins = 0;
     int st_pass = 1;
+    bool soft_counted = false;
 
     // ---- pass 1: the fixed window of every view that sees q in front of it; candidate t = rank * V + view ----
     {
@@ -582,7 +599,13 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         // a large box of new pixels in some view: give the query to tile_search (depth-culled tiles), see raster_search
         if (TILES && GW == 32 && rv.ztab != nullptr && budget == 0u && !negf) {
             const int newpx = rect_empty(B) ? 0 : (B.x1 - B.x0) * (B.y1 - B.y0) - (rect_empty(A) ? 0 : (A.x1 - A.x0) * (A.y1 - A.y0));
-            if (g.any(have_k && mine && !done && newpx >= kTileMinPixels)) return false;
+            if (g.any(have_k && mine && !done && newpx >= kTileMinPixels)) {
+                if (soft_count == nullptr) return false;
+                if (!soft_counted) {
+                    soft_counted = true;
+                    if (gl == 0) atomicAdd(soft_count, 1u);
+                }
+            }
         }
 
         // ---- scan B \ A of every view: four strips per view (top, bottom, left, right), GW/4 views per round ----

@@ -387,17 +387,58 @@ def _corr_workspace(dev: torch.device, n_levels: int, B: int, M: int) -> torch.T
     return ws
 
 
+class _HardQueryPolicy:
+    """defer="auto": whether the next fused launch hands its large-box queries to the tile-search kernel.  Every launch leaves
+    the number of such queries in its scratch; it is copied to pinned host memory asynchronously and looked at when the NEXT
+    call is issued (no synchronisation: the decision is one call stale).  Deferral pays when several per cent of the queries
+    float in free space (a window that starts with static tracks, mvtracker.py:510) and costs ~10 % when only a few do."""
+    ON, OFF = 0.015, 0.0075      # fraction of a launch's queries; hysteresis
+
+    def __init__(self):
+        self.deferring = True    # a sequence starts with static tracks
+        self.pinned = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.event, self.queries, self.last_fraction = None, 0, None
+
+    def mode(self) -> int:
+        if self.event is not None and self.event.query():
+            self.last_fraction = float(self.pinned[0]) / max(1, self.queries)
+            self.event = None
+            if self.last_fraction > self.ON:
+                self.deferring = True
+            elif self.last_fraction < self.OFF:
+                self.deferring = False
+        return 1 if self.deferring else 2
+
+    def record(self, ws: torch.Tensor, queries: int):
+        if self.event is None and not torch.cuda.is_current_stream_capturing():
+            self.pinned.copy_(ws[:4].view(torch.int32), non_blocking=True)
+            self.queries = queries
+            self.event = torch.cuda.Event()
+            self.event.record()
+
+
+_hard_policy = {}     # device index -> _HardQueryPolicy
+
+
+def hard_query_policy(dev: torch.device) -> _HardQueryPolicy:
+    pol = _hard_policy.get(dev.index)
+    if pol is None:
+        pol = _hard_policy[dev.index] = _HardQueryPolicy()
+    return pol
+
+
 def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, groups=1, add_offset=True, add_xyz=False,
              out: Optional[torch.Tensor] = None, return_idx=False, idx_hint: Optional[torch.Tensor] = None,
-             idx_out: Optional[torch.Tensor] = None, defer: bool = True):
+             idx_out: Optional[torch.Tensor] = None, defer="auto"):
     """levels: sequence of (where, fvec [B,N,C], k) with where = Grid | Cloud | Search.
     -> out [B, M, sum_l k_l*D] fp32 (level-major columns, the layout of torch.cat(fcorrs, -1) at mvtracker.py:374),
     D = groups + 3*add_offset + 3*add_xyz.
     idx_hint [L,B,M,k] int32: warm start (any k points per query, e.g. the previous iteration's idx); idx_out: buffer that
     receives the neighbour indices (may be the same tensor as idx_hint).
-    defer: hand the library its scratch so that queries with large pixel boxes (tracks in free space) are finished by the
-    tile-search kernel instead of holding the fused kernel's warps (needs tile tables on every level: cloud_build(...,
-    want_tiles=True) or tile_depth_build; same results either way)."""
+    defer: True = queries with large pixel boxes (tracks in free space) are finished by the tile-search kernel instead of
+    holding the fused kernel's warps (needs tile tables on every level: cloud_build(..., want_tiles=True) or
+    tile_depth_build); False = one kernel; "auto" = decided from the count the previous launch left (_HardQueryPolicy).
+    Same results either way."""
     _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
     B, M, Cc = targets.shape
     tg = targets.contiguous()
@@ -430,12 +471,18 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     for t in (idx, idx_hint):
         if t is not None:
             assert t.dtype == torch.int32 and t.is_contiguous() and t.numel() == n * B * M * int(levels[0][2])
-    ws = None
+    ws, mode, pol = None, 0, None
     if defer and not os.environ.get("MVT_NO_DEFER") and all(sr.c.tile_z for sr in keep):
         ws = _corr_workspace(tg.device, n, B, M)
+        mode = 1
+        if defer == "auto":
+            pol = hard_query_policy(tg.device)
+            mode = pol.mode()
     check(lib().mvt_knn_corr(lv, n, B, M, Cc, int(groups), _feat_dtype(tg), _ptr(tg), _ptr(cq), int(bool(add_offset)),
-                             int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _ptr(ws),
+                             int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _ptr(ws), mode,
                              _stream()), "mvt_knn_corr")
+    if pol is not None:
+        pol.record(ws, n * B * M)
     return (out, idx) if return_idx else out
 
 

@@ -56,9 +56,9 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert b"V*H*W" in L.mvt_last_error()
     lv = (_lib.CorrLevel * 4)()
     lv[0] = _lib.CorrLevel(_lib.Search(256, 256, None, None, 0, 8, 0, 0, 0, 0.0, 0), 256, 16, 0)
-    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, None)
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 1, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, 0, None)
     assert rc == -1 and b"k should be less than or equal to N" in L.mvt_last_error()   # mvtracker.py:785
-    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, None)
+    rc = L.mvt_knn_corr(lv, 1, 1, 4, 128, 3, 0, dummy, dummy, 1, 0, dummy, 64, 0, None, None, None, 0, None)
     assert rc == -1 and b"groups" in L.mvt_last_error()                                 # mvtracker.py:786-787
     outs = (_lib.LevelOut * 4)()
     assert L.mvt_cloud_build(dummy, 0, dummy, dummy, 2, 2, 8, 16, 16, 4.0, 0, outs, 0x10, None) == -1   # level 4

@@ -535,6 +535,8 @@ def test_corr_deferred_free_space_queries_identical(dtype):
     coords[:, 300:340] = centres[torch.arange(40, device=DEV) % 4] + 0.2 * torch.randn(3, 40, 3, device=DEV, generator=g)
     lv = [(c, c.fvec, 16) for c in clouds]
     a, ia = ops.knn_corr(lv, targets, coords, return_idx=True, defer=False)
+    s_, is_ = ops.knn_corr(lv, targets, coords, return_idx=True, defer="auto")      # whatever the policy picks: same bits
+    assert torch.equal(is_, ia) and torch.equal(s_, a)
     b, ib = ops.knn_corr(lv, targets, coords, return_idx=True, defer=True)
     torch.cuda.synchronize()
     counters = ops._corr_ws[torch.cuda.current_device()][:8].view(torch.int32).cpu().tolist()
@@ -542,6 +544,15 @@ def test_corr_deferred_free_space_queries_identical(dtype):
     assert torch.equal(ia, ib) and torch.equal(a, b)
     _, oi = oracle.knn(16, clouds[0].xyz.cpu().numpy(), coords.cpu().numpy())
     assert (ib[0].cpu().numpy() == oi).all()
+    # count-only mode (what the adaptive policy runs while few queries are hard): one kernel, same bits, same count
+    pol = ops.hard_query_policy(torch.device(DEV, torch.cuda.current_device()))
+    pol.deferring, pol.event = False, None
+    d_, id_ = ops.knn_corr(lv, targets, coords, return_idx=True, defer="auto")
+    torch.cuda.synchronize()
+    c2 = ops._corr_ws[torch.cuda.current_device()][:8].view(torch.int32).cpu().tolist()
+    assert c2[0] == counters[0] and c2[1] == 0, (c2, counters)
+    assert torch.equal(id_, ia) and torch.equal(d_, a)
+    assert pol.mode() == 1 and pol.last_fraction > 0.1        # ... and the next call defers: most of these queries are hard
     # warm start + deferral (the cap travels with the deferred query)
     c, ic = ops.knn_corr(lv, targets, coords, return_idx=True, idx_hint=ia.clone(), defer=True)
     assert torch.equal(ic, ia) and torch.equal(c, a)
