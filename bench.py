@@ -50,12 +50,16 @@ def parse_args():
     ap.add_argument("--cell-scale", type=float, default=0.0)
     ap.add_argument("--search", default="raster", choices=["raster", "grid"],
                     help="raster: search the depth rasters directly (no index build); grid: hashed grid")
-    ap.add_argument("--dist-mode", default="p2p", choices=["p2p", "tracks", "views"],
+    ap.add_argument("--dist-mode", default="fused", choices=["fused", "p2p", "tracks", "views"],
                     help="N > 1: tracks = replicate the 16-byte records, search per track shard; views = search own views, merge candidates")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="N > 1: strong = ONE window sharded over the ranks (views, then tracks; the default, what the path's "
                          "multi-GPU design is about); weak = every rank tracks its own sequence's window with the single-GPU path "
                          "(independent replicas, no exchange)")
+    ap.add_argument("--step", default="advance", choices=["advance", "window"],
+                    help="advance (default): a step is ONE WINDOW ADVANCE of a sequence -- the 6 new frames are built into the "
+                         "per-frame cloud cache (the other 6 are shared with the previous window) + iters x knn_corr over the 12-frame "
+                         "window; window: every step rebuilds all 12 frames, as the reference does (mvtracker.py:297-306)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--warm-start", action="store_true",
                     help="N = 1: iterations 2..4 of a window start their searches from the previous iteration's neighbours "
@@ -285,12 +289,18 @@ def config_dict(w, args, world=1, weak=False):
             f"{world} GPUs: independent replicas, each rank runs the single-GPU path on its own sequence's window (no exchange)" if weak else
             (f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
              f"index lists all-gathered; records of locally owned neighbours all-reduced (NCCL)" if getattr(args, "dist_mode", "tracks") == "tracks" else
+             f"{world} GPUs: views sharded for the cloud build (features stay local, 16-byte point records multicast into every rank's replica); per iteration ONE persistent "
+             f"kernel per rank: search of the rank's track shard -> 8-byte records into the OWNER's inbox (peer stores over NVLink) -> owner-side gather + correlation "
+             f"-> result records multicast to every rank -> in-kernel epoch exchange; no NCCL, no barrier launch on the data path" if args.dist_mode == "fused" else
              f"{world} GPUs: views sharded for the cloud build (features stay local); point records, index lists and result records are stored by the producing kernels "
              f"straight into every rank's buffers (symmetric memory, NVSwitch multicast stores), two signal-pad barriers per iteration, no NCCL on the data path" if args.dist_mode == "p2p" else
              f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard (two bounded phases), merged indices all-gathered, result records all-reduced (NCCL)"),"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
             "levels": LEVELS, "k": K_NN, "iters": args.iters, "warm_start": bool(getattr(args, "warm_start", False)), "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
+            "step": ("one window advance of a sequence: 6 new frames built into the per-frame cloud cache (24 distinct frames, cycled: the new "
+                     "frames differ every step) + iters x knn_corr over the 12-frame window" if getattr(args, "step", "advance") == "advance"
+                     and not weak and getattr(args, "search", "raster") == "raster" else "one window, all 12 frames rebuilt every step"),
             "l2": "inputs_exceed_l2 (feature maps and clouds are > 126 MB and are rewritten every step)"}
 
 
@@ -331,31 +341,72 @@ def run_ours(args):
     pw = 1 if weak else world          # ranks ONE window is sharded over
 
     # ---- synthetic inputs, identical on every rank (same seed); tracks are sampled from the full level-0 cloud ---------
-    sc = synth.make_scene(V, w["H"], w["W"], S=S_WINDOW, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac,
+    from mvtracker_b200.dist import ShardedSequence
+    from mvtracker_b200.hotpath import WindowSequence
+    advance = args.step == "advance" and not weak and args.search == "raster"
+    HOP = S_WINDOW // 2
+    S_POOL = 4 * HOP if advance else S_WINDOW      # advance: a pool of 24 distinct frames, cycled (window j = blocks j, j+1 mod 4)
+    sc = synth.make_scene(V, w["H"], w["W"], S=S_POOL, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac,
                           seed=72 + (rank if weak else 0), device=dev, dtype=fdtype)
-    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
-    c0 = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=[0], want_fvec=False, want_spacing=False)[0]
+    fm_pool, dp_pool = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous()
+    K_pool, E_pool = sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
+    c0 = ops.cloud_build(fm_pool, dp_pool, K_pool, E_pool, stride=STRIDE, levels=[0], want_fvec=False, want_spacing=False)[0]
     # tracks follow the surface at their pixel (+ N(0, 2 cm)), i.e. near the cloud in every frame like converged tracks
-    base_coords, base_targets = synth.make_tracks(c0.xyz, N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype, valid=c0.xyz4[..., 3] > 0)
+    pool_coords, _ = synth.make_tracks(c0.xyz, N, S_POOL, C=C_FEAT, seed=73, dtype=fdtype, valid=c0.xyz4[..., 3] > 0)
+    _, base_targets = synth.make_tracks(c0.xyz[:S_WINDOW], N, S_WINDOW, C=C_FEAT, seed=73, dtype=fdtype)
     del c0
+
+    def frames_of(j):          # pool frames of window j
+        if not advance:
+            return list(range(S_WINDOW))
+        a, b = j % 4, (j + 1) % 4
+        return list(range(HOP * a, HOP * a + HOP)) + list(range(HOP * b, HOP * b + HOP))
+
     g = torch.Generator(device=dev).manual_seed(74)
-    coords_it = [(base_coords + 0.01 * torch.randn(base_coords.shape, device=dev, generator=g)).contiguous() for _ in range(iters)]
+    jit = [0.01 * torch.randn(S_WINDOW, N, 3, device=dev, generator=g) for _ in range(iters)]
+    n_types = 4 if advance else 1
+    coords_win = [[(pool_coords[frames_of(t)] + jit[i]).contiguous() for i in range(iters)] for t in range(n_types)]
+    cams_win = [(K_pool[:, frames_of(t)].contiguous(), E_pool[:, frames_of(t)].contiguous()) for t in range(n_types)]
+    coords_it = coords_win[0]
     targets_it = [(base_targets * (1.0 - 0.1 * i)).contiguous() for i in range(iters)]
     width = LEVELS * K_NN * 4
     outs = [torch.empty(S_WINDOW, N, width, device=dev, dtype=torch.float32) for _ in range(iters)]
-    K_all, E_all = K, E
+    v0, v1 = 0, V
     if pw > 1:
         v0, v1 = view_range(rank, world, V)
-        fm, dp, K, E = fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous()
+        fm_pool, dp_pool = fm_pool[v0:v1].contiguous(), dp_pool[v0:v1].contiguous()
         del sc
         torch.cuda.empty_cache()
+    cams_loc = [(Kw[v0:v1].contiguous(), Ew[v0:v1].contiguous()) for Kw, Ew in cams_win]
+    fm, dp = fm_pool[:, :S_WINDOW], dp_pool[:, :S_WINDOW]          # window 0 (the whole input of --step window)
+    K, E = cams_loc[0]
+    K_all, E_all = cams_win[0]
+    n_built = HOP if advance else S_WINDOW                         # frames whose clouds a steady-state step builds
 
     # ---- one step = the hot path of one sliding window; output buffers are allocated once and rebuilt in place --------
-    state = {"win": None}
+    state = {"win": None, "seq": None, "j": 0}
 
     def step(ev=None):
         if ev is not None: ev[0].record()
-        if pw == 1:
+        if advance:
+            if state["seq"] is None:
+                Hs, Ws = w["Hs"], w["Ws"]
+                state["seq"] = (WindowSequence(V, Hs, Ws, C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN) if pw == 1 else
+                                ShardedSequence(V, v0, v1, Hs, Ws, C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN, mode=args.dist_mode))
+                j, new = 0, slice(0, S_WINDOW)
+            else:
+                j = state["j"] + 1
+                b = (j + 1) % 4
+                new = slice(HOP * b, HOP * b + HOP)
+            t = j % 4
+            if pw == 1:
+                win = state["seq"].push(fm_pool[:, new], dp_pool[:, new], cams_win[t][0], cams_win[t][1])
+                win.warm_start = bool(args.warm_start)
+            else:
+                win = state["seq"].push(fm_pool[:, new], dp_pool[:, new], cams_loc[t][0], cams_loc[t][1], cams_win[t][0], cams_win[t][1])
+            state["j"] = j
+            cw = coords_win[t]
+        elif pw == 1:
             clouds = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=(args.search == "grid"),
                                      reuse=None if state["win"] is None else state["win"].clouds,
                                      want_tiles=(args.search == "raster"))
@@ -365,17 +416,19 @@ def run_ours(args):
                 grids = ops.build_grids([(c.xyz, None, c.spacing) for c in clouds], k_hint=K_NN, cell_scale=args.cell_scale)
             win = WindowClouds(clouds, grids, K_NN, 1, True, False)
             win.warm_start = bool(args.warm_start)
+            cw = coords_win[0]
         else:
-            win = ShardedWindow.build(fm, dp, K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
-                                      intrs_all=K_all, extrs_all=E_all, mode=args.dist_mode)
-            if ev is not None: ev[1].record()
+            win = ShardedWindow.build(fm.contiguous(), dp.contiguous(), K, E, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN,
+                                      reuse=state["win"], intrs_all=K_all, extrs_all=E_all, mode=args.dist_mode)
+            cw = coords_win[0]
+        if ev is not None and (advance or pw > 1): ev[1].record()
         if ev is not None: ev[2].record()
         for i in range(iters):
-            # "p2p": the result block is returned where the ranks' kernels stored it (symmetric memory; valid until the
+            # "p2p" / "fused": the result block is returned where the ranks' kernels stored it (symmetric memory; valid until the
             # next-but-one corr call), as the fused kernel writes into the caller's buffer at N = 1 -- no extra copy
-            state["out"] = win.corr(targets_it[i], coords_it[i], out=None if getattr(win, "mode", "") == "p2p" else outs[i])
+            state["out"] = win.corr(targets_it[i], cw[i], out=None if getattr(win, "mode", "") in ("p2p", "fused") else outs[i])
             if ev is not None: ev[3 + i].record()
-        state["win"] = win
+        state["win"], state["coords"] = win, cw
 
     def sync():
         torch.cuda.synchronize()
@@ -434,12 +487,12 @@ def run_ours(args):
     v_loc = fm.shape[0]
     q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4          # 9164 B (fp32) / 4812 B (bf16)
     corr_bytes = LEVELS * S_WINDOW * N * q_bytes / pw                                 # per rank: its share of the gathers
-    pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * S_WINDOW
-    cloud_bytes = fm.numel() * esz + dp.numel() * 4 + pts * (C_FEAT * esz + 12)       # SURVEY.md 8d (xyz4 records not counted)
+    pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * n_built
+    cloud_bytes = (fm.numel() * esz + dp.numel() * 4) * n_built // S_WINDOW + pts * (C_FEAT * esz + 12)   # SURVEY.md 8d (xyz4 records not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
                      "what": "fused knn_corr kernel" if pw == 1 else "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
-        "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6,
+        "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6, "frames_built": n_built,
                         "what": "camera_prep + cloud_build (4 levels, one pass) + tile depth tables" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
     }
     if args.search == "grid" and pw == 1:
@@ -465,14 +518,32 @@ def run_ours(args):
     line["hot_path_frames_per_s"] = {"value": w["T"] / (n_win * ms_step * 1e-3), "frames": w["T"], "windows": n_win,
                                      "what": "T / (windows x step): hot path only, not MVTracker.forward end to end"}
 
+    # ---- the build of a whole 12-frame window (what the reference does every window), for the build kernel's own roofline --------
+    if advance and pw == 1:
+        full_bytes = cloud_bytes * S_WINDOW // n_built
+        ws = None
+        for _ in range(2):
+            ws = ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, want_tiles=True, reuse=ws)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(3):
+            ops.cloud_build(fm, dp, K, E, stride=STRIDE, levels=range(LEVELS), want_spacing=False, want_tiles=True, reuse=ws)
+        b.record(); torch.cuda.synchronize()
+        t_full = a.elapsed_time(b) / 3
+        kern["cloud_build_full"] = {"ms": t_full, "alg_bytes": full_bytes, "gbs": full_bytes / t_full / 1e6, "frac": full_bytes / t_full / 1e6 / peak,
+                                    "frames_built": S_WINDOW, "what": "all 12 frames of a window rebuilt (not part of the step)"}
+        del ws
+
     # ---- the timed step's output, sampled against the oracle (every N) ----------------------------------------------------------
     if not args.no_verify and not weak:
-        line.update(verify_output(state["win"], state["out"], targets_it[iters - 1], coords_it[iters - 1], world, rank,
+        line.update(verify_output(state["win"], state["out"], targets_it[iters - 1], state["coords"][iters - 1], world, rank,
                                   args.dtype == "bf16"))
 
     # ---- two more track distributions on the same window (cold search each), N = 1 ---------------------------------------------
     if world == 1 and not args.no_distributions and args.search == "raster":
-        kern.update(time_distributions(args, w, ops, synth, WindowClouds, state["win"], fm, dp, K, E, targets_it[0], dev, peak, esz))
+        fr = frames_of(state["j"])
+        kern.update(time_distributions(args, w, ops, synth, WindowClouds, state["win"], fm_pool[:, fr].contiguous(), dp_pool[:, fr].contiguous(),
+                                       cams_win[state["j"] % n_types][0], cams_win[state["j"] % n_types][1], targets_it[0], dev, peak, esz))
 
     # ---- adjacent kernels, timed outside the step: not part of `value` -----------------------------
     if world == 1 and not args.no_adjacent and args.search == "raster":
@@ -480,7 +551,7 @@ def run_ours(args):
 
     # ---- e2e: same metric through the reference-facing API with HOST buffers ---------------------------------------------
     if not args.no_e2e:
-        e2e = run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0 if pw > 1 else 0, K_all, E_all, weak)
+        e2e = run_e2e(args, w, world, rank, dev, fm_pool, dp_pool, cams_loc, cams_win, coords_win, targets_it, v0, v1, advance, weak)
         line["e2e"] = e2e
     state["win"] = None
     state["out"] = None
@@ -488,7 +559,8 @@ def run_ours(args):
         sampler.stop()
     if world == 1 and not args.no_model:
         # BASELINE.json metric (ii): MVTracker.forward end to end, reference seam vs drop-in, on this GPU
-        del fm, dp, sc, outs, coords_it, targets_it, base_coords, base_targets
+        del fm, dp, fm_pool, dp_pool, sc, outs, coords_it, coords_win, targets_it, pool_coords, base_targets
+        state["seq"] = None
         torch.cuda.empty_cache()
         try:
             line["e2e_frames_per_s"] = model_frames_per_s([n for n in args.model_workloads.split(",") if n], dev, iters)
@@ -681,45 +753,64 @@ def model_frames_per_s(names, dev, iters):
     return out
 
 
-def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, K_all, E_all, weak=False):
-    """Each step: this rank's inputs pinned host -> device, the public API (N = 1: the drop-in mirror of the reference seam --
-    init_pointcloud_from_rgbd per level, PointcloudCorrBlock per level, corr_sample per (iteration, level), torch.cat;
-    N > 1: mvtracker_b200.dist.ShardedWindow), then every iteration's correlation block -> pinned host."""
+def run_e2e(args, w, world, rank, dev, fm_pool, dp_pool, cams_loc, cams_win, coords_win, targets_it, v0, v1, advance, weak=False):
+    """The same step through the repo's public API with HOST buffers: every step copies the frames the window adds (6 with
+    --step advance, 12 with --step window; this rank's views) and the window's cameras from pinned host memory, advances the
+    sequence (N = 1: mvtracker_b200.hotpath.WindowSequence / WindowClouds; N > 1: mvtracker_b200.dist.ShardedSequence /
+    ShardedWindow), and per iteration copies track positions + features in and the correlation block out (N > 1: each
+    rank reads back the rows of ITS track shard -- together the ranks return the block once)."""
     import torch
     import torch.distributed as dist
-    from mvtracker_b200 import dropin
-    from mvtracker_b200.dist import ShardedWindow
+    from mvtracker_b200.dist import ShardedSequence, ShardedWindow, track_shard
+    from mvtracker_b200.hotpath import WindowClouds, WindowSequence
     iters, N, V = args.iters, w["N"], w["V"]
     pw = 1 if weak else world
-    host_in = [t.cpu().pin_memory() for t in (fm, dp, K, E)]
-    host_cam = [t.cpu().pin_memory() for t in (K_all, E_all)]
-    host_ct = [(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(coords_it, targets_it)]
-    host_out = [torch.empty(S_WINDOW, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
-    h2d = sum(t.numel() * t.element_size() for t in host_in) + sum(c.numel() * c.element_size() + t.numel() * t.element_size() for c, t in host_ct)
+    HOP = S_WINDOW // 2
+    nblk = fm_pool.shape[1] // HOP
+    host_fm = [fm_pool[:, HOP * b:HOP * b + HOP].contiguous().cpu().pin_memory() for b in range(nblk)]
+    host_dp = [dp_pool[:, HOP * b:HOP * b + HOP].contiguous().cpu().pin_memory() for b in range(nblk)]
+    host_cam = [[t.cpu().pin_memory() for t in (cl[0], cl[1], cw[0], cw[1])] for cl, cw in zip(cams_loc, cams_win)]
+    host_ct = [[(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(cw, targets_it)] for cw in coords_win]
+    Ms = track_shard(pw, N)
+    lo, hi = (rank * Ms, min((rank + 1) * Ms, N)) if pw > 1 else (0, N)
+    host_out = [torch.empty(S_WINDOW, max(hi - lo, 0), LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
+    n_new = HOP if advance else S_WINDOW
+    h2d = (host_fm[0].numel() * host_fm[0].element_size() + host_dp[0].numel() * 4) * (n_new // HOP) \
+        + sum(t.numel() * t.element_size() for t in host_cam[0]) \
+        + sum(c.numel() * c.element_size() + t.numel() * t.element_size() for c, t in host_ct[0])
     d2h = sum(t.numel() * t.element_size() for t in host_out)
-    state = {"win": None}
+    state = {"seq": None, "win": None, "j": 0}
+    Hs, Ws = w["Hs"], w["Ws"]
+    fdtype = fm_pool.dtype
 
     def step():
-        fmd, dpd, Kd, Ed = [t.to(dev, non_blocking=True) for t in host_in]
-        if pw == 1:
-            blocks = []
-            for lvl in range(LEVELS):
-                xyz, fvec = dropin.init_pointcloud_from_rgbd(fmd[None], dpd[None, :, :, None], Kd[None], Ed[None], stride=STRIDE, level=lvl)
-                blocks.append(dropin.PointcloudCorrBlock(k=K_NN, groups=1, xyz=xyz, fvec=fvec, corr_add_neighbor_offset=True,
-                                                         corr_add_neighbor_xyz=False))
+        first = state["seq"] is None and state["win"] is None
+        if advance:
+            j = 0 if first else state["j"] + 1
+            blocks = [0, 1] if first else [(j + 1) % 4]
         else:
-            Ka, Ea = [t.to(dev, non_blocking=True) for t in host_cam]
-            win = ShardedWindow.build(fmd, dpd, Kd, Ed, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
+            j, blocks = 0, [0, 1]
+        t = j % len(host_cam)
+        fmd = torch.cat([host_fm[b].to(dev, non_blocking=True) for b in blocks], 1) if len(blocks) > 1 else host_fm[blocks[0]].to(dev, non_blocking=True)
+        dpd = torch.cat([host_dp[b].to(dev, non_blocking=True) for b in blocks], 1) if len(blocks) > 1 else host_dp[blocks[0]].to(dev, non_blocking=True)
+        Kl, El, Ka, Ea = [x.to(dev, non_blocking=True) for x in host_cam[t]]
+        if advance:
+            if first:
+                state["seq"] = (WindowSequence(V, Hs, Ws, C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN) if pw == 1 else
+                                ShardedSequence(V, v0, v1, Hs, Ws, C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN, mode=args.dist_mode))
+            win = state["seq"].push(fmd, dpd, Ka, Ea) if pw == 1 else state["seq"].push(fmd, dpd, Kl, El, Ka, Ea)
+        elif pw == 1:
+            win = WindowClouds.build(fmd, dpd, Ka, Ea, stride=STRIDE, k=K_NN)
+        else:
+            win = ShardedWindow.build(fmd, dpd, Kl, El, v0, V, stride=STRIDE, levels=range(LEVELS), k=K_NN, reuse=state["win"],
                                       intrs_all=Ka, extrs_all=Ea, mode=args.dist_mode)
-            state["win"] = win
+        state["win"], state["j"] = win, j
         for i in range(iters):
-            coords = host_ct[i][0].to(dev, non_blocking=True)
-            ffeats = host_ct[i][1].to(dev, non_blocking=True)
-            if pw == 1:
-                fcorrs = [blocks[l].corr_sample(ffeats, coords).reshape(S_WINDOW, N, -1) for l in range(LEVELS)]
-                host_out[i].copy_(torch.cat(fcorrs, dim=-1), non_blocking=True)
-            else:
-                host_out[i].copy_(win.corr(ffeats, coords), non_blocking=True)
+            coords = host_ct[t][i][0].to(dev, non_blocking=True)
+            ffeats = host_ct[t][i][1].to(dev, non_blocking=True)
+            res = win.corr(ffeats, coords)
+            if hi > lo:
+                host_out[i].copy_(res[:, lo:hi], non_blocking=True)
 
     def sync():
         torch.cuda.synchronize()
@@ -746,12 +837,13 @@ def run_e2e(args, w, world, rank, dev, fm, dp, K, E, coords_it, targets_it, v0, 
         dist.all_reduce(hb)
         h2d, d2h = int(hb[0].item()), int(hb[1].item())
     ms /= n
-    dropin.clear_caches()
+    state["seq"] = state["win"] = None
     queries = iters * LEVELS * S_WINDOW * N * (world if weak else 1)
     return {"value": queries / (ms * 1e-3), "unit": "queries/s", "ms_per_step": ms, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": n,
-            "api": ("mvtracker_b200.dropin (init_pointcloud_from_rgbd / PointcloudCorrBlock.corr_sample)" if pw == 1 else
-                    "mvtracker_b200.dist.ShardedWindow (build / corr)") + ", pinned host buffers, all ranks summed"}
+            "api": ("mvtracker_b200.hotpath." + ("WindowSequence.push" if advance else "WindowClouds.build") + " / .corr" if pw == 1 else
+                    "mvtracker_b200.dist." + ("ShardedSequence.push" if advance else "ShardedWindow.build") + " / .corr")
+                   + ", pinned host buffers, all ranks summed"}
 
 
 if __name__ == "__main__":

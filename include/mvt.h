@@ -90,11 +90,15 @@ int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *depths, cons
  * overlap, mvtracker.py:297-306 vs :549-555): fmaps / depths are frame runs of views that are fmaps_view_stride /
  * depths_view_stride ELEMENTS apart (e.g. frames 6..11 of a [V,12,C,H,W] tensor: pointer at frame 6, view stride 12*C*H*W),
  * the camera record of (view v, frame s) is cam + (v*cam_view_stride + s)*MVT_CAM_STRIDE, and the output pointers of
- * `levels` point at the first frame to write inside the caller's per-frame arrays.  0 strides = dense. */
+ * `levels` point at the first frame to write inside the caller's per-frame arrays.  0 strides = dense.
+ * records (optional, [MVT_MAX_LEVELS], see mvt_cloud_build_shared below): also store these views' 16-byte records into the
+ * replicated per-frame arrays of every rank, at views view_offset.. of V_total (pointers at the first frame to write). */
+struct mvt_peers;
 int mvt_cloud_build_frames(const void *fmaps, long long fmaps_view_stride, int feat_dtype, const float *depths,
                            long long depths_view_stride, const float *cam, int cam_view_stride,
                            int V, int S, int C, int H, int W, float stride, int depth_avg,
-                           const mvt_level_out *levels, int level_mask, void *stream);
+                           const mvt_level_out *levels, int level_mask, const struct mvt_peers *records, int view_offset,
+                           int V_total, void *stream);
 
 /* Hashed uniform grid over B independent clouds ("segments", one per frame) of N points each. */
 size_t mvt_grid_workspace_bytes(int B, int N);
@@ -303,6 +307,44 @@ int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B,
                              int n_shards, int shard, const int *idx, const void *targets, const float *coords,
                              const mvt_peers *out, long long out_row_stride, const float *const *all_xyz4,
                              const long long *n_all, void *stream);
+
+/* ---- one kernel per refinement iteration: search + exchange + correlation + exchange (csrc/mvt_shard.cu) ----------------------
+ * The compute-then-collective chain of the calls above (mvt_knn_idx_shared -> barrier -> mvt_corr_from_idx_shared ->
+ * barrier: four stages, every rank walking every query's list) as ONE persistent kernel per rank:
+ *   phase A  each rank searches ITS track shard over the replicated records; the search knows the owner of every neighbour
+ *            (index -> view -> rank) and pushes an 8-byte record {query, slot, owner-local index} straight into the OWNER's
+ *            inbox (peer store over NVLink); records are self-validating (top bit), no fence or counter per record;
+ *   phase B  a warp that runs out of searches turns to this rank's inboxes and, as records arrive, gathers the feature row it
+ *            owns, correlates it with the query's target row and stores the [corr, dx, dy, dz] record into the result block
+ *            of every rank (multicast store) -- the correlation of early queries overlaps the search tail of late ones;
+ *   end      the last block of a rank resets its counters, signals `epoch` to every peer and waits for theirs: when the
+ *            kernel has completed on a rank, that rank's result block is complete.
+ * No host-visible barrier, no NCCL, one launch.  Records are bit-identical to mvt_knn_corr's (same per-row arithmetic).
+ * C == 128, groups == 1, k <= 16 (a multiple of 4), add_offset = 1, add_xyz = 0. */
+typedef struct mvt_shard_level {
+    mvt_search search;        /* raster mode over the replicated records of ALL views at this level (+ tile tables) */
+    const float *xyz4_local;  /* [B, n_local, 4] records of the views this rank owns */
+    const void *fvec_local;   /* [B, n_local, C] feature rows of the views this rank owns */
+    long long n_local;        /* owned points per frame at this level */
+    int hw;                   /* H_l * W_l: points per view */
+} mvt_shard_level;
+
+typedef struct mvt_shard_ctx {
+    mvt_peers inbox;          /* symmetric: per rank [n_ranks][inbox_cap] 8-byte records, zeroed once by the caller */
+    mvt_peers ctrl;           /* symmetric: per rank 2*MVT_MAX_PEERS 8-byte words (totals, epochs), zeroed once */
+    mvt_peers result;         /* symmetric: per rank [B, M, n_levels*k*4] fp32; mc = its multicast address or NULL */
+    void *local;              /* this rank's private counters: mvt_shard_local_bytes() bytes, zeroed once */
+    long long inbox_cap;      /* records per (destination, source) pair: >= n_levels * B * ceil(M / n_ranks) * k */
+    int rank, n_ranks;
+    int view_first[MVT_MAX_PEERS + 1];   /* rank r owns views view_first[r] .. view_first[r+1]-1 (contiguous, ascending) */
+} mvt_shard_ctx;
+
+size_t mvt_shard_local_bytes(void);
+/* targets [B, M, C] and coords [B, M, 3]: ALL tracks (replicated inputs, as the replicated transformer holds them); rank r
+ * searches tracks r*Ms .. (r+1)*Ms-1, Ms = ceil(M / n_ranks).  epoch: a number that grows by one per call on every rank. */
+int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                   const void *targets, const float *coords, const mvt_shard_ctx *ctx, long long result_row_stride,
+                   unsigned long long epoch, void *stream);
 
 /* Debug / profiling: per-segment grid parameters copied out for inspection.
  * info [B,16] device fp32: ox,oy,oz,h,nx,ny,nz,n_valid,n_cells_used,table_slots,... */

@@ -16,7 +16,7 @@ SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build"
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
            "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
            "mvt_tile_depth_build", "mvt_track_input", "mvt_knn_corr_backward",
-           "mvt_cloud_build_backward", "mvt_lift_pixels")
+           "mvt_cloud_build_backward", "mvt_lift_pixels", "mvt_shard_iter", "mvt_shard_local_bytes")
 
 
 class LevelOut(C.Structure):
@@ -48,6 +48,16 @@ class Peers(C.Structure):
     _fields_ = [("mc", C.c_void_p), ("ptr", C.c_void_p * 8), ("n", C.c_int)]
 
 
+class ShardLevel(C.Structure):
+    _fields_ = [("search", Search), ("xyz4_local", C.c_void_p), ("fvec_local", C.c_void_p), ("n_local", C.c_longlong),
+                ("hw", C.c_int)]
+
+
+class ShardCtx(C.Structure):
+    _fields_ = [("inbox", Peers), ("ctrl", Peers), ("result", Peers), ("local", C.c_void_p), ("inbox_cap", C.c_longlong),
+                ("rank", C.c_int), ("n_ranks", C.c_int), ("view_first", C.c_int * 9)]
+
+
 class MvtError(RuntimeError):
     pass
 
@@ -76,7 +86,7 @@ def lib():
     L.mvt_launch_count.restype = C.c_ulonglong
     L.mvt_camera_prep.argtypes = [vp, vp, ci, vp, vp]
     L.mvt_cloud_build.argtypes = [vp, ci, vp, vp, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
-    L.mvt_cloud_build_frames.argtypes = [vp, ll, ci, vp, ll, vp, ci, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, vp]
+    L.mvt_cloud_build_frames.argtypes = [vp, ll, ci, vp, ll, vp, ci, ci, ci, ci, ci, ci, cf, ci, C.POINTER(LevelOut), ci, C.POINTER(Peers), ci, ci, vp]
     L.mvt_grid_workspace_bytes.argtypes = [ci, ci]
     L.mvt_grid_workspace_bytes.restype = C.c_size_t
     L.mvt_grid_build.argtypes = [C.POINTER(GridJob), ci, vp]
@@ -93,6 +103,9 @@ def lib():
     L.mvt_knn_idx_shared.argtypes = [C.POINTER(Search), ci, ci, vp, ci, ci, ci, ci, C.POINTER(Peers), vp]
     L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll,
                                            C.POINTER(vp), C.POINTER(ll), vp]
+    L.mvt_shard_iter.argtypes = [C.POINTER(ShardLevel), ci, ci, ci, ci, ci, ci, vp, vp, C.POINTER(ShardCtx), ll, C.c_ulonglong, vp]
+    L.mvt_shard_local_bytes.argtypes = []
+    L.mvt_shard_local_bytes.restype = C.c_size_t
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]
     L.mvt_tile_depth_floats.argtypes = [ci, ci, ci, ci]
@@ -105,7 +118,7 @@ def lib():
     for name in SYMBOLS:
         f = getattr(L, name)
         if name not in ("mvt_last_error", "mvt_grid_workspace_bytes", "mvt_launch_count", "mvt_tile_depth_floats",
-                        "mvt_knn_corr_workspace_bytes"):
+                        "mvt_knn_corr_workspace_bytes", "mvt_shard_local_bytes"):
             f.restype = ci
     _lib = L
     return L

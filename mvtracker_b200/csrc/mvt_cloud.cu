@@ -441,9 +441,11 @@ MVT_EXPORT int mvt_cloud_build(const void *fmaps, int feat_dtype, const float *d
 MVT_EXPORT int mvt_cloud_build_frames(const void *fmaps, long long fmaps_view_stride, int feat_dtype, const float *depths,
                                       long long depths_view_stride, const float *cam, int cam_view_stride,
                                       int V, int S, int C, int H, int W, float stride, int depth_avg,
-                                      const mvt_level_out *levels, int level_mask, void *stream) {
-    return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, nullptr, 0, V,
-                            stream, fmaps_view_stride, depths_view_stride, cam_view_stride);
+                                      const mvt_level_out *levels, int level_mask, const mvt_peers *records, int view_offset,
+                                      int V_total, void *stream) {
+    return cloud_build_impl(fmaps, feat_dtype, depths, cam, V, S, C, H, W, stride, depth_avg, levels, level_mask, records,
+                            records ? view_offset : 0, records ? V_total : V, stream, fmaps_view_stride, depths_view_stride,
+                            cam_view_stride);
 }
 
 MVT_EXPORT int mvt_cloud_build_shared(const void *fmaps, int feat_dtype, const float *depths, const float *cam,

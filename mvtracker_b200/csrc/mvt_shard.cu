@@ -18,6 +18,7 @@
 // (mvtracker_b200/dist.py drives this with torch.distributed / NCCL.)  Replaces, for N > 1, the single-GPU fused kernel
 // of mvt_knn.cu; same arithmetic, bit-identical neighbour sets and offsets, identical correlations.
 #include "mvt_search.cuh"
+#include "mvt_corr.cuh"
 
 namespace mvt {
 
@@ -295,6 +296,281 @@ __global__ void __launch_bounds__(256, MVT_CIDX_MINB) corr_from_idx_kernel(const
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// One kernel per refinement iteration: search -> records to the owners' inboxes -> correlation -> result records to all
+// ---------------------------------------------------------------------------------------------------------------
+struct ShardLocal {             // this rank's private counters (zero between launches)
+    unsigned work;              // phase A: next query of my shard
+    unsigned a_done, b_done;    // blocks that left phase A / phase B
+    unsigned err;               // set when a wait timed out (a peer never showed up): results are then invalid
+    unsigned tail[MVT_MAX_PEERS];     // records I have pushed to owner o
+    unsigned cursor[MVT_MAX_PEERS];   // next record of source s to take from my inbox
+};
+struct ShardLevelDev {
+    SearchDev sd;
+    const float4 *xyz4_local;
+    const void *fvec_local;
+    long long n_local;
+    int hw;
+};
+struct ShardParams {
+    ShardLevelDev lv[MVT_MAX_LEVELS];
+    int n_levels, B, M, Ms, k;
+    const void *targets;
+    const float *coords;
+    u64 *inbox[MVT_MAX_PEERS];        // every rank's inbox as mapped here ([n_ranks][cap] each)
+    u64 *ctrl[MVT_MAX_PEERS];         // every rank's control words: [0..7] total of source s (+1), [8..15] epoch of source s
+    PeersDev result;
+    ShardLocal *local;
+    long long cap, row_stride;
+    int rank, n;
+    int view_first[MVT_MAX_PEERS + 1];
+    u64 epoch;
+    float scale;
+    unsigned n_items;
+};
+constexpr u64 kRecValid = 1ull << 63;
+constexpr unsigned long long kShardTimeoutNs = 4000000000ull;
+
+__device__ __forceinline__ void st_sys(u64 *p, u64 v) { asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ void st_release_sys(u64 *p, u64 v) { asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ u64 ld_sys(const u64 *p) {
+    u64 v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ u64 ld_acquire_sys(const u64 *p) {
+    u64 v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned ld_volatile_u32(const unsigned *p) { return *reinterpret_cast<const volatile unsigned *>(p); }
+__device__ __forceinline__ unsigned long long now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Phase A, one query of my track shard by one warp: exact search over the replicated records, then one 8-byte record per
+// neighbour into the inbox of the rank that owns the neighbour's feature row:
+//   [63] valid | [62:58] slot j | [57:32] query id ((lvl * B + b) * M + m) | [31:0] index among the owner's points
+__device__ __forceinline__ void shard_search_item(const ShardParams &p, const unsigned char *win_tab, int lvl, int b, int mm) {
+    const int lane = threadIdx.x & 31;
+    const int m = p.rank * p.Ms + mm;
+    if (m >= p.M) return;                                 // padding of the last shard
+    const ShardLevelDev &L = p.lv[lvl];
+    const long long q = (long long)b * p.M + m;
+    const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+    const Group<32> g(lane);
+    TopK tk;
+    raster_search<32, true>(g, L.sd.rv, win_tab, b, true, qx, qy, qz, p.k, tk, L.sd.g.stats, (int)q);
+    const int idx = key_idx(tk.t);
+    const bool mine = lane < p.k;
+    const bool none = mine && idx == kNoIdx;
+    const unsigned qid = (unsigned)(((long long)lvl * p.B + b) * p.M + m);
+    if (none)       // fewer than k searchable points: nobody owns this record -- zeros, from here
+        store_all(p.result, (size_t)((q * p.row_stride + (long long)lvl * p.k * 4) >> 2) + lane, make_float4(0.f, 0.f, 0.f, 0.f));
+    int owner = 0x100 + lane;                              // lanes without a record: a group of their own
+    unsigned loc = 0u;
+    if (mine && !none) {
+        const int v = idx / L.hw;
+        owner = 0;
+#pragma unroll
+        for (int r = 1; r < MVT_MAX_PEERS; ++r)
+            if (r < p.n && v >= p.view_first[r]) owner = r;
+        loc = (unsigned)(idx - p.view_first[owner] * L.hw);
+    }
+    const unsigned grp = __match_any_sync(FULL, owner);
+    const bool has = mine && !none;
+    const int leader = __ffs(grp) - 1;
+    unsigned base = 0u;
+    if (has && lane == leader) base = atomicAdd(&p.local->tail[owner], (unsigned)__popc(grp));
+    base = __shfl_sync(FULL, base, leader);                // every lane reads its own group's leader
+    if (has) {
+        const unsigned slot = base + (unsigned)__popc(grp & ((1u << lane) - 1u));
+        const u64 rec = kRecValid | ((u64)lane << 58) | ((u64)qid << 32) | (u64)loc;
+        st_sys(p.inbox[owner] + (size_t)p.rank * p.cap + slot, rec);
+    }
+}
+
+
+// Phase B, one batch of 32 consecutive records of source `src` (lane i holds record i, 0 = none) by one warp: the feature
+// rows named by the records are gathered sixteen at a time, correlated with their queries' target rows (per-row arithmetic
+// and lane order of the fused single-GPU kernel), and each lane stores its record's [corr, dx, dy, dz] to every rank.
+template <bool BF16>
+__device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64 rec) {
+    const int lane = threadIdx.x & 31;
+    const unsigned valid = __ballot_sync(FULL, (rec & kRecValid) != 0ull);
+    if (valid == 0u) return;
+    const unsigned BM = (unsigned)p.B * (unsigned)p.M;
+    float corr_mine = 0.f;
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r) {
+        if (((valid >> (16 * r)) & 0xffffu) == 0u) continue;            // (uniform)
+        float tot;
+        if (!BF16) {
+            float pr[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const u64 rj = __shfl_sync(FULL, rec, 16 * r + j);
+                pr[j] = 0.f;
+                if (rj & kRecValid) {                                     // (uniform)
+                    const unsigned qid = (unsigned)(rj >> 32) & 0x3ffffffu, li = (unsigned)rj;
+                    const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+                    const ShardLevelDev &L = p.lv[lvl];
+                    const float4 f = __ldg(reinterpret_cast<const float4 *>(L.fvec_local) + ((size_t)b * L.n_local + li) * 32 + lane);
+                    const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + (size_t)bm * 32 + lane);
+                    pr[j] = dot4(tg, f);
+                }
+            }
+            tot = transpose_reduce16(pr, lane);                           // lane L: total of record L >> 1 of this round
+            tot = __shfl_sync(FULL, tot, (2 * lane) & 31);                // lane l: total of record l & 15
+        } else {
+            const int half = lane >> 4;
+            float pr[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const u64 rj = __shfl_sync(FULL, rec, 16 * r + 2 * i + half);
+                pr[i] = 0.f;
+                if (rj & kRecValid) {
+                    const unsigned qid = (unsigned)(rj >> 32) & 0x3ffffffu, li = (unsigned)rj;
+                    const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+                    const ShardLevelDev &L = p.lv[lvl];
+                    const uint4 f = __ldg(reinterpret_cast<const uint4 *>(L.fvec_local) + ((size_t)b * L.n_local + li) * 16 + (lane & 15));
+                    const uint4 tg = __ldg(reinterpret_cast<const uint4 *>(p.targets) + (size_t)bm * 16 + (lane & 15));
+                    pr[i] = dot8_bf16(tg, f);
+                }
+            }
+            tot = transpose_reduce8_half(pr, lane);
+            // record j of the round lives in half (j & 1), lanes 2 * (j >> 1) (+1) of that half
+            tot = __shfl_sync(FULL, tot, ((lane & 1) << 4) | (((lane & 15) >> 1) << 1));
+        }
+        if ((lane >> 4) == r) corr_mine = tot;
+    }
+    if (rec & kRecValid) {
+        const unsigned qid = (unsigned)(rec >> 32) & 0x3ffffffu, li = (unsigned)rec, j = (unsigned)(rec >> 58) & 31u;
+        const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+        const ShardLevelDev &L = p.lv[lvl];
+        const float4 n = __ldg(L.xyz4_local + (size_t)b * L.n_local + li);
+        const float qx = __ldg(p.coords + (size_t)bm * 3), qy = __ldg(p.coords + (size_t)bm * 3 + 1), qz = __ldg(p.coords + (size_t)bm * 3 + 2);
+        store_all(p.result, (size_t)(((long long)bm * p.row_stride + (long long)lvl * p.k * 4) >> 2) + j,
+                  make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz));
+    }
+}
+
+// Phase B driver of one warp: takes batches from this rank's inboxes until every source has delivered its total and all of
+// it has been taken.  Returns false on a timeout.
+template <bool BF16>
+__device__ __forceinline__ bool shard_consume(const ShardParams &p, const int start) {
+    const int lane = threadIdx.x & 31;
+    u64 *inbox = p.inbox[p.rank];
+    const u64 *total = p.ctrl[p.rank];
+    unsigned exhausted = 0u;
+    const unsigned all = (1u << p.n) - 1u;
+    int src = start % p.n, idle = 0;
+    unsigned long long t_last = now_ns();                                 // last time this warp got a batch
+    while (exhausted != all) {
+        bool took = false;
+        if (!((exhausted >> src) & 1u)) {
+            const unsigned c = ld_volatile_u32(&p.local->cursor[src]);
+            const u64 tot = ld_sys(total + src);                          // records of this source + 1, 0 = not known yet
+            if (tot != 0ull && (u64)c + 1ull >= tot) {
+                exhausted |= 1u << src;
+            } else if ((long long)c < p.cap && (ld_sys(inbox + (size_t)src * p.cap + c) & kRecValid)) {
+                unsigned i0 = 0u;
+                if (lane == 0) i0 = atomicAdd(&p.local->cursor[src], 32u);
+                i0 = __shfl_sync(FULL, i0, 0);
+                const long long pos = (long long)i0 + lane;
+                u64 rec = 0ull;
+                if (pos < p.cap) {
+                    u64 *slot = inbox + (size_t)src * p.cap + pos;
+                    const unsigned long long t0 = now_ns();
+                    for (;;) {
+                        rec = ld_sys(slot);
+                        if (rec & kRecValid) break;
+                        const u64 tt = ld_sys(total + src);
+                        if (tt != 0ull && (u64)pos + 1ull >= tt) { rec = 0ull; break; }      // beyond the source's last record
+                        __nanosleep(64);
+                        if (now_ns() - t0 > kShardTimeoutNs) { p.local->err = 1u; rec = 0ull; break; }
+                    }
+                    if (rec & kRecValid) *slot = 0ull;                    // the inbox is empty again for the next launch
+                }
+                shard_corr_batch<BF16>(p, rec);
+                took = true;
+            }
+        }
+        if (took) { idle = 0; t_last = now_ns(); continue; }
+        src = (src + 1 == p.n) ? 0 : src + 1;
+        if (++idle > p.n) {                                               // a whole round without work: back off
+            __nanosleep(128);
+            if (now_ns() - t_last > kShardTimeoutNs || ld_volatile_u32(&p.local->err)) { p.local->err = 1u; return false; }
+        }
+    }
+    return true;
+}
+
+
+#ifndef MVT_SHARD_THREADS
+#define MVT_SHARD_THREADS 256
+#endif
+#ifndef MVT_SHARD_MINB
+#define MVT_SHARD_MINB 4
+#endif
+// One wave of blocks (all resident: a block never waits for a block that is not running).  Every warp first draws searches
+// of this rank's track shard (phase A), then consumes this rank's inboxes (phase B); the last block out runs the epilogue.
+template <bool BF16>
+__global__ void __launch_bounds__(MVT_SHARD_THREADS, MVT_SHARD_MINB) shard_iter_kernel(const ShardParams p) {
+    __shared__ unsigned warps_a, warps_b;
+    if (threadIdx.x == 0) { warps_a = 0u; warps_b = 0u; }
+    MVT_WARP_SCRATCH(win_tab, MVT_SHARD_THREADS / 32);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    ShardLocal *loc = p.local;
+    const unsigned per_level = (unsigned)p.B * (unsigned)p.Ms;
+
+    // ---- phase A: the searches of my track shard, level-major (one level's records stay hot in L2) ----
+    for (;;) {
+        unsigned item = 0u;
+        if (lane == 0) item = atomicAdd(&loc->work, 1u);
+        item = __shfl_sync(FULL, item, 0);
+        if (item >= p.n_items) break;
+        const unsigned lvl = item / per_level, rem = item - lvl * per_level;
+        const unsigned b = rem / (unsigned)p.Ms, mm = rem - b * (unsigned)p.Ms;
+        shard_search_item(p, win_tab, (int)lvl, (int)b, (int)mm);
+    }
+    // the last warp of the last block to leave phase A knows every count: tell each owner how many records to expect
+    __threadfence();
+    if (lane == 0) {
+        if (atomicAdd(&warps_a, 1u) == (unsigned)nwarps - 1u && atomicAdd(&loc->a_done, 1u) == gridDim.x - 1u) {
+            __threadfence();
+            for (int o = 0; o < p.n; ++o) st_sys(p.ctrl[o] + p.rank, (u64)atomicAdd(&loc->tail[o], 0u) + 1ull);
+        }
+    }
+    __syncwarp();
+
+    // ---- phase B: correlate what arrives in my inboxes ----
+    shard_consume<BF16>(p, p.rank + 1 + (int)(blockIdx.x * nwarps + (threadIdx.x >> 5)));
+
+    // ---- end: the last block out resets this rank's state, signals the epoch and waits for every peer's ----
+    __threadfence_system();            // this warp's result stores are performed before its block counts as done
+    if (lane == 0 && atomicAdd(&warps_b, 1u) == (unsigned)nwarps - 1u && atomicAdd(&loc->b_done, 1u) == gridDim.x - 1u) {
+        __threadfence_system();
+        loc->work = 0u; loc->a_done = 0u; loc->b_done = 0u;
+        for (int r = 0; r < MVT_MAX_PEERS; ++r) { loc->tail[r] = 0u; loc->cursor[r] = 0u; }
+        u64 *mine = p.ctrl[p.rank];
+        for (int r = 0; r < p.n; ++r) mine[r] = 0ull;                     // next launch's totals start unknown
+        __threadfence_system();
+        for (int r = 0; r < p.n; ++r) st_release_sys(p.ctrl[r] + MVT_MAX_PEERS + p.rank, p.epoch);
+        const unsigned long long t0 = now_ns();
+        for (int r = 0; r < p.n; ++r)
+            while (ld_acquire_sys(mine + MVT_MAX_PEERS + r) < p.epoch) {
+                __nanosleep(64);
+                if (now_ns() - t0 > kShardTimeoutNs) { loc->err = 1u; break; }
+            }
+    }
+}
+
 }  // namespace mvt
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -431,5 +707,78 @@ MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int 
     const unsigned grid = one_wave_grid(n_items, MVT_KEYS_THREADS / 32, MVT_KEYS_MINB);
     knn_keys_kernel<true><<<grid, MVT_KEYS_THREADS, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("knn_idx_shared");
+    return MVT_OK;
+}
+
+MVT_EXPORT size_t mvt_shard_local_bytes(void) { return sizeof(mvt::ShardLocal); }
+
+MVT_EXPORT int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
+                              const void *targets, const float *coords, const mvt_shard_ctx *ctx, long long result_row_stride,
+                              unsigned long long epoch, void *stream) {
+    using namespace mvt;
+    MVT_CHECK_ARG(levels && targets && coords && ctx && ctx->local, "mvt_shard_iter: null pointer");
+    MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_shard_iter: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
+    MVT_CHECK_ARG(B > 0 && B <= 65535 && M > 0, "mvt_shard_iter: bad shape B=%d M=%d", B, M);
+    MVT_CHECK_ARG(C == 128, "mvt_shard_iter: the sharded path supports C == 128, groups == 1 (got C=%d)", C);
+    MVT_CHECK_ARG(k >= 4 && k <= 16 && k % 4 == 0, "mvt_shard_iter: k must be 4, 8, 12 or 16 (got %d)", k);
+    MVT_CHECK_ARG(feat_dtype == MVT_F32 || feat_dtype == MVT_BF16, "mvt_shard_iter: feat_dtype %d", feat_dtype);
+    MVT_CHECK_ARG(ctx->n_ranks >= 1 && ctx->n_ranks <= MVT_MAX_PEERS && ctx->rank >= 0 && ctx->rank < ctx->n_ranks,
+                  "mvt_shard_iter: rank %d of %d", ctx->rank, ctx->n_ranks);
+    MVT_CHECK_ARG(ctx->inbox.n == ctx->n_ranks && ctx->ctrl.n == ctx->n_ranks && ctx->result.n == ctx->n_ranks,
+                  "mvt_shard_iter: the symmetric buffers must name all %d ranks", ctx->n_ranks);
+    MVT_CHECK_ARG((long long)n_levels * B * M < (1ll << 26), "mvt_shard_iter: too many queries for the record format (%lld)",
+                  (long long)n_levels * B * M);
+    MVT_CHECK_ARG(epoch > 0 && result_row_stride % 4 == 0 && (((uintptr_t)targets) & 15) == 0, "mvt_shard_iter: epoch / alignment");
+    ShardParams p;
+    p.n_levels = n_levels; p.B = B; p.M = M; p.k = k;
+    p.n = ctx->n_ranks; p.rank = ctx->rank;
+    p.Ms = (M + p.n - 1) / p.n;
+    p.targets = targets; p.coords = coords;
+    p.local = (ShardLocal *)ctx->local;
+    p.cap = ctx->inbox_cap; p.row_stride = result_row_stride;
+    p.epoch = epoch; p.scale = sqrtf((float)C);
+    MVT_CHECK_ARG(p.cap >= (long long)n_levels * B * p.Ms * k && p.cap < (1ll << 31), "mvt_shard_iter: inbox_cap %lld too small", p.cap);
+    for (int r = 0; r < MVT_MAX_PEERS; ++r) {
+        p.inbox[r] = r < p.n ? (u64 *)ctx->inbox.ptr[r] : nullptr;
+        p.ctrl[r] = r < p.n ? (u64 *)ctx->ctrl.ptr[r] : nullptr;
+        MVT_CHECK_ARG(r >= p.n || (p.inbox[r] && p.ctrl[r] && ctx->result.ptr[r]), "mvt_shard_iter: rank %d: null peer mapping", r);
+    }
+    p.result = peers_dev(&ctx->result);
+    for (int r = 0; r <= MVT_MAX_PEERS; ++r) p.view_first[r] = ctx->view_first[r <= p.n ? r : p.n];
+    MVT_CHECK_ARG(p.view_first[0] == 0, "mvt_shard_iter: view_first[0] must be 0");
+    for (int r = 0; r < p.n; ++r) MVT_CHECK_ARG(p.view_first[r + 1] >= p.view_first[r], "mvt_shard_iter: view_first must ascend");
+    for (int l = 0; l < n_levels; ++l) {
+        const mvt_shard_level &u = levels[l];
+        int rc = make_search(&u.search, B, 0, p.lv[l].sd, "mvt_shard_iter");
+        if (rc) return rc;
+        MVT_CHECK_ARG(p.lv[l].sd.raster, "mvt_shard_iter: needs the raster search");
+        MVT_CHECK_ARG(u.hw == u.search.H * u.search.W && p.view_first[p.n] == u.search.V, "mvt_shard_iter: level %d: views / raster mismatch", l);
+        const long long nloc = (long long)(p.view_first[p.rank + 1] - p.view_first[p.rank]) * u.hw;
+        MVT_CHECK_ARG(u.n_local == nloc && (nloc == 0 || (u.xyz4_local && u.fvec_local)), "mvt_shard_iter: level %d: n_local %lld != %lld", l, u.n_local, nloc);
+        MVT_CHECK_ARG((((uintptr_t)u.xyz4_local | (uintptr_t)u.fvec_local) & 15) == 0, "mvt_shard_iter: level %d: 16-byte alignment", l);
+        p.lv[l].xyz4_local = (const float4 *)u.xyz4_local; p.lv[l].fvec_local = u.fvec_local; p.lv[l].n_local = u.n_local; p.lv[l].hw = u.hw;
+    }
+    for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
+    const long long n_items = (long long)n_levels * B * p.Ms;
+    p.n_items = (unsigned)n_items;
+    // all blocks must be resident (phase B waits for phase A of blocks of the same grid): a cooperative launch of one wave
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const void *fn = feat_dtype == MVT_BF16 ? (const void *)shard_iter_kernel<true> : (const void *)shard_iter_kernel<false>;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, MVT_SHARD_THREADS, 0) != cudaSuccess || per_sm < 1 || sms < 1) {
+        set_error("mvt_shard_iter: occupancy query failed");
+        return MVT_E_CUDA;
+    }
+    long long need = (n_items + MVT_SHARD_THREADS / 32 - 1) / (MVT_SHARD_THREADS / 32);
+    long long wave = (long long)sms * per_sm;
+    const unsigned grid = (unsigned)(need < wave ? (need > 0 ? need : 1) : wave);
+    void *args[] = {(void *)&p};
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(MVT_SHARD_THREADS), args, 0, (cudaStream_t)stream);
+    if (e != cudaSuccess) {
+        set_error("mvt_shard_iter: cooperative launch failed: %s", cudaGetErrorString(e));
+        return MVT_E_CUDA;
+    }
+    MVT_CHECK_LAUNCH("shard_iter");
     return MVT_OK;
 }

@@ -122,14 +122,16 @@ class ShardedWindow:
         if mode is None:
             mode = "tracks" if intrs_all is not None else "views"
         world = dist.get_world_size(group) if dist.is_initialized() else 1
-        if mode == "p2p" and (world == 1 or V_total < world or not symmetric_memory_available()):
+        if mode in ("p2p", "fused") and (world == 1 or V_total < world or not symmetric_memory_available()):
             mode = "tracks"         # needs >= 2 ranks, a view on every rank and symmetric memory
         Vloc = fmaps_local.shape[0]
         levels = list(levels)
         clouds = []
-        if mode == "p2p":
-            return cls._build_p2p(fmaps_local, depths_local, intrs_local, extrs_local, v0, V_total, stride, levels, k, group,
-                                  backend, reuse, intrs_all, extrs_all)
+        if mode in ("p2p", "fused"):
+            win = cls._build_p2p(fmaps_local, depths_local, intrs_local, extrs_local, v0, V_total, stride, levels, k, group,
+                                 backend, reuse, intrs_all, extrs_all)
+            win.mode = mode
+            return win
         if Vloc > 0:
             clouds = backend.cloud_build(fmaps_local, depths_local, intrs_local, extrs_local, stride=stride, levels=levels,
                                          want_spacing=False, reuse=None if reuse is None else reuse.clouds)
@@ -157,7 +159,7 @@ class ShardedWindow:
         # fills in the offsets from its replica (a quarter of the bytes -- measured equal at 8 GPUs, 3% slower at 2: the
         # exchange is bound by the number of small stores, not by their size)
         win.split_records = bool(os.environ.get("MVT_SPLIT_RECORDS"))
-        if reuse is not None and reuse.mode == "p2p":
+        if reuse is not None and reuse.mode in ("p2p", "fused"):
             win._bufs = reuse._bufs
         shared = {}
         for l in levels:
@@ -252,6 +254,8 @@ class ShardedWindow:
             return self._corr_tracks(targets, coords, out, mark)
         if self.mode == "p2p":
             return self._corr_p2p(targets, coords, out, mark)
+        if self.mode == "fused":
+            return self._corr_fused(targets, coords, out, mark)
         keys = self._buf("keys", (N, L, S, Ms, k), torch.int64, dev)
         recv = self._buf("recv", (N, L, S, Ms, k), torch.int64, dev) if N > 1 else keys
         offs = [self.v0 * c.H * c.W for c in self.clouds]
@@ -370,3 +374,115 @@ class ShardedWindow:
             out.copy_(res.t)
             return out
         return res.t
+
+    def _corr_fused(self, targets, coords, out, mark):
+        """mode "fused": ONE persistent kernel per rank and iteration (mvt_shard_iter): it searches this rank's track shard,
+        pushes one 8-byte record per neighbour into the inbox of the rank that owns the neighbour's features, correlates the
+        records arriving in its own inbox and stores the results into every rank's block; the kernel ends with a cross-rank
+        epoch exchange, so there is no barrier launch and no list walk (mvtracker_b200/csrc/mvt_shard.cu)."""
+        be, N, k, L = self.be, self.world, self.k, self.levels
+        S, M, _ = targets.shape
+        dev = targets.device
+        st = self._bufs.get("shard_state")
+        Ms = track_shard(N, M)
+        cap = L * S * Ms * k
+        if st is None or st.cap != cap or st.results[0][0].shape != (S, M, L * k * 4):
+            inbox = self._shared("inbox", (N, cap), torch.int64, dev)
+            ctrl = self._shared("ctrl", (16,), torch.int64, dev)
+            res = [self._shared(f"out{i}", (S, M, L * k * 4), torch.float32, dev) for i in range(2)]
+            inbox.t.zero_(); ctrl.t.zero_()
+            torch.cuda.current_stream().synchronize()
+            inbox.barrier()
+            spans = [view_range(r, N, self.V_total) for r in range(N)]
+            st = be.ShardState(self.rank, N, [a for a, _ in spans] + [self.V_total], (inbox.t, inbox.peers), (ctrl.t, ctrl.peers),
+                               [(r.t, r.peers) for r in res], cap, dev)
+            self._bufs["shard_state"] = st
+        res = be.shard_iter(self.full, self.clouds, targets, coords, k, st)
+        mark()
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+
+
+def _offset_peers(peers, nbytes: int):
+    """The same symmetric buffer, every mapping (and the multicast address) advanced by nbytes."""
+    from ._lib import Peers
+    q = Peers()
+    q.n = peers.n
+    q.mc = (peers.mc + nbytes) if peers.mc else None
+    for r in range(peers.n):
+        q.ptr[r] = peers.ptr[r] + nbytes
+    return q
+
+
+class ShardedSequence:
+    """Sliding windows of ONE sequence across ranks with the per-frame cloud cache (the multi-GPU WindowSequence): rank r
+    keeps the clouds of ITS views in a local CloudArena and every rank keeps the replicated 16-byte search records of ALL
+    views in a symmetric-memory arena of the same slots.  push() builds only the frames a window adds -- the producing
+    kernel stores their records into every rank's arena (multicast) -- and returns a ShardedWindow over the current run."""
+
+    def __init__(self, V_total: int, v0: int, v1: int, H: int, W: int, C: int, dtype, device, S: int = 12, hop: Optional[int] = None,
+                 stride=4, levels: Sequence[int] = (0, 1, 2, 3), k=16, slots: Optional[int] = None, group=None, backend=None,
+                 mode: str = "fused"):
+        if backend is None:
+            from . import ops as backend
+        self.be, self.group, self.mode = backend, group, mode
+        self.V, self.v0, self.v1, self.H, self.W = V_total, v0, v1, H, W
+        self.S, self.hop, self.stride, self.levels, self.k = int(S), int(hop or S // 2), float(stride), list(levels), k
+        if slots is None:
+            per = backend.CloudArena.bytes_per_frame(v1 - v0, H, W, C, torch.empty(0, dtype=dtype).element_size(), levels) \
+                + sum(V_total * (H >> l) * (W >> l) * 16 for l in levels)
+            slots = int(max(self.S + self.hop, min(4 * self.S, (torch.cuda.mem_get_info(device)[0] // 3) // max(per, 1))))
+            t = torch.tensor([slots], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)      # the symmetric arenas must have one size
+            slots = int(t.item())
+        self.slots = slots
+        self.arena = backend.CloudArena(v1 - v0, H, W, C, dtype, device, levels, slots, stride, want_valid=False)
+        self.rec = {l: SharedBuffer((slots, V_total * (H >> l) * (W >> l), 4), torch.float32, device, group) for l in levels}
+        self.tiles = {l: torch.empty(slots, V_total, ((H >> l) + 7) // 8, ((W >> l) + 7) // 8, 2, device=device) for l in levels}
+        self.win = ShardedWindow([], v0, v1, V_total, k, group, backend, n_levels=len(self.levels))
+        self.win.mode = mode
+        self.slot0 = None
+        self.frames_built = 0
+
+    def push(self, fmaps_new, depths_new, intrs_local, extrs_local, intrs_all, extrs_all) -> "ShardedWindow":
+        """fmaps_new [Vloc, n, C, H, W] / depths_new [Vloc, n, H, W]: the frames this window adds, THIS rank's views (all S of the
+        first window, `hop` afterwards); intrs / extrs _local [Vloc, S, ...] and _all [V, S, ...]: cameras of the whole window."""
+        be, S, hop, ar = self.be, self.S, self.hop, self.arena
+        n = fmaps_new.shape[1]
+        any_rec = self.rec[self.levels[0]]
+        any_rec.barrier()                       # every rank has finished reading the window that is about to change
+        if self.slot0 is None:
+            assert n == S, f"the first window needs all {S} frames"
+            self.slot0, first_new = 0, 0
+        else:
+            assert n == hop, f"a later window adds {hop} frames"
+            self.slot0 += hop
+            if self.slot0 + S > self.slots:
+                ar.move(self.slot0, 0, S - hop)
+                for l in self.levels:           # (each rank moves its own replica; nobody writes it before the barrier below)
+                    self.rec[l].t[0:S - hop].copy_(self.rec[l].t[self.slot0:self.slot0 + S - hop])
+                    self.tiles[l][0:S - hop].copy_(self.tiles[l][self.slot0:self.slot0 + S - hop])
+                self.slot0 = 0
+                any_rec.barrier()
+            first_new = S - hop
+        s_new = self.slot0 + first_new
+        cam_loc = be.camera_prep(intrs_local, extrs_local)
+        cam_run = cam_loc.reshape(-1)[first_new * cam_loc.shape[1]:]
+        tgt = ar.run(s_new, n, cam_run, tiles_ready=False)
+        shared = {l: _offset_peers(self.rec[l].peers, s_new * self.rec[l].t[0].numel() * 4) for l in self.levels}
+        be.cloud_build(fmaps_new, depths_new, None, None, stride=self.stride, levels=self.levels, want_spacing=False, cam=cam_run,
+                       reuse=tgt, shared_records=shared, view_offset=self.v0, V_total=self.V, cam_view_stride=S)
+        any_rec.barrier()                       # every rank's records of the new frames have arrived everywhere
+        cam_all = be.camera_prep(intrs_all, extrs_all)
+        # tile tables of the new frames of the replicated records (every rank, its own replica)
+        new_full = [be.Cloud(l, None, None, None, None, self.rec[l].t[s_new:s_new + n], cam_all.reshape(-1)[first_new * cam_all.shape[1]:],
+                             self.V, self.H >> l, self.W >> l, self.stride * (1 << l), self.tiles[l][s_new:s_new + n]) for l in self.levels]
+        be.tile_depth_build(new_full, cam_view_stride=S)
+        sl = slice(self.slot0, self.slot0 + S)
+        self.win.clouds = ar.run(self.slot0, S, cam_loc)
+        self.win.full = [be.Cloud(l, None, None, None, None, self.rec[l].t[sl], cam_all, self.V, self.H >> l, self.W >> l,
+                                  self.stride * (1 << l), self.tiles[l][sl], True) for l in self.levels]
+        self.frames_built += n
+        return self.win

@@ -174,22 +174,23 @@ def cloud_build(fmaps, depths, intrs, extrs, stride=4, levels: Sequence[int] = (
         clouds.append(Cloud(l, xyz, fvec, valid.view(torch.bool) if want_valid else None, spacing, xyz4, cam, V, Hl, Wl,
                             float(stride) * (1 << l), old.tile_z if reuse is not None else None, False, neg))
     dense = fm_vs == S * Cc * H * W and dp_vs == S * H * W and not cam_view_stride
-    if shared_records is None and dense:
-        check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
-                                    int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
-    elif shared_records is None:
-        check(lib().mvt_cloud_build_frames(_ptr(fm), int(fm_vs), _feat_dtype(fm), _ptr(dp), int(dp_vs), _ptr(cam),
-                                           int(cam_view_stride), V, S, Cc, H, W, float(stride), int(depth_interp_mode == "avg"),
-                                           outs, mask, _stream()), "mvt_cloud_build_frames")
-    else:
-        if not dense:
-            fm, dp = fm.contiguous(), dp.contiguous()
+    recs = None
+    if shared_records is not None:
         recs = (_lib.Peers * _lib.MAX_LEVELS)()
         for l in levels:
             recs[l] = shared_records[l]
+    if recs is None and dense:
+        check(lib().mvt_cloud_build(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
+                                    int(depth_interp_mode == "avg"), outs, mask, _stream()), "mvt_cloud_build")
+    elif dense:
         check(lib().mvt_cloud_build_shared(_ptr(fm), _feat_dtype(fm), _ptr(dp), _ptr(cam), V, S, Cc, H, W, float(stride),
                                            int(depth_interp_mode == "avg"), outs, mask, recs, int(view_offset),
                                            int(V if V_total is None else V_total), _stream()), "mvt_cloud_build_shared")
+    else:
+        check(lib().mvt_cloud_build_frames(_ptr(fm), int(fm_vs), _feat_dtype(fm), _ptr(dp), int(dp_vs), _ptr(cam),
+                                           int(cam_view_stride), V, S, Cc, H, W, float(stride), int(depth_interp_mode == "avg"),
+                                           outs, mask, recs, int(view_offset), int(V if V_total is None else V_total), _stream()),
+              "mvt_cloud_build_frames")
     if want_tiles and want_xyz4:
         tile_depth_build(clouds, cam_view_stride=cam_view_stride)
     return clouds
@@ -398,8 +399,11 @@ class _HardQueryPolicy:
         self.deferring = True    # a sequence starts with static tracks
         self.pinned = torch.zeros(1, dtype=torch.int32).pin_memory()
         self.event, self.queries, self.last_fraction = None, 0, None
+        self.calls = 0
 
     def mode(self) -> int:
+        if torch.cuda.is_current_stream_capturing():     # a captured launch keeps the mode it was captured with
+            return 1 if self.deferring else 2
         if self.event is not None and self.event.query():
             self.last_fraction = float(self.pinned[0]) / max(1, self.queries)
             self.event = None
@@ -410,7 +414,9 @@ class _HardQueryPolicy:
         return 1 if self.deferring else 2
 
     def record(self, ws: torch.Tensor, queries: int):
-        if self.event is None and not torch.cuda.is_current_stream_capturing():
+        self.calls += 1
+        # (a sample every few launches: the 4-byte copy costs a few microseconds of stream time)
+        if self.event is None and (self.calls & 3) == 1 and not torch.cuda.is_current_stream_capturing():
             self.pinned.copy_(ws[:4].view(torch.int32), non_blocking=True)
             self.queries = queries
             self.event = torch.cuda.Event()
@@ -706,3 +712,70 @@ def corr_from_idx_shared(owned: Sequence, idx: torch.Tensor, targets: torch.Tens
     check(lib().mvt_corr_from_idx_shared(lv, L, B, M, Cc, _feat_dtype(tg), int(k), int(idx.shape[0]), int(shard), _ptr(idx),
                                          _ptr(tg), _ptr(cq), C.byref(peers), int(row_stride), rp, na, _stream()),
           "mvt_corr_from_idx_shared")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# one kernel per refinement iteration across ranks (mvt_shard_iter)
+# ---------------------------------------------------------------------------------------------------------------------
+def plain_peers(t: torch.Tensor) -> "_lib.Peers":
+    """A one-rank mvt_peers over an ordinary tensor (no multicast): what a single process passes where the multi-GPU
+    path passes symmetric buffers."""
+    p = _lib.Peers()
+    p.n, p.mc = 1, None
+    p.ptr[0] = t.data_ptr()
+    return p
+
+
+class ShardState:
+    """The buffers of mvt_shard_iter for one rank: inbox [n_ranks, cap] int64, ctrl [16] int64, two alternating result
+    blocks [B, M, L*k*4] fp32 (each given as (tensor, peers)), private counters, the epoch.  mvtracker_b200.dist allocates the
+    first three in symmetric memory; with n_ranks == 1 plain tensors do (tests, single-GPU use)."""
+
+    def __init__(self, rank: int, n_ranks: int, view_first: Sequence[int], inbox, ctrl, results, cap: int, device):
+        self.rank, self.n, self.view_first = int(rank), int(n_ranks), [int(v) for v in view_first]
+        self.inbox, self.ctrl, self.results, self.cap = inbox, ctrl, results, int(cap)
+        self.local = torch.zeros(int(lib().mvt_shard_local_bytes()), device=device, dtype=torch.uint8)
+        self.epoch, self.flip = 0, 1
+
+    @classmethod
+    def single(cls, V: int, n_levels: int, B: int, M: int, k: int, device) -> "ShardState":
+        cap = n_levels * B * M * k
+        inbox = torch.zeros(1, cap, device=device, dtype=torch.int64)
+        ctrl = torch.zeros(2 * _lib.Peers.ptr.size // C.sizeof(C.c_void_p), device=device, dtype=torch.int64)
+        res = [torch.empty(B, M, n_levels * k * 4, device=device, dtype=torch.float32) for _ in range(2)]
+        return cls(0, 1, [0, V], (inbox, plain_peers(inbox)), (ctrl, plain_peers(ctrl)), [(r, plain_peers(r)) for r in res], cap, device)
+
+    def error(self) -> bool:
+        """A wait inside the kernel timed out (a peer never arrived): the last results are invalid."""
+        return bool(self.local[12:16].view(torch.int32).item())
+
+
+def shard_iter(full: Sequence[Cloud], local: Sequence[Cloud], targets: torch.Tensor, coords: torch.Tensor, k: int,
+               st: ShardState) -> torch.Tensor:
+    """One refinement iteration's correlation block across ranks in ONE kernel launch per rank (mvt_shard_iter).
+    full: per level, the search-only Cloud over the replicated records of all views (tile tables built);
+    local: per level, this rank's Cloud (xyz4 + fvec of its views); targets [B,M,C] / coords [B,M,3]: all tracks.
+    -> the result block [B, M, L*k*4] of this rank (complete when the kernel has finished; alternates between two buffers)."""
+    _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
+    B, M, Cc = targets.shape
+    tg, cq = targets.contiguous(), _f32c(coords)
+    L = len(full)
+    lv = (_lib.ShardLevel * L)()
+    keep = []
+    for i, (f, c) in enumerate(zip(full, local)):
+        sr = Search.from_cloud(f, tiles=True)
+        keep.append(sr)
+        if c.fvec.dtype != tg.dtype:
+            raise MvtError(f"targets dtype {tg.dtype} != fvec dtype {c.fvec.dtype}")
+        lv[i] = _lib.ShardLevel(sr.c, c.xyz4.data_ptr(), c.fvec.data_ptr(), c.xyz4.shape[1], f.H * f.W)
+    st.flip = 1 - st.flip
+    st.epoch += 1
+    res, res_peers = st.results[st.flip]
+    ctx = _lib.ShardCtx()
+    ctx.inbox, ctx.ctrl, ctx.result = st.inbox[1], st.ctrl[1], res_peers
+    ctx.local, ctx.inbox_cap, ctx.rank, ctx.n_ranks = st.local.data_ptr(), st.cap, st.rank, st.n
+    for r in range(9):
+        ctx.view_first[r] = st.view_first[min(r, st.n)]
+    check(lib().mvt_shard_iter(lv, L, B, M, Cc, _feat_dtype(tg), int(k), _ptr(tg), _ptr(cq), C.byref(ctx), res.stride(1),
+                               st.epoch, _stream()), "mvt_shard_iter")
+    return res

@@ -160,3 +160,34 @@ def test_peer_store_kernels_equal_fused(world, dtype, split):
         if split and not local[r]:
             continue            # a rank without views runs no kernel (dist.py's "p2p" mode needs a view on every rank)
         assert torch.equal(outs[r], fused)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_shard_iter_single_rank_equals_fused_kernel(dtype):
+    """mvt_shard_iter with one rank (plain buffers instead of symmetric memory): the persistent search -> inbox -> correlation
+    kernel must reproduce the fused single-GPU kernel bit for bit, leave its inbox and counters empty for the next launch
+    (two launches in a row, different queries), and handle queries with fewer than k searchable points."""
+    sc = synth.make_scene(3, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.2, seed=131, device=DEV, dtype=dtype)
+    clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_tiles=True)
+    M, k = 301, 16
+    st = ops.ShardState.single(3, 4, 3, M, k, torch.device(DEV))
+    for seed in (132, 133, 134):
+        coords, targets = synth.make_tracks(clouds[0].xyz[0], M, 3, seed=seed, dtype=dtype, jitter=0.05)
+        coords[:, :9] += 2.0                              # far from every surface: tile search inside the persistent kernel
+        want = ops.knn_corr([(c, c.fvec, k) for c in clouds], targets, coords, defer=False)
+        got = ops.shard_iter(clouds, clouds, targets, coords, k, st)
+        torch.cuda.synchronize()
+        assert not st.error()
+        assert torch.equal(got, want), (seed, (got != want).any(-1).sum().item())
+        assert int(st.inbox[0].abs().sum().item()) == 0 and int(st.local.view(torch.int32).abs().sum().item()) == 0
+        assert st.ctrl[0][:8].abs().sum().item() == 0 and int(st.ctrl[0][8].item()) == st.epoch
+    # a coarse level with fewer points than k in a tiny raster: zero records come from the searching rank
+    sc2 = synth.make_scene(2, 8 * 4, 8 * 4, S=2, C=128, zero_frac=0.0, seed=135, device=DEV, dtype=dtype)
+    cl2 = ops.cloud_build(sc2.fmaps[0], sc2.depths[0, :, :, 0], sc2.intrs[0], sc2.extrs[0], levels=[0, 3], want_tiles=True)
+    assert cl2[1].xyz.shape[1] == 2
+    coords, targets = synth.make_tracks(cl2[0].xyz[0], 40, 2, seed=136, dtype=dtype)
+    st2 = ops.ShardState.single(2, 2, 2, 40, 4, torch.device(DEV))
+    got = ops.shard_iter(cl2, cl2, targets, coords, 4, st2)
+    want = ops.knn_corr([(cl2[0], cl2[0].fvec, 4)], targets, coords, defer=False)
+    torch.cuda.synchronize()
+    assert torch.equal(got[:, :, :16], want) and (got[:, :, 16 + 8:] == 0).all() and not st2.error()
