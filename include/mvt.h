@@ -310,15 +310,17 @@ int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B,
 
 /* ---- one kernel per refinement iteration: search + exchange + correlation + exchange (csrc/mvt_shard.cu) ----------------------
  * The compute-then-collective chain of the calls above (mvt_knn_idx_shared -> barrier -> mvt_corr_from_idx_shared ->
- * barrier: four stages, every rank walking every query's list) as ONE persistent kernel per rank:
- *   phase A  each rank searches ITS track shard over the replicated records; the search knows the owner of every neighbour
- *            (index -> view -> rank) and pushes an 8-byte record {query, slot, owner-local index} straight into the OWNER's
- *            inbox (peer store over NVLink); records are self-validating (top bit), no fence or counter per record;
- *   phase B  a warp that runs out of searches turns to this rank's inboxes and, as records arrive, gathers the feature row it
- *            owns, correlates it with the query's target row and stores the [corr, dx, dy, dz] record into the result block
- *            of every rank (multicast store) -- the correlation of early queries overlaps the search tail of late ones;
- *   end      the last block of a rank resets its counters, signals `epoch` to every peer and waits for theirs: when the
- *            kernel has completed on a rank, that rank's result block is complete.
+ * barrier: four stages, every rank walking every query's list) as ONE kernel launch per rank:
+ *   producers  (the block shape of the fused single-GPU kernel) one warp per query of THIS rank's track shard: window search
+ *              over the replicated records; the search knows the owner of every neighbour (index -> view -> rank) and pushes
+ *              an 8-byte record {query, slot, owner-local index} straight into the OWNER's inbox (peer store over NVLink);
+ *              records are self-validating (top bit), no fence or counter per record; queries with large pixel boxes are
+ *              deferred to the consumers (tile search);
+ *   consumers  one wave of blocks at the end of the same grid: as records arrive in this rank's inboxes they gather the
+ *              feature rows it owns, correlate them with the queries' target rows and store the [corr, dx, dy, dz] records
+ *              into the result block of every rank (multicast store) -- overlapping the search tails of all ranks;
+ *   end        the last consumer warp of a rank resets its counters, signals `epoch` to every peer and waits for theirs: when
+ *              the kernel has completed on a rank, that rank's result block is complete.
  * No host-visible barrier, no NCCL, one launch.  Records are bit-identical to mvt_knn_corr's (same per-row arithmetic).
  * C == 128, groups == 1, k <= 16 (a multiple of 4), add_offset = 1, add_xyz = 0. */
 typedef struct mvt_shard_level {
@@ -333,13 +335,13 @@ typedef struct mvt_shard_ctx {
     mvt_peers inbox;          /* symmetric: per rank [n_ranks][inbox_cap] 8-byte records, zeroed once by the caller */
     mvt_peers ctrl;           /* symmetric: per rank 2*MVT_MAX_PEERS 8-byte words (totals, epochs), zeroed once */
     mvt_peers result;         /* symmetric: per rank [B, M, n_levels*k*4] fp32; mc = its multicast address or NULL */
-    void *local;              /* this rank's private counters: mvt_shard_local_bytes() bytes, zeroed once */
+    void *local;              /* this rank's private scratch: mvt_shard_local_bytes(...) bytes, 16-byte aligned, zeroed once */
     long long inbox_cap;      /* records per (destination, source) pair: >= n_levels * B * ceil(M / n_ranks) * k */
     int rank, n_ranks;
     int view_first[MVT_MAX_PEERS + 1];   /* rank r owns views view_first[r] .. view_first[r+1]-1 (contiguous, ascending) */
 } mvt_shard_ctx;
 
-size_t mvt_shard_local_bytes(void);
+size_t mvt_shard_local_bytes(int n_levels, int B, int M, int n_ranks);
 /* targets [B, M, C] and coords [B, M, 3]: ALL tracks (replicated inputs, as the replicated transformer holds them); rank r
  * searches tracks r*Ms .. (r+1)*Ms-1, Ms = ceil(M / n_ranks).  epoch: a number that grows by one per call on every rank. */
 int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,

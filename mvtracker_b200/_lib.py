@@ -104,7 +104,7 @@ def lib():
     L.mvt_corr_from_idx_shared.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Peers), ll,
                                            C.POINTER(vp), C.POINTER(ll), vp]
     L.mvt_shard_iter.argtypes = [C.POINTER(ShardLevel), ci, ci, ci, ci, ci, ci, vp, vp, C.POINTER(ShardCtx), ll, C.c_ulonglong, vp]
-    L.mvt_shard_local_bytes.argtypes = []
+    L.mvt_shard_local_bytes.argtypes = [ci, ci, ci, ci]
     L.mvt_shard_local_bytes.restype = C.c_size_t
     L.mvt_topk_merge.argtypes = [vp, ci, ll, ci, vp, vp, vp]
     L.mvt_corr_from_idx.argtypes = [C.POINTER(OwnedLevel), ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, ll, vp]

@@ -19,6 +19,7 @@
 // of mvt_knn.cu; same arithmetic, bit-identical neighbour sets and offsets, identical correlations.
 #include "mvt_search.cuh"
 #include "mvt_corr.cuh"
+#include <stdlib.h>
 
 namespace mvt {
 
@@ -301,12 +302,18 @@ __global__ void __launch_bounds__(256, MVT_CIDX_MINB) corr_from_idx_kernel(const
 // One kernel per refinement iteration: search -> records to the owners' inboxes -> correlation -> result records to all
 // ---------------------------------------------------------------------------------------------------------------
 struct ShardLocal {             // this rank's private counters (zero between launches)
-    unsigned work;              // phase A: next query of my shard
-    unsigned a_done, b_done;    // blocks that left phase A / phase B
+    unsigned prod_done;         // producer warps (one query each) that have pushed their records or deferred their query
+    unsigned hard_count;        // queries deferred to the tile search (large pixel boxes), hard_cursor taken, hard_done finished
+    unsigned hard_cursor;
     unsigned err;               // set when a wait timed out (a peer never showed up): results are then invalid
+    unsigned hard_done;
+    unsigned published;         // 1 once this rank's totals have been sent to the owners
+    unsigned cons_done;         // consumer warps that have left
+    unsigned pad;
     unsigned tail[MVT_MAX_PEERS];     // records I have pushed to owner o
     unsigned cursor[MVT_MAX_PEERS];   // next record of source s to take from my inbox
 };
+struct ShardHard { unsigned qid, pad; u64 cap; };   // a deferred query: ((lvl * B + b) * Ms + mm), k-th key found so far
 struct ShardLevelDev {
     SearchDev sd;
     const float4 *xyz4_local;
@@ -328,7 +335,10 @@ struct ShardParams {
     int view_first[MVT_MAX_PEERS + 1];
     u64 epoch;
     float scale;
-    unsigned n_items;
+    unsigned n_items;           // real queries of my shard: n_levels * B * (tracks of my shard)
+    unsigned n_cons_blocks;     // consumer blocks: n_early in the grid's first row (extra columns), the rest in its last z slice
+    unsigned n_early, nx;       // nx: producer columns of the grid
+    ShardHard *hard;            // [n_levels * B * Ms] deferred-query list (local)
 };
 constexpr u64 kRecValid = 1ull << 63;
 constexpr unsigned long long kShardTimeoutNs = 4000000000ull;
@@ -352,23 +362,17 @@ __device__ __forceinline__ unsigned long long now_ns() {
     return t;
 }
 
-// Phase A, one query of my track shard by one warp: exact search over the replicated records, then one 8-byte record per
-// neighbour into the inbox of the rank that owns the neighbour's feature row:
-//   [63] valid | [62:58] slot j | [57:32] query id ((lvl * B + b) * M + m) | [31:0] index among the owner's points
-__device__ __forceinline__ void shard_search_item(const ShardParams &p, const unsigned char *win_tab, int lvl, int b, int mm) {
+// One 8-byte record per neighbour of a finished search into the inbox of the rank that owns the neighbour's feature row:
+//   [63] valid | [62:58] slot j | [57:56] level | [55:50] frame b | [49:32] track m | [31:0] index among the owner's points
+// tkt: lane j holds the j-th neighbour's key.
+__device__ __forceinline__ void shard_push_records(const ShardParams &p, int lvl, int b, int m, u64 tkt) {
     const int lane = threadIdx.x & 31;
-    const int m = p.rank * p.Ms + mm;
-    if (m >= p.M) return;                                 // padding of the last shard
     const ShardLevelDev &L = p.lv[lvl];
     const long long q = (long long)b * p.M + m;
-    const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
-    const Group<32> g(lane);
-    TopK tk;
-    raster_search<32, true>(g, L.sd.rv, win_tab, b, true, qx, qy, qz, p.k, tk, L.sd.g.stats, (int)q);
-    const int idx = key_idx(tk.t);
+    const int idx = key_idx(tkt);
     const bool mine = lane < p.k;
     const bool none = mine && idx == kNoIdx;
-    const unsigned qid = (unsigned)(((long long)lvl * p.B + b) * p.M + m);
+    const unsigned qid = ((unsigned)lvl << 24) | ((unsigned)b << 18) | (unsigned)m;
     if (none)       // fewer than k searchable points: nobody owns this record -- zeros, from here
         store_all(p.result, (size_t)((q * p.row_stride + (long long)lvl * p.k * 4) >> 2) + lane, make_float4(0.f, 0.f, 0.f, 0.f));
     int owner = 0x100 + lane;                              // lanes without a record: a group of their own
@@ -394,7 +398,6 @@ __device__ __forceinline__ void shard_search_item(const ShardParams &p, const un
     }
 }
 
-
 // Phase B, one batch of 32 consecutive records of source `src` (lane i holds record i, 0 = none) by one warp: the feature
 // rows named by the records are gathered sixteen at a time, correlated with their queries' target rows (per-row arithmetic
 // and lane order of the fused single-GPU kernel), and each lane stores its record's [corr, dx, dy, dz] to every rank.
@@ -403,7 +406,6 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
     const int lane = threadIdx.x & 31;
     const unsigned valid = __ballot_sync(FULL, (rec & kRecValid) != 0ull);
     if (valid == 0u) return;
-    const unsigned BM = (unsigned)p.B * (unsigned)p.M;
     float corr_mine = 0.f;
 #pragma unroll 1
     for (int r = 0; r < 2; ++r) {
@@ -416,8 +418,8 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
                 const u64 rj = __shfl_sync(FULL, rec, 16 * r + j);
                 pr[j] = 0.f;
                 if (rj & kRecValid) {                                     // (uniform)
-                    const unsigned qid = (unsigned)(rj >> 32) & 0x3ffffffu, li = (unsigned)rj;
-                    const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+                    const unsigned qid = (unsigned)(rj >> 32), li = (unsigned)rj;
+                    const unsigned lvl = (qid >> 24) & 3u, b = (qid >> 18) & 63u, bm = b * (unsigned)p.M + (qid & 0x3ffffu);
                     const ShardLevelDev &L = p.lv[lvl];
                     const float4 f = __ldg(reinterpret_cast<const float4 *>(L.fvec_local) + ((size_t)b * L.n_local + li) * 32 + lane);
                     const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + (size_t)bm * 32 + lane);
@@ -434,8 +436,8 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
                 const u64 rj = __shfl_sync(FULL, rec, 16 * r + 2 * i + half);
                 pr[i] = 0.f;
                 if (rj & kRecValid) {
-                    const unsigned qid = (unsigned)(rj >> 32) & 0x3ffffffu, li = (unsigned)rj;
-                    const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+                    const unsigned qid = (unsigned)(rj >> 32), li = (unsigned)rj;
+                    const unsigned lvl = (qid >> 24) & 3u, b = (qid >> 18) & 63u, bm = b * (unsigned)p.M + (qid & 0x3ffffu);
                     const ShardLevelDev &L = p.lv[lvl];
                     const uint4 f = __ldg(reinterpret_cast<const uint4 *>(L.fvec_local) + ((size_t)b * L.n_local + li) * 16 + (lane & 15));
                     const uint4 tg = __ldg(reinterpret_cast<const uint4 *>(p.targets) + (size_t)bm * 16 + (lane & 15));
@@ -449,8 +451,8 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
         if ((lane >> 4) == r) corr_mine = tot;
     }
     if (rec & kRecValid) {
-        const unsigned qid = (unsigned)(rec >> 32) & 0x3ffffffu, li = (unsigned)rec, j = (unsigned)(rec >> 58) & 31u;
-        const unsigned lvl = qid / BM, bm = qid - lvl * BM, b = bm / (unsigned)p.M;
+        const unsigned qid = (unsigned)(rec >> 32), li = (unsigned)rec, j = (unsigned)(rec >> 58) & 31u;
+        const unsigned lvl = (qid >> 24) & 3u, b = (qid >> 18) & 63u, bm = b * (unsigned)p.M + (qid & 0x3ffffu);
         const ShardLevelDev &L = p.lv[lvl];
         const float4 n = __ldg(L.xyz4_local + (size_t)b * L.n_local + li);
         const float qx = __ldg(p.coords + (size_t)bm * 3), qy = __ldg(p.coords + (size_t)bm * 3 + 1), qz = __ldg(p.coords + (size_t)bm * 3 + 2);
@@ -459,43 +461,106 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
     }
 }
 
-// Phase B driver of one warp: takes batches from this rank's inboxes until every source has delivered its total and all of
-// it has been taken.  Returns false on a timeout.
+// Housekeeping of a consumer warp (warp-uniform): (1) finish one deferred query of this rank, if there is one -- tile search,
+// then its records go to the owners; tickets, not compare-and-swap: thousands of warps contend for a few hundred entries;
+// (2) once every producer warp and every deferred query of this rank is through, tell each owner how many records to expect.
+// Returns true when it did a query.  Called from every wait of the consumer, so that a warp that waits for records never
+// keeps the deferred queries (on which the end of the record streams depends) from being done.
+__device__ __forceinline__ bool shard_service(const ShardParams &p, int &ticket) {
+    const int lane = threadIdx.x & 31;
+    ShardLocal *loc = p.local;
+    bool did = false;
+    if (ticket < 0) {
+        const unsigned cur = ld_volatile_u32(&loc->hard_cursor), cnt = ld_volatile_u32(&loc->hard_count);
+        if (cur < cnt) {
+            unsigned t = 0u;
+            if (lane == 0) t = atomicAdd(&loc->hard_cursor, 1u);
+            ticket = (int)__shfl_sync(FULL, t, 0);
+        }
+    }
+    if (ticket >= 0) {
+        if ((unsigned)ticket < ld_volatile_u32(&loc->hard_count)) {
+            volatile ShardHard *e = p.hard + ticket;
+            const unsigned long long t0 = now_ns();
+            while (e->pad != (unsigned)p.epoch) {                         // counted before written: wait for the writer
+                __nanosleep(32);
+                if (now_ns() - t0 > kShardTimeoutNs) { loc->err = 1u; break; }
+            }
+            const unsigned qid = e->qid;
+            const u64 cap = e->cap;
+            const unsigned per_level = (unsigned)p.B * (unsigned)p.Ms;
+            const unsigned lvl = qid / per_level, rem = qid - lvl * per_level, b = rem / (unsigned)p.Ms, mm = rem - b * (unsigned)p.Ms;
+            const int m = p.rank * p.Ms + (int)mm;
+            const long long q = (long long)b * p.M + m;
+            const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+            TopK tk;
+            tk.init();
+            tk.th = cap;
+            tk = tile_search(p.lv[lvl].sd.rv, (int)b, qx, qy, qz, p.k, tk, p.lv[lvl].sd.g.stats);
+            shard_push_records(p, (int)lvl, (int)b, m, tk.t);
+            __threadfence();
+            if (lane == 0) atomicAdd(&loc->hard_done, 1u);
+            ticket = -1;
+            did = true;
+        } else if (ld_volatile_u32(&loc->prod_done) == p.n_items) {
+            __threadfence();                                              // every producer is through: the count is final
+            if ((unsigned)ticket >= ld_volatile_u32(&loc->hard_count)) ticket = -1;          // a ticket past the end: void
+        }
+    }
+    if (!did && ld_volatile_u32(&loc->published) == 0u && ld_volatile_u32(&loc->prod_done) == p.n_items) {
+        __threadfence();                                                  // prod_done complete => hard_count is final
+        const unsigned cnt = ld_volatile_u32(&loc->hard_count);
+        if (ld_volatile_u32(&loc->hard_done) == cnt && lane == 0 && atomicCAS(&loc->published, 0u, 1u) == 0u) {
+            __threadfence();
+            for (int o = 0; o < p.n; ++o) st_sys(p.ctrl[o] + p.rank, (u64)atomicAdd(&loc->tail[o], 0u) + 1ull);
+        }
+        __syncwarp();
+    }
+    return did;
+}
+
+// A consumer warp: housekeeping (above), and batches of 32 records from this rank's inboxes, until every source has delivered
+// its total and all of it has been taken.
 template <bool BF16>
 __device__ __forceinline__ bool shard_consume(const ShardParams &p, const int start) {
     const int lane = threadIdx.x & 31;
+    ShardLocal *loc = p.local;
     u64 *inbox = p.inbox[p.rank];
     const u64 *total = p.ctrl[p.rank];
     unsigned exhausted = 0u;
     const unsigned all = (1u << p.n) - 1u;
-    int src = start % p.n, idle = 0;
-    unsigned long long t_last = now_ns();                                 // last time this warp got a batch
+    int src = start % p.n, idle = 0, ticket = -1;
+    unsigned long long t_last = now_ns();                                 // last time this warp found work
     while (exhausted != all) {
-        bool took = false;
-        if (!((exhausted >> src) & 1u)) {
-            const unsigned c = ld_volatile_u32(&p.local->cursor[src]);
+        bool took = shard_service(p, ticket);
+        if (!took && !((exhausted >> src) & 1u)) {
+            const unsigned c = ld_volatile_u32(&loc->cursor[src]);
             const u64 tot = ld_sys(total + src);                          // records of this source + 1, 0 = not known yet
             if (tot != 0ull && (u64)c + 1ull >= tot) {
                 exhausted |= 1u << src;
             } else if ((long long)c < p.cap && (ld_sys(inbox + (size_t)src * p.cap + c) & kRecValid)) {
                 unsigned i0 = 0u;
-                if (lane == 0) i0 = atomicAdd(&p.local->cursor[src], 32u);
+                if (lane == 0) i0 = atomicAdd(&loc->cursor[src], 32u);
                 i0 = __shfl_sync(FULL, i0, 0);
                 const long long pos = (long long)i0 + lane;
+                u64 *slot = inbox + (size_t)src * p.cap + (pos < p.cap ? pos : 0);
                 u64 rec = 0ull;
-                if (pos < p.cap) {
-                    u64 *slot = inbox + (size_t)src * p.cap + pos;
-                    const unsigned long long t0 = now_ns();
-                    for (;;) {
+                bool have = pos >= p.cap;
+                const unsigned long long t0 = now_ns();
+                for (;;) {                                                // (warp-uniform loop: the housekeeping needs all lanes)
+                    if (!have) {
                         rec = ld_sys(slot);
-                        if (rec & kRecValid) break;
-                        const u64 tt = ld_sys(total + src);
-                        if (tt != 0ull && (u64)pos + 1ull >= tt) { rec = 0ull; break; }      // beyond the source's last record
-                        __nanosleep(64);
-                        if (now_ns() - t0 > kShardTimeoutNs) { p.local->err = 1u; rec = 0ull; break; }
+                        have = (rec & kRecValid) != 0ull;
+                        if (!have) {
+                            const u64 tt = ld_sys(total + src);
+                            if (tt != 0ull && (u64)pos + 1ull >= tt) { rec = 0ull; have = true; }    // beyond the source's last record
+                        }
                     }
-                    if (rec & kRecValid) *slot = 0ull;                    // the inbox is empty again for the next launch
+                    if (__all_sync(FULL, have)) break;
+                    if (!shard_service(p, ticket)) __nanosleep(64);
+                    if (now_ns() - t0 > kShardTimeoutNs) { loc->err = 1u; if (!have) rec = 0ull; break; }
                 }
+                if (rec & kRecValid) *slot = 0ull;                        // the inbox is empty again for the next launch
                 shard_corr_batch<BF16>(p, rec);
                 took = true;
             }
@@ -504,59 +569,67 @@ __device__ __forceinline__ bool shard_consume(const ShardParams &p, const int st
         src = (src + 1 == p.n) ? 0 : src + 1;
         if (++idle > p.n) {                                               // a whole round without work: back off
             __nanosleep(128);
-            if (now_ns() - t_last > kShardTimeoutNs || ld_volatile_u32(&p.local->err)) { p.local->err = 1u; return false; }
+            if (now_ns() - t_last > kShardTimeoutNs || ld_volatile_u32(&loc->err)) { loc->err = 1u; return false; }
         }
     }
     return true;
 }
 
-
 #ifndef MVT_SHARD_THREADS
-#define MVT_SHARD_THREADS 256
+#define MVT_SHARD_THREADS 64
 #endif
 #ifndef MVT_SHARD_MINB
-#define MVT_SHARD_MINB 4
+#define MVT_SHARD_MINB 18
 #endif
-// One wave of blocks (all resident: a block never waits for a block that is not running).  Every warp first draws searches
-// of this rank's track shard (phase A), then consumes this rank's inboxes (phase B); the last block out runs the epilogue.
+// Grid (ceil(Ms / warps per block), B, n_levels + 1).  z < n_levels: PRODUCER blocks, the shape of the fused single-GPU kernel
+// -- one warp per query of this rank's track shard: window search, then one record per neighbour into the owner's inbox; a
+// query with a large pixel box is deferred to the consumers.  z == n_levels: CONSUMER blocks (the first n_cons_blocks of the
+// slice; one wave).  Blocks are dispatched in order, so a consumer starts only when every producer block of this rank has at
+// least been placed: consumers wait for producers (here and on the peers), producers wait for nobody.
 template <bool BF16>
 __global__ void __launch_bounds__(MVT_SHARD_THREADS, MVT_SHARD_MINB) shard_iter_kernel(const ShardParams p) {
-    __shared__ unsigned warps_a, warps_b;
-    if (threadIdx.x == 0) { warps_a = 0u; warps_b = 0u; }
     MVT_WARP_SCRATCH(win_tab, MVT_SHARD_THREADS / 32);
-    __syncthreads();
-    const int lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     ShardLocal *loc = p.local;
-    const unsigned per_level = (unsigned)p.B * (unsigned)p.Ms;
-
-    // ---- phase A: the searches of my track shard, level-major (one level's records stay hot in L2) ----
-    for (;;) {
-        unsigned item = 0u;
-        if (lane == 0) item = atomicAdd(&loc->work, 1u);
-        item = __shfl_sync(FULL, item, 0);
-        if (item >= p.n_items) break;
-        const unsigned lvl = item / per_level, rem = item - lvl * per_level;
-        const unsigned b = rem / (unsigned)p.Ms, mm = rem - b * (unsigned)p.Ms;
-        shard_search_item(p, win_tab, (int)lvl, (int)b, (int)mm);
-    }
-    // the last warp of the last block to leave phase A knows every count: tell each owner how many records to expect
-    __threadfence();
-    if (lane == 0) {
-        if (atomicAdd(&warps_a, 1u) == (unsigned)nwarps - 1u && atomicAdd(&loc->a_done, 1u) == gridDim.x - 1u) {
+    unsigned cb = 0xffffffffu;                  // consumer block id, if this block is one
+    if (blockIdx.x >= p.nx) {
+        // extra columns: the first row's are the EARLY consumers -- dispatched right behind the first producers, they overlap
+        // the correlation with the searches (a bounded share of the resident blocks: producers always find room)
+        if (blockIdx.y != 0u || blockIdx.z != 0u) return;
+        cb = blockIdx.x - p.nx;
+    } else if ((int)blockIdx.z < p.n_levels) {
+        const int mm = (int)blockIdx.x * nwarps + wib;
+        const int m = p.rank * p.Ms + mm;
+        if (mm >= p.Ms || m >= p.M) return;
+        const int b = blockIdx.y, lvl = blockIdx.z;
+        const ShardLevelDev &L = p.lv[lvl];
+        const long long q = (long long)b * p.M + m;
+        const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
+        const Group<32> g(lane);
+        TopK tk;
+        const bool exact = raster_windows<32, true>(g, L.sd.rv, win_tab, b, true, qx, qy, qz, p.k, tk, L.sd.g.stats, (int)q, kEmptyKey64, 0u);
+        if (exact) {
+            shard_push_records(p, lvl, b, m, tk.t);
+        } else if (lane == 0) {
+            const unsigned i = atomicAdd(&loc->hard_count, 1u);
+            ShardHard *e = p.hard + i;
+            e->qid = (unsigned)((lvl * p.B + b) * p.Ms + mm);
+            e->cap = tk.th | 0xffffffffull;
             __threadfence();
-            for (int o = 0; o < p.n; ++o) st_sys(p.ctrl[o] + p.rank, (u64)atomicAdd(&loc->tail[o], 0u) + 1ull);
+            e->pad = (unsigned)p.epoch;                                   // the tag last: the entry is complete when it shows
         }
+        __threadfence();
+        if (lane == 0) atomicAdd(&loc->prod_done, 1u);
+        return;
     }
-    __syncwarp();
-
-    // ---- phase B: correlate what arrives in my inboxes ----
-    shard_consume<BF16>(p, p.rank + 1 + (int)(blockIdx.x * nwarps + (threadIdx.x >> 5)));
-
-    // ---- end: the last block out resets this rank's state, signals the epoch and waits for every peer's ----
-    __threadfence_system();            // this warp's result stores are performed before its block counts as done
-    if (lane == 0 && atomicAdd(&warps_b, 1u) == (unsigned)nwarps - 1u && atomicAdd(&loc->b_done, 1u) == gridDim.x - 1u) {
+    if (cb == 0xffffffffu) cb = p.n_early + blockIdx.y * p.nx + blockIdx.x;      // last z slice: the late consumers
+    if (cb >= p.n_cons_blocks) return;
+    shard_consume<BF16>(p, p.rank + 1 + (int)(cb * nwarps + wib));
+    // ---- end: the last consumer warp resets this rank's state, signals the epoch and waits for every peer's ----
+    __threadfence_system();            // this warp's result stores are performed before it counts as done
+    if (lane == 0 && atomicAdd(&loc->cons_done, 1u) == p.n_cons_blocks * (unsigned)nwarps - 1u) {
         __threadfence_system();
-        loc->work = 0u; loc->a_done = 0u; loc->b_done = 0u;
+        loc->prod_done = 0u; loc->hard_count = 0u; loc->hard_cursor = 0u; loc->hard_done = 0u; loc->published = 0u; loc->cons_done = 0u;
         for (int r = 0; r < MVT_MAX_PEERS; ++r) { loc->tail[r] = 0u; loc->cursor[r] = 0u; }
         u64 *mine = p.ctrl[p.rank];
         for (int r = 0; r < p.n; ++r) mine[r] = 0ull;                     // next launch's totals start unknown
@@ -710,7 +783,11 @@ MVT_EXPORT int mvt_knn_idx_shared(const mvt_search *searches, int n_levels, int 
     return MVT_OK;
 }
 
-MVT_EXPORT size_t mvt_shard_local_bytes(void) { return sizeof(mvt::ShardLocal); }
+MVT_EXPORT size_t mvt_shard_local_bytes(int n_levels, int B, int M, int n_ranks) {
+    if (n_levels <= 0 || B <= 0 || M <= 0 || n_ranks <= 0) return 0;
+    const long long Ms = ((long long)M + n_ranks - 1) / n_ranks;
+    return 256 + sizeof(mvt::ShardHard) * (size_t)n_levels * (size_t)B * (size_t)Ms;
+}
 
 MVT_EXPORT int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B, int M, int C, int feat_dtype, int k,
                               const void *targets, const float *coords, const mvt_shard_ctx *ctx, long long result_row_stride,
@@ -726,8 +803,7 @@ MVT_EXPORT int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B
                   "mvt_shard_iter: rank %d of %d", ctx->rank, ctx->n_ranks);
     MVT_CHECK_ARG(ctx->inbox.n == ctx->n_ranks && ctx->ctrl.n == ctx->n_ranks && ctx->result.n == ctx->n_ranks,
                   "mvt_shard_iter: the symmetric buffers must name all %d ranks", ctx->n_ranks);
-    MVT_CHECK_ARG((long long)n_levels * B * M < (1ll << 26), "mvt_shard_iter: too many queries for the record format (%lld)",
-                  (long long)n_levels * B * M);
+    MVT_CHECK_ARG(B <= 64 && M <= (1 << 18), "mvt_shard_iter: the record format holds B <= 64 frames, M <= 262144 tracks (got %d, %d)", B, M);
     MVT_CHECK_ARG(epoch > 0 && result_row_stride % 4 == 0 && (((uintptr_t)targets) & 15) == 0, "mvt_shard_iter: epoch / alignment");
     ShardParams p;
     p.n_levels = n_levels; p.B = B; p.M = M; p.k = k;
@@ -759,26 +835,30 @@ MVT_EXPORT int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B
         p.lv[l].xyz4_local = (const float4 *)u.xyz4_local; p.lv[l].fvec_local = u.fvec_local; p.lv[l].n_local = u.n_local; p.lv[l].hw = u.hw;
     }
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
-    const long long n_items = (long long)n_levels * B * p.Ms;
-    p.n_items = (unsigned)n_items;
-    // all blocks must be resident (phase B waits for phase A of blocks of the same grid): a cooperative launch of one wave
-    int dev = 0, sms = 0, per_sm = 0;
+    const long long mine = (long long)p.M - (long long)p.rank * p.Ms;
+    const long long tracks = mine < 0 ? 0 : (mine > p.Ms ? p.Ms : mine);
+    p.n_items = (unsigned)((long long)n_levels * B * tracks);
+    static_assert(sizeof(ShardLocal) <= 256, "ShardLocal must fit the first 256 bytes of the local buffer");
+    p.hard = reinterpret_cast<ShardHard *>(reinterpret_cast<unsigned char *>(ctx->local) + 256);
+    int dev = 0, sms = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const void *fn = feat_dtype == MVT_BF16 ? (const void *)shard_iter_kernel<true> : (const void *)shard_iter_kernel<false>;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, MVT_SHARD_THREADS, 0) != cudaSuccess || per_sm < 1 || sms < 1) {
-        set_error("mvt_shard_iter: occupancy query failed");
-        return MVT_E_CUDA;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = kNumSMs;
+    const int wpb = MVT_SHARD_THREADS / 32;
+    p.nx = (unsigned)((p.Ms + wpb - 1) / wpb);
+    const long long slice = (long long)p.nx * B, wave = (long long)sms * MVT_SHARD_MINB;
+    static int early_pct = -1;
+    if (early_pct < 0) {
+        const char *e = getenv("MVT_SHARD_EARLY_PCT");             // share of one wave that consumes from the start (tuning knob)
+        early_pct = e ? atoi(e) : 0;
+        if (early_pct < 0 || early_pct > 75) early_pct = 0;
     }
-    long long need = (n_items + MVT_SHARD_THREADS / 32 - 1) / (MVT_SHARD_THREADS / 32);
-    long long wave = (long long)sms * per_sm;
-    const unsigned grid = (unsigned)(need < wave ? (need > 0 ? need : 1) : wave);
-    void *args[] = {(void *)&p};
-    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(MVT_SHARD_THREADS), args, 0, (cudaStream_t)stream);
-    if (e != cudaSuccess) {
-        set_error("mvt_shard_iter: cooperative launch failed: %s", cudaGetErrorString(e));
-        return MVT_E_CUDA;
-    }
+    p.n_early = (unsigned)(wave * early_pct / 100);
+    const long long late = slice < wave - p.n_early ? slice : wave - p.n_early;
+    p.n_cons_blocks = p.n_early + (unsigned)(late > 0 ? late : 0);
+    if (p.n_cons_blocks == 0u) { p.n_early = 1u; p.n_cons_blocks = 1u; }
+    const dim3 grid(p.nx + p.n_early, (unsigned)B, (unsigned)n_levels + 1u);
+    if (feat_dtype == MVT_BF16) shard_iter_kernel<true><<<grid, MVT_SHARD_THREADS, 0, (cudaStream_t)stream>>>(p);
+    else shard_iter_kernel<false><<<grid, MVT_SHARD_THREADS, 0, (cudaStream_t)stream>>>(p);
     MVT_CHECK_LAUNCH("shard_iter");
     return MVT_OK;
 }

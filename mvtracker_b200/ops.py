@@ -734,7 +734,9 @@ class ShardState:
     def __init__(self, rank: int, n_ranks: int, view_first: Sequence[int], inbox, ctrl, results, cap: int, device):
         self.rank, self.n, self.view_first = int(rank), int(n_ranks), [int(v) for v in view_first]
         self.inbox, self.ctrl, self.results, self.cap = inbox, ctrl, results, int(cap)
-        self.local = torch.zeros(int(lib().mvt_shard_local_bytes()), device=device, dtype=torch.uint8)
+        B, M, _ = results[0][0].shape
+        # private counters + the deferred-query list (sized for MAX_LEVELS levels of this rank's track shard)
+        self.local = torch.zeros(int(lib().mvt_shard_local_bytes(_lib.MAX_LEVELS, B, M, self.n)), device=device, dtype=torch.uint8)
         self.epoch, self.flip = 0, 1
 
     @classmethod
