@@ -338,6 +338,7 @@ struct ShardParams {
     unsigned n_items;           // real queries of my shard: n_levels * B * (tracks of my shard)
     unsigned n_cons_blocks;     // consumer blocks: n_early in the grid's first row (extra columns), the rest in its last z slice
     unsigned n_early, nx;       // nx: producer columns of the grid
+    int no_local;               // debug (MVT_SHARD_NO_LOCAL): locally owned neighbours go through the inbox as well
     ShardHard *hard;            // [n_levels * B * Ms] deferred-query list (local)
 };
 constexpr u64 kRecValid = 1ull << 63;
@@ -365,6 +366,11 @@ __device__ __forceinline__ unsigned long long now_ns() {
 // One 8-byte record per neighbour of a finished search into the inbox of the rank that owns the neighbour's feature row:
 //   [63] valid | [62:58] slot j | [57:56] level | [55:50] frame b | [49:32] track m | [31:0] index among the owner's points
 // tkt: lane j holds the j-th neighbour's key.
+// The neighbours whose rows THIS rank owns are not pushed: the searching warp correlates them itself (shard_local_corr).
+template <bool BF16>
+__device__ __forceinline__ void shard_local_corr(const ShardParams &p, int lvl, int b, int m, bool local, unsigned loc);
+
+template <bool BF16>
 __device__ __forceinline__ void shard_push_records(const ShardParams &p, int lvl, int b, int m, u64 tkt) {
     const int lane = threadIdx.x & 31;
     const ShardLevelDev &L = p.lv[lvl];
@@ -385,8 +391,11 @@ __device__ __forceinline__ void shard_push_records(const ShardParams &p, int lvl
             if (r < p.n && v >= p.view_first[r]) owner = r;
         loc = (unsigned)(idx - p.view_first[owner] * L.hw);
     }
+    const bool local = mine && !none && owner == p.rank && !p.no_local;
+    if (__any_sync(FULL, local)) shard_local_corr<BF16>(p, lvl, b, m, local, loc);      // (uniform)
+    if (local) owner = 0x100 + lane;                       // ... and is not sent anywhere
     const unsigned grp = __match_any_sync(FULL, owner);
-    const bool has = mine && !none;
+    const bool has = mine && !none && !local;
     const int leader = __ffs(grp) - 1;
     unsigned base = 0u;
     if (has && lane == leader) base = atomicAdd(&p.local->tail[owner], (unsigned)__popc(grp));
@@ -395,6 +404,54 @@ __device__ __forceinline__ void shard_push_records(const ShardParams &p, int lvl
         const unsigned slot = base + (unsigned)__popc(grp & ((1u << lane) - 1u));
         const u64 rec = kRecValid | ((u64)lane << 58) | ((u64)qid << 32) | (u64)loc;
         st_sys(p.inbox[owner] + (size_t)p.rank * p.cap + slot, rec);
+    }
+}
+
+// The searching warp's own share of the correlation: lane j < k holds neighbour j; `local` = this rank owns its feature row
+// (index `loc` among the rank's points).  Same gather, per-row arithmetic and lane order as the fused single-GPU kernel
+// (mvt_knn.cu: corr_epilogue), with the rows of the other ranks' neighbours left out.
+template <bool BF16>
+__device__ __forceinline__ void shard_local_corr(const ShardParams &p, int lvl, int b, int m, bool local, unsigned loc) {
+    const int lane = threadIdx.x & 31;
+    const ShardLevelDev &L = p.lv[lvl];
+    const size_t bm = (size_t)b * p.M + m;
+    float corr_mine;
+    if (!BF16) {
+        const float4 tg = __ldg(reinterpret_cast<const float4 *>(p.targets) + bm * 32 + lane);
+        const float4 *fv = reinterpret_cast<const float4 *>(L.fvec_local) + (size_t)b * L.n_local * 32 + lane;
+        float pr[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const unsigned ij = __shfl_sync(FULL, loc, j);
+            const bool on = __shfl_sync(FULL, (int)local, j) != 0;
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (on) f = __ldg(fv + (size_t)ij * 32);
+            pr[j] = dot4(tg, f);
+        }
+        const float tot = transpose_reduce16(pr, lane);
+        corr_mine = __shfl_sync(FULL, tot, (2 * lane) & 31);
+    } else {
+        const uint4 tgh = __ldg(reinterpret_cast<const uint4 *>(p.targets) + bm * 16 + (lane & 15));
+        const uint4 *fv = reinterpret_cast<const uint4 *>(L.fvec_local) + (size_t)b * L.n_local * 16 + (lane & 15);
+        const int half = lane >> 4;
+        float pr[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int j = 2 * i + half;
+            const unsigned ij = __shfl_sync(FULL, loc, j);
+            const bool on = __shfl_sync(FULL, (int)local, j) != 0;
+            uint4 f = make_uint4(0u, 0u, 0u, 0u);
+            if (on) f = __ldg(fv + (size_t)ij * 16);
+            pr[i] = dot8_bf16(tgh, f);
+        }
+        const float tot = transpose_reduce8_half(pr, lane);
+        corr_mine = __shfl_sync(FULL, tot, ((lane & 1) << 4) | ((lane >> 1) << 1));
+    }
+    if (local) {
+        const float4 n = __ldg(L.xyz4_local + (size_t)b * L.n_local + loc);
+        const float qx = __ldg(p.coords + bm * 3), qy = __ldg(p.coords + bm * 3 + 1), qz = __ldg(p.coords + bm * 3 + 2);
+        store_all(p.result, (size_t)(((long long)bm * p.row_stride + (long long)lvl * p.k * 4) >> 2) + lane,
+                  make_float4(__fdiv_rn(corr_mine, p.scale), n.x - qx, n.y - qy, n.z - qz));
     }
 }
 
@@ -466,6 +523,7 @@ __device__ __forceinline__ void shard_corr_batch(const ShardParams &p, const u64
 // (2) once every producer warp and every deferred query of this rank is through, tell each owner how many records to expect.
 // Returns true when it did a query.  Called from every wait of the consumer, so that a warp that waits for records never
 // keeps the deferred queries (on which the end of the record streams depends) from being done.
+template <bool BF16>
 __device__ __forceinline__ bool shard_service(const ShardParams &p, int &ticket) {
     const int lane = threadIdx.x & 31;
     ShardLocal *loc = p.local;
@@ -497,7 +555,7 @@ __device__ __forceinline__ bool shard_service(const ShardParams &p, int &ticket)
             tk.init();
             tk.th = cap;
             tk = tile_search(p.lv[lvl].sd.rv, (int)b, qx, qy, qz, p.k, tk, p.lv[lvl].sd.g.stats);
-            shard_push_records(p, (int)lvl, (int)b, m, tk.t);
+            shard_push_records<BF16>(p, (int)lvl, (int)b, m, tk.t);
             __threadfence();
             if (lane == 0) atomicAdd(&loc->hard_done, 1u);
             ticket = -1;
@@ -532,7 +590,7 @@ __device__ __forceinline__ bool shard_consume(const ShardParams &p, const int st
     int src = start % p.n, idle = 0, ticket = -1;
     unsigned long long t_last = now_ns();                                 // last time this warp found work
     while (exhausted != all) {
-        bool took = shard_service(p, ticket);
+        bool took = shard_service<BF16>(p, ticket);
         if (!took && !((exhausted >> src) & 1u)) {
             const unsigned c = ld_volatile_u32(&loc->cursor[src]);
             const u64 tot = ld_sys(total + src);                          // records of this source + 1, 0 = not known yet
@@ -557,7 +615,7 @@ __device__ __forceinline__ bool shard_consume(const ShardParams &p, const int st
                         }
                     }
                     if (__all_sync(FULL, have)) break;
-                    if (!shard_service(p, ticket)) __nanosleep(64);
+                    if (!shard_service<BF16>(p, ticket)) __nanosleep(64);
                     if (now_ns() - t0 > kShardTimeoutNs) { loc->err = 1u; if (!have) rec = 0ull; break; }
                 }
                 if (rec & kRecValid) *slot = 0ull;                        // the inbox is empty again for the next launch
@@ -609,7 +667,7 @@ __global__ void __launch_bounds__(MVT_SHARD_THREADS, MVT_SHARD_MINB) shard_iter_
         TopK tk;
         const bool exact = raster_windows<32, true>(g, L.sd.rv, win_tab, b, true, qx, qy, qz, p.k, tk, L.sd.g.stats, (int)q, kEmptyKey64, 0u);
         if (exact) {
-            shard_push_records(p, lvl, b, m, tk.t);
+            shard_push_records<BF16>(p, lvl, b, m, tk.t);
         } else if (lane == 0) {
             const unsigned i = atomicAdd(&loc->hard_count, 1u);
             ShardHard *e = p.hard + i;
@@ -853,6 +911,10 @@ MVT_EXPORT int mvt_shard_iter(const mvt_shard_level *levels, int n_levels, int B
         if (early_pct < 0 || early_pct > 75) early_pct = 0;
     }
     p.n_early = (unsigned)(wave * early_pct / 100);
+    {
+        const char *e = getenv("MVT_SHARD_NO_LOCAL");
+        p.no_local = (e && e[0] == '1') ? 1 : 0;
+    }
     const long long late = slice < wave - p.n_early ? slice : wave - p.n_early;
     p.n_cons_blocks = p.n_early + (unsigned)(late > 0 ? late : 0);
     if (p.n_cons_blocks == 0u) { p.n_early = 1u; p.n_cons_blocks = 1u; }

@@ -162,11 +162,15 @@ def test_peer_store_kernels_equal_fused(world, dtype, split):
         assert torch.equal(outs[r], fused)
 
 
+@pytest.mark.parametrize("no_local", ["0", "1"])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_shard_iter_single_rank_equals_fused_kernel(dtype):
+def test_shard_iter_single_rank_equals_fused_kernel(dtype, no_local, monkeypatch):
     """mvt_shard_iter with one rank (plain buffers instead of symmetric memory): the persistent search -> inbox -> correlation
     kernel must reproduce the fused single-GPU kernel bit for bit, leave its inbox and counters empty for the next launch
-    (two launches in a row, different queries), and handle queries with fewer than k searchable points."""
+    (two launches in a row, different queries), and handle queries with fewer than k searchable points.
+    no_local = 1 (MVT_SHARD_NO_LOCAL): also the neighbours this rank owns travel through its inbox -- the path every record
+    takes between ranks -- instead of being correlated by the searching warp."""
+    monkeypatch.setenv("MVT_SHARD_NO_LOCAL", no_local)
     sc = synth.make_scene(3, 48 * 4, 64 * 4, S=3, C=128, zero_frac=0.2, seed=131, device=DEV, dtype=dtype)
     clouds = ops.cloud_build(sc.fmaps[0], sc.depths[0, :, :, 0], sc.intrs[0], sc.extrs[0], levels=[0, 1, 2, 3], want_tiles=True)
     M, k = 301, 16
