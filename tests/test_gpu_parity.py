@@ -546,7 +546,7 @@ def test_corr_deferred_free_space_queries_identical(dtype):
     assert (ib[0].cpu().numpy() == oi).all()
     # count-only mode (what the adaptive policy runs while few queries are hard): one kernel, same bits, same count
     pol = ops.hard_query_policy(torch.device(DEV, torch.cuda.current_device()))
-    pol.deferring, pol.event = False, None
+    pol.deferring, pol.event, pol.calls = False, None, 0      # calls = 0: the next launch is one the policy samples
     d_, id_ = ops.knn_corr(lv, targets, coords, return_idx=True, defer="auto")
     torch.cuda.synchronize()
     c2 = ops._corr_ws[torch.cuda.current_device()][:8].view(torch.int32).cpu().tolist()
