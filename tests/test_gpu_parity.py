@@ -552,7 +552,7 @@ def test_corr_deferred_free_space_queries_identical(dtype):
     c2 = ops._corr_ws[torch.cuda.current_device()][:8].view(torch.int32).cpu().tolist()
     assert c2[0] == counters[0] and c2[1] == 0, (c2, counters)
     assert torch.equal(id_, ia) and torch.equal(d_, a)
-    assert pol.mode() == 1 and pol.last_fraction > 0.1        # ... and the next call defers: most of these queries are hard
+    assert pol.mode() == 1 and pol.last_fraction > 0.05       # ... and the next call defers: many of these queries are hard
     # warm start + deferral (the cap travels with the deferred query)
     c, ic = ops.knn_corr(lv, targets, coords, return_idx=True, idx_hint=ia.clone(), defer=True)
     assert torch.equal(ic, ia) and torch.equal(c, a)
