@@ -190,6 +190,25 @@ int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C
                  float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
                  void *workspace, int hard_query_mode, void *stream);
 
+/* mvt_knn_corr for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, arithmetic and results as mvt_knn_corr with a workspace, but the scratch (the list of deferred large-box
+ * queries) is a file-scope `static __device__` array of MVT_KNN_CORR_NOALLOC_BYTES inside libmvt.so -- every GPU that loads
+ * the library holds that much until the process exits.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine); the caller passes inputs and outputs only.
+ * Limit: mvt_knn_corr_workspace_bytes(n_levels, B, M) <= MVT_KNN_CORR_NOALLOC_BYTES, i.e. n_levels * B * M <=
+ * MVT_KNN_CORR_NOALLOC_QUERIES (BASELINE.json config 2: 4 * 12 * 2048 = 98 304); larger shapes are refused with
+ * MVT_E_WORKSPACE and a message in mvt_last_error().  hard_query_mode 1 or 2 as above (0 would not use the scratch: refused).
+ * ALL calls on one GPU share the array (per process): it keeps the previous call's list, the counters at its head are
+ * cleared on the call's stream before the kernels run; two calls that overlap on the GPU (different streams without an
+ * ordering between them) race on it -- serialise them or use mvt_knn_corr with one workspace per stream. */
+#define MVT_KNN_CORR_NOALLOC_BYTES (4u << 20)
+#define MVT_KNN_CORR_NOALLOC_QUERIES ((MVT_KNN_CORR_NOALLOC_BYTES - 256u) / 16u)
+int mvt_knn_corr_noalloc(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
+                         const void *targets, const float *coords, int add_offset, int add_xyz,
+                         float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
+                         int hard_query_mode, void *stream);
+
 /* k = 1 search returning the nearest point's feature row (feature init, mvtracker.py:636-643).
  * fvec [B,N,C]; feat_out [B,M,C] feature dtype; idx_out optional [B,M] int32. */
 int mvt_knn_gather(const mvt_search *search, const void *fvec, int feat_dtype, int B, int C,

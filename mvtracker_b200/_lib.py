@@ -10,9 +10,12 @@ SO_PATH = os.environ.get("MVT_LIB") or os.path.join(_HERE, "libmvt.so")   # MVT_
 MVT_F32, MVT_BF16 = 0, 1
 MAX_LEVELS, MAX_K, MAX_JOBS = 4, 32, 8
 CAM_STRIDE, MAX_VIEWS = 48, 32
+MVT_OK, MVT_E_ARG, MVT_E_CUDA, MVT_E_WORKSPACE = 0, -1, -2, -3
+NOALLOC_BYTES = 4 << 20                          # MVT_KNN_CORR_NOALLOC_BYTES: static scratch of mvt_knn_corr_noalloc
+NOALLOC_QUERIES = (NOALLOC_BYTES - 256) // 16    # MVT_KNN_CORR_NOALLOC_QUERIES
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_cloud_build_frames", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_corr_workspace_bytes", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_corr_workspace_bytes", "mvt_knn_corr_noalloc", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
            "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
            "mvt_tile_depth_build", "mvt_track_input", "mvt_knn_corr_backward",
@@ -93,6 +96,7 @@ def lib():
     L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
     L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp, ci, vp]
     L.mvt_knn_corr_workspace_bytes.argtypes = [ci, ci, ci]
+    L.mvt_knn_corr_noalloc.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, ci, vp]
     L.mvt_knn_corr_workspace_bytes.restype = C.c_size_t
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]
     L.mvt_grid_info.argtypes = [vp, ci, ci, vp, vp]

@@ -8,6 +8,7 @@
 // Roofline of knn_corr: HBM bound on the neighbour-feature gather.  Algorithmic bytes per query (k=16, C=128, fp32):
 //   read 12 (xyz) + 512 (target) + 16*(512 + 12) (neighbour rows + xyz), write 16*16  = 9 164 B  (SURVEY.md 8d).
 // The neighbour rows go HBM -> registers -> dot product; they are never written back.
+#include <mutex>
 #include "mvt_search.cuh"
 #include "mvt_corr.cuh"
 
@@ -595,6 +596,60 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
         MVT_CHECK_LAUNCH("knn_corr_hard");
     }
     return MVT_OK;
+}
+
+// ---- mvt_knn_corr without any allocation: the deferred-query list lives in a static device array (include/mvt.h) ------------
+// The array's name is a host-side stand-in in host code, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MVT_KNN_CORR_NOALLOC_BYTES];
+static_assert(sizeof(mvt::HardEntry) == 16, "MVT_KNN_CORR_NOALLOC_QUERIES assumes 16-byte entries");
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+void *g_noalloc_ptr[kMaxDevices] = {};
+
+int noalloc_scratch(void **ptr) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        mvt::set_error("mvt_knn_corr_noalloc: cudaGetDevice failed or device %d out of range", dev);
+        return MVT_E_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);      // this device's copy of the array
+        if (e != cudaSuccess || p == nullptr) {
+            mvt::set_error("mvt_knn_corr_noalloc: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return MVT_E_CUDA;
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *ptr = g_noalloc_ptr[dev];
+    return MVT_OK;
+}
+}   // namespace
+
+MVT_EXPORT int mvt_knn_corr_noalloc(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
+                                    const void *targets, const float *coords, int add_offset, int add_xyz,
+                                    float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint,
+                                    int *idx_out, int hard_query_mode, void *stream) {
+    MVT_CHECK_ARG(hard_query_mode == 1 || hard_query_mode == 2,
+                  "mvt_knn_corr_noalloc: hard_query_mode must be 1 or 2 (got %d; mode 0 uses no scratch: call mvt_knn_corr)", hard_query_mode);
+    MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS && B > 0 && M >= 0, "mvt_knn_corr_noalloc: bad shape n_levels=%d B=%d M=%d",
+                  n_levels, B, M);
+    const unsigned long long queries = (unsigned long long)n_levels * (unsigned long long)B * (unsigned long long)M;
+    if (queries > MVT_KNN_CORR_NOALLOC_QUERIES || mvt_knn_corr_workspace_bytes(n_levels, B, M) > MVT_KNN_CORR_NOALLOC_BYTES) {
+        mvt::set_error("mvt_knn_corr_noalloc: n_levels*B*M = %llu exceeds the static scratch (%u queries, %u bytes); use mvt_knn_corr "
+                       "with a caller-owned workspace", queries, (unsigned)MVT_KNN_CORR_NOALLOC_QUERIES, (unsigned)MVT_KNN_CORR_NOALLOC_BYTES);
+        return MVT_E_WORKSPACE;
+    }
+    void *scratch = nullptr;
+    int rc = noalloc_scratch(&scratch);
+    if (rc) return rc;
+    // mvt_knn_corr clears the counters at the head of the scratch on `stream` before its kernels run, and launches only
+    return mvt_knn_corr(levels, n_levels, B, M, C, G, feat_dtype, targets, coords, add_offset, add_xyz, out, out_row_stride,
+                        out_frame_stride, idx_hint, idx_out, scratch, hard_query_mode, stream);
 }
 
 MVT_EXPORT int mvt_debug_set_group_width(int lanes) {
