@@ -50,8 +50,10 @@ def parse_args():
     ap.add_argument("--cell-scale", type=float, default=0.0)
     ap.add_argument("--search", default="raster", choices=["raster", "grid"],
                     help="raster: search the depth rasters directly (no index build); grid: hashed grid")
-    ap.add_argument("--dist-mode", default="fused", choices=["fused", "p2p", "tracks", "views"],
-                    help="N > 1: tracks = replicate the 16-byte records, search per track shard; views = search own views, merge candidates")
+    ap.add_argument("--dist-mode", default="frames", choices=["frames", "fused", "p2p", "tracks", "views"],
+                    help="N > 1: frames (default) = the window's frames are sharded round robin, each rank runs the fused kernel on its "
+                         "frames x all tracks and stores the records into every rank's block; fused / p2p = views sharded for the build, "
+                         "tracks for the search (one persistent kernel / four stages per iteration); tracks / views = NCCL transports")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="N > 1: strong = ONE window sharded over the ranks (views, then tracks; the default, what the path's "
                          "multi-GPU design is about); weak = every rank tracks its own sequence's window with the single-GPU path "
@@ -287,7 +289,11 @@ def run_reference(args):
 def config_dict(w, args, world=1, weak=False):
     return {"parallelism": "1 GPU: fused knn_corr kernel" if world == 1 else
             f"{world} GPUs: independent replicas, each rank runs the single-GPU path on its own sequence's window (no exchange)" if weak else
-            (f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
+            (f"{world} GPUs: the FRAMES of the window (the batch axis of the reference's kNN correlation: independent units) are sharded round robin, frame t on rank "
+             f"t % {world}; each rank builds and caches its frames' clouds of all views (nothing of a cloud crosses NVLink) and per iteration runs the single-GPU fused "
+             f"kernel on its frames x all tracks, whose epilogue stores every result record into every rank's block (multimem.st over NVSwitch); one signal-pad barrier per "
+             f"iteration, no NCCL on the data path" if getattr(args, "dist_mode", "") == "frames" else
+             f"{world} GPUs: views sharded for the cloud build (features stay local); 16-byte point records all-gathered once per window; exact search per track shard; "
              f"index lists all-gathered; records of locally owned neighbours all-reduced (NCCL)" if getattr(args, "dist_mode", "tracks") == "tracks" else
              f"{world} GPUs: views sharded for the cloud build (features stay local, 16-byte point records multicast into every rank's replica); per iteration ONE persistent "
              f"kernel per rank: search of the rank's track shard -> 8-byte records into the OWNER's inbox (peer stores over NVLink) -> owner-side gather + correlation "
@@ -341,9 +347,12 @@ def run_ours(args):
     pw = 1 if weak else world          # ranks ONE window is sharded over
 
     # ---- synthetic inputs, identical on every rank (same seed); tracks are sampled from the full level-0 cloud ---------
-    from mvtracker_b200.dist import ShardedSequence
+    from mvtracker_b200.dist import FrameShardedSequence, ShardedSequence
     from mvtracker_b200.hotpath import WindowSequence
     advance = args.step == "advance" and not weak and args.search == "raster"
+    frames_mode = pw > 1 and args.dist_mode == "frames"
+    if frames_mode and (not advance or (4 * (S_WINDOW // 2)) % world):
+        args.dist_mode, frames_mode = "p2p", False      # the frame pool (24 frames, cycled) must split evenly over the ranks
     HOP = S_WINDOW // 2
     S_POOL = 4 * HOP if advance else S_WINDOW      # advance: a pool of 24 distinct frames, cycled (window j = blocks j, j+1 mod 4)
     sc = synth.make_scene(V, w["H"], w["W"], S=S_POOL, C=C_FEAT, stride=STRIDE, zero_frac=args.zero_frac,
@@ -372,7 +381,11 @@ def run_ours(args):
     width = LEVELS * K_NN * 4
     outs = [torch.empty(S_WINDOW, N, width, device=dev, dtype=torch.float32) for _ in range(iters)]
     v0, v1 = 0, V
-    if pw > 1:
+    if frames_mode:        # this rank's frames of the pool (all views): pool frame p belongs to rank p % world
+        fm_pool, dp_pool = fm_pool[:, rank::world].contiguous(), dp_pool[:, rank::world].contiguous()
+        del sc
+        torch.cuda.empty_cache()
+    elif pw > 1:
         v0, v1 = view_range(rank, world, V)
         fm_pool, dp_pool = fm_pool[v0:v1].contiguous(), dp_pool[v0:v1].contiguous()
         del sc
@@ -382,13 +395,32 @@ def run_ours(args):
     K, E = cams_loc[0]
     K_all, E_all = cams_win[0]
     n_built = HOP if advance else S_WINDOW                         # frames whose clouds a steady-state step builds
+    if frames_mode:
+        n_built = (HOP + world - 1) // world                       # ... on the rank that builds most (all views of them)
+
+    def local_run(ts):         # global frame numbers (consecutive multiples of world apart) -> slice of this rank's pool frames
+        li = [((t % S_POOL) - rank) // world for t in ts]
+        assert li == list(range(li[0], li[0] + len(li)))
+        return slice(li[0], li[0] + len(li))
 
     # ---- one step = the hot path of one sliding window; output buffers are allocated once and rebuilt in place --------
     state = {"win": None, "seq": None, "j": 0}
 
     def step(ev=None):
         if ev is not None: ev[0].record()
-        if advance:
+        if advance and frames_mode:
+            if state["seq"] is None:
+                state["seq"] = FrameShardedSequence(V, w["Hs"], w["Ws"], C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN)
+                j = 0
+            else:
+                j = state["j"] + 1
+            t = j % 4
+            ts = state["seq"].new_frames()
+            new = local_run(ts) if ts else None
+            win = state["seq"].push(fm_pool[:, new] if ts else None, dp_pool[:, new] if ts else None, cams_win[t][0], cams_win[t][1])
+            state["j"] = j
+            cw = coords_win[t]
+        elif advance:
             if state["seq"] is None:
                 Hs, Ws = w["Hs"], w["Ws"]
                 state["seq"] = (WindowSequence(V, Hs, Ws, C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN) if pw == 1 else
@@ -426,7 +458,7 @@ def run_ours(args):
         for i in range(iters):
             # "p2p" / "fused": the result block is returned where the ranks' kernels stored it (symmetric memory; valid until the
             # next-but-one corr call), as the fused kernel writes into the caller's buffer at N = 1 -- no extra copy
-            state["out"] = win.corr(targets_it[i], cw[i], out=None if getattr(win, "mode", "") in ("p2p", "fused") else outs[i])
+            state["out"] = win.corr(targets_it[i], cw[i], out=None if getattr(win, "mode", "") in ("p2p", "fused", "frames") else outs[i])
             if ev is not None: ev[3 + i].record()
         state["win"], state["coords"] = win, cw
 
@@ -484,14 +516,16 @@ def run_ours(args):
 
     # ---- roofline (algorithmic bytes / measured time / measured HBM peak), per GPU -----------------------------------------
     peak, peak_src = _peak()
-    v_loc = fm.shape[0]
+    v_loc = fm.shape[0]        # (frames mode: all views, of ceil(HOP / world) frames)
     q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4          # 9164 B (fp32) / 4812 B (bf16)
     corr_bytes = LEVELS * S_WINDOW * N * q_bytes / pw                                 # per rank: its share of the gathers
     pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * n_built
-    cloud_bytes = (fm.numel() * esz + dp.numel() * 4) * n_built // S_WINDOW + pts * (C_FEAT * esz + 12)   # SURVEY.md 8d (xyz4 records not counted)
+    cloud_bytes = (fm[:, :1].numel() * esz + dp[:, :1].numel() * 4) * n_built + pts * (C_FEAT * esz + 12)   # SURVEY.md 8d (xyz4 records not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
-                     "what": "fused knn_corr kernel" if pw == 1 else "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
+                     "what": "fused knn_corr kernel" if pw == 1 else
+                     "fused knn_corr kernel on this rank's frames, records stored into every rank's block + one barrier (per iteration)" if frames_mode else
+                     "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6, "frames_built": n_built,
                         "what": "camera_prep + cloud_build (4 levels, one pass) + tile depth tables" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
     }
@@ -637,10 +671,16 @@ def verify_output(win, out, targets, coords, world, rank, bf16, n_tracks=64, fra
     sel = torch.linspace(0, N - 1, min(n_tracks, N), device=out.device).long()
     worst, bad_sets, checked = 0.0, 0, 0
     sharded = hasattr(win, "full") and getattr(win, "full", None) is not None
-    n_levels = len(win.full) if sharded else len(win.clouds)
+    by_frames = getattr(win, "mode", "") == "frames"       # every rank checks the frames IT owns, in the replicated block
+    n_levels = len(win.levels) if by_frames else len(win.full) if sharded else len(win.clouds)
+    if by_frames:
+        frames = sorted({0, len(win.run) - 1}) if win.run else ()
     for l in range(n_levels):
         for f in frames:
-            if sharded:
+            if by_frames:
+                xyz, fvec = win.clouds[l].xyz[f], win.clouds[l].fvec[f]
+                f = win.pos0 + f * win.world                # local frame -> position in the window
+            elif sharded:
                 xyz = win.full[l].xyz4[f, :, :3].contiguous()
                 mine = win.clouds[l].fvec[f].contiguous()
                 parts = [torch.empty_like(mine) for _ in range(world)]
@@ -761,11 +801,13 @@ def run_e2e(args, w, world, rank, dev, fm_pool, dp_pool, cams_loc, cams_win, coo
     rank reads back the rows of ITS track shard -- together the ranks return the block once)."""
     import torch
     import torch.distributed as dist
-    from mvtracker_b200.dist import ShardedSequence, ShardedWindow, track_shard
+    from mvtracker_b200.dist import FrameShardedSequence, ShardedSequence, ShardedWindow, track_shard
     from mvtracker_b200.hotpath import WindowClouds, WindowSequence
     iters, N, V = args.iters, w["N"], w["V"]
     pw = 1 if weak else world
     HOP = S_WINDOW // 2
+    if pw > 1 and args.dist_mode == "frames" and advance:
+        return run_e2e_frames(args, w, world, rank, dev, fm_pool, dp_pool, cams_win, coords_win, targets_it)
     nblk = fm_pool.shape[1] // HOP
     host_fm = [fm_pool[:, HOP * b:HOP * b + HOP].contiguous().cpu().pin_memory() for b in range(nblk)]
     host_dp = [dp_pool[:, HOP * b:HOP * b + HOP].contiguous().cpu().pin_memory() for b in range(nblk)]
@@ -844,6 +886,82 @@ def run_e2e(args, w, world, rank, dev, fm_pool, dp_pool, cams_loc, cams_win, coo
             "api": ("mvtracker_b200.hotpath." + ("WindowSequence.push" if advance else "WindowClouds.build") + " / .corr" if pw == 1 else
                     "mvtracker_b200.dist." + ("ShardedSequence.push" if advance else "ShardedWindow.build") + " / .corr")
                    + ", pinned host buffers, all ranks summed"}
+
+
+def run_e2e_frames(args, w, world, rank, dev, fm_loc, dp_loc, cams_win, coords_win, targets_it):
+    """run_e2e for --dist-mode frames: every step copies THIS rank's new frames (all views) and the window's cameras from pinned
+    host memory and advances mvtracker_b200.dist.FrameShardedSequence; per iteration track positions + features go in and each
+    rank reads back the rows of the frames it computed (together the ranks return the block once)."""
+    import torch
+    import torch.distributed as dist
+    from mvtracker_b200.dist import FrameShardedSequence
+    iters, N, V = args.iters, w["N"], w["V"]
+    S_POOL = fm_loc.shape[1] * world
+    host_fm, host_dp = fm_loc.cpu().pin_memory(), dp_loc.cpu().pin_memory()            # [V, S_POOL / world, ...]
+    host_cam = [[t.cpu().pin_memory() for t in cw] for cw in cams_win]
+    host_ct = [[(c.cpu().pin_memory(), t.cpu().pin_memory()) for c, t in zip(cw, targets_it)] for cw in coords_win]
+    most = (S_WINDOW + world - 1) // world
+    host_out = [torch.empty(most, N, LEVELS * K_NN * 4, dtype=torch.float32).pin_memory() for _ in range(iters)]
+    state = {"seq": None, "j": 0, "h2d": 0, "d2h": 0}
+
+    def step(count=False):
+        if state["seq"] is None:
+            state["seq"], j = FrameShardedSequence(V, w["Hs"], w["Ws"], C_FEAT, fm_loc.dtype, dev, S=S_WINDOW, k=K_NN), 0
+        else:
+            j = state["j"] + 1
+        seq, t = state["seq"], j % len(host_cam)
+        ts = seq.new_frames()
+        fmd = dpd = None
+        if ts:
+            a = ((ts[0] % S_POOL) - rank) // world
+            fmd = torch.empty((V, len(ts)) + tuple(host_fm.shape[2:]), device=dev, dtype=host_fm.dtype)
+            dpd = torch.empty((V, len(ts)) + tuple(host_dp.shape[2:]), device=dev, dtype=host_dp.dtype)
+            for v in range(V):      # one contiguous pinned run per view (a strided slice of pinned memory would be staged by the host)
+                fmd[v].copy_(host_fm[v, a:a + len(ts)], non_blocking=True)
+                dpd[v].copy_(host_dp[v, a:a + len(ts)], non_blocking=True)
+        Ka, Ea = [x.to(dev, non_blocking=True) for x in host_cam[t]]
+        win = seq.push(fmd, dpd, Ka, Ea)
+        state["j"] = j
+        nb = (0 if fmd is None else fmd.numel() * fmd.element_size() + dpd.numel() * 4) + Ka.numel() * 4 + Ea.numel() * 4
+        nd = 0
+        for i in range(iters):
+            coords = host_ct[t][i][0].to(dev, non_blocking=True)
+            ffeats = host_ct[t][i][1].to(dev, non_blocking=True)
+            res = win.corr(ffeats, coords)
+            nw = len(win.run)
+            if nw:
+                host_out[i][:nw].copy_(res[win.pos0::world][:nw], non_blocking=True)
+            nb += coords.numel() * 4 + ffeats.numel() * ffeats.element_size()
+            nd += nw * N * LEVELS * K_NN * 16
+        if count:
+            state["h2d"] += nb
+            state["d2h"] += nd
+
+    def sync():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    n = max(4, min(args.steps, 12))
+    for _ in range(3):
+        step()
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        step(True)
+    e1.record()
+    sync()
+    tt = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    hb = torch.tensor([state["h2d"] / n, state["d2h"] / n], device=dev, dtype=torch.float64)
+    dist.all_reduce(hb)
+    ms = float(tt.item()) / n
+    state["seq"] = None
+    queries = iters * LEVELS * S_WINDOW * N
+    return {"value": queries / (ms * 1e-3), "unit": "queries/s", "ms_per_step": ms, "h2d_bytes_per_step": int(hb[0].item()),
+            "d2h_bytes_per_step": int(hb[1].item()), "steps": n,
+            "api": "mvtracker_b200.dist.FrameShardedSequence.push / .corr, pinned host buffers, all ranks summed (mean per step)"}
 
 
 if __name__ == "__main__":

@@ -327,6 +327,24 @@ int mvt_corr_from_idx_shared(const mvt_owned_level *levels, int n_levels, int B,
                              const mvt_peers *out, long long out_row_stride, const float *const *all_xyz4,
                              const long long *n_all, void *stream);
 
+/* ---- frames sharded over the GPUs: the fused kernel storing into every rank's result block ------------------------------------
+ * The frames of a window are the batch axis of the reference's kNN correlation (corr_sample runs on [B*S, ...] clouds,
+ * mvtracker.py:800-846; frame s of the window only ever meets frame s of the cloud): they are independent units.  A rank that
+ * owns a subset of the window's frames holds those frames' clouds of ALL views, runs mvt_knn_corr's fused kernel for its
+ * frames x all tracks, and stores each 16-byte [corr, dx, dy, dz] record into the [S, M, n_levels*k*4] block of EVERY rank
+ * (one multimem.st through `out->mc`, or one store per peer mapping without multicast) -- the all-gather of the results is the
+ * kernel's own epilogue; a cross-rank barrier after the launch completes the block.  No index lists, no inboxes, no second
+ * kernel.  groups = 1, add_offset = 1, add_xyz = 0, C and k as mvt_knn_corr's fast path or not (any C works).
+ * B: this rank's frames (levels[].search describe the clouds of exactly these frames, in order); targets / coords point at
+ * the rows of the FIRST local frame inside the replicated [S, M, .] tensors and consecutive local frames are
+ * query_frame_stride queries apart (round-robin ownership over N ranks: N*M); `out` (ptr[] / mc already offset to the first
+ * local frame's rows) with out_frame_stride floats between local frames, out_row_stride between tracks.
+ * workspace / hard_query_mode: as mvt_knn_corr. */
+int mvt_knn_corr_shared(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int feat_dtype,
+                        const void *targets, const float *coords, long long query_frame_stride,
+                        const mvt_peers *out, long long out_row_stride, long long out_frame_stride,
+                        void *workspace, int hard_query_mode, void *stream);
+
 /* ---- one kernel per refinement iteration: search + exchange + correlation + exchange (csrc/mvt_shard.cu) ----------------------
  * The compute-then-collective chain of the calls above (mvt_knn_idx_shared -> barrier -> mvt_corr_from_idx_shared ->
  * barrier: four stages, every rank walking every query's list) as ONE kernel launch per rank:

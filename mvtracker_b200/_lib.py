@@ -15,7 +15,7 @@ NOALLOC_BYTES = 4 << 20                          # MVT_KNN_CORR_NOALLOC_BYTES: s
 NOALLOC_QUERIES = (NOALLOC_BYTES - 256) // 16    # MVT_KNN_CORR_NOALLOC_QUERIES
 
 SYMBOLS = ("mvt_version", "mvt_last_error", "mvt_camera_prep", "mvt_cloud_build", "mvt_cloud_build_frames", "mvt_grid_workspace_bytes",
-           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_corr_workspace_bytes", "mvt_knn_corr_noalloc", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
+           "mvt_grid_build", "mvt_knn", "mvt_knn_corr", "mvt_knn_corr_workspace_bytes", "mvt_knn_corr_noalloc", "mvt_knn_corr_shared", "mvt_knn_gather", "mvt_grid_info", "mvt_launch_count", "mvt_debug_set_stats",
            "mvt_debug_set_group_width", "mvt_knn_keys", "mvt_topk_merge", "mvt_corr_from_idx",
            "mvt_cloud_build_shared", "mvt_knn_idx_shared", "mvt_corr_from_idx_shared", "mvt_tile_depth_floats",
            "mvt_tile_depth_build", "mvt_track_input", "mvt_knn_corr_backward",
@@ -96,6 +96,7 @@ def lib():
     L.mvt_knn.argtypes = [C.POINTER(Search), ci, vp, ci, ci, vp, ci, vp, vp]
     L.mvt_knn_corr.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, vp, ci, vp]
     L.mvt_knn_corr_workspace_bytes.argtypes = [ci, ci, ci]
+    L.mvt_knn_corr_shared.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, vp, vp, ll, C.POINTER(Peers), ll, ll, vp, ci, vp]
     L.mvt_knn_corr_noalloc.argtypes = [C.POINTER(CorrLevel), ci, ci, ci, ci, ci, ci, vp, vp, ci, ci, vp, ll, ll, vp, vp, ci, vp]
     L.mvt_knn_corr_workspace_bytes.restype = C.c_size_t
     L.mvt_knn_gather.argtypes = [C.POINTER(Search), vp, ci, ci, ci, vp, ci, vp, vp, vp]

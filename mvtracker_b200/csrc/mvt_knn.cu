@@ -73,7 +73,11 @@ struct CorrParams {
     int *idx_out;
     const int *idx_hint;   // [n_levels,B,M,k] or null: any k points of the same clouds (e.g. last iteration's neighbours)
     float scale;      // sqrt(C/G)
-    int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4)
+    int vec_out;      // 1: every neighbour record is one aligned float4 (D == 4); 2: ... stored through the NVSwitch multicast
+                      // address `out` (multimem.st: one store lands in every rank's block); 3: ... stored to every rank's mapping
+    long long q_frame_stride;   // queries between two frames of targets / coords (M when they are dense [B, M, .])
+    float *peer[MVT_MAX_PEERS]; // vec_out == 3: the output block of every rank (peer[0] == out)
+    int n_peers;
     unsigned *hard;   // deferred queries (see knn_corr_hard_kernel): [0] count, [1] cursor, entries (uint4) from byte 256; or null
     int hard_mode;    // 1: defer the large-box queries; 2: only count them in hard[0] and finish them in place
 };
@@ -189,7 +193,16 @@ __device__ __forceinline__ void corr_epilogue(const CorrParams &p, const CorrLev
             float cv = ok ? __fdiv_rn(corr_mine, p.scale) : 0.f;
             float *o = orow + (size_t)gl * D;
             if (p.vec_out) {
-                *reinterpret_cast<float4 *>(o) = ok ? make_float4(cv, n.x - qx, n.y - qy, n.z - qz) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 rec = ok ? make_float4(cv, n.x - qx, n.y - qy, n.z - qz) : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p.vec_out == 1) {
+                    *reinterpret_cast<float4 *>(o) = rec;
+                } else if (p.vec_out == 2) {
+                    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(rec.x), "f"(rec.y),
+                                 "f"(rec.z), "f"(rec.w) : "memory");
+                } else {
+                    const long long off = o - p.out;
+                    for (int r = 0; r < p.n_peers; ++r) *reinterpret_cast<float4 *>(p.peer[r] + off) = rec;
+                }
             } else {
                 int wpos = 0;
                 o[wpos++] = cv;
@@ -241,7 +254,7 @@ __global__ void __launch_bounds__(MVT_CORR_THREADS, MVT_CORR_MINB) knn_corr_kern
     if (GW == 32 && !live) return;
     const int m = live ? m_raw : p.M - 1;
     const int b = blockIdx.y, lvl = blockIdx.z;
-    const long long q = (long long)b * p.M + m;
+    const long long q = (long long)b * p.q_frame_stride + m;
     const CorrLevelDev &L = p.lv[lvl];
     const int k = L.k;
     const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
@@ -317,7 +330,7 @@ __global__ void __launch_bounds__(64, MVT_HARD_MINB) knn_corr_hard_kernel(const 
         const int m = (int)(e.qid % (unsigned)p.M);
         const unsigned fr = e.qid / (unsigned)p.M;
         const int b = (int)(fr % (unsigned)p.B), lvl = (int)(fr / (unsigned)p.B);
-        const long long q = (long long)b * p.M + m;
+        const long long q = (long long)b * p.q_frame_stride + m;
         const CorrLevelDev &L = p.lv[lvl];
         const float qx = __ldg(p.coords + q * 3), qy = __ldg(p.coords + q * 3 + 1), qz = __ldg(p.coords + q * 3 + 2);
         TopK tk;
@@ -514,12 +527,18 @@ MVT_EXPORT size_t mvt_knn_corr_workspace_bytes(int n_levels, int B, int M) {
     return 256 + sizeof(mvt::HardEntry) * (size_t)n_levels * (size_t)B * (size_t)M;
 }
 
-MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
-                            const void *targets, const float *coords, int add_offset, int add_xyz,
-                            float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
-                            void *workspace, int hard_query_mode, void *stream) {
+// out_peers != null: `out` is ignored; the records go to every rank's block (mvt_knn_corr_shared).
+static int knn_corr_impl(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
+                         const void *targets, const float *coords, long long query_frame_stride, int add_offset, int add_xyz,
+                         float *out, const mvt_peers *out_peers, long long out_row_stride, long long out_frame_stride,
+                         const int *idx_hint, int *idx_out, void *workspace, int hard_query_mode, void *stream) {
     using namespace mvt;
+    if (out_peers) {
+        MVT_CHECK_ARG(out_peers->n >= 1 && out_peers->n <= MVT_MAX_PEERS, "mvt_knn_corr_shared: out has %d peers", out_peers->n);
+        out = (float *)(out_peers->mc ? out_peers->mc : out_peers->ptr[0]);
+    }
     MVT_CHECK_ARG(levels && targets && coords && out, "mvt_knn_corr: null pointer");
+    MVT_CHECK_ARG(query_frame_stride >= M, "mvt_knn_corr: query frame stride %lld < M", query_frame_stride);
     MVT_CHECK_ARG(n_levels >= 1 && n_levels <= MVT_MAX_LEVELS, "mvt_knn_corr: n_levels must be 1..%d (got %d)", MVT_MAX_LEVELS, n_levels);
     MVT_CHECK_ARG(B > 0 && M >= 0 && C > 0, "mvt_knn_corr: bad shape B=%d M=%d C=%d", B, M, C);
     MVT_CHECK_ARG(G >= 1 && G <= C && C % G == 0, "mvt_knn_corr: groups=%d must divide C=%d", G, C);   // mvtracker.py:786-787
@@ -531,6 +550,9 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     p.targets = targets; p.coords = coords; p.out = out; p.row_stride = out_row_stride;
     p.frame_stride = out_frame_stride ? out_frame_stride : (long long)M * out_row_stride; p.idx_out = idx_out; p.idx_hint = idx_hint;
     p.scale = sqrtf((float)C / (float)G);
+    p.q_frame_stride = query_frame_stride;
+    p.n_peers = 0;
+    for (int r = 0; r < MVT_MAX_PEERS; ++r) p.peer[r] = nullptr;
     const int D = G + 3 * p.add_offset + 3 * p.add_xyz;
     bool fast = (C == 128 && G == 1);
     bool vec = (D == 4) && (((uintptr_t)out & 15) == 0) && (out_row_stride % 4 == 0) && (out_frame_stride % 4 == 0);
@@ -553,6 +575,19 @@ MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, i
     }
     for (int l = n_levels; l < MVT_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
     p.vec_out = vec ? 1 : 0;
+    if (out_peers) {
+        MVT_CHECK_ARG(vec, "mvt_knn_corr_shared: needs 16-byte records (groups = 1, add_offset = 1, add_xyz = 0) and 16-byte aligned rows");
+        if (out_peers->mc) {
+            p.vec_out = 2;
+        } else {
+            p.vec_out = 3;
+            p.n_peers = out_peers->n;
+            for (int r = 0; r < out_peers->n; ++r) {
+                MVT_CHECK_ARG(out_peers->ptr[r] && ((uintptr_t)out_peers->ptr[r] & 15) == 0, "mvt_knn_corr_shared: peer %d pointer", r);
+                p.peer[r] = (float *)out_peers->ptr[r];
+            }
+        }
+    }
     MVT_CHECK_ARG(feat_dtype == MVT_F32 || (fast && aligned), "mvt_knn_corr: bf16 features need C=128, groups=1, k<=16, 16-byte aligned rows");
     MVT_CHECK_ARG(B <= 65535, "mvt_knn_corr: B=%d too large", B);
     cudaStream_t st = (cudaStream_t)stream;
@@ -650,6 +685,24 @@ MVT_EXPORT int mvt_knn_corr_noalloc(const mvt_corr_level *levels, int n_levels, 
     // mvt_knn_corr clears the counters at the head of the scratch on `stream` before its kernels run, and launches only
     return mvt_knn_corr(levels, n_levels, B, M, C, G, feat_dtype, targets, coords, add_offset, add_xyz, out, out_row_stride,
                         out_frame_stride, idx_hint, idx_out, scratch, hard_query_mode, stream);
+}
+
+MVT_EXPORT int mvt_knn_corr(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int G, int feat_dtype,
+                            const void *targets, const float *coords, int add_offset, int add_xyz,
+                            float *out, long long out_row_stride, long long out_frame_stride, const int *idx_hint, int *idx_out,
+                            void *workspace, int hard_query_mode, void *stream) {
+    MVT_CHECK_ARG(out, "mvt_knn_corr: null pointer");
+    return knn_corr_impl(levels, n_levels, B, M, C, G, feat_dtype, targets, coords, M, add_offset, add_xyz, out, nullptr, out_row_stride,
+                         out_frame_stride, idx_hint, idx_out, workspace, hard_query_mode, stream);
+}
+
+MVT_EXPORT int mvt_knn_corr_shared(const mvt_corr_level *levels, int n_levels, int B, int M, int C, int feat_dtype,
+                                   const void *targets, const float *coords, long long query_frame_stride,
+                                   const mvt_peers *out, long long out_row_stride, long long out_frame_stride,
+                                   void *workspace, int hard_query_mode, void *stream) {
+    MVT_CHECK_ARG(out, "mvt_knn_corr_shared: null pointer");
+    return knn_corr_impl(levels, n_levels, B, M, C, 1, feat_dtype, targets, coords, query_frame_stride, 1, 0, nullptr, out, out_row_stride,
+                         out_frame_stride, nullptr, nullptr, workspace, hard_query_mode, stream);
 }
 
 MVT_EXPORT int mvt_debug_set_group_width(int lanes) {

@@ -486,3 +486,143 @@ class ShardedSequence:
                                   self.stride * (1 << l), self.tiles[l][sl], True) for l in self.levels]
         self.frames_built += n
         return self.win
+
+
+def frame_owner(t: int, world: int) -> int:
+    """Rank that owns global frame t: round robin, so that the 12 consecutive frames of a window AND the 6 frames an advance
+    adds spread over the ranks, and a frame keeps its owner (and its cached cloud) while windows slide over it."""
+    return t % world
+
+
+class FrameShardedSequence:
+    """Sliding windows of ONE sequence with the FRAMES of a window sharded over the ranks (mode "frames").
+
+    The frames of a window are the batch axis of the reference's kNN correlation (mvtracker.py:800-846 runs on [B*S, ...]:
+    frame s of the tracks only meets frame s of the cloud): independent units.  Rank r owns the global frames t with
+    t % world == r, builds and caches THEIR clouds of all views (a local CloudArena: nothing of a cloud ever crosses NVLink,
+    neither features nor search records), and per refinement iteration runs the single-GPU fused kernel on its frames x all
+    tracks; the kernel's epilogue stores every 16-byte result record into the [S, M, levels*k*4] block of EVERY rank
+    (multimem.st through the NVSwitch multicast address), one signal-pad barrier completes the block.  Per iteration the
+    node moves S*M*levels*k*16 bytes to each rank (50 MB for the panoptic window) and nothing else.
+
+        seq = FrameShardedSequence(V, H', W', C, dtype, device)
+        ts = seq.new_frames()                                  # global frame numbers this rank has to supply next
+        win = seq.push(fmaps[:, ts], depths[:, ts], intrs_win, extrs_win)
+        fcorrs = win.corr(ffeats, coords)                      # [S, M, width], complete on every rank
+
+    Results are bit-identical to the single-GPU kernel (it IS that kernel, on a subset of the frames)."""
+
+    def __init__(self, V: int, H: int, W: int, C: int, dtype, device, S: int = 12, hop: Optional[int] = None, stride=4,
+                 levels: Sequence[int] = (0, 1, 2, 3), k=16, slots: Optional[int] = None, group=None, backend=None,
+                 rank: Optional[int] = None, world: Optional[int] = None, shared_out: Optional[torch.Tensor] = None):
+        if backend is None:
+            from . import ops as backend
+        self.be, self.group = backend, group
+        live = dist.is_initialized() and world is None
+        self.world = world if world is not None else (dist.get_world_size(group) if live else 1)
+        self.rank = rank if rank is not None else (dist.get_rank(group) if live else 0)
+        self.S, self.hop, self.k, self.levels = int(S), int(hop or S // 2), k, list(levels)
+        self.width = len(self.levels) * k * 4
+        most = (self.S + self.world - 1) // self.world              # frames of one window a rank can own
+        if slots is None:
+            slots = 4 * most
+        if slots < 2 * most:
+            raise ValueError(f"{most} frames per window and rank need at least {2 * most} slots")
+        self.arena = backend.CloudArena(V, H, W, C, dtype, device, self.levels, slots, stride, want_valid=False)
+        self.device = device
+        self.shared_out = shared_out        # emulated ranks of one process: all of them store into this block, no exchange
+        if shared_out is not None or self.world == 1:
+            self.transport = "local"
+        elif symmetric_memory_available():
+            self.transport = "multicast"
+        else:
+            self.transport = "allreduce"    # gloo / no symmetric memory: zeros + the local frames' records, summed
+        self.mode = "frames"
+        self.windows, self.frames_built = 0, 0
+        self.slot0, self.run = 0, []        # global frame numbers of the current run, slot of run[i] = slot0 + i
+        self.clouds, self.pos0 = [], 0
+        self._res, self._flip = {}, 0
+
+    # ---- which frames --------------------------------------------------------------------------------------------------------
+    def window_frames(self, w: Optional[int] = None) -> range:
+        w = self.windows if w is None else w
+        return range(self.hop * w, self.hop * w + self.S)
+
+    def new_frames(self) -> List[int]:
+        """Global numbers of the frames the next push() adds AND this rank owns (ascending; may be empty)."""
+        w = self.windows
+        added = self.window_frames(w) if w == 0 else range(self.hop * w + self.S - self.hop, self.hop * w + self.S)
+        return [t for t in added if frame_owner(t, self.world) == self.rank]
+
+    # ---- build ---------------------------------------------------------------------------------------------------------------
+    def push(self, fmaps_new, depths_new, intrs_win, extrs_win) -> "FrameShardedSequence":
+        """fmaps_new [V, n, C, H', W'] / depths_new [V, n, H', W'] (or [V, n, 1, H', W']): the frames new_frames() named, ALL
+        views (None / n = 0 when this rank owns none of the added frames); intrs_win [V, S, 3, 3] / extrs_win [V, S, 3, 4]:
+        the cameras of the whole window (replicated: a few kilobytes)."""
+        be, ar = self.be, self.arena
+        new = self.new_frames()
+        n = 0 if fmaps_new is None else fmaps_new.shape[1]
+        if n != len(new):
+            raise ValueError(f"rank {self.rank} adds frames {new} to window {self.windows}, got {n} frames")
+        t0 = self.hop * self.windows
+        kept = [t for t in self.run if t >= t0]                    # a suffix of the run: frames the windows share
+        slot0 = self.slot0 + len(self.run) - len(kept)
+        if slot0 + len(kept) + n > ar.slots:                        # wrap: the kept frames go to the front
+            if kept:
+                ar.move(slot0, 0, len(kept))
+            slot0 = 0
+        self.slot0, self.run = slot0, kept + new
+        nw = len(self.run)
+        self.pos0 = (self.run[0] - t0) if nw else 0                # window positions pos0, pos0 + world, ...
+        self.clouds = []
+        if nw:
+            pos = [t - t0 for t in self.run]
+            cam = be.camera_prep(intrs_win[:, pos].contiguous(), extrs_win[:, pos].contiguous())      # record v * nw + i
+            if n:
+                first_new = len(kept)
+                ar.build(slot0 + first_new, fmaps_new, depths_new, cam.reshape(-1)[first_new * cam.shape[1]:], nw)
+            self.clouds = ar.run(slot0, nw, cam)
+        self.windows += 1
+        self.frames_built += n
+        return self
+
+    # ---- one refinement iteration ----------------------------------------------------------------------------------------------
+    def _result(self, S: int, M: int):
+        key = (S, M)
+        if key not in self._res:
+            if self.transport == "multicast":
+                self._res[key] = [SharedBuffer((S, M, self.width), torch.float32, self.device, self.group) for _ in range(2)]
+            else:
+                self._res[key] = [torch.empty(S, M, self.width, device=self.device, dtype=torch.float32) for _ in range(2)]
+        self._flip ^= 1
+        return self._res[key][self._flip]
+
+    def corr(self, targets: torch.Tensor, coords: torch.Tensor, out: Optional[torch.Tensor] = None, marks=None) -> torch.Tensor:
+        """targets [S, M, C], coords [S, M, 3] (all frames, replicated) -> [S, M, levels*k*4], complete on every rank.
+        Two result blocks alternate: the block an iteration stores into was last read two iterations ago, and every rank has
+        passed the barrier of the iteration in between, so one barrier per iteration orders everything."""
+        be = self.be
+        S, M, _ = targets.shape
+        lv = [(c, c.fvec, self.k) for c in self.clouds]
+        if self.transport == "local":
+            res = self.shared_out if self.shared_out is not None else self._result(S, M)
+            if self.clouds:
+                be.knn_corr_shared(lv, targets, coords, self.pos0, self.world, be.plain_peers(res), self.width)
+        elif self.transport == "multicast":
+            buf = self._result(S, M)
+            if self.clouds:
+                be.knn_corr_shared(lv, targets, coords, self.pos0, self.world, buf.peers, self.width)
+            if marks is not None:
+                marks.append(torch.cuda.Event(enable_timing=True)); marks[-1].record()
+            buf.barrier()
+            res = buf.t
+        else:
+            res = self._result(S, M)
+            res.zero_()
+            if self.clouds:
+                be.knn_corr_shared(lv, targets, coords, self.pos0, self.world, be.plain_peers(res), self.width)
+            dist.all_reduce(res, group=self.group)      # one non-zero contributor per record: the sum is exact
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res

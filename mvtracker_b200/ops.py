@@ -492,6 +492,58 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
     return (out, idx) if return_idx else out
 
 
+def offset_peers(peers: "_lib.Peers", nbytes: int) -> "_lib.Peers":
+    """The same symmetric buffer, every mapping (and the multicast address) advanced by nbytes."""
+    q = _lib.Peers()
+    q.n = peers.n
+    q.mc = (peers.mc + nbytes) if peers.mc else None
+    for r in range(peers.n):
+        q.ptr[r] = peers.ptr[r] + nbytes
+    return q
+
+
+def knn_corr_shared(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, frame0: int, frame_step: int,
+                    out_peers: "_lib.Peers", width: Optional[int] = None, defer="auto") -> None:
+    """The fused kernel for THIS rank's frames of a window, storing into every rank's result block (mvt_knn_corr_shared).
+    levels: (where, fvec, k) over the clouds of the B local frames, which are frames frame0, frame0 + frame_step, ... of
+    targets [S, M, C] / coords [S, M, 3] (replicated, contiguous).  out_peers: the [S, M, width] fp32 block of every rank
+    (its multicast address or the peer mappings; width = n_levels * k * 4 unless given)."""
+    _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
+    S, M, Cc = targets.shape
+    if not targets.is_contiguous() or not coords.is_contiguous() or coords.dtype != torch.float32:
+        raise MvtError("knn_corr_shared: targets / coords must be contiguous (coords fp32)")
+    n = len(levels)
+    lv = (CorrLevel * _lib.MAX_LEVELS)()
+    off, keep, B = 0, [], None
+    for i, (where, fvec, k) in enumerate(levels):
+        sr = _as_search(where)
+        keep.append(sr)
+        B = sr.B if B is None else B
+        if sr.B != B or fvec.dtype != targets.dtype or not fvec.is_contiguous() or fvec.shape[-1] != Cc:
+            raise MvtError("knn_corr_shared: levels must cover the same frames; fvec contiguous [B,N,C] of the targets' dtype")
+        lv[i] = CorrLevel(sr.c, fvec.data_ptr(), int(k), off)
+        off += int(k) * 4
+    width = off if width is None else int(width)
+    if B == 0:
+        return
+    if frame0 < 0 or frame_step < 1 or frame0 + (B - 1) * frame_step >= S or width < off:
+        raise MvtError(f"knn_corr_shared: frames {frame0} + i*{frame_step}, i < {B}, do not fit the {S}-frame window")
+    esz = targets.element_size()
+    ws, mode, pol = None, 0, None
+    if defer and not os.environ.get("MVT_NO_DEFER") and all(sr.c.tile_z for sr in keep):
+        ws = _corr_workspace(targets.device, n, B, M)
+        mode = 1
+        if defer == "auto":
+            pol = hard_query_policy(targets.device)
+            mode = pol.mode()
+    out = offset_peers(out_peers, frame0 * M * width * 4)
+    check(lib().mvt_knn_corr_shared(lv, n, B, M, Cc, _feat_dtype(targets), C.c_void_p(targets.data_ptr() + frame0 * M * Cc * esz),
+                                    C.c_void_p(coords.data_ptr() + frame0 * M * 12), frame_step * M, C.byref(out), width,
+                                    frame_step * M * width, _ptr(ws), mode, _stream()), "mvt_knn_corr_shared")
+    if pol is not None:
+        pol.record(ws, n * B * M)
+
+
 def knn_corr_backward(fvec: torch.Tensor, targets: torch.Tensor, idx: torch.Tensor, grad_out: torch.Tensor, groups: int = 1,
                       grad_targets: Optional[torch.Tensor] = None, grad_fvec: Optional[torch.Tensor] = None):
     """Row f2: backward of one level of corr_sample (mvtracker.py:827-835) given the forward pass's neighbour lists.

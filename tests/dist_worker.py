@@ -40,6 +40,30 @@ for dtype in (torch.float32, torch.bfloat16):
                     print(f"rank {rank}: MISMATCH mode={mode} (ran as {win.mode}) dtype={dtype} window {it} rep {rep}: "
                           f"{(got != want).any(-1).sum().item()} rows differ, timeout flag {err}", flush=True)
         dist.barrier()
+# mode "frames": frames sharded round robin, every rank's fused kernel stores into every rank's block (multimem.st / peer stores)
+from mvtracker_b200.dist import FrameShardedSequence
+T, hop = 24, 6
+for dtype in (torch.float32, torch.bfloat16):
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=T, C=128, zero_frac=0.1, seed=75, device=dev, dtype=dtype)
+    fm, dp, K, E = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous(), sc.extrs[0].contiguous()
+    seq = FrameShardedSequence(V, Hs, Ws, 128, dtype, dev, S=S, hop=hop)
+    for wdw in range(3):
+        win = slice(hop * wdw, hop * wdw + S)
+        full = ops.cloud_build(fm[:, win].contiguous(), dp[:, win].contiguous(), K[:, win].contiguous(), E[:, win].contiguous(),
+                               levels=range(4), want_spacing=False)
+        coords, targets = synth.make_tracks(full[0].xyz, N, S, seed=80 + wdw, dtype=dtype, valid=full[0].xyz4[..., 3] > 0)
+        coords[:, :11] += 1.5
+        want = ops.knn_corr([(c, c.fvec, 16) for c in full], targets, coords, defer=False)
+        ts = seq.new_frames()
+        seq.push(fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
+        for rep in range(3):
+            got = seq.corr(targets, coords)
+            torch.cuda.synchronize()
+            if not torch.equal(got, want) or seq.transport != "multicast":
+                ok = False
+                print(f"rank {rank}: MISMATCH mode=frames ({seq.transport}) dtype={dtype} window {wdw} rep {rep}: "
+                      f"{(got != want).any(-1).sum().item()} rows differ", flush=True)
+    dist.barrier()
 t = torch.tensor([0 if ok else 1], device=dev)
 dist.all_reduce(t)
 if rank == 0:

@@ -168,3 +168,117 @@ def test_view_ranges_partition_the_views():
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
     assert track_shard(8, 4096) == 512 and track_shard(3, 10) == 4
+
+
+# ---- mode "frames" (dist.FrameShardedSequence): frame ownership, the per-rank cloud cache, window positions, the exchange ----------
+class _FakeFrameCloud:
+    def __init__(self, level, frames, cam):
+        self.level, self.frames, self.cam, self.fvec = level, frames, cam, None
+
+
+class FrameBackend:
+    """Stand-in with the arena / kernel interface FrameShardedSequence uses.  A frame's "cloud" is what was built into its slot;
+    the "kernel" writes, for every local frame, a value that depends on that frame's inputs, its camera and its window
+    position's targets / coords -- any mix-up of slots, positions or cameras changes it."""
+
+    class CloudArena:
+        def __init__(self, V, H, W, C, dtype, device, levels, slots, stride, want_valid=False):
+            self.slots, self.levels, self.store, self.moves, self.built = slots, list(levels), {}, 0, []
+
+        def build(self, slot0, fmaps, depths, cam_run, cam_view_stride):
+            V, n = fmaps.shape[:2]
+            for i in range(n):
+                assert 0 <= slot0 + i < self.slots
+                cam_i = torch.stack([cam_run[(v * cam_view_stride + i) * 4:(v * cam_view_stride + i) * 4 + 4] for v in range(V)])
+                self.store[slot0 + i] = (fmaps[:, i].clone(), depths[:, i].clone(), cam_i.clone())
+                self.built.append(slot0 + i)
+
+        def run(self, slot0, n, cam):
+            assert slot0 + n <= self.slots
+            return [_FakeFrameCloud(l, [self.store[slot0 + i] for i in range(n)], cam) for l in self.levels]
+
+        def move(self, src, dst, n):
+            assert src >= dst + n
+            for i in range(n):
+                self.store[dst + i] = self.store[src + i]
+            self.moves += 1
+
+    @staticmethod
+    def camera_prep(intrs, extrs):          # [V, n, 3, 3], [V, n, 3, 4] -> [V * n, 4] records (v * n + i)
+        V, n = intrs.shape[:2]
+        return torch.cat([intrs.reshape(V * n, 9)[:, :1], extrs.reshape(V * n, 12)[:, 9:12]], 1).contiguous()
+
+    @staticmethod
+    def plain_peers(t):
+        return t
+
+    @staticmethod
+    def frame_value(level, fm, dp, cam, targets_f, coords_f, k):
+        a = fm[..., ::1 << level, ::1 << level].double().sum() + dp.double().sum() + (cam.double() * torch.arange(1, 5)).sum()
+        return (a + targets_f.double().sum(-1, keepdim=True) * (level + 1) + coords_f.double().sum(-1, keepdim=True)).float().expand(-1, k * 4)
+
+    @classmethod
+    def knn_corr_shared(cls, levels, targets, coords, frame0, frame_step, out, width):
+        for li, (c, _, k) in enumerate(levels):
+            for i, (fm, dp, cam_built) in enumerate(c.frames):
+                V = fm.shape[0]
+                cam_now = torch.stack([c.cam[v * len(c.frames) + i] for v in range(V)])
+                assert torch.equal(cam_now, cam_built)               # the window's record of this frame = the one it was built with
+                f = frame0 + i * frame_step
+                out[f, :, li * k * 4:(li + 1) * k * 4] = cls.frame_value(c.level, fm, dp, cam_now, targets[f], coords[f], k)
+
+
+def _frames_inputs(T=30, V=2, C=3, H=4, W=8, M=5, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    fm = torch.randn(V, T, C, H, W, generator=g)
+    dp = torch.rand(V, T, H, W, generator=g)
+    K = torch.randn(V, T, 3, 3, generator=g)
+    E = torch.randn(V, T, 3, 4, generator=g)
+    return fm, dp, K, E, M
+
+
+def _frames_worker(rank, world, port, S, hop, n_win, ret):
+    from mvtracker_b200.dist import FrameShardedSequence
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        fm, dp, K, E, M = _frames_inputs()
+        most = (S + world - 1) // world
+        seq = FrameShardedSequence(fm.shape[0], 4, 8, 3, torch.float32, "cpu", S=S, hop=hop, levels=(0, 1), k=2, backend=FrameBackend(),
+                                   slots=2 * most)
+        assert seq.transport == "allreduce"
+        outs = []
+        for w in range(n_win):
+            win = slice(hop * w, hop * w + S)
+            ts = seq.new_frames()
+            assert all(t % world == rank for t in ts)
+            seq.push(fm[:, ts] if ts else None, dp[:, ts] if ts else None, K[:, win], E[:, win])
+            g = torch.Generator().manual_seed(100 + w)
+            targets, coords = torch.randn(S, M, 3, generator=g), torch.randn(S, M, 3, generator=g)
+            outs.append(seq.corr(targets, coords).clone().numpy())
+        ret[rank] = (outs, seq.frames_built, sorted(seq.arena.built), seq.arena.moves)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,S,hop,n_win", [(2, 12, 6, 4), (3, 12, 6, 4), (2, 4, 1, 10)])
+def test_frame_sharded_sequence_over_gloo(world, S, hop, n_win):
+    port = 31500 + os.getpid() % 2000 + 10 * world + S
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_frames_worker, args=(world, port, S, hop, n_win, ret), nprocs=world, join=True)
+    fm, dp, K, E, M = _frames_inputs()
+    be = FrameBackend
+    for w in range(n_win):
+        g = torch.Generator().manual_seed(100 + w)
+        targets, coords = torch.randn(S, M, 3, generator=g), torch.randn(S, M, 3, generator=g)
+        want = torch.empty(S, M, 2 * 2 * 4)
+        for f in range(S):
+            t = hop * w + f
+            cam = be.camera_prep(K[:, t:t + 1], E[:, t:t + 1])
+            for l in (0, 1):
+                want[f, :, l * 8:(l + 1) * 8] = be.frame_value(l, fm[:, t], dp[:, t], cam, targets[f], coords[f], 2)
+        for r in range(world):
+            assert np.array_equal(ret[r][0][w], want.numpy()), f"window {w}, rank {r}"
+    assert sum(ret[r][1] for r in range(world)) == S + (n_win - 1) * hop        # every frame built once, by its owner
+    assert any(ret[r][3] > 0 for r in range(world))                               # the small arenas did wrap around

@@ -195,3 +195,42 @@ def test_shard_iter_single_rank_equals_fused_kernel(dtype, no_local, monkeypatch
     want = ops.knn_corr([(cl2[0], cl2[0].fvec, 4)], targets, coords, defer=False)
     torch.cuda.synchronize()
     assert torch.equal(got[:, :, :16], want) and (got[:, :, 16 + 8:] == 0).all() and not st2.error()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_frame_sharded_sequence_equals_fused_kernel(world, dtype):
+    """mode "frames" (dist.FrameShardedSequence): `world` emulated ranks, each owning the frames t % world == r with a cloud
+    cache of its own, store through mvt_knn_corr_shared into one result block -- which must equal the single-GPU fused
+    kernel on the freshly built window, for four sliding windows (cache reuse, wrap-around of the small arenas, per-frame
+    cameras, ranks that add no frame to a window)."""
+    from mvtracker_b200.dist import FrameShardedSequence
+    V, Hs, Ws, S, hop, M, T = 3, 40, 56, 12, 6, 301, 30
+    sc = synth.make_scene(V, Hs * 4, Ws * 4, S=T, C=128, zero_frac=0.1, seed=17, device=DEV, dtype=dtype)
+    fm, dp, K = sc.fmaps[0], sc.depths[0, :, :, 0].contiguous(), sc.intrs[0].contiguous()
+    E = sc.extrs[0].clone()
+    E[:, :, :, 3] += 0.01 * torch.arange(T, device=DEV, dtype=torch.float32)[None, :, None]      # cameras differ per frame
+    out = torch.empty(S, M, 256, device=DEV)
+    most = (S + world - 1) // world
+    seqs = [FrameShardedSequence(V, Hs, Ws, 128, dtype, DEV, S=S, hop=hop, rank=r, world=world, shared_out=out, slots=2 * most)
+            for r in range(world)]
+    for w in range(4):
+        t0 = hop * w
+        win = slice(t0, t0 + S)
+        full = ops.cloud_build(fm[:, win].contiguous(), dp[:, win].contiguous(), K[:, win].contiguous(), E[:, win].contiguous(),
+                               levels=range(4), want_valid=True, want_tiles=True)
+        coords, targets = synth.make_tracks(full[0].xyz, M, S, seed=40 + w, valid=full[0].valid, dtype=dtype)
+        coords[:, :9] += 0.8                                      # free-space queries (the deferred path)
+        want = ops.knn_corr([(c, c.fvec, 16) for c in full], targets, coords, defer=False)
+        out.fill_(float("nan"))
+        added = []
+        for seq in seqs:
+            ts = seq.new_frames()
+            added += ts
+            seq.push(fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
+        assert sorted(added) == list(range(t0, t0 + S) if w == 0 else range(t0 + S - hop, t0 + S))
+        for rep in range(2):
+            for seq in seqs:
+                assert seq.corr(targets, coords) is out
+            assert torch.equal(out, want), f"window {w}: {(out != want).any(-1).sum().item()} rows differ"
+    assert sum(seq.frames_built for seq in seqs) == S + 3 * hop          # every frame was built exactly once, by its owner

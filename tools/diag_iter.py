@@ -11,14 +11,14 @@ import torch
 import torch.distributed as dist
 
 from mvtracker_b200 import ops, synth
-from mvtracker_b200.dist import ShardedWindow, view_range
+from mvtracker_b200.dist import FrameShardedSequence, ShardedWindow, view_range
 
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 name = sys.argv[1] if len(sys.argv) > 1 else "panoptic"
-modes = sys.argv[2].split(",") if len(sys.argv) > 2 else ["fused", "p2p"]
+modes = sys.argv[2].split(",") if len(sys.argv) > 2 else ["frames", "fused", "p2p"]
 w = synth.WORKLOADS[name]
 V, N, S = w["V"], w["N"], 12
 sc = synth.make_scene(V, w["H"], w["W"], S=S, C=128, zero_frac=0.05, seed=72, device=dev)
@@ -29,8 +29,13 @@ want = ops.knn_corr([(c, c.fvec, 16) for c in full], targets, coords, defer=Fals
 v0, v1 = view_range(rank, world, V)
 knobs = " ".join(f"{k[10:].lower()}={os.environ[k]}" for k in ("MVT_SHARD_EARLY_PCT", "MVT_SHARD_DEFER", "MVT_SHARD_NO_LOCAL") if k in os.environ)
 for mode in modes:
-    win = ShardedWindow.build(fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous(),
-                              v0, V, intrs_all=K, extrs_all=E, mode=mode)
+    if mode == "frames":
+        win = FrameShardedSequence(V, w["H"] // 4, w["W"] // 4, 128, torch.float32, dev, S=S)
+        ts = win.new_frames()
+        win.push(fm[:, ts].contiguous(), dp[:, ts].contiguous(), K, E)
+    else:
+        win = ShardedWindow.build(fm[v0:v1].contiguous(), dp[v0:v1].contiguous(), K[v0:v1].contiguous(), E[v0:v1].contiguous(),
+                                  v0, V, intrs_all=K, extrs_all=E, mode=mode)
     for _ in range(3):
         got = win.corr(targets, coords)
     torch.cuda.synchronize()
