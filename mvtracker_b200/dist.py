@@ -540,7 +540,7 @@ class FrameShardedSequence:
         self.mode = "frames"
         self.windows, self.frames_built = 0, 0
         self.slot0, self.run = 0, []        # global frame numbers of the current run, slot of run[i] = slot0 + i
-        self.clouds, self.pos0 = [], 0
+        self.clouds, self.searches, self.pos0 = [], [], 0
         self._res, self._flip = {}, 0
 
     # ---- which frames --------------------------------------------------------------------------------------------------------
@@ -574,14 +574,18 @@ class FrameShardedSequence:
         self.slot0, self.run = slot0, kept + new
         nw = len(self.run)
         self.pos0 = (self.run[0] - t0) if nw else 0                # window positions pos0, pos0 + world, ...
-        self.clouds = []
+        self.clouds, self.searches = [], []
         if nw:
-            pos = [t - t0 for t in self.run]
-            cam = be.camera_prep(intrs_win[:, pos].contiguous(), extrs_win[:, pos].contiguous())      # record v * nw + i
+            # the local frames' camera records, record v * nw + i (a strided slice of the window's: no index tensor, no host copy)
+            cam_win = be.camera_prep(intrs_win, extrs_win)
+            V = intrs_win.shape[0]
+            cam = cam_win.view(V, self.S, -1)[:, self.pos0::self.world][:, :nw].contiguous().view(V * nw, -1)
             if n:
                 first_new = len(kept)
                 ar.build(slot0 + first_new, fmaps_new, depths_new, cam.reshape(-1)[first_new * cam.shape[1]:], nw)
             self.clouds = ar.run(slot0, nw, cam)
+            make = getattr(be, "Search", None)         # the kernels' search descriptors, made once per window
+            self.searches = [make.from_cloud(c) for c in self.clouds] if make is not None else list(self.clouds)
         self.windows += 1
         self.frames_built += n
         return self
@@ -603,7 +607,7 @@ class FrameShardedSequence:
         passed the barrier of the iteration in between, so one barrier per iteration orders everything."""
         be = self.be
         S, M, _ = targets.shape
-        lv = [(c, c.fvec, self.k) for c in self.clouds]
+        lv = [(sr, c.fvec, self.k) for sr, c in zip(self.searches, self.clouds)]
         if self.transport == "local":
             res = self.shared_out if self.shared_out is not None else self._result(S, M)
             if self.clouds:
