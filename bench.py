@@ -506,7 +506,9 @@ def run_ours(args):
     for e in evs:
         step(e)
     # keep the GPU busy long enough for nvidia-smi to have samples of the loaded clocks
-    while time.time() - t_wall0 < 1.2:
+    # (the SAME number of extra steps on every rank -- from the all-reduced time, not from each rank's own wall clock: the
+    # sharded modes synchronise inside step(), ranks that enqueue different numbers of steps would wait for each other forever)
+    for _ in range(max(0, min(2000, int((1200.0 - total_ms) / max(ms_step, 1e-3)) + 1))):
         step()
     sync()
     t_cloud = sum(e[0].elapsed_time(e[1]) for e in evs) / n_split
