@@ -540,7 +540,7 @@ class FrameShardedSequence:
         self.mode = "frames"
         self.windows, self.frames_built = 0, 0
         self.slot0, self.run = 0, []        # global frame numbers of the current run, slot of run[i] = slot0 + i
-        self.clouds, self.searches, self.pos0 = [], [], 0
+        self.clouds, self.plan, self.pos0 = [], None, 0
         self._res, self._flip = {}, 0
 
     # ---- which frames --------------------------------------------------------------------------------------------------------
@@ -574,7 +574,7 @@ class FrameShardedSequence:
         self.slot0, self.run = slot0, kept + new
         nw = len(self.run)
         self.pos0 = (self.run[0] - t0) if nw else 0                # window positions pos0, pos0 + world, ...
-        self.clouds, self.searches = [], []
+        self.clouds, self.plan = [], None
         if nw:
             # the local frames' camera records, record v * nw + i (a strided slice of the window's: no index tensor, no host copy)
             cam_win = be.camera_prep(intrs_win, extrs_win)
@@ -584,8 +584,9 @@ class FrameShardedSequence:
                 first_new = len(kept)
                 ar.build(slot0 + first_new, fmaps_new, depths_new, cam.reshape(-1)[first_new * cam.shape[1]:], nw)
             self.clouds = ar.run(slot0, nw, cam)
-            make = getattr(be, "Search", None)         # the kernels' search descriptors, made once per window
-            self.searches = [make.from_cloud(c) for c in self.clouds] if make is not None else list(self.clouds)
+            make = getattr(be, "CorrPlan", None)       # the kernel's per-level descriptors, made once per window
+            lv = [(c, c.fvec, self.k) for c in self.clouds]
+            self.plan = make(lv) if make is not None else lv
         self.windows += 1
         self.frames_built += n
         return self
@@ -607,7 +608,7 @@ class FrameShardedSequence:
         passed the barrier of the iteration in between, so one barrier per iteration orders everything."""
         be = self.be
         S, M, _ = targets.shape
-        lv = [(sr, c.fvec, self.k) for sr, c in zip(self.searches, self.clouds)]
+        lv = self.plan
         if self.transport == "local":
             res = self.shared_out if self.shared_out is not None else self._result(S, M)
             if self.clouds:

@@ -502,44 +502,66 @@ def offset_peers(peers: "_lib.Peers", nbytes: int) -> "_lib.Peers":
     return q
 
 
-def knn_corr_shared(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, frame0: int, frame_step: int,
+class CorrPlan:
+    """The per-level descriptors of a fused correlation call, made once for a set of clouds and reused by every launch on
+    them (a refinement loop calls the kernel `iters` times per window on the same clouds: the ctypes structs are not rebuilt)."""
+
+    def __init__(self, levels: Sequence):
+        self.n = len(levels)
+        self.lv = (CorrLevel * _lib.MAX_LEVELS)()
+        self.keep, self.B, off = [], None, 0
+        self.dtype, self.C = levels[0][1].dtype, levels[0][1].shape[-1]
+        for i, (where, fvec, k) in enumerate(levels):
+            sr = _as_search(where)
+            self.keep.append((sr, fvec))
+            self.B = sr.B if self.B is None else self.B
+            if sr.B != self.B or fvec.dtype != self.dtype or not fvec.is_contiguous() or fvec.shape[-1] != self.C:
+                raise MvtError("CorrPlan: levels must cover the same frames; fvec contiguous [B,N,C] of one dtype")
+            self.lv[i] = CorrLevel(sr.c, fvec.data_ptr(), int(k), off)
+            off += int(k) * 4
+        self.width = off
+        self.tiles = all(sr.c.tile_z for sr, _ in self.keep)
+        self.fd = _feat_dtype(levels[0][1])
+        self._peers = {}
+
+    def peers_at(self, out_peers: "_lib.Peers", nbytes: int):
+        key = (out_peers.ptr[0], out_peers.mc, nbytes)
+        q = self._peers.get(key)
+        if q is None:
+            q = self._peers[key] = offset_peers(out_peers, nbytes)
+        return q
+
+
+def knn_corr_shared(levels, targets: torch.Tensor, coords: torch.Tensor, frame0: int, frame_step: int,
                     out_peers: "_lib.Peers", width: Optional[int] = None, defer="auto") -> None:
     """The fused kernel for THIS rank's frames of a window, storing into every rank's result block (mvt_knn_corr_shared).
-    levels: (where, fvec, k) over the clouds of the B local frames, which are frames frame0, frame0 + frame_step, ... of
-    targets [S, M, C] / coords [S, M, 3] (replicated, contiguous).  out_peers: the [S, M, width] fp32 block of every rank
-    (its multicast address or the peer mappings; width = n_levels * k * 4 unless given)."""
-    _need_cuda(targets, "targets"); _need_cuda(coords, "coords")
+    levels: (where, fvec, k) over the clouds of the B local frames -- or a CorrPlan made from them --, which are frames
+    frame0, frame0 + frame_step, ... of targets [S, M, C] / coords [S, M, 3] (replicated, contiguous).  out_peers: the
+    [S, M, width] fp32 block of every rank (its multicast address or the peer mappings; width = n_levels * k * 4 unless given)."""
+    plan = levels if isinstance(levels, CorrPlan) else CorrPlan(levels)
     S, M, Cc = targets.shape
-    if not targets.is_contiguous() or not coords.is_contiguous() or coords.dtype != torch.float32:
-        raise MvtError("knn_corr_shared: targets / coords must be contiguous (coords fp32)")
-    n = len(levels)
-    lv = (CorrLevel * _lib.MAX_LEVELS)()
-    off, keep, B = 0, [], None
-    for i, (where, fvec, k) in enumerate(levels):
-        sr = _as_search(where)
-        keep.append(sr)
-        B = sr.B if B is None else B
-        if sr.B != B or fvec.dtype != targets.dtype or not fvec.is_contiguous() or fvec.shape[-1] != Cc:
-            raise MvtError("knn_corr_shared: levels must cover the same frames; fvec contiguous [B,N,C] of the targets' dtype")
-        lv[i] = CorrLevel(sr.c, fvec.data_ptr(), int(k), off)
-        off += int(k) * 4
-    width = off if width is None else int(width)
+    if not (targets.is_cuda and coords.is_cuda and targets.is_contiguous() and coords.is_contiguous()) or coords.dtype != torch.float32:
+        raise MvtError("knn_corr_shared: targets / coords must be contiguous CUDA tensors (coords fp32)")
+    if targets.dtype != plan.dtype or Cc != plan.C:
+        raise MvtError("knn_corr_shared: targets do not match the clouds' features")
+    n, B = plan.n, plan.B
+    width = plan.width if width is None else int(width)
     if B == 0:
         return
-    if frame0 < 0 or frame_step < 1 or frame0 + (B - 1) * frame_step >= S or width < off:
+    if frame0 < 0 or frame_step < 1 or frame0 + (B - 1) * frame_step >= S or width < plan.width:
         raise MvtError(f"knn_corr_shared: frames {frame0} + i*{frame_step}, i < {B}, do not fit the {S}-frame window")
-    esz = targets.element_size()
     ws, mode, pol = None, 0, None
-    if defer and not os.environ.get("MVT_NO_DEFER") and all(sr.c.tile_z for sr in keep):
+    if defer and plan.tiles and not os.environ.get("MVT_NO_DEFER"):
         ws = _corr_workspace(targets.device, n, B, M)
         mode = 1
         if defer == "auto":
             pol = hard_query_policy(targets.device)
             mode = pol.mode()
-    out = offset_peers(out_peers, frame0 * M * width * 4)
-    check(lib().mvt_knn_corr_shared(lv, n, B, M, Cc, _feat_dtype(targets), C.c_void_p(targets.data_ptr() + frame0 * M * Cc * esz),
-                                    C.c_void_p(coords.data_ptr() + frame0 * M * 12), frame_step * M, C.byref(out), width,
-                                    frame_step * M * width, _ptr(ws), mode, _stream()), "mvt_knn_corr_shared")
+    out = plan.peers_at(out_peers, frame0 * M * width * 4)
+    check(lib().mvt_knn_corr_shared(plan.lv, n, B, M, Cc, plan.fd, targets.data_ptr() + frame0 * M * Cc * targets.element_size(),
+                                    coords.data_ptr() + frame0 * M * 12, frame_step * M, C.byref(out), width,
+                                    frame_step * M * width, None if ws is None else ws.data_ptr(), mode,
+                                    torch.cuda.current_stream().cuda_stream), "mvt_knn_corr_shared")
     if pol is not None:
         pol.record(ws, n * B * M)
 
