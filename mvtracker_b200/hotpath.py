@@ -113,6 +113,10 @@ class WindowSequence:
         self.slot0 = None           # first slot of the current window's run
         self.windows = 0
         self.frames_built = 0
+        # wrap-around: the S - hop frames the NEXT window keeps are copied to the front of the arena on a side stream while the
+        # current window's iterations run (they only read the run; the correlation kernel leaves most of the HBM bandwidth idle)
+        self._side = torch.cuda.Stream(device=device) if torch.device(device).type == "cuda" else None
+        self._moved = None          # event: the copy to the front has finished
 
     def push(self, fmaps_new, depths_new, intrs_win, extrs_win) -> WindowClouds:
         """fmaps_new [V, n, C, H', W'] / depths_new [V, n, H', W'] (or [V, n, 1, H', W']): the frames this window adds -- all S
@@ -128,7 +132,11 @@ class WindowSequence:
                 raise ValueError(f"a later window adds {hop} frames, got {n}")
             self.slot0 += hop
             if self.slot0 + S > ar.slots:                      # wrap: keep the S - hop shared frames, at the front
-                ar.move(self.slot0, 0, S - hop)
+                if self._moved is not None:                    # ... where the side stream has put them already
+                    torch.cuda.current_stream().wait_event(self._moved)
+                    self._moved = None
+                else:
+                    ar.move(self.slot0, 0, S - hop)
                 self.slot0 = 0
             first_new = S - hop
         cam = ops.camera_prep(intrs_win, extrs_win)             # [V*S, CAM_STRIDE], record v*S + s
@@ -136,4 +144,13 @@ class WindowSequence:
         ar.build(self.slot0 + first_new, fmaps_new, depths_new, cam_run, S, self.mode)
         self.windows += 1
         self.frames_built += n
+        nxt = self.slot0 + hop
+        if self._side is not None and nxt + S > ar.slots and self.slot0 >= S and not torch.cuda.is_current_stream_capturing():
+            # the next push wraps: start moving the frames it keeps (this window's last S - hop) now; slot0 >= S: neither this
+            # window's run nor the one returned before it touches the front slots
+            self._side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self._side):
+                ar.move(nxt, 0, S - hop)
+                self._moved = torch.cuda.Event()
+                self._moved.record()
         return WindowClouds(ar.run(self.slot0, S, cam), None, *self.args)
