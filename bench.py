@@ -721,8 +721,9 @@ def time_distributions(args, w, ops, synth, WindowClouds, win, fm, dp, K, E, bas
     out_buf = torch.empty(S_WINDOW, N, LEVELS * K_NN * 4, device=dev, dtype=torch.float32)
 
     def timed(wn, coords):
-        for _ in range(2):
-            wn.corr(base_targets, coords, out=out_buf)
+        for _ in range(10):         # steady state of THIS distribution: ops.knn_corr's deferral policy samples every 4th launch
+            wn.corr(base_targets, coords, out=out_buf)      # and acts one call later (no host sync in the product path)
+            torch.cuda.synchronize()
         ms = 0.0
         for _ in range(reps):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -730,7 +731,9 @@ def time_distributions(args, w, ops, synth, WindowClouds, win, fm, dp, K, E, bas
             torch.cuda.synchronize()
             ms += a.elapsed_time(b)
         ms /= reps
-        return {"ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak}
+        pol = ops.hard_query_policy(dev)
+        return {"ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "deferral": bool(pol.deferring),
+                "hard_query_fraction": pol.last_fraction}
 
     res = {}
     c0 = win.clouds[0]
