@@ -67,6 +67,9 @@ def parse_args():
                     help="N = 1: iterations 2..4 of a window start their searches from the previous iteration's neighbours "
                          "(exact; off by default so that every timed iteration does the full cold search)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-prefetch", action="store_true",
+                    help="N > 1, --dist-mode frames: build a window's new frames at the start of its step instead of on a side stream "
+                         "during the previous window's iterations")
     ap.add_argument("--no-verify", action="store_true", help="skip the sampled check of the last step's output against the oracle")
     ap.add_argument("--no-distributions", action="store_true",
                     help="skip the extra timed track distributions (static init, 40 %% invalid depth); N = 1 only")
@@ -302,6 +305,8 @@ def config_dict(w, args, world=1, weak=False):
              f"straight into every rank's buffers (symmetric memory, NVSwitch multicast stores), two signal-pad barriers per iteration, no NCCL on the data path" if args.dist_mode == "p2p" else
              f"{world} GPUs: views sharded for the cloud build (features stay local), candidate keys all-to-all per track shard (two bounded phases), merged indices all-gathered, result records all-reduced (NCCL)"),"workload": f"{w['name']}: {w['V']} views {w['H']}x{w['W']} (stride {STRIDE} -> {w['Hs']}x{w['Ws']}), "
                         f"{w['V'] * w['Hs'] * w['Ws']} fused points/frame at level 0, window S={S_WINDOW}, {w['N']} tracks",
+            "pipeline": ("window j+1's new frames are built on a side stream while window j's iterations run (every build inside the timed region)"
+                         if world > 1 and not weak and getattr(args, "dist_mode", "") == "frames" and not getattr(args, "no_prefetch", False) else "none"),
             "levels": LEVELS, "k": K_NN, "iters": args.iters, "warm_start": bool(getattr(args, "warm_start", False)), "C": C_FEAT, "groups": 1, "search": getattr(args, "search", None),
             "queries_per_step": args.iters * LEVELS * S_WINDOW * w["N"], "zero_depth_frac": args.zero_frac,
             "step": ("one window advance of a sequence: 6 new frames built into the per-frame cloud cache (24 distinct frames, cycled: the new "
@@ -409,15 +414,22 @@ def run_ours(args):
     def step(ev=None):
         if ev is not None: ev[0].record()
         if advance and frames_mode:
+            # software pipeline: window j + 1's frames are built on a side stream while window j's iterations run (every build is
+            # inside the timed region; --no-prefetch builds at the start of the step instead)
+            def inputs(seq, jj):
+                ts = seq.new_frames()
+                new = local_run(ts) if ts else None
+                return (fm_pool[:, new] if ts else None, dp_pool[:, new] if ts else None, cams_win[jj % 4][0], cams_win[jj % 4][1])
             if state["seq"] is None:
                 state["seq"] = FrameShardedSequence(V, w["Hs"], w["Ws"], C_FEAT, fdtype, dev, S=S_WINDOW, k=K_NN)
                 j = 0
+                win = state["seq"].push(*inputs(state["seq"], 0))
             else:
                 j = state["j"] + 1
+                win = state["seq"].push() if not args.no_prefetch else state["seq"].push(*inputs(state["seq"], j))
+            if not args.no_prefetch:
+                state["seq"].prefetch(*inputs(state["seq"], j + 1))
             t = j % 4
-            ts = state["seq"].new_frames()
-            new = local_run(ts) if ts else None
-            win = state["seq"].push(fm_pool[:, new] if ts else None, dp_pool[:, new] if ts else None, cams_win[t][0], cams_win[t][1])
             state["j"] = j
             cw = coords_win[t]
         elif advance:
@@ -512,6 +524,10 @@ def run_ours(args):
         step()
     sync()
     t_cloud = sum(e[0].elapsed_time(e[1]) for e in evs) / n_split
+    overlapped = frames_mode and not args.no_prefetch
+    if overlapped:      # the build ran on the side stream, overlapped with the iterations: its own duration (last step's), for the record
+        lb = state["seq"].last_build
+        t_cloud = max(t_cloud, lb[0].elapsed_time(lb[1])) if lb is not None else t_cloud
     t_grid = sum(e[1].elapsed_time(e[2]) for e in evs) / n_split
     t_corr = sum(e[2 + i].elapsed_time(e[3 + i]) for e in evs for i in range(iters)) / (n_split * iters)
     clocks = sampler.window(t_wall0, time.time()) if sampler else None
@@ -529,7 +545,8 @@ def run_ours(args):
                      "fused knn_corr kernel on this rank's frames, records stored into every rank's block + one barrier (per iteration)" if frames_mode else
                      "search kernel + index exchange + corr_from_idx + result exchange (per iteration)"},
         "cloud_build": {"ms": t_cloud, "launches_per_step": 1, "alg_bytes": cloud_bytes, "gbs": cloud_bytes / t_cloud / 1e6, "frames_built": n_built,
-                        "what": "camera_prep + cloud_build (4 levels, one pass) + tile depth tables" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")},
+                        "what": "camera_prep + cloud_build (4 levels, one pass) + tile depth tables" + ("" if pw == 1 or args.dist_mode != "tracks" else " + all-gather of the 16-byte records")
+                                + (" -- on a side stream, overlapped with the previous window's iterations (its own duration on rank 0; not additive with the iterations)" if overlapped else "")},
     }
     if args.search == "grid" and pw == 1:
         kern["grid_build"] = {"ms": t_grid, "launches_per_step": 6, "alg_bytes": 0, "gbs": 0.0}

@@ -542,6 +542,7 @@ class FrameShardedSequence:
         self.slot0, self.run = 0, []        # global frame numbers of the current run, slot of run[i] = slot0 + i
         self.clouds, self.plan, self.pos0 = [], None, 0
         self._res, self._flip = {}, 0
+        self._pending, self._side, self.last_build = None, None, None
 
     # ---- which frames --------------------------------------------------------------------------------------------------------
     def window_frames(self, w: Optional[int] = None) -> range:
@@ -555,10 +556,8 @@ class FrameShardedSequence:
         return [t for t in added if frame_owner(t, self.world) == self.rank]
 
     # ---- build ---------------------------------------------------------------------------------------------------------------
-    def push(self, fmaps_new, depths_new, intrs_win, extrs_win) -> "FrameShardedSequence":
-        """fmaps_new [V, n, C, H', W'] / depths_new [V, n, H', W'] (or [V, n, 1, H', W']): the frames new_frames() named, ALL
-        views (None / n = 0 when this rank owns none of the added frames); intrs_win [V, S, 3, 3] / extrs_win [V, S, 3, 4]:
-        the cameras of the whole window (replicated: a few kilobytes)."""
+    def _stage(self, fmaps_new, depths_new, intrs_win, extrs_win):
+        """Builds (on the current stream) what the next window adds and returns that window's state; self is not changed."""
         be, ar = self.be, self.arena
         new = self.new_frames()
         n = 0 if fmaps_new is None else fmaps_new.shape[1]
@@ -571,25 +570,69 @@ class FrameShardedSequence:
             if kept:
                 ar.move(slot0, 0, len(kept))
             slot0 = 0
-        self.slot0, self.run = slot0, kept + new
-        nw = len(self.run)
-        self.pos0 = (self.run[0] - t0) if nw else 0                # window positions pos0, pos0 + world, ...
-        self.clouds, self.plan = [], None
+        run = kept + new
+        nw = len(run)
+        pos0 = (run[0] - t0) if nw else 0                           # window positions pos0, pos0 + world, ...
+        clouds, plan = [], None
         if nw:
             # the local frames' camera records, record v * nw + i (a strided slice of the window's: no index tensor, no host copy)
             cam_win = be.camera_prep(intrs_win, extrs_win)
             V = intrs_win.shape[0]
-            cam = cam_win.view(V, self.S, -1)[:, self.pos0::self.world][:, :nw].contiguous().view(V * nw, -1)
+            cam = cam_win.view(V, self.S, -1)[:, pos0::self.world][:, :nw].contiguous().view(V * nw, -1)
             if n:
                 first_new = len(kept)
                 ar.build(slot0 + first_new, fmaps_new, depths_new, cam.reshape(-1)[first_new * cam.shape[1]:], nw)
-            self.clouds = ar.run(slot0, nw, cam)
+            clouds = ar.run(slot0, nw, cam)
             make = getattr(be, "CorrPlan", None)       # the kernel's per-level descriptors, made once per window
-            lv = [(c, c.fvec, self.k) for c in self.clouds]
-            self.plan = make(lv) if make is not None else lv
+            lv = [(c, c.fvec, self.k) for c in clouds]
+            plan = make(lv) if make is not None else lv
+        return dict(slot0=slot0, run=run, pos0=pos0, clouds=clouds, plan=plan, n=n)
+
+    def _adopt(self, st) -> "FrameShardedSequence":
+        self.slot0, self.run, self.pos0, self.clouds, self.plan = st["slot0"], st["run"], st["pos0"], st["clouds"], st["plan"]
         self.windows += 1
-        self.frames_built += n
+        self.frames_built += st["n"]
         return self
+
+    def push(self, fmaps_new=None, depths_new=None, intrs_win=None, extrs_win=None) -> "FrameShardedSequence":
+        """fmaps_new [V, n, C, H', W'] / depths_new [V, n, H', W'] (or [V, n, 1, H', W']): the frames new_frames() named, ALL
+        views (None / n = 0 when this rank owns none of the added frames); intrs_win [V, S, 3, 3] / extrs_win [V, S, 3, 4]:
+        the cameras of the whole window (replicated: a few kilobytes).  After prefetch(...): push() without arguments."""
+        if self._pending is not None:
+            st, done = self._pending
+            self._pending = None
+            if done is not None:
+                torch.cuda.current_stream().wait_event(done)
+            return self._adopt(st)
+        if intrs_win is None:
+            raise ValueError("push() without arguments needs a prefetch() before it")
+        return self._adopt(self._stage(fmaps_new, depths_new, intrs_win, extrs_win))
+
+    def prefetch(self, fmaps_new, depths_new, intrs_win, extrs_win) -> None:
+        """push()'s work for the NEXT window, started now on a side stream: its frames are built (and, at a wrap-around, the
+        frames it keeps are moved) while the current window's iterations run -- those only read the current run, and a rank's
+        correlation kernels leave the GPU idle at every barrier and in their tails (at N = 8 a rank computes 1-2 frames per
+        iteration).  The inputs must stay untouched until the push() that follows.  Needs an arena of >= 3 windows' worth of
+        local frames (the next run must not overlap the current one); a smaller arena builds at push() as before."""
+        most = (self.S + self.world - 1) // self.world
+        if self._pending is not None:
+            raise RuntimeError("one prefetch() per push()")
+        if self.device is None or torch.device(self.device).type != "cuda" or self.arena.slots < 3 * most or self.windows == 0:
+            self._pending = (self._stage(fmaps_new, depths_new, intrs_win, extrs_win), None)
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        main = torch.cuda.current_stream()
+        self._side.wait_stream(main)                # inputs are ready; earlier readers of the slots about to be written are done
+        with torch.cuda.stream(self._side):
+            t_a = torch.cuda.Event(enable_timing=True); t_a.record()
+            st = self._stage(fmaps_new, depths_new, intrs_win, extrs_win)
+            done = torch.cuda.Event(enable_timing=True); done.record()
+        for c in st["clouds"]:
+            if c.cam is not None:
+                c.cam.record_stream(main)           # allocated on the side stream, read by the main stream's kernels later
+        self.last_build = (t_a, done)
+        self._pending = (st, done)
 
     # ---- one refinement iteration ----------------------------------------------------------------------------------------------
     def _result(self, S: int, M: int):

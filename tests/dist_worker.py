@@ -54,10 +54,18 @@ for dtype in (torch.float32, torch.bfloat16):
         coords, targets = synth.make_tracks(full[0].xyz, N, S, seed=80 + wdw, dtype=dtype, valid=full[0].xyz4[..., 3] > 0)
         coords[:, :11] += 1.5
         want = ops.knn_corr([(c, c.fvec, 16) for c in full], targets, coords, defer=False)
-        ts = seq.new_frames()
-        seq.push(fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
+        if wdw == 0:
+            ts = seq.new_frames()
+            seq.push(fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
+        else:
+            seq.push()                                  # the window that was prefetched during the previous window's iterations
         for rep in range(3):
             got = seq.corr(targets, coords)
+            if rep == 0 and wdw < 2:                    # build the next window's frames on the side stream, under the iterations
+                ts = seq.new_frames()
+                nxt = slice(hop * (wdw + 1), hop * (wdw + 1) + S)
+                held = (fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, nxt], E[:, nxt])
+                seq.prefetch(*held)
             torch.cuda.synchronize()
             if not torch.equal(got, want) or seq.transport != "multicast":
                 ok = False

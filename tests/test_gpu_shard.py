@@ -197,9 +197,10 @@ def test_shard_iter_single_rank_equals_fused_kernel(dtype, no_local, monkeypatch
     assert torch.equal(got[:, :, :16], want) and (got[:, :, 16 + 8:] == 0).all() and not st2.error()
 
 
+@pytest.mark.parametrize("prefetch", [False, True])
 @pytest.mark.parametrize("world", [1, 2, 3, 8])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_frame_sharded_sequence_equals_fused_kernel(world, dtype):
+def test_frame_sharded_sequence_equals_fused_kernel(world, dtype, prefetch):
     """mode "frames" (dist.FrameShardedSequence): `world` emulated ranks, each owning the frames t % world == r with a cloud
     cache of its own, store through mvt_knn_corr_shared into one result block -- which must equal the single-GPU fused
     kernel on the freshly built window, for four sliding windows (cache reuse, wrap-around of the small arenas, per-frame
@@ -212,9 +213,17 @@ def test_frame_sharded_sequence_equals_fused_kernel(world, dtype):
     E[:, :, :, 3] += 0.01 * torch.arange(T, device=DEV, dtype=torch.float32)[None, :, None]      # cameras differ per frame
     out = torch.empty(S, M, 256, device=DEV)
     most = (S + world - 1) // world
-    seqs = [FrameShardedSequence(V, Hs, Ws, 128, dtype, DEV, S=S, hop=hop, rank=r, world=world, shared_out=out, slots=2 * most)
-            for r in range(world)]
-    for w in range(4):
+    # prefetch: window w + 1 is built on a side stream while window w's iterations run (needs 3 windows' worth of slots)
+    seqs = [FrameShardedSequence(V, Hs, Ws, 128, dtype, DEV, S=S, hop=hop, rank=r, world=world, shared_out=out,
+                                 slots=(3 if prefetch else 2) * most) for r in range(world)]
+    n_win = 4
+
+    def inputs(seq, w):
+        ts = seq.new_frames()
+        win = slice(hop * w, hop * w + S)
+        return ts, (fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
+
+    for w in range(n_win):
         t0 = hop * w
         win = slice(t0, t0 + S)
         full = ops.cloud_build(fm[:, win].contiguous(), dp[:, win].contiguous(), K[:, win].contiguous(), E[:, win].contiguous(),
@@ -225,12 +234,21 @@ def test_frame_sharded_sequence_equals_fused_kernel(world, dtype):
         out.fill_(float("nan"))
         added = []
         for seq in seqs:
-            ts = seq.new_frames()
-            added += ts
-            seq.push(fm[:, ts].contiguous() if ts else None, dp[:, ts].contiguous() if ts else None, K[:, win], E[:, win])
-        assert sorted(added) == list(range(t0, t0 + S) if w == 0 else range(t0 + S - hop, t0 + S))
+            if prefetch and w > 0:
+                seq.push()                              # adopts what was prefetched during the previous window's iterations
+            else:
+                ts, args = inputs(seq, w)
+                added += ts
+                seq.push(*args)
+        if not prefetch or w == 0:
+            assert sorted(added) == list(range(t0, t0 + S) if w == 0 else range(t0 + S - hop, t0 + S))
+        held = []
         for rep in range(2):
             for seq in seqs:
                 assert seq.corr(targets, coords) is out
+                if prefetch and rep == 0 and w + 1 < n_win:
+                    ts, args = inputs(seq, w + 1)
+                    held.append(args)                   # (inputs stay alive and untouched until the push)
+                    seq.prefetch(*args)
             assert torch.equal(out, want), f"window {w}: {(out != want).any(-1).sum().item()} rows differ"
     assert sum(seq.frames_built for seq in seqs) == S + 3 * hop          # every frame was built exactly once, by its owner
