@@ -124,3 +124,20 @@ def test_forward_under_inference_mode_and_bf16_autocast(seq):
     # the drop-in; the tracks (stock init: they stay where they start) and the shapes are what can be compared
     assert d["traj_all"] <= 2e-2 * d["scale"], d
     assert o16["vis_e"].shape == s16["vis_e"].shape and torch.isfinite(o16["vis_e"]).all() and torch.isfinite(o16["traj_e"]).all()
+
+
+def test_forward_builds_every_frame_once(seq):
+    """The per-frame cloud cache inside the real model: forward() walks T = 24 frames in three windows of 12 (hop 6,
+    mvtracker.py:522-566); through the wrapped smart_cat the drop-in proves that the first 6 frames of windows 2 and 3 are
+    the previous window's last 6 and builds 12 + 6 + 6 = 24 frames' clouds -- the reference (and a drop-in that could not
+    prove the provenance) builds 36."""
+    from oracle import model_harness as mh
+    from mvtracker_b200 import dropin
+    model = mh.build_model(seed=72, device="cuda")
+    built = lambda: sum(s.frames_built for s in dropin._arenas.values())      # noqa: E731
+    windows = lambda: sum(s.windows for s in dropin._arenas.values())        # noqa: E731
+    b0, w0 = built(), windows()
+    out, _ = mh.forward(model, seq, iters=2, seam="dropin")
+    assert windows() - w0 == 3
+    assert built() - b0 == T, f"{built() - b0} frames built for a {T}-frame sequence"
+    assert torch.isfinite(out["traj_e"]).all()
