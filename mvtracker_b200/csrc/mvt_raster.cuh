@@ -36,6 +36,11 @@ struct RasterView {
 #define MVT_TOPK_BUF 0
 #endif
 constexpr int kTile = 8;          // == MVT_TILE
+#ifndef MVT_VCONST
+#define MVT_VCONST 0        // 1 (A/B): lane-constant view in the first pass when V divides 32.  Measured SLOWER on B200 (panoptic
+                            // 0.757 vs 0.715 ms, DROID -- which does not even take the path -- 0.301 vs 0.283): same 56 registers,
+                            // the second copy of the loop body costs more than the ~80 instructions per query it saves
+#endif
 constexpr int kTileMinPixels = 384;   // a pass that would read this many new pixels of one view goes to tile_search instead
 
 #ifndef MVT_M0
@@ -459,6 +464,16 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
         if (GW == 32) {
             // the first 32 * kTQ candidates (all of them for V <= 8): tournament selection instead of sort + insertions
             u64 key[kTQ];
+#if MVT_VCONST
+            // V divides 32 (1, 2, 4, 8, 16, 32 views): candidate t = j * 32 + lane belongs to view lane % V whatever j is, so the
+            // view's window origin, front bit and point offset are lane constants -- two shuffles per query, not per candidate
+            const bool vconst = (32 % V) == 0;                         // (uniform)
+            const int vl = gl & (V - 1);
+            const int x0v = g.shfl(x00, vconst ? vl : 0), y0v = g.shfl(y00, vconst ? vl : 0);
+            const bool frv = (front_mask >> vl) & 1u;
+            const unsigned basev = (unsigned)vl * (unsigned)HW;
+            const int per = vconst ? 32 / V : 0, rk0 = vconst ? gl / V : 0;
+#endif
 #pragma unroll
             for (int h = 0; h < kTQ / kCB; ++h) {
                 float4 p[kCB];
@@ -466,6 +481,17 @@ __device__ __forceinline__ bool raster_windows(const Group<GW> &g, const RasterV
                 bool ok[kCB];
 #pragma unroll
                 for (int c = 0; c < kCB; ++c) {
+#if MVT_VCONST
+                    if (vconst) {
+                        const int rk = (h * kCB + c) * per + rk0;
+                        const unsigned wo = win_tab[min(rk, kNW - 1)];
+                        const int px = x0v + (int)(wo & 15u), py = y0v + (int)(wo >> 4);
+                        ok[c] = rk < kNW && frv && (unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H;
+                        id[c] = (int)(basev + (unsigned)py * (unsigned)W + (unsigned)px);
+                        p[c] = ok[c] ? __ldg(frame + id[c]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        continue;
+                    }
+#endif
                     const int t = (h * kCB + c) * 32 + gl;
                     const int rk = (int)(((unsigned)t * magic) >> 16), v = t - rk * V;
                     const unsigned wo = win_tab[min(rk, kNW - 1)];
