@@ -72,6 +72,9 @@ __global__ void camera_prep_kernel(const float *__restrict__ intrs, const float 
 #ifndef MVT_CLOUD_MINB
 #define MVT_CLOUD_MINB 4
 #endif
+#ifndef MVT_CLOUD_PACKED
+#define MVT_CLOUD_PACKED 1      // bf16 features: shared-memory tiles of channel PAIRS, 64-channel chunks (0: the fp32-tile path)
+#endif
 constexpr int TH = 8;     // tile rows   (level-0 pixels) = one level-3 pixel high
 constexpr int TW = 32;    // tile cols   (level-0 pixels) = four level-3 pixels wide
 constexpr int CC = 32;    // channels per smem chunk
@@ -154,6 +157,42 @@ __device__ __forceinline__ void pool_tile(const float *src, int ss, int sw, floa
         int y = px / dw, x = px - y * dw;
         const float *s = src + c * ss + (2 * y) * sw + 2 * x;
         dst[c * ds + px] = round_t<T>(mean4(s[0], s[1], s[sw], s[sw + 1]));
+    }
+}
+
+// ---- 2-byte features, packed: the shared-memory tiles hold bf16 PAIRS (channels 2i, 2i+1 of one pixel in one 32-bit word), so a
+// chunk is 64 channels in the space of 32 fp32 ones: half the chunk iterations (barriers, pooling passes), half the shared-memory
+// stores per loaded byte, and a pixel's chunk is 128 contiguous bytes on the store side (8 lanes x 16 B) as in the fp32 path.
+// Values are bf16 at every level, exactly as chained avg_pool2d on a bf16 tensor rounds them (level 0 is a bit copy).
+__device__ __forceinline__ unsigned pool_pair(unsigned s0, unsigned s1, unsigned s2, unsigned s3) {
+    const float a = mean4(__uint_as_float(s0 << 16), __uint_as_float(s1 << 16), __uint_as_float(s2 << 16), __uint_as_float(s3 << 16));
+    const float b = mean4(__uint_as_float(s0 & 0xffff0000u), __uint_as_float(s1 & 0xffff0000u), __uint_as_float(s2 & 0xffff0000u),
+                          __uint_as_float(s3 & 0xffff0000u));
+    const __nv_bfloat162 r = __floats2bfloat162_rn(a, b);       // .x (low half) = a
+    return *reinterpret_cast<const unsigned *>(&r);
+}
+__device__ __forceinline__ void pool_tile_packed(const unsigned *src, int ss, int sw, unsigned *dst, int ds, int dw, int dnpx) {
+    const int c = threadIdx.x & 31;      // channel pair
+    for (int px = threadIdx.x >> 5; px < dnpx; px += 8) {
+        int y = px / dw, x = px - y * dw;
+        const unsigned *s = src + c * ss + (2 * y) * sw + 2 * x;
+        dst[c * ds + px] = pool_pair(s[0], s[1], s[sw], s[sw + 1]);
+    }
+}
+// tile[cp * cs + px], 32 channel pairs -> out rows: 8 lanes x 16 B (4 pairs each) = the pixel's 64-channel chunk, 128 B contiguous
+template <int LOG_TW>
+__device__ __forceinline__ void store_tile_packed(const unsigned *tile, int cs, int npx, __nv_bfloat16 *out, size_t frame_base, int Wl,
+                                                  int Hl, int gx0, int gy0, int C, int c0) {
+    const int tid = threadIdx.x, c4 = tid & 7;
+    for (int px = tid >> 3; px < npx; px += 32) {
+        int ly = px >> LOG_TW, lx = px & ((1 << LOG_TW) - 1);
+        int gy = gy0 + ly, gx = gx0 + lx;
+        if (gy < Hl && gx < Wl) {
+            uint4 w;
+            w.x = tile[(4 * c4 + 0) * cs + px]; w.y = tile[(4 * c4 + 1) * cs + px];
+            w.z = tile[(4 * c4 + 2) * cs + px]; w.w = tile[(4 * c4 + 3) * cs + px];
+            *reinterpret_cast<uint4 *>(out + (frame_base + (size_t)gy * Wl + gx) * C + c0 + 8 * c4) = w;
+        }
     }
 }
 
@@ -277,6 +316,67 @@ __global__ void __launch_bounds__(256, MVT_CLOUD_MINB) cloud_build_kernel(const 
     const size_t pix = (size_t)(y0 + yy) * W + (x0 + xx);
     const bool pairs = ((W & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.fmaps) & 3) == 0) && ((p.fm_vstride & 1) == 0);   // 4-byte pixel pairs are aligned
 
+#if MVT_CLOUD_PACKED
+    if (sizeof(T) == 2 && pairs && (C & 63) == 0 &&
+        (((reinterpret_cast<uintptr_t>(p.fvec[0]) | reinterpret_cast<uintptr_t>(p.fvec[1]) | reinterpret_cast<uintptr_t>(p.fvec[2]) |
+           reinterpret_cast<uintptr_t>(p.fvec[3])) & 15) == 0)) {
+        unsigned *w0 = reinterpret_cast<unsigned *>(t0), *w1 = reinterpret_cast<unsigned *>(t1);
+        unsigned *w2 = reinterpret_cast<unsigned *>(t2), *w3 = reinterpret_cast<unsigned *>(t3);
+        __nv_bfloat16 *f0 = reinterpret_cast<__nv_bfloat16 *>(p.fvec[0]), *f1 = reinterpret_cast<__nv_bfloat16 *>(p.fvec[1]);
+        __nv_bfloat16 *f2 = reinterpret_cast<__nv_bfloat16 *>(p.fvec[2]), *f3 = reinterpret_cast<__nv_bfloat16 *>(p.fvec[3]);
+        const int q = tid >> 7, r2 = (tid >> 4) & 7, pp = tid & 15;
+        const bool in2 = (y0 + r2 < H) && (x0 + 2 * pp < W);
+        const size_t pix2 = (size_t)(y0 + r2) * W + (size_t)(x0 + 2 * pp);
+        const bool swap = (tid >> 4) & 1;          // rows r2, r2+1 of a warp map to the same banks: alternate the order
+        const __nv_bfloat16 *fmh = reinterpret_cast<const __nv_bfloat16 *>(fm);
+        for (int c0 = 0; c0 < C; c0 += 2 * CC) {
+            __syncthreads();   // previous chunk's readers of the tiles are done
+            // thread (q, r2, pp): pixels (2pp, 2pp+1) of row r2, channel pairs q, q+2, ..., q+30: all 32 loads (4 B each: two pixels
+            // of one channel) are in flight before the first shared-memory store
+            unsigned val[CC];
+#pragma unroll
+            for (int i = 0; i < CC / 2; ++i) {
+                const int ch = c0 + 2 * (2 * i + q);
+                val[2 * i] = val[2 * i + 1] = 0u;
+                if (in2) {
+                    val[2 * i] = __ldg(reinterpret_cast<const unsigned *>(fmh + (size_t)ch * HW + pix2));
+                    val[2 * i + 1] = __ldg(reinterpret_cast<const unsigned *>(fmh + (size_t)(ch + 1) * HW + pix2));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < CC / 2; ++i) {
+                unsigned *d = w0 + (2 * i + q) * S0 + r2 * 32 + 2 * pp;
+                const unsigned lo = __byte_perm(val[2 * i], val[2 * i + 1], 0x5410);     // pixel 2pp:   {ch, ch+1}
+                const unsigned hi = __byte_perm(val[2 * i], val[2 * i + 1], 0x7632);     // pixel 2pp+1: {ch, ch+1}
+                if (swap) { d[1] = hi; d[0] = lo; } else { d[0] = lo; d[1] = hi; }
+            }
+            __syncthreads();
+            if (need1) pool_tile_packed(w0, S0, 32, w1, S1, 16, 64);
+            if (f0 && (p.level_mask & 1)) store_tile_packed<5>(w0, S0, 256, f0, ((size_t)s * p.V + v) * HW, W, H, x0, y0, C, c0);
+            if (!need1) continue;
+            __syncthreads();
+            if (need2) pool_tile_packed(w1, S1, 16, w2, S2, 8, 16);
+            if (f1 && (p.level_mask & 2)) {
+                int Hl = H >> 1, Wl = W >> 1;
+                store_tile_packed<4>(w1, S1, 64, f1, ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 1, y0 >> 1, C, c0);
+            }
+            if (!need2) continue;
+            __syncthreads();
+            if (need3) pool_tile_packed(w2, S2, 8, w3, S3, 4, 4);
+            if (f2 && (p.level_mask & 4)) {
+                int Hl = H >> 2, Wl = W >> 2;
+                store_tile_packed<3>(w2, S2, 16, f2, ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 2, y0 >> 2, C, c0);
+            }
+            if (!need3) continue;
+            __syncthreads();
+            if (f3 && (p.level_mask & 8)) {
+                int Hl = H >> 3, Wl = W >> 3;
+                store_tile_packed<2>(w3, S3, 4, f3, ((size_t)s * p.V + v) * Hl * Wl, Wl, Hl, x0 >> 3, y0 >> 3, C, c0);
+            }
+        }
+        return;
+    }
+#endif
     for (int c0 = 0; c0 < C; c0 += CC) {
         __syncthreads();   // previous chunk's readers of t0..t3 are done
         if (sizeof(T) == 2 && pairs) {
