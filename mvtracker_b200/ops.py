@@ -389,11 +389,14 @@ def _corr_workspace(dev: torch.device, n_levels: int, B: int, M: int) -> torch.T
 
 
 class _HardQueryPolicy:
-    """defer="auto": whether the next fused launch hands its large-box queries to the tile-search kernel.  Every launch leaves
-    the number of such queries in its scratch; it is copied to pinned host memory asynchronously and looked at when the NEXT
-    call is issued (no synchronisation: the decision is one call stale).  Deferral pays when several per cent of the queries
-    float in free space (a window that starts with static tracks, mvtracker.py:510) and costs ~10 % when only a few do."""
+    """defer="auto": whether the next fused launch hands its large-box queries to the tile-search kernel.  Deferral pays when
+    several per cent of the queries float in free space (a window that starts with static tracks, mvtracker.py:510) and costs
+    ~8 % when only a few do; even COUNTING them costs ~3 % (the deferral build of the kernel is larger, and the fused kernel is
+    sensitive to its instruction footprint).  So while few queries are hard the plain kernel runs (mode 0) and every PROBE-th
+    launch counts (mode 2); while deferring (mode 1) every launch leaves its count anyway.  A count is copied to pinned host
+    memory asynchronously and looked at when a later call is issued (no synchronisation: the decision is a call or more stale)."""
     ON, OFF = 0.015, 0.0075      # fraction of a launch's queries; hysteresis
+    PROBE = 8
 
     def __init__(self):
         self.deferring = True    # a sequence starts with static tracks
@@ -403,7 +406,7 @@ class _HardQueryPolicy:
 
     def mode(self) -> int:
         if torch.cuda.is_current_stream_capturing():     # a captured launch keeps the mode it was captured with
-            return 1 if self.deferring else 2
+            return 1 if self.deferring else 0
         if self.event is not None and self.event.query():
             self.last_fraction = float(self.pinned[0]) / max(1, self.queries)
             self.event = None
@@ -411,12 +414,14 @@ class _HardQueryPolicy:
                 self.deferring = True
             elif self.last_fraction < self.OFF:
                 self.deferring = False
-        return 1 if self.deferring else 2
+        if self.deferring:
+            return 1
+        return 2 if self.calls % self.PROBE == 0 else 0
 
-    def record(self, ws: torch.Tensor, queries: int):
+    def record(self, ws: torch.Tensor, queries: int, mode: int):
         self.calls += 1
-        # (a sample every few launches: the 4-byte copy costs a few microseconds of stream time)
-        if self.event is None and (self.calls & 3) == 1 and not torch.cuda.is_current_stream_capturing():
+        # (mode 1: a sample every few launches -- the 4-byte copy costs a few microseconds of stream time)
+        if mode != 0 and self.event is None and (mode == 2 or (self.calls & 3) == 1) and not torch.cuda.is_current_stream_capturing():
             self.pinned.copy_(ws[:4].view(torch.int32), non_blocking=True)
             self.queries = queries
             self.event = torch.cuda.Event()
@@ -488,7 +493,7 @@ def knn_corr(levels: Sequence, targets: torch.Tensor, coords: torch.Tensor, grou
                              int(bool(add_xyz)), _ptr(out), row_stride, frame_stride, _ptr(idx_hint), _ptr(idx), _ptr(ws), mode,
                              _stream()), "mvt_knn_corr")
     if pol is not None:
-        pol.record(ws, n * B * M)
+        pol.record(ws, n * B * M, mode)
     return (out, idx) if return_idx else out
 
 
@@ -563,7 +568,7 @@ def knn_corr_shared(levels, targets: torch.Tensor, coords: torch.Tensor, frame0:
                                     frame_step * M * width, None if ws is None else ws.data_ptr(), mode,
                                     torch.cuda.current_stream().cuda_stream), "mvt_knn_corr_shared")
     if pol is not None:
-        pol.record(ws, n * B * M)
+        pol.record(ws, n * B * M, mode)
 
 
 def knn_corr_backward(fvec: torch.Tensor, targets: torch.Tensor, idx: torch.Tensor, grad_out: torch.Tensor, groups: int = 1,
