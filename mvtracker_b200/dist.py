@@ -544,6 +544,11 @@ class FrameShardedSequence:
         self._res, self._flip = {}, 0
         self._pending, self._side, self.last_build = None, None, None
 
+    @property
+    def has_prefetch(self) -> bool:
+        """A prefetch() is waiting for its push()."""
+        return self._pending is not None
+
     # ---- which frames --------------------------------------------------------------------------------------------------------
     def window_frames(self, w: Optional[int] = None) -> range:
         w = self.windows if w is None else w
