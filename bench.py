@@ -517,8 +517,11 @@ def run_ours(args):
     sync()
     if frames_mode:
         step(pipeline=False)        # (adopts the window prefetched by the last timed step; the split below builds in line)
+    built0 = state["seq"].frames_built if frames_mode else 0
     for e in evs:
         step(e, pipeline=False)
+    if frames_mode:                 # frames THIS rank built per split step (a rank builds 0 or 1 frame per advance at N = 8)
+        n_built = max((state["seq"].frames_built - built0) / n_split, 1e-9)
     # keep the GPU busy long enough for nvidia-smi to have samples of the loaded clocks
     # (the SAME number of extra steps on every rank -- from the all-reduced time, not from each rank's own wall clock: the
     # sharded modes synchronise inside step(), ranks that enqueue different numbers of steps would wait for each other forever)
@@ -537,7 +540,7 @@ def run_ours(args):
     q_bytes = 12 + C_FEAT * esz + K_NN * (C_FEAT * esz + 12) + K_NN * 4 * 4          # 9164 B (fp32) / 4812 B (bf16)
     corr_bytes = LEVELS * S_WINDOW * N * q_bytes / pw                                 # per rank: its share of the gathers
     pts = sum(v_loc * (w["Hs"] >> l) * (w["Ws"] >> l) for l in range(LEVELS)) * n_built
-    cloud_bytes = (fm[:, :1].numel() * esz + dp[:, :1].numel() * 4) * n_built + pts * (C_FEAT * esz + 12)   # SURVEY.md 8d (xyz4 records not counted)
+    cloud_bytes = int((fm[:, :1].numel() * esz + dp[:, :1].numel() * 4) * n_built + pts * (C_FEAT * esz + 12))   # SURVEY.md 8d (xyz4 records not counted)
     kern = {
         "knn_corr": {"ms": t_corr, "launches_per_step": iters, "alg_bytes": corr_bytes, "gbs": corr_bytes / t_corr / 1e6,
                      "what": "fused knn_corr kernel" if pw == 1 else
