@@ -606,8 +606,9 @@ class FrameShardedSequence:
         if self._pending is not None:
             st, done = self._pending
             self._pending = None
-            if done is not None:
-                torch.cuda.current_stream().wait_event(done)
+            if st is None:                      # prefetch() could not run ahead: `done` holds its arguments, build now
+                return self._adopt(self._stage(*done))
+            torch.cuda.current_stream().wait_event(done)
             return self._adopt(st)
         if intrs_win is None:
             raise ValueError("push() without arguments needs a prefetch() before it")
@@ -623,7 +624,7 @@ class FrameShardedSequence:
         if self._pending is not None:
             raise RuntimeError("one prefetch() per push()")
         if self.device is None or torch.device(self.device).type != "cuda" or self.arena.slots < 3 * most or self.windows == 0:
-            self._pending = (self._stage(fmaps_new, depths_new, intrs_win, extrs_win), None)
+            self._pending = (None, (fmaps_new, depths_new, intrs_win, extrs_win))       # built by the push() that follows
             return
         if self._side is None:
             self._side = torch.cuda.Stream(device=self.device)

@@ -250,12 +250,22 @@ def _frames_worker(rank, world, port, S, hop, n_win, ret):
         outs = []
         for w in range(n_win):
             win = slice(hop * w, hop * w + S)
-            ts = seq.new_frames()
-            assert all(t % world == rank for t in ts)
-            seq.push(fm[:, ts] if ts else None, dp[:, ts] if ts else None, K[:, win], E[:, win])
+            if seq.has_prefetch:
+                seq.push()                      # the window handed over by prefetch() during the previous one
+            else:
+                ts = seq.new_frames()
+                assert all(t % world == rank for t in ts)
+                seq.push(fm[:, ts] if ts else None, dp[:, ts] if ts else None, K[:, win], E[:, win])
             g = torch.Generator().manual_seed(100 + w)
             targets, coords = torch.randn(S, M, 3, generator=g), torch.randn(S, M, 3, generator=g)
             outs.append(seq.corr(targets, coords).clone().numpy())
+            if w % 2 == 0 and w + 1 < n_win:    # every other window is staged ahead (on a CPU device: built at once, adopted by push())
+                nxt = slice(hop * (w + 1), hop * (w + 1) + S)
+                ts = seq.new_frames()
+                seq.prefetch(fm[:, ts] if ts else None, dp[:, ts] if ts else None, K[:, nxt], E[:, nxt])
+                with pytest.raises(RuntimeError):
+                    seq.prefetch(None, None, K[:, nxt], E[:, nxt])
+                outs[-1] = seq.corr(targets, coords).clone().numpy()      # the current window is untouched by the staging
         ret[rank] = (outs, seq.frames_built, sorted(seq.arena.built), seq.arena.moves)
     finally:
         dist.destroy_process_group()
